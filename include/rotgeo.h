@@ -1,0 +1,115 @@
+/*
+ * rotgeo — B200-native (sm_100a) rotated-box IoU and rotated NMS.
+ * C ABI of librotgeo.so: the drop-in boundary for the reference's rotated
+ * geometry hot path.  Plain pointers and sizes only.
+ *
+ * Every entry point replaces a native op the reference reaches through
+ * `mmcv.ops` (mmcv-full `_ext`, un-vendored; the reference-side bindings are
+ * the python names imported at the file:line cited on each function).
+ *
+ * Conventions
+ *   - all data pointers are DEVICE pointers unless a name ends in `_host`;
+ *   - the caller owns every buffer (inputs, outputs, workspace); the library
+ *     never allocates or frees device memory and keeps no pointer after return;
+ *   - every call is asynchronous on `stream` (a cudaStream_t passed as void*);
+ *   - return value: 0 = ok, negative = error (rotgeo_last_error() has text);
+ *   - boxes are rows (cx, cy, w, h, theta_radians) with `stride` floats
+ *     between rows (5, or 6 for det rows carrying a score column — the
+ *     reference hands such rows over at mmrotate/core/evaluation/eval_map.py:60-62).
+ */
+#ifndef ROTGEO_H_
+#define ROTGEO_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ROTGEO_OK 0
+#define ROTGEO_ERR_ARG (-1)        /* bad argument (null pointer, negative size, bad mode) */
+#define ROTGEO_ERR_WORKSPACE (-2)  /* workspace too small / misaligned */
+#define ROTGEO_ERR_CUDA (-3)       /* a CUDA runtime call or launch failed */
+
+#define ROTGEO_MODE_IOU 0
+#define ROTGEO_MODE_IOF 1          /* intersection / area(first box) */
+
+/* ABI version (major*1000 + minor). */
+int rotgeo_version(void);
+
+/* Thread-local text of the last error on this thread ("" if none). */
+const char *rotgeo_last_error(void);
+
+/* ---- packed SoA box layout ------------------------------------------------
+ * The kernels read boxes from two float4 planes (plane0 = cx, cy, r, area;
+ * plane1 = cos, sin, w/2, h/2), padded to a multiple of 128 boxes.
+ * rotgeo_packed_bytes(n) is the size of one packed set; the buffer must be
+ * 16-byte aligned. */
+size_t rotgeo_packed_bytes(int64_t n);
+
+/* AoS rows -> packed SoA.  `gather` (nullable, int64[n]) selects rows:
+ * packed[i] = boxes[gather[i]].  `min_wh` > 0 clamps w,h from below first
+ * (the reference clamps to 1e-3 at
+ * mmrotate/core/bbox/iou_calculators/rotate_iou2d_calculator.py:84-87);
+ * pass 0 for no clamp.  `offsets` (nullable, float[n], indexed like the
+ * SOURCE rows) is added to cx and cy before packing — the class/level offset
+ * trick of mmrotate/core/post_processing/bbox_nms_rotated.py:73-77. */
+int rotgeo_pack_boxes(const float *boxes, int64_t n, int stride, const int64_t *gather,
+                      const float *offsets, float min_wh, void *packed, void *stream);
+
+/* ---- rotated IoU -----------------------------------------------------------
+ * Replaces ext_module.box_iou_rotated (mmcv.ops.box_iou_rotated), bound by the
+ * reference at mmrotate/core/bbox/iou_calculators/rotate_iou2d_calculator.py:2,89,
+ * mmrotate/core/evaluation/eval_map.py:6,60 and
+ * mmrotate/datasets/pipelines/transforms.py:8,369.
+ *
+ * out[i * ld_out + j] = IoU (mode 0) or IoF (mode 1) of boxes1[i], boxes2[j].
+ * Workspace: rotgeo_iou_workspace_bytes(n1, n2), 16-byte aligned. */
+size_t rotgeo_iou_workspace_bytes(int64_t n1, int64_t n2);
+int rotgeo_iou_pairwise(const float *boxes1, int64_t n1, int stride1, const float *boxes2,
+                        int64_t n2, int stride2, int mode, float min_wh, float *out,
+                        int64_t ld_out, void *workspace, size_t workspace_bytes, void *stream);
+
+/* Same on already-packed sets (no workspace; lets a caller keep anchors or
+ * ground truth packed across calls). */
+int rotgeo_iou_pairwise_packed(const void *packed1, int64_t n1, const void *packed2, int64_t n2,
+                               int mode, float *out, int64_t ld_out, void *stream);
+
+/* aligned=True variant: out[i] = IoU(boxes1[i], boxes2[i]). */
+int rotgeo_iou_aligned(const float *boxes1, const float *boxes2, int64_t n, int stride1,
+                       int stride2, int mode, float min_wh, float *out, void *stream);
+
+/* ---- rotated NMS -----------------------------------------------------------
+ * Replaces ext_module.nms_rotated (mmcv.ops.nms_rotated), bound by the
+ * reference at mmrotate/core/post_processing/bbox_nms_rotated.py:3,80,122,
+ * mmrotate/core/patch/merge_results.py:4,116, mmrotate/datasets/dota.py:16,379,
+ * and reached through mmcv.ops.batched_nms at
+ * mmrotate/models/dense_heads/oriented_rpn_head.py:275 and rotated_rpn_head.py:515.
+ *
+ * Greedy suppression with the reference's CPU semantics: visiting boxes in
+ * `order`, a kept box i suppresses every later j of the same segment with
+ * IoU(i, j) >= iou_threshold.
+ *
+ *   boxes / stride    AoS rows as above (n rows)
+ *   offsets           nullable float[n]: added to cx, cy (class-offset trick)
+ *   order             int64[n]: indices into boxes, score-descending over ALL boxes
+ *   seg_order         nullable int64[n]: the same indices sorted segment-major,
+ *                     score-descending inside each segment (null = one segment,
+ *                     `order` is used)
+ *   seg_offsets_host  HOST int64[num_segments + 1]: segment boundaries in
+ *                     seg_order (null when seg_order is null)
+ *   keep_out          int64[n]: kept indices into boxes, in `order` order
+ *   num_keep_out      int64[1] (device): how many were kept
+ *
+ * Workspace: rotgeo_nms_workspace_bytes(n, seg_offsets_host, num_segments). */
+size_t rotgeo_nms_workspace_bytes(int64_t n, const int64_t *seg_offsets_host, int64_t num_segments);
+int rotgeo_nms(const float *boxes, int64_t n, int stride, const float *offsets,
+               const int64_t *order, const int64_t *seg_order, const int64_t *seg_offsets_host,
+               int64_t num_segments, float iou_threshold, int64_t *keep_out,
+               int64_t *num_keep_out, void *workspace, size_t workspace_bytes, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ROTGEO_H_ */

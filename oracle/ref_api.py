@@ -1,0 +1,116 @@
+"""ORACLE — TEST INFRASTRUCTURE ONLY.  CPU restatement of the reference's
+python front-ends around the native ops, calling the C oracle (oracle/ref.py)
+exactly where the reference calls ``mmcv.ops``.  Every function follows the
+reference file:line it cites, class separation by the coordinate-offset trick
+included, so that keep indices can be compared one-to-one with the CUDA path.
+"""
+import numpy as np
+import torch
+
+from . import ref
+
+
+def _nms(dets, scores, thr):
+    """oracle stand-in for mmcv.ops.nms_rotated on CPU torch tensors"""
+    if dets.shape[0] == 0:
+        return dets, None
+    out, keep = ref.nms_rotated(dets.detach().cpu().numpy(), scores.detach().cpu().numpy(), thr)
+    return torch.from_numpy(out).to(dets.dtype), torch.from_numpy(keep)
+
+
+def rbbox_overlaps(b1, b2, mode='iou', is_aligned=False):
+    """reference rotate_iou2d_calculator.py:53-89 (clone, clamp 1e-3, native op)"""
+    b1 = b1.detach().clone().float()
+    b2 = b2.detach().clone().float()
+    b1[:, 2:4].clamp_(min=1e-3)
+    b2[:, 2:4].clamp_(min=1e-3)
+    out = ref.box_iou_rotated(b1.numpy(), b2.numpy(), mode, is_aligned)
+    return torch.from_numpy(out)
+
+
+def multiclass_nms_rotated(multi_bboxes, multi_scores, score_thr, iou_thr, max_num=-1,
+                           score_factors=None):
+    """reference bbox_nms_rotated.py:6-92; returns (dets, labels, keep)"""
+    num_classes = multi_scores.size(1) - 1
+    if multi_bboxes.shape[1] > 5:
+        bboxes = multi_bboxes.view(multi_scores.size(0), -1, 5)
+    else:
+        bboxes = multi_bboxes[:, None].expand(multi_scores.size(0), num_classes, 5)
+    scores = multi_scores[:, :-1]
+    labels = torch.arange(num_classes, dtype=torch.long).view(1, -1).expand_as(scores)
+    bboxes, scores, labels = bboxes.reshape(-1, 5), scores.reshape(-1), labels.reshape(-1)
+    valid = scores > score_thr
+    if score_factors is not None:
+        sf = score_factors.view(-1, 1).expand(multi_scores.size(0), num_classes).reshape(-1)
+        scores = scores * sf
+    inds = valid.nonzero(as_tuple=False).squeeze(1)
+    bboxes, scores, labels = bboxes[inds], scores[inds], labels[inds]
+    if bboxes.numel() == 0:
+        return torch.cat([bboxes, scores[:, None]], -1), labels, inds
+    max_coordinate = bboxes[:, :2].max() + bboxes[:, 2:4].max()
+    offsets = labels.to(bboxes) * (max_coordinate + 1)
+    for_nms = bboxes.clone()
+    for_nms[:, :2] = for_nms[:, :2] + offsets[:, None]
+    _, keep = _nms(for_nms, scores, iou_thr)
+    if max_num > 0:
+        keep = keep[:max_num]
+    return torch.cat([bboxes[keep], scores[keep][:, None]], 1), labels[keep], keep
+
+
+def aug_multiclass_nms_rotated(merged_bboxes, merged_labels, score_thr, iou_thr, max_num, classes):
+    """reference bbox_nms_rotated.py:95-144"""
+    bboxes, labels = [], []
+    for cls in range(classes):
+        cb = merged_bboxes[merged_labels == cls]
+        inds = cb[:, -1] > score_thr
+        if len(inds) == 0:
+            continue
+        cur = cb[inds, :]
+        dets, _ = _nms(cur[:, :5], cur[:, -1], iou_thr)
+        if dets.size(0) == 0:
+            continue
+        bboxes.append(dets)
+        labels.append(merged_bboxes.new_full((dets.shape[0],), cls, dtype=torch.long))
+    if bboxes:
+        bboxes, labels = torch.cat(bboxes), torch.cat(labels)
+        if bboxes.shape[0] > max_num:
+            _, i = bboxes[:, -1].sort(descending=True, stable=True)
+            bboxes, labels = bboxes[i[:max_num]], labels[i[:max_num]]
+    else:
+        bboxes = merged_bboxes.new_zeros((0, merged_bboxes.size(-1)))
+        labels = merged_bboxes.new_zeros((0,), dtype=torch.long)
+    return bboxes, labels
+
+
+def batched_nms_rotated(boxes, scores, idxs, iou_threshold, class_agnostic=False):
+    """mmcv.ops.batched_nms with type='nms_rotated' (SURVEY.md §8(a) a9): centre
+    offsets idxs*(max+1), one NMS call, score-descending keep."""
+    if class_agnostic:
+        for_nms = boxes
+    else:
+        max_coordinate = boxes[..., :2].max() + boxes[..., 2:4].max()
+        offsets = idxs.to(boxes) * (max_coordinate + torch.tensor(1).to(boxes))
+        for_nms = torch.cat([boxes[..., :2] + offsets[:, None], boxes[..., 2:5]], dim=-1)
+    _, keep = _nms(for_nms, scores, iou_threshold)
+    return torch.cat([boxes[keep], scores[keep][:, None]], -1), keep
+
+
+def merge_results(results, offsets, iou_thr=0.1):
+    """reference merge_results.py:69-127 (rotated, no masks); mutates results in
+    place like the reference's translate_bboxes"""
+    num_patches, num_classes = len(results), len(results[0])
+    merged = []
+    for cls in range(num_classes):
+        dets = []
+        for i in range(num_patches):
+            d = results[i][cls]
+            d[:, :2] = d[:, :2] + offsets[i]
+            dets.append(d)
+        dets = np.concatenate(dets, axis=0)
+        if dets.size == 0:
+            merged.append(dets)
+            continue
+        t = torch.from_numpy(dets)
+        out, _ = _nms(t[:, :-1], t[:, -1], iou_thr)
+        merged.append(out.numpy())
+    return merged

@@ -1,0 +1,63 @@
+"""ctypes loader of librotgeo.so (the C-ABI declared in include/rotgeo.h).
+
+There is no fallback of any kind: if the library is missing or a call fails the
+caller gets a RuntimeError.  The CPU oracle under oracle/ is never imported here.
+"""
+import ctypes
+import os
+
+_PKG = os.path.dirname(os.path.abspath(__file__))
+SO_PATH = os.path.join(_PKG, 'librotgeo.so')
+
+# every symbol include/rotgeo.h declares (tests check the export list against this)
+SYMBOLS = (
+    'rotgeo_version', 'rotgeo_last_error', 'rotgeo_packed_bytes', 'rotgeo_pack_boxes',
+    'rotgeo_iou_workspace_bytes', 'rotgeo_iou_pairwise', 'rotgeo_iou_pairwise_packed',
+    'rotgeo_iou_aligned', 'rotgeo_nms_workspace_bytes', 'rotgeo_nms',
+)
+
+_lib = None
+
+
+class RotgeoError(RuntimeError):
+    pass
+
+
+def load():
+    """dlopen librotgeo.so and declare the prototypes.  Raises if it is not built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(SO_PATH):
+        raise RotgeoError(
+            'librotgeo.so is not built (%s). Run `python -m orientedobjectdetection_b200.build` '
+            '(needs nvcc). There is no CPU fallback.' % SO_PATH)
+    L = ctypes.CDLL(SO_PATH)
+    vp, i64, i32, f32, sz = (ctypes.c_void_p, ctypes.c_int64, ctypes.c_int, ctypes.c_float,
+                             ctypes.c_size_t)
+    L.rotgeo_version.restype = i32
+    L.rotgeo_last_error.restype = ctypes.c_char_p
+    L.rotgeo_packed_bytes.argtypes = [i64]
+    L.rotgeo_packed_bytes.restype = sz
+    L.rotgeo_pack_boxes.argtypes = [vp, i64, i32, vp, vp, f32, vp, vp]
+    L.rotgeo_pack_boxes.restype = i32
+    L.rotgeo_iou_workspace_bytes.argtypes = [i64, i64]
+    L.rotgeo_iou_workspace_bytes.restype = sz
+    L.rotgeo_iou_pairwise.argtypes = [vp, i64, i32, vp, i64, i32, i32, f32, vp, i64, vp, sz, vp]
+    L.rotgeo_iou_pairwise.restype = i32
+    L.rotgeo_iou_pairwise_packed.argtypes = [vp, i64, vp, i64, i32, vp, i64, vp]
+    L.rotgeo_iou_pairwise_packed.restype = i32
+    L.rotgeo_iou_aligned.argtypes = [vp, vp, i64, i32, i32, i32, f32, vp, vp]
+    L.rotgeo_iou_aligned.restype = i32
+    L.rotgeo_nms_workspace_bytes.argtypes = [i64, vp, i64]
+    L.rotgeo_nms_workspace_bytes.restype = sz
+    L.rotgeo_nms.argtypes = [vp, i64, i32, vp, vp, vp, vp, i64, f32, vp, vp, vp, sz, vp]
+    L.rotgeo_nms.restype = i32
+    _lib = L
+    return L
+
+
+def check(rc, what):
+    if rc != 0:
+        msg = load().rotgeo_last_error().decode('utf-8', 'replace')
+        raise RotgeoError('%s failed (code %d): %s' % (what, rc, msg))

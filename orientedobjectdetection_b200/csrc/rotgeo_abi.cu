@@ -1,0 +1,174 @@
+// extern "C" boundary of librotgeo.so (see include/rotgeo.h).  Argument
+// checking, workspace carving and launches only; no allocation, no sync.
+#include <stdarg.h>
+#include <stdio.h>
+
+#include <vector>
+
+#include "../../include/rotgeo.h"
+#include "rotgeo_device.cuh"
+#include "rotgeo_internal.h"
+
+namespace {
+
+thread_local char g_err[256] = "";
+
+int fail(int code, const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+int cuda_fail(const char *what) {
+    cudaError_t e = cudaGetLastError();
+    return fail(ROTGEO_ERR_CUDA, "%s: %s", what, cudaGetErrorString(e));
+}
+
+inline bool aligned16(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+}  // namespace
+
+extern "C" {
+
+int rotgeo_version(void) { return 1000; }
+
+const char *rotgeo_last_error(void) { return g_err; }
+
+size_t rotgeo_packed_bytes(int64_t n) {
+    if (n < 0) return 0;
+    return (size_t)rotgeo::padded_count(n) * 2 * sizeof(float4);
+}
+
+int rotgeo_pack_boxes(const float *boxes, int64_t n, int stride, const int64_t *gather,
+                      const float *offsets, float min_wh, void *packed, void *stream) {
+    if (n < 0 || stride < 5) return fail(ROTGEO_ERR_ARG, "pack: n=%lld stride=%d", (long long)n, stride);
+    if (n == 0) return ROTGEO_OK;
+    if (!boxes || !packed) return fail(ROTGEO_ERR_ARG, "pack: null pointer");
+    if (!aligned16(packed)) return fail(ROTGEO_ERR_ARG, "pack: packed buffer must be 16-byte aligned");
+    if (rotgeo::launch_pack(boxes, n, stride, gather, offsets, min_wh, packed,
+                            rotgeo::padded_count(n), (cudaStream_t)stream))
+        return cuda_fail("pack launch");
+    return ROTGEO_OK;
+}
+
+size_t rotgeo_iou_workspace_bytes(int64_t n1, int64_t n2) {
+    return align_up(rotgeo_packed_bytes(n1), 256) + align_up(rotgeo_packed_bytes(n2), 256);
+}
+
+int rotgeo_iou_pairwise_packed(const void *packed1, int64_t n1, const void *packed2, int64_t n2,
+                               int mode, float *out, int64_t ld_out, void *stream) {
+    if (n1 < 0 || n2 < 0 || (mode != 0 && mode != 1) || ld_out < n2)
+        return fail(ROTGEO_ERR_ARG, "iou: n1=%lld n2=%lld mode=%d ld_out=%lld", (long long)n1,
+                    (long long)n2, mode, (long long)ld_out);
+    if (n1 == 0 || n2 == 0) return ROTGEO_OK;
+    if (!packed1 || !packed2 || !out) return fail(ROTGEO_ERR_ARG, "iou: null pointer");
+    if (!aligned16(packed1) || !aligned16(packed2))
+        return fail(ROTGEO_ERR_ARG, "iou: packed buffers must be 16-byte aligned");
+    const int rc = rotgeo::launch_iou_pairwise(packed1, n1, packed2, n2, mode, out, ld_out,
+                                               (cudaStream_t)stream);
+    if (rc == -1) return fail(ROTGEO_ERR_ARG, "iou: too many tiles");
+    if (rc) return cuda_fail("iou launch");
+    return ROTGEO_OK;
+}
+
+int rotgeo_iou_pairwise(const float *boxes1, int64_t n1, int stride1, const float *boxes2,
+                        int64_t n2, int stride2, int mode, float min_wh, float *out,
+                        int64_t ld_out, void *workspace, size_t workspace_bytes, void *stream) {
+    if (n1 < 0 || n2 < 0 || stride1 < 5 || stride2 < 5)
+        return fail(ROTGEO_ERR_ARG, "iou: n1=%lld n2=%lld stride1=%d stride2=%d", (long long)n1,
+                    (long long)n2, stride1, stride2);
+    if (n1 == 0 || n2 == 0) return ROTGEO_OK;
+    if (!boxes1 || !boxes2) return fail(ROTGEO_ERR_ARG, "iou: null pointer");
+    if (!workspace || !aligned16(workspace) || workspace_bytes < rotgeo_iou_workspace_bytes(n1, n2))
+        return fail(ROTGEO_ERR_WORKSPACE, "iou: workspace %zu < %zu bytes or misaligned",
+                    workspace_bytes, rotgeo_iou_workspace_bytes(n1, n2));
+    char *ws = reinterpret_cast<char *>(workspace);
+    void *pk1 = ws;
+    void *pk2 = ws + align_up(rotgeo_packed_bytes(n1), 256);
+    int rc = rotgeo_pack_boxes(boxes1, n1, stride1, nullptr, nullptr, min_wh, pk1, stream);
+    if (rc) return rc;
+    rc = rotgeo_pack_boxes(boxes2, n2, stride2, nullptr, nullptr, min_wh, pk2, stream);
+    if (rc) return rc;
+    return rotgeo_iou_pairwise_packed(pk1, n1, pk2, n2, mode, out, ld_out, stream);
+}
+
+int rotgeo_iou_aligned(const float *boxes1, const float *boxes2, int64_t n, int stride1,
+                       int stride2, int mode, float min_wh, float *out, void *stream) {
+    if (n < 0 || stride1 < 5 || stride2 < 5 || (mode != 0 && mode != 1))
+        return fail(ROTGEO_ERR_ARG, "iou_aligned: n=%lld mode=%d", (long long)n, mode);
+    if (n == 0) return ROTGEO_OK;
+    if (!boxes1 || !boxes2 || !out) return fail(ROTGEO_ERR_ARG, "iou_aligned: null pointer");
+    if (rotgeo::launch_iou_aligned(boxes1, boxes2, n, stride1, stride2, mode, min_wh, out,
+                                   (cudaStream_t)stream))
+        return cuda_fail("iou_aligned launch");
+    return ROTGEO_OK;
+}
+
+size_t rotgeo_nms_workspace_bytes(int64_t n, const int64_t *seg_offsets_host, int64_t num_segments) {
+    if (n <= 0) return 0;
+    rotgeo::NmsPlan plan;
+    rotgeo::nms_plan(n, seg_offsets_host, num_segments, &plan, nullptr);
+    return plan.total_bytes;
+}
+
+int rotgeo_nms(const float *boxes, int64_t n, int stride, const float *offsets,
+               const int64_t *order, const int64_t *seg_order, const int64_t *seg_offsets_host,
+               int64_t num_segments, float iou_threshold, int64_t *keep_out,
+               int64_t *num_keep_out, void *workspace, size_t workspace_bytes, void *stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    if (n < 0 || stride < 5) return fail(ROTGEO_ERR_ARG, "nms: n=%lld stride=%d", (long long)n, stride);
+    if (!num_keep_out) return fail(ROTGEO_ERR_ARG, "nms: null num_keep_out");
+    if (n == 0) {
+        if (cudaMemsetAsync(num_keep_out, 0, sizeof(int64_t), st) != cudaSuccess)
+            return cuda_fail("nms memset");
+        return ROTGEO_OK;
+    }
+    if (!boxes || !order || !keep_out) return fail(ROTGEO_ERR_ARG, "nms: null pointer");
+    const bool segmented = seg_order != nullptr;
+    if (segmented) {
+        if (!seg_offsets_host || num_segments < 1)
+            return fail(ROTGEO_ERR_ARG, "nms: seg_order given without seg_offsets_host");
+        if (seg_offsets_host[0] != 0 || seg_offsets_host[num_segments] != n)
+            return fail(ROTGEO_ERR_ARG, "nms: seg_offsets_host must run from 0 to n");
+        for (int64_t s = 0; s < num_segments; ++s)
+            if (seg_offsets_host[s + 1] < seg_offsets_host[s])
+                return fail(ROTGEO_ERR_ARG, "nms: seg_offsets_host not monotone");
+    } else {
+        seg_offsets_host = nullptr;
+        num_segments = 1;
+    }
+    rotgeo::NmsPlan plan;
+    std::vector<rotgeo::NmsSegment> segs((size_t)num_segments);
+    rotgeo::nms_plan(n, seg_offsets_host, num_segments, &plan, segs.data());
+    if (!workspace || !aligned16(workspace) || workspace_bytes < plan.total_bytes)
+        return fail(ROTGEO_ERR_WORKSPACE, "nms: workspace %zu < %zu bytes or misaligned",
+                    workspace_bytes, plan.total_bytes);
+    int max_words = 0;
+    for (const auto &g : segs) max_words = g.words > max_words ? g.words : max_words;
+    if ((size_t)max_words * 8 > 200 * 1024)
+        return fail(ROTGEO_ERR_ARG, "nms: a segment of more than %d boxes is not supported",
+                    200 * 1024 / 8 * 64);
+    char *ws = reinterpret_cast<char *>(workspace);
+    void *packed = ws + plan.off_packed;
+    rotgeo::NmsSegment *segs_dev = reinterpret_cast<rotgeo::NmsSegment *>(ws + plan.off_segments);
+    uint64_t *mask = reinterpret_cast<uint64_t *>(ws + plan.off_mask);
+    uint8_t *flags = reinterpret_cast<uint8_t *>(ws + plan.off_flags);
+    // pageable source: the runtime stages the bytes before returning, so `segs`
+    // may die at scope exit
+    if (cudaMemcpyAsync(segs_dev, segs.data(), segs.size() * sizeof(rotgeo::NmsSegment),
+                        cudaMemcpyHostToDevice, st) != cudaSuccess)
+        return cuda_fail("nms segment upload");
+    const int64_t *sorder = segmented ? seg_order : order;
+    if (rotgeo::launch_pack(boxes, n, stride, sorder, offsets, 0.f, packed, plan.n_pad, st))
+        return cuda_fail("nms pack launch");
+    const int rc = rotgeo::launch_nms(plan, packed, segs_dev, max_words, order, sorder,
+                                      iou_threshold, mask, flags, keep_out, num_keep_out, st);
+    if (rc == -1) return fail(ROTGEO_ERR_ARG, "nms: too many tiles");
+    if (rc) return cuda_fail("nms launch");
+    return ROTGEO_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,189 @@
+// rotgeo device-side geometry: packed box layout, the centre-distance reject
+// test and the exact rotated-rectangle intersection.  sm_100a only.
+//
+// Replaces (does not translate) mmcv's single_box_iou_rotated
+// (box_iou_rotated_utils.hpp; reached by the reference at
+// mmrotate/core/bbox/iou_calculators/rotate_iou2d_calculator.py:89).  mmcv
+// collects up to 24 candidate points, Graham-scans them and sums a triangle
+// fan — variable-length local arrays and an in-thread sort.  Here the
+// intersection area comes from Green's theorem over the CLIPPED EDGES of both
+// rectangles (Sutherland-Hodgman's half-plane clipping applied per edge in
+// Liang-Barsky form): fixed work, registers only, no sort, no local memory.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace rotgeo {
+
+constexpr int kPackPad = 128;  // packed sets are padded to a multiple of this many boxes
+
+__host__ __device__ inline int64_t padded_count(int64_t n) {
+    return (n + kPackPad - 1) / kPackPad * kPackPad;
+}
+
+// plane0: (cx, cy, r, area)   r = circumscribed-circle radius, slightly inflated
+// plane1: (cos, sin, a, b)    a = w/2, b = h/2
+struct PackedView {
+    const float4 *p0;
+    const float4 *p1;
+};
+
+// n_pad = number of float4 slots per plane (padded_count(n) for the IoU entry
+// points; the NMS workspace adds slack so tiles may start at any box)
+__host__ __device__ inline PackedView packed_view(const void *base, int64_t n_pad) {
+    PackedView v;
+    v.p0 = reinterpret_cast<const float4 *>(base);
+    v.p1 = v.p0 + n_pad;
+    return v;
+}
+
+// Conservative reject: true when the circumscribed circles are disjoint, so the
+// rectangles cannot touch and the reference value is exactly 0.
+__device__ __forceinline__ bool circles_disjoint(float ax, float ay, float ar, float bx, float by,
+                                                 float br) {
+    float dx = ax - bx, dy = ay - by;
+    float rs = ar + br;
+    return fmaf(dx, dx, dy * dy) > rs * rs;
+}
+
+__device__ __forceinline__ float fmax3(float a, float b, float c) { return fmaxf(fmaxf(a, b), c); }
+__device__ __forceinline__ float fmin3(float a, float b, float c) { return fminf(fminf(a, b), c); }
+
+// Intersection area of rectangle A and rectangle B.
+//
+// Frame: B's own (origin at B's centre, axes along B's sides), so B is the
+// slab |x|<=aB, |y|<=bB.  A's centre is (X, Y), A's long-axis direction is
+// e = (c, s) with c, s forced >= tiny > 0 by two exact symmetries (A rotated by
+// pi is the same box; mirroring the frame about B's x axis keeps B).  Exactly
+// parallel sides are thereby treated as an infinitesimal rotation — a valid
+// nearby configuration, so the area is continuous there (no special cases).
+//
+// Each of the 16 line/line crossings is evaluated ONCE: its parameter on A's
+// side clips A's edge, and the same point re-expressed on B's side clips B's
+// edge.  That keeps the clipped boundary a closed polygon even when two sides
+// are nearly parallel and the crossing itself is ill-conditioned.
+//
+// 2*area = sum over the 8 edges of (clipped length) * cross(edge dir, point-origin);
+// the origin is put at the centre of the SMALLER box to limit cancellation.
+__device__ __forceinline__ float rect_intersection_area(float4 A0, float4 A1, float4 B0,
+                                                        float4 B1) {
+    const float aA = A1.z, bA = A1.w, aB = B1.z, bB = B1.w;
+    const float dx = A0.x - B0.x, dy = A0.y - B0.y;
+    float c = fmaf(A1.x, B1.x, A1.y * B1.y);
+    float s = fmaf(A1.y, B1.x, -A1.x * B1.y);
+    const float X = fmaf(dx, B1.x, dy * B1.y);
+    float Y = fmaf(dy, B1.x, -dx * B1.y);
+    if (c < 0.f) { c = -c; s = -s; }
+    if (s < 0.f) { s = -s; Y = -Y; }
+    c = fmaxf(c, 1e-12f);
+    s = fmaxf(s, 1e-12f);
+    const float rc = __frcp_rn(c), rs = __frcp_rn(s);
+    const float n2 = fmaf(c, c, s * s);
+    const bool a_small = A0.w < B0.w;
+    // origin O = lam*(X,Y): lam = 1 -> A's centre, 0 -> B's centre
+    const float kE = a_small ? 0.f : fmaf(c, Y, -s * X);
+    const float kF = a_small ? 0.f : fmaf(c, X, s * Y);
+    const float lX = a_small ? X : 0.f;
+    const float lY = a_small ? Y : 0.f;
+    const float bAs = bA * s, bAc = bA * c, aAc = aA * c, aAs = aA * s;
+    const float wE = bA * n2, wF = aA * n2;
+
+    float acc = 0.f;
+    float yE[2][2], xE[2][2], yF[2][2], xF[2][2];  // [sigma: 0 = +, 1 = -][rho: 0 = +, 1 = -]
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+        const float g = k ? -1.f : 1.f;
+        // A's two long sides: q + t*(c, s), t in [-aA, aA]
+        {
+            const float qx = fmaf(-g, bAs, X), qy = fmaf(g, bAc, Y);
+            const float txm = (-aB - qx) * rc, txp = (aB - qx) * rc;
+            const float tym = (-bB - qy) * rs, typ = (bB - qy) * rs;
+            const float lo = fmax3(-aA, txm, tym), hi = fmin3(aA, txp, typ);
+            acc = fmaf(fmaxf(hi - lo, 0.f), fmaf(g, kE, wE), acc);
+            yE[k][1] = fmaf(txm, s, qy);
+            yE[k][0] = fmaf(txp, s, qy);
+            xE[k][1] = fmaf(tym, c, qx);
+            xE[k][0] = fmaf(typ, c, qx);
+        }
+        // A's two short sides: p + t*(-s, c), t in [-bA, bA]
+        {
+            const float px = fmaf(g, aAc, X), py = fmaf(g, aAs, Y);
+            const float txp = (px - aB) * rs, txm = (px + aB) * rs;
+            const float tym = (-bB - py) * rc, typ = (bB - py) * rc;
+            const float lo = fmax3(-bA, txp, tym), hi = fmin3(bA, txm, typ);
+            acc = fmaf(fmaxf(hi - lo, 0.f), fmaf(g, kF, wF), acc);
+            yF[k][0] = fmaf(txp, c, py);
+            yF[k][1] = fmaf(txm, c, py);
+            xF[k][1] = fmaf(-tym, s, px);
+            xF[k][0] = fmaf(-typ, s, px);
+        }
+    }
+#pragma unroll
+    for (int r = 0; r < 2; ++r) {
+        const float g = r ? -1.f : 1.f;
+        // B's side x = g*aB, parameter y in [-bB, bB]
+        {
+            const float lo = fmax3(-bB, yE[1][r], yF[1][r]);
+            const float hi = fmin3(bB, yE[0][r], yF[0][r]);
+            acc = fmaf(fmaxf(hi - lo, 0.f), fmaf(-g, lX, aB), acc);
+        }
+        // B's side y = g*bB, parameter x in [-aB, aB]
+        {
+            const float lo = fmax3(-aB, xE[0][r], xF[1][r]);
+            const float hi = fmin3(aB, xE[1][r], xF[0][r]);
+            acc = fmaf(fmaxf(hi - lo, 0.f), fmaf(-g, lY, bB), acc);
+        }
+    }
+    float inter = fmaxf(0.5f * acc, 0.f);
+    return fminf(inter, fminf(A0.w, B0.w));
+}
+
+// IoU (mode 0) or IoF (mode 1, divide by A's area).  Areas below 1e-14 give 0
+// like the reference's native code (SURVEY.md §8(c) Spec A step 2).
+template <int MODE>
+__device__ __forceinline__ float rect_overlap(float4 A0, float4 A1, float4 B0, float4 B1) {
+    const float inter = rect_intersection_area(A0, A1, B0, B1);
+    const float base = MODE == 0 ? (A0.w + B0.w - inter) : A0.w;
+    const float v = __fdividef(inter, base);
+    return (A0.w < 1e-14f || B0.w < 1e-14f) ? 0.f : v;
+}
+
+// ---- TMA (bulk async copy) + mbarrier helpers, raw PTX -----------------------
+__device__ __forceinline__ uint32_t smem_u32(const void *p) {
+    return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void fence_mbar_init() {
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)),
+                 "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+// 1-D bulk copy global -> shared through the TMA unit (SASS: UBLKCP); bytes and
+// both addresses must be multiples of 16.
+__device__ __forceinline__ void tma_load_1d(void *dst_smem, const void *src_gmem, uint32_t bytes,
+                                            uint64_t *bar) {
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+        ::"r"(smem_u32(dst_smem)), "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
+        : "memory");
+}
+
+}  // namespace rotgeo

@@ -1,0 +1,46 @@
+// Host-side launch helpers shared by the C-ABI translation unit.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace rotgeo {
+
+int launch_pack(const float *boxes, int64_t n, int stride, const int64_t *gather,
+                const float *offsets, float min_wh, void *packed, int64_t n_pad,
+                cudaStream_t stream);
+
+int launch_iou_pairwise(const void *packed1, int64_t n1, const void *packed2, int64_t n2, int mode,
+                        float *out, int64_t ld_out, cudaStream_t stream);
+
+int launch_iou_aligned(const float *boxes1, const float *boxes2, int64_t n, int stride1,
+                       int stride2, int mode, float min_wh, float *out, cudaStream_t stream);
+
+// One segment of a segmented NMS, in units of sorted positions.
+struct NmsSegment {
+    int64_t start;      // first sorted position
+    int64_t len;        // boxes in the segment
+    int64_t mask_base;  // first u64 word of this segment's suppression mask
+    int64_t tile_base;  // first tile id of this segment in the bitmask grid
+    int32_t words;      // u64 words per mask row (even)
+    int32_t row_blocks; // ceil(len / 64)
+};
+
+struct NmsPlan {
+    int64_t n;
+    int64_t n_pad;       // float4 slots per packed plane (with tile slack)
+    int64_t num_segments;
+    int64_t total_tiles;
+    int64_t mask_words;
+    // workspace layout (byte offsets)
+    size_t off_packed, off_segments, off_mask, off_flags, off_seg_keep, total_bytes;
+};
+
+void nms_plan(int64_t n, const int64_t *seg_offsets_host, int64_t num_segments, NmsPlan *plan,
+              NmsSegment *segments_out /* nullable, num_segments entries */);
+
+int launch_nms(const NmsPlan &plan, const void *packed, const NmsSegment *segments_dev,
+               int max_words, const int64_t *order, const int64_t *seg_order, float thr,
+               uint64_t *mask, uint8_t *flags, int64_t *keep_out, int64_t *num_keep_out,
+               cudaStream_t stream);
+
+}  // namespace rotgeo

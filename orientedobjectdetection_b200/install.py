@@ -1,0 +1,76 @@
+"""``patch()`` rebinds the reference's names to this package when mmcv /
+mmrotate are importable (they are not in this image).  The
+nine modules that bind the names at import time are listed in SURVEY.md §8(b).
+"""
+import importlib
+
+from . import core, ops
+
+_L1 = {'box_iou_rotated': ops.box_iou_rotated, 'nms_rotated': ops.nms_rotated,
+       'batched_nms': ops.batched_nms}
+_L1_MODULES = (
+    'mmcv.ops',
+    'mmrotate.core.bbox.iou_calculators.rotate_iou2d_calculator',
+    'mmrotate.core.evaluation.eval_map',
+    'mmrotate.datasets.pipelines.transforms',
+    'mmrotate.core.post_processing.bbox_nms_rotated',
+    'mmrotate.core.patch.merge_results',
+    'mmrotate.datasets.dota',
+    'mmrotate.models.dense_heads.rotated_rpn_head',
+    'mmrotate.models.dense_heads.oriented_rpn_head',
+)
+_L2 = {
+    'mmrotate.core.bbox.iou_calculators.rotate_iou2d_calculator':
+        {'rbbox_overlaps': core.rbbox_overlaps},
+    'mmrotate.core.bbox.iou_calculators': {'rbbox_overlaps': core.rbbox_overlaps},
+    'mmrotate.core.bbox': {'rbbox_overlaps': core.rbbox_overlaps},
+    'mmrotate.core.post_processing.bbox_nms_rotated':
+        {'multiclass_nms_rotated': core.multiclass_nms_rotated,
+         'aug_multiclass_nms_rotated': core.aug_multiclass_nms_rotated},
+    'mmrotate.core.post_processing':
+        {'multiclass_nms_rotated': core.multiclass_nms_rotated,
+         'aug_multiclass_nms_rotated': core.aug_multiclass_nms_rotated},
+    'mmrotate.core.patch.merge_results': {'merge_results': core.merge_results},
+    'mmrotate.core.patch': {'merge_results': core.merge_results},
+    'mmrotate.core': {'rbbox_overlaps': core.rbbox_overlaps,
+                      'multiclass_nms_rotated': core.multiclass_nms_rotated,
+                      'aug_multiclass_nms_rotated': core.aug_multiclass_nms_rotated,
+                      'merge_results': core.merge_results},
+}
+
+
+def patch(strict=False):
+    """Rebind every name; returns the list of (module, name) pairs patched.
+    Modules that are not importable are skipped unless ``strict``."""
+    done = []
+    for modname in _L1_MODULES:
+        try:
+            mod = importlib.import_module(modname)
+        except Exception:
+            if strict:
+                raise
+            continue
+        for name, fn in _L1.items():
+            if hasattr(mod, name):
+                setattr(mod, name, fn)
+                done.append((modname, name))
+    for modname, names in _L2.items():
+        try:
+            mod = importlib.import_module(modname)
+        except Exception:
+            if strict:
+                raise
+            continue
+        for name, fn in names.items():
+            if hasattr(mod, name):
+                setattr(mod, name, fn)
+                done.append((modname, name))
+    try:   # configs say iou_calculator=dict(type='RBboxOverlaps2D')
+        from mmdet.core.bbox.iou_calculators import IOU_CALCULATORS
+        IOU_CALCULATORS.register_module(name='RBboxOverlaps2D', force=True,
+                                        module=core.RBboxOverlaps2D)
+        done.append(('mmdet IOU_CALCULATORS', 'RBboxOverlaps2D'))
+    except Exception:
+        if strict:
+            raise
+    return done

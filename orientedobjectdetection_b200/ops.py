@@ -1,0 +1,211 @@
+"""Operator-level seam: the three names the reference binds with
+``from mmcv.ops import box_iou_rotated, nms_rotated, batched_nms`` (reference
+mmrotate/core/bbox/iou_calculators/rotate_iou2d_calculator.py:2,
+mmrotate/core/post_processing/bbox_nms_rotated.py:3,
+mmrotate/core/patch/merge_results.py:4, mmrotate/datasets/dota.py:16,
+mmrotate/models/dense_heads/oriented_rpn_head.py:6, rotated_rpn_head.py:7) with
+the same signatures, argument meaning, return conventions and error behaviour
+(§8(b)).
+
+Everything computes on the GPU through librotgeo.so.  CPU tensors (three
+reference call sites pass them: eval_map.py:60-62, transforms.py:369-371,
+merge_results.py:115 with device='cpu') are moved to the current CUDA device
+and the result is returned on the caller's device — a transfer, never a CPU
+implementation.  No GPU or no library => RuntimeError.
+"""
+import numpy as np
+import torch
+
+from . import _lib
+
+_MODE = {'iou': 0, 'iof': 1}
+
+
+def _cuda_device(*tensors):
+    for t in tensors:
+        if t is not None and t.is_cuda:
+            return t.device
+    if not torch.cuda.is_available():
+        raise RuntimeError('rotgeo: no CUDA device available and there is no CPU fallback')
+    return torch.device('cuda', torch.cuda.current_device())
+
+
+def _rows_f32(t, dev):
+    """(n, >=5) tensor -> float32 CUDA tensor whose rows are readable with a
+    row stride (only the first five columns are ever read)."""
+    t = t.detach()
+    if t.dtype != torch.float32 or t.device != dev:
+        t = t.to(device=dev, dtype=torch.float32)
+    if t.dim() != 2 or t.stride(1) != 1 or t.stride(0) < 5:
+        t = t.contiguous()
+    return t
+
+
+def _stream(dev):
+    return torch.cuda.current_stream(dev).cuda_stream
+
+
+def _overlaps(bboxes1, bboxes2, mode, aligned, min_wh):
+    """shared body of box_iou_rotated / rbbox_overlaps (min_wh fuses the clamp
+    of rotate_iou2d_calculator.py:84-87 into the pack kernel)."""
+    assert mode in _MODE
+    rows, cols = bboxes1.size(0), bboxes2.size(0)
+    if aligned:
+        assert rows == cols
+    out_shape = (rows,) if aligned else (rows, cols)
+    if rows * cols == 0:
+        return bboxes1.new_zeros(out_shape)
+    dev = _cuda_device(bboxes1, bboxes2)
+    b1, b2 = _rows_f32(bboxes1, dev), _rows_f32(bboxes2, dev)
+    L = _lib.load()
+    with torch.cuda.device(dev):
+        out = torch.empty(out_shape, dtype=torch.float32, device=dev)
+        if aligned:
+            _lib.check(L.rotgeo_iou_aligned(b1.data_ptr(), b2.data_ptr(), rows, b1.stride(0),
+                                            b2.stride(0), _MODE[mode], float(min_wh),
+                                            out.data_ptr(), _stream(dev)), 'rotgeo_iou_aligned')
+        else:
+            nbytes = L.rotgeo_iou_workspace_bytes(rows, cols)
+            ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+            _lib.check(L.rotgeo_iou_pairwise(b1.data_ptr(), rows, b1.stride(0), b2.data_ptr(),
+                                             cols, b2.stride(0), _MODE[mode], float(min_wh),
+                                             out.data_ptr(), cols, ws.data_ptr(), nbytes,
+                                             _stream(dev)), 'rotgeo_iou_pairwise')
+    if out.dtype != bboxes1.dtype or out.device != bboxes1.device:
+        out = out.to(device=bboxes1.device, dtype=bboxes1.dtype)
+    return out
+
+
+def box_iou_rotated(bboxes1, bboxes2, mode='iou', aligned=False, clockwise=True):
+    """Drop-in for ``mmcv.ops.box_iou_rotated``.
+
+    ``bboxes1`` (N,5+) and ``bboxes2`` (M,5+) rows ``(cx, cy, w, h, theta)``;
+    returns (N, M) or (N,) when ``aligned``.  ``mode`` 'iou' | 'iof' (first
+    argument is the foreground).  ``clockwise=False`` negates both angles,
+    which leaves every value unchanged (mirror invariance), so it is accepted
+    and has no effect.
+    """
+    return _overlaps(bboxes1, bboxes2, mode, aligned, 0.0)
+
+
+def _nms_keep(boxes, scores, iou_threshold, seg_ids=None, offsets=None):
+    """kept indices (int64, score-descending, on the CUDA device) of a greedy
+    rotated NMS; ``seg_ids`` (int64/ints per box) restricts suppression to boxes
+    of equal id, ``offsets`` (float per box) is added to cx, cy first."""
+    dev = _cuda_device(boxes, scores)
+    n = boxes.size(0)
+    b = _rows_f32(boxes, dev)
+    s = scores.detach().to(device=dev, dtype=torch.float32).reshape(-1)
+    L = _lib.load()
+    with torch.cuda.device(dev):
+        # ties: lower index first (the reference's sort is unspecified there)
+        order = torch.sort(s, descending=True, stable=True).indices
+        seg_order_ptr, seg_off_ptr, nseg = None, None, 0
+        seg_off = None
+        if seg_ids is not None:
+            seg = seg_ids.detach().to(device=dev, dtype=torch.int64).reshape(-1)
+            uniq, inv, counts = torch.unique(seg, sorted=True, return_inverse=True,
+                                             return_counts=True)
+            seg_order = order[torch.sort(inv[order], stable=True).indices].contiguous()
+            seg_off = np.zeros(counts.numel() + 1, dtype=np.int64)
+            seg_off[1:] = np.cumsum(counts.cpu().numpy())
+            seg_order_ptr, seg_off_ptr, nseg = seg_order.data_ptr(), seg_off.ctypes.data, counts.numel()
+        off_ptr = None
+        if offsets is not None:
+            offsets = offsets.detach().to(device=dev, dtype=torch.float32).contiguous()
+            off_ptr = offsets.data_ptr()
+        nbytes = L.rotgeo_nms_workspace_bytes(n, seg_off_ptr, nseg)
+        ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+        keep = torch.empty(n, dtype=torch.int64, device=dev)
+        nkeep = torch.empty(1, dtype=torch.int64, device=dev)
+        _lib.check(L.rotgeo_nms(b.data_ptr(), n, b.stride(0), off_ptr, order.data_ptr(),
+                                seg_order_ptr, seg_off_ptr, nseg, float(iou_threshold),
+                                keep.data_ptr(), nkeep.data_ptr(), ws.data_ptr(), nbytes,
+                                _stream(dev)), 'rotgeo_nms')
+        k = int(nkeep.item())          # the one sync: sizes the output
+    return keep[:k]
+
+
+def nms_rotated(dets, scores, iou_threshold, labels=None, clockwise=True):
+    """Drop-in for ``mmcv.ops.nms_rotated``.
+
+    Returns ``(cat(dets[keep], scores[keep,None]) (K,6), keep (K,) int64)`` with
+    ``keep`` indexing the input in descending-score order, and ``(dets, None)``
+    for empty input.  Suppression follows the reference's CPU kernel
+    (``IoU >= iou_threshold``).  ``labels``: mmcv appends them as a 6th column
+    that neither of its kernels compares, so they do not separate classes there
+    and do not here (the reference never passes them; class separation is the
+    offset trick of bbox_nms_rotated.py:73-77).  ``clockwise`` has no effect on
+    IoU (see box_iou_rotated).
+    """
+    if dets.shape[0] == 0:
+        return dets, None
+    assert dets.size(1) == 5, 'dets must be (N, 5) rotated boxes'
+    keep = _nms_keep(dets, scores, iou_threshold)
+    keep = keep.to(dets.device)
+    out = torch.cat((dets[keep], scores[keep].reshape(-1, 1).to(dets.dtype)), dim=1)
+    return out, keep
+
+
+def _nms_horizontal(boxes, scores, iou_threshold, **kwargs):
+    """axis-aligned ``mmcv.ops.nms`` stand-in (OUT OF north_star scope, library
+    call: the fork's RPN configs select type='nms' on obb2xyxy boxes,
+    configs/oriented_rcnn/oriented_rcnn_r50_fpn_1x_dota_le90.py:93,116)."""
+    from torchvision.ops import nms as tv_nms
+    dev = _cuda_device(boxes, scores)
+    keep = tv_nms(boxes.to(dev).float(), scores.to(dev).float(), float(iou_threshold))
+    keep = keep.to(boxes.device)
+    return torch.cat((boxes[keep], scores[keep].reshape(-1, 1)), dim=1), keep
+
+
+_NMS_TYPES = {'nms_rotated': nms_rotated, 'nms': _nms_horizontal}
+
+
+def batched_nms(boxes, scores, idxs, nms_cfg, class_agnostic=False):
+    """Drop-in for ``mmcv.ops.batched_nms`` (called at
+    reference oriented_rpn_head.py:275, rotated_rpn_head.py:515).
+
+    NMS among boxes of equal ``idxs`` only.  ``nms_cfg``: dict with ``type``
+    ('nms_rotated' for 5-column boxes, 'nms' for 4-column ones),
+    ``iou_threshold``/``iou_thr``, optional ``class_agnostic``, ``split_thr``,
+    ``max_num``.  Returns ``(cat(boxes[keep], scores[keep,None]), keep)`` in
+    descending-score order.  The rotated type runs as ONE segmented launch
+    whatever the box count (mmcv loops over ids once N >= split_thr; the kept
+    set and order are the same).
+    """
+    if nms_cfg is None:
+        scores, inds = scores.sort(descending=True)
+        return torch.cat([boxes[inds], scores[:, None]], -1), inds
+    cfg = dict(nms_cfg)
+    class_agnostic = cfg.pop('class_agnostic', class_agnostic)
+    nms_type = cfg.pop('type', 'nms')
+    cfg.pop('split_thr', None)
+    max_num = cfg.pop('max_num', -1)
+    if nms_type not in _NMS_TYPES:
+        raise KeyError('unsupported nms type %r' % (nms_type,))
+    thr = cfg.pop('iou_threshold', cfg.pop('iou_thr', None))
+    if thr is None:
+        raise TypeError("nms_cfg needs 'iou_threshold'")
+    if boxes.shape[0] == 0:
+        return torch.cat([boxes, scores[:, None]], -1), boxes.new_zeros((0,), dtype=torch.long)
+
+    if nms_type == 'nms_rotated' and boxes.size(-1) == 5:
+        offsets, seg = None, None
+        if not class_agnostic:
+            # same float arithmetic as mmcv: max(cx,cy) + max(w,h) + 1, times the id
+            max_coordinate = boxes[..., :2].max() + boxes[..., 2:4].max()
+            offsets = idxs.to(boxes) * (max_coordinate + torch.tensor(1).to(boxes))
+            seg = idxs
+        keep = _nms_keep(boxes, scores, thr, seg_ids=seg, offsets=offsets).to(boxes.device)
+    else:
+        if class_agnostic:
+            b = boxes
+        else:
+            max_coordinate = boxes.max()
+            off = idxs.to(boxes) * (max_coordinate + torch.tensor(1).to(boxes))
+            b = boxes + off[:, None]
+        _, keep = _nms_horizontal(b, scores, thr)
+    if max_num > 0:
+        keep = keep[:max_num]
+    out = torch.cat([boxes[keep], scores[keep][:, None]], -1)
+    return out, keep

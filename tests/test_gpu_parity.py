@@ -1,0 +1,179 @@
+"""GPU parity: the CUDA path (through the C-ABI, via the python seam) against
+the CPU oracle on the same seeded inputs.  Bars (BASELINE.json north_star):
+IoU within 1e-5 absolute; NMS keep indices identical except at pairs whose IoU
+lies within 1e-5 of the threshold (none occur on these seeds; a divergence is
+reported with the offending pair)."""
+import numpy as np
+import pytest
+import torch
+
+import orientedobjectdetection_b200 as rg
+from oracle import ref, ref_api
+from orientedobjectdetection_b200 import synth
+
+pytestmark = pytest.mark.gpu
+IOU_TOL = 1e-5
+
+
+def _cuda(a):
+    return torch.from_numpy(np.ascontiguousarray(a)).cuda()
+
+
+def _explain_nms_divergence(boxes, scores, thr, got, want):
+    """first position where the keep lists differ + the band pair that explains it"""
+    k = next((i for i in range(min(len(got), len(want))) if got[i] != want[i]),
+             min(len(got), len(want)))
+    culprit = want[k] if k < len(want) else got[k]
+    other = got[k] if k < len(got) else want[k]
+    for idx in (culprit, other):
+        prev = np.array(list(want[:k]), dtype=np.int64)
+        if prev.size:
+            ious = ref.box_iou_rotated(boxes[prev], boxes[idx:idx + 1])[:, 0]
+            near = np.abs(ious - np.float32(thr)) <= IOU_TOL
+            if near.any():
+                j = int(prev[np.argmax(near)])
+                return 'band pair (%d,%d) oracle IoU %.8f thr %.8f' % (j, idx, ious[np.argmax(near)], thr)
+    return 'UNEXPLAINED divergence at keep position %d (got %s, want %s)' % (
+        k, got[k:k + 3], want[k:k + 3])
+
+
+def _assert_keep(boxes, scores, thr, got, want):
+    got, want = [int(v) for v in got], [int(v) for v in want]
+    if got != want:
+        why = _explain_nms_divergence(boxes, scores, thr, got, want)
+        assert why.startswith('band pair'), why
+        pytest.skip('keep lists differ only inside the 1e-5 threshold band: ' + why)
+
+
+# ------------------------------------------------------------------ IoU
+def test_golden_overlaps(golden_dir):
+    import json, os
+    g = json.load(open(os.path.join(golden_dir, 'overlaps_golden.json')))
+    ious = rg.rbbox_overlaps(torch.tensor(g['predict']).cuda(), torch.tensor(g['gt']).cuda())
+    assert ious.shape == (3, 4) and ious.is_cuda
+    assert torch.allclose(ious.cpu(), torch.tensor(g['expect_ious']), atol=g['atol'])
+    want = ref_api.rbbox_overlaps(torch.tensor(g['predict']), torch.tensor(g['gt']))
+    assert (ious.cpu() - want).abs().max() <= IOU_TOL
+
+
+@pytest.mark.parametrize('n,m,extent', [(1000, 1000, 1024.0), (700, 333, 200.0), (257, 129, 50.0),
+                                        (1, 1, 10.0), (64, 128, 100.0), (65, 131, 100.0)])
+@pytest.mark.parametrize('mode', ['iou', 'iof'])
+def test_iou_matrix_vs_oracle(n, m, extent, mode):
+    a, b = synth.c1_iou(seed=0, n=n, m=m, extent=extent)
+    want = ref.box_iou_rotated(a, b, mode)
+    got = rg.box_iou_rotated(_cuda(a), _cuda(b), mode).cpu().numpy()
+    assert got.shape == want.shape
+    assert np.abs(got - want).max() <= IOU_TOL
+    assert ((got > 0) == (want > 0)).mean() > 0.999
+
+
+def test_iou_aligned_and_strided_rows():
+    a, b = synth.c1_iou(seed=2, n=500, m=500, extent=120.0)
+    want = ref.box_iou_rotated(a, b, aligned=True)
+    got = rg.box_iou_rotated(_cuda(a), _cuda(b), aligned=True).cpu().numpy()
+    assert got.shape == (500,) and np.abs(got - want).max() <= IOU_TOL
+    a6 = np.concatenate([a, np.full((500, 1), 0.5, np.float32)], 1)       # (m,6) det rows
+    got6 = rg.box_iou_rotated(_cuda(a6), _cuda(b)).cpu().numpy()
+    assert np.abs(got6 - ref.box_iou_rotated(a, b)).max() <= IOU_TOL
+    calc = rg.RBboxOverlaps2D()
+    got7 = calc(_cuda(a6), _cuda(b)).cpu().numpy()
+    assert np.abs(got7 - ref.box_iou_rotated(a, b)).max() <= IOU_TOL
+
+
+def test_iou_cpu_tensor_roundtrip_and_float64():
+    a, b = synth.c1_iou(seed=4, n=40, m=30, extent=80.0)
+    out = rg.box_iou_rotated(torch.from_numpy(a), torch.from_numpy(b))
+    assert not out.is_cuda and out.dtype == torch.float32
+    assert np.abs(out.numpy() - ref.box_iou_rotated(a, b)).max() <= IOU_TOL
+    out64 = rg.box_iou_rotated(torch.from_numpy(a).double(), torch.from_numpy(b).double())
+    assert out64.dtype == torch.float64
+
+
+def test_iou_empty_and_errors():
+    e = torch.zeros((0, 5)).cuda()
+    b = _cuda(synth.le90_boxes(7, 0))
+    assert rg.rbbox_overlaps(e, b).shape == (0, 7)
+    assert rg.rbbox_overlaps(b, e).shape == (7, 0)
+    assert rg.rbbox_overlaps(e, e, is_aligned=True).shape == (0, 1)
+    with pytest.raises(AssertionError):
+        rg.rbbox_overlaps(b, b, mode='giou')
+    with pytest.raises(AssertionError):
+        rg.rbbox_overlaps(b, b[:3], is_aligned=True)
+
+
+def test_iou_stress_sets():
+    """near-duplicates / clamped sizes: the fp32 reference itself is unstable
+    there (it differs from its own float64 instantiation by up to O(1)), so the
+    bar is the float64 oracle; elsewhere the fp32 oracle."""
+    st = synth.stress_boxes(0)
+    for name in ('base', 'axis', 'far', 'dup', 'tiny'):
+        x = st['base'] if name in ('base', 'axis', 'dup') else st[name]
+        y = st[name]
+        got = rg.box_iou_rotated(_cuda(x), _cuda(y)).cpu().numpy()
+        w32 = ref.box_iou_rotated(x, y)
+        w64 = ref.box_iou_rotated(x.astype(np.float64), y.astype(np.float64))
+        stable = np.abs(w32 - w64) <= 1e-6
+        assert np.abs(got - w32)[stable].max() <= IOU_TOL, name
+        assert np.abs(got - w64).max() <= IOU_TOL, name
+        assert np.isfinite(got).all()
+    got = rg.box_iou_rotated(_cuda(st['huge']), _cuda(st['base'])).cpu().numpy()
+    assert np.abs(got - ref.box_iou_rotated(st['huge'], st['base'])).max() <= IOU_TOL
+
+
+# ------------------------------------------------------------------ NMS
+@pytest.mark.parametrize('n,extent,thr', [(300, 150.0, 0.1), (2000, 400.0, 0.3), (5000, 1024.0, 0.1),
+                                          (129, 60.0, 0.5), (1, 10.0, 0.1), (64, 50.0, 0.8)])
+def test_nms_rotated_vs_oracle(n, extent, thr):
+    boxes = synth.le90_boxes(n, 21, extent)
+    scores = synth.unique_scores(n, 21)
+    wd, wk = ref.nms_rotated(boxes, scores, thr)
+    gd, gk = rg.nms_rotated(_cuda(boxes), _cuda(scores), thr)
+    assert gk.dtype == torch.int64 and gd.shape[1] == 6
+    _assert_keep(boxes, scores, thr, gk.cpu().numpy(), wk)
+    assert np.array_equal(gd.cpu().numpy(), wd)
+
+
+def test_nms_empty_and_ties():
+    d, k = rg.nms_rotated(torch.zeros((0, 5)).cuda(), torch.zeros((0,)).cuda(), 0.1)
+    assert k is None and d.shape == (0, 5)
+    b = _cuda(np.array([[0, 0, 2, 2, 0], [50, 0, 2, 2, 0], [0, 0, 2, 2, 0]], np.float32))
+    _, k = rg.nms_rotated(b, _cuda(np.array([0.5, 0.5, 0.5], np.float32)), 0.1)
+    assert k.tolist() == [0, 1]
+
+
+@pytest.mark.parametrize('dense', [False, True])
+@pytest.mark.parametrize('seed', [0, 1])
+def test_multiclass_nms_c2(seed, dense):
+    """C2: 2000 proposals x 15 classes (Rotated RetinaNet post-process shape)."""
+    n = 2000 if not dense else 600      # dense: all 15 classes pass -> 9000 candidates
+    mb, ms = synth.c2_multiclass(seed, n=n, dense=dense)
+    wd, wl, wk = ref_api.multiclass_nms_rotated(torch.from_numpy(mb), torch.from_numpy(ms), 0.05, 0.1, 2000)
+    gd, gl, gk = rg.multiclass_nms_rotated(_cuda(mb), _cuda(ms), 0.05, dict(iou_thr=0.1), 2000,
+                                           return_inds=True)
+    assert gk.cpu().tolist() == wk.tolist()
+    assert torch.equal(gl.cpu(), wl) and torch.equal(gd.cpu(), wd)
+
+
+def test_batched_nms_c4_image():
+    boxes, scores, ids = synth.c4_rpn_image(seed=3, per_level=600)
+    wd, wk = ref_api.batched_nms_rotated(torch.from_numpy(boxes), torch.from_numpy(scores),
+                                         torch.from_numpy(ids), 0.8)
+    gd, gk = rg.batched_nms(_cuda(boxes), _cuda(scores), _cuda(ids),
+                            dict(type='nms_rotated', iou_threshold=0.8))
+    assert gk.cpu().tolist() == wk.tolist()
+    assert torch.equal(gd.cpu(), wd)
+
+
+def test_merge_results_c5_small():
+    import copy
+    res, offs, shape = synth.c5_patch_results(seed=0, width=3000, height=3000, dets_per_patch=150)
+    want = ref_api.merge_results(copy.deepcopy(res), offs, 0.1)
+    mine = copy.deepcopy(res)
+    got = rg.merge_results(mine, offs, shape, iou_thr=0.1, device='cuda')
+    assert len(got) == len(want) == 15
+    for g, w in zip(got, want):
+        assert g.shape == w.shape and np.array_equal(g, w)
+    # in-place translation of the caller's arrays, like the reference
+    assert np.array_equal(mine[1][0][:, 2:], res[1][0][:, 2:])
+    assert not np.array_equal(mine[1][0][:, :2], res[1][0][:, :2]) or res[1][0].size == 0
