@@ -1,0 +1,337 @@
+#!/usr/bin/env python
+"""bench.py — rotated IoU Gpairs/s (headline, BASELINE.json C3: 8192x8192 le90
+boxes, one such block per GPU) and rotated-NMS boxes/s (secondary, C2/C4), next
+to the CPU restatement of the reference's mmcv path timed on this box's cores.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl rotgeo|reference]
+
+One JSON line on stdout (rank 0).  See DESIGN.md "Measurement" for definitions.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+N_ROWS = 8192          # rows per GPU (weak scaling: the global matrix is (N_ROWS*G) x N_COLS)
+N_COLS = 8192
+EXTENT = 4096.0
+FLOP_PER_PAIR = 450.0  # mandatory part of the reference algorithm
+FP32_PEAK_TFLOPS = 148 * 128 * 2 * 1.965e9 / 1e12   # 74.5, theoretical at max boost
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=20)
+    ap.add_argument('--warmup', type=int, default=5)
+    ap.add_argument('--impl', default='rotgeo', choices=['rotgeo', 'reference'])
+    ap.add_argument('--no-secondary', action='store_true')
+    ap.add_argument('--no-cpu-baseline', action='store_true')
+    return ap.parse_args()
+
+
+def peaks():
+    p = os.path.join(ROOT, 'MEASURED_PEAKS.json')
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return float(d['hbm_gbs']), 'measured (MEASURED_PEAKS.json hbm_gbs, burst copy)'
+    return 6650.0, 'fallback (B200_PROFILING.md)'
+
+
+class ClockSampler(object):
+    """nvidia-smi clocks / throttle reasons sampled while the timed region runs"""
+    Q = ('clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,'
+         'clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,'
+         'clocks_event_reasons.sw_power_cap')
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ['nvidia-smi', '-i', str(self.index), '--query-gpu=' + self.Q,
+                 '--format=csv,noheader,nounits', '-lms', '100'],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(',')])
+
+    def stop(self):
+        if self.proc is None:
+            return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['nvidia-smi unavailable']}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                mx.append(float(r[1]))
+            except Exception:
+                continue
+            for nm, v in zip(names, r[3:7]):
+                if v.lower().startswith('active'):
+                    reasons.add(nm)
+        return {'sm_mhz': float(np.median(sm)) if sm else None,
+                'sm_max_mhz': float(max(mx)) if mx else None,
+                'samples': len(sm), 'reasons': sorted(reasons)}
+
+
+def cpu_iou_sample(a, b, rows, threads):
+    """oracle on a row slice of the same workload; returns (Gpairs/s, seconds)"""
+    from oracle import ref
+    ref.box_iou_rotated(a[:64], b, threads=threads)       # warm-up
+    t0 = time.perf_counter()
+    ref.box_iou_rotated(a[:rows], b, threads=threads)
+    dt = time.perf_counter() - t0
+    return rows * b.shape[0] / dt / 1e9, dt
+
+
+def run_reference(args, rank):
+    """--impl reference: the CPU restatement of the reference's mmcv path (the
+    real mmcv cannot be installed here), all host threads, rank 0 only."""
+    if rank != 0:
+        return
+    from oracle import ref
+    from orientedobjectdetection_b200 import synth
+    a, b = synth.c3_iou(0, N_ROWS, N_COLS, EXTENT)
+    a[:, 2:4] = np.maximum(a[:, 2:4], 1e-3)
+    b[:, 2:4] = np.maximum(b[:, 2:4], 1e-3)
+    threads = min(ref.max_threads(), len(os.sched_getaffinity(0)))
+    rows = 1024
+    for _ in range(max(1, min(args.warmup, 2))):
+        ref.box_iou_rotated(a[:rows], b, threads=threads)
+    times = []
+    for s in range(args.steps):
+        lo = (s * rows) % N_ROWS
+        t0 = time.perf_counter()
+        ref.box_iou_rotated(a[lo:lo + rows], b, threads=threads)
+        times.append(time.perf_counter() - t0)
+    ms = 1e3 * float(np.mean(times))
+    val = rows * N_COLS / (ms * 1e-3) / 1e9
+    sample = '%d-row slice x %d columns of the 8192x8192 C3 matrix per step' % (rows, N_COLS)
+    print(json.dumps({
+        'impl': 'reference', 'metric': 'rotated_iou_gpairs_per_s', 'value': val, 'unit': 'Gpairs/s',
+        'n_gpus': args.gpus, 'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': ms,
+        'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32',
+        'data': 'synthetic',
+        'config': {'workload': 'C3 rbbox_overlaps 8192x8192 le90 boxes, extent 4096, seed 0',
+                   'sample': sample},
+        'cpu_baseline': {'value': val, 'unit': 'Gpairs/s', 'cores': threads, 'kind': 'port',
+                         'sample': sample},
+        'e2e': {'value': val, 'unit': 'Gpairs/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+    }))
+
+
+def timed_steps(torch, fn, steps, flush, stream_sync):
+    """per-step CUDA events on the current stream; L2 is flushed between steps
+    OUTSIDE the events.  returns list of ms."""
+    out = []
+    for _ in range(steps):
+        flush()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        fn()
+        e1.record()
+        e1.synchronize()
+        out.append(e0.elapsed_time(e1))
+    return out
+
+
+def secondary_nms(torch, rg, synth, reps=5):
+    """rotated-NMS boxes/s on one GPU, device-resident inputs, through the public
+    python API (includes its single D2H sync)."""
+    res = {}
+
+    def best(fn):
+        fn()
+        ts = []
+        for _ in range(reps):
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            fn()
+            torch.cuda.synchronize()
+            ts.append(time.perf_counter() - t0)
+        return min(ts)
+
+    for name, dense in (('c2_multiclass_nms_2000x15_sparse', False), ('c2_multiclass_nms_2000x15_dense', True)):
+        mb, ms = synth.c2_multiclass(0, dense=dense)
+        mbd, msd = torch.from_numpy(mb).cuda(), torch.from_numpy(ms).cuda()
+        ncand = int((ms[:, :-1] > 0.05).sum())
+        t = best(lambda: rg.multiclass_nms_rotated(mbd, msd, 0.05, dict(iou_thr=0.1), 2000))
+        res[name] = {'boxes': ncand, 'ms': 1e3 * t, 'boxes_per_s': ncand / t}
+    boxes, scores, ids = synth.c4_rpn_image(0)
+    bd, sd, idd = (torch.from_numpy(x).cuda() for x in (boxes, scores, ids))
+    t = best(lambda: rg.batched_nms(bd, sd, idd, dict(type='nms_rotated', iou_threshold=0.8)))
+    res['c4_batched_nms_1img_5x2000'] = {'boxes': len(boxes), 'ms': 1e3 * t, 'boxes_per_s': len(boxes) / t}
+    n = 30000
+    b1 = torch.from_numpy(synth.le90_boxes(n, 9, 1024.0)).cuda()
+    s1 = torch.from_numpy(synth.unique_scores(n, 9)).cuda()
+    t = best(lambda: rg.nms_rotated(b1, s1, 0.1))
+    res['nms_rotated_single_segment_30000'] = {'boxes': n, 'ms': 1e3 * t, 'boxes_per_s': n / t}
+    return res
+
+
+def run_rotgeo(args, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+
+    import orientedobjectdetection_b200 as rg
+    from orientedobjectdetection_b200 import _lib, synth
+    assert torch.cuda.is_available(), 'bench.py needs a CUDA device (no CPU fallback)'
+    torch.cuda.set_device(local_rank)
+    dev = torch.device('cuda', local_rank)
+    if world > 1:
+        dist.init_process_group('nccl', device_id=dev)
+    L = _lib.load()
+
+    # rank r owns rows [r*N_ROWS, (r+1)*N_ROWS) of the global matrix; columns replicated
+    a = synth.le90_boxes(N_ROWS, 1000 + rank, EXTENT)
+    b = synth.le90_boxes(N_COLS, 1, EXTENT)
+    a_host, b_host = torch.from_numpy(a).pin_memory(), torch.from_numpy(b).pin_memory()
+    a_dev, b_dev = a_host.to(dev), b_host.to(dev)
+    out = torch.empty((N_ROWS, N_COLS), dtype=torch.float32, device=dev)
+    nbytes = L.rotgeo_iou_workspace_bytes(N_ROWS, N_COLS)
+    ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+    flush_buf = torch.empty(512 << 20, dtype=torch.uint8, device=dev)
+    stream = torch.cuda.current_stream().cuda_stream
+    pk1 = ws.data_ptr()
+    pk2 = pk1 + (L.rotgeo_packed_bytes(N_ROWS) + 255) // 256 * 256
+
+    def flush():
+        flush_buf.zero_()
+
+    def step():      # the C-ABI call rbbox_overlaps makes: pack x2 (clamp 1e-3 fused) + tile kernel
+        _lib.check(L.rotgeo_iou_pairwise(a_dev.data_ptr(), N_ROWS, 5, b_dev.data_ptr(), N_COLS, 5, 0,
+                                         1e-3, out.data_ptr(), N_COLS, ws.data_ptr(), nbytes, stream),
+                   'rotgeo_iou_pairwise')
+
+    def kernel_only():
+        _lib.check(L.rotgeo_iou_pairwise_packed(pk1, N_ROWS, pk2, N_COLS, 0, out.data_ptr(), N_COLS,
+                                                stream), 'rotgeo_iou_pairwise_packed')
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    torch.cuda.synchronize()
+    ms = timed_steps(torch, step, args.steps, flush, None)
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    total_ms = torch.tensor([sum(ms)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(total_ms, op=dist.ReduceOp.MAX)
+    total_ms = float(total_ms.item())
+    ms_per_step = total_ms / args.steps
+    value = world * N_ROWS * N_COLS / (ms_per_step * 1e-3) / 1e9
+
+    # dominant kernel alone (same stream, CUDA events, L2 flushed between launches)
+    kms = timed_steps(torch, kernel_only, args.steps, flush, None)
+    clocks = sampler.stop() if rank == 0 else None
+    k_ms = float(np.mean(kms))
+    alg_bytes = 4.0 * N_ROWS * N_COLS + 32.0 * (N_ROWS + N_COLS)
+    peak, peak_src = peaks()
+    achieved = alg_bytes / (k_ms * 1e-3) / 1e9
+    pairs_s = N_ROWS * N_COLS / (k_ms * 1e-3)
+
+    # end to end through the public API with HOST buffers (pinned in, pinned out)
+    e2e_steps = max(3, min(args.steps, 10))
+    rg.rbbox_overlaps(a_host, b_host)
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        res = rg.rbbox_overlaps(a_host, b_host)
+    torch.cuda.synchronize()
+    e2e_t = torch.tensor([(time.perf_counter() - t0) / e2e_steps], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(e2e_t, op=dist.ReduceOp.MAX)
+    e2e_val = world * N_ROWS * N_COLS / float(e2e_t.item()) / 1e9
+    assert res.shape == (N_ROWS, N_COLS) and not res.is_cuda
+
+    line = {
+        'metric': 'rotated_iou_gpairs_per_s', 'value': value, 'unit': 'Gpairs/s', 'n_gpus': world,
+        'steps': args.steps, 'warmup': max(args.warmup, 3), 'ms_per_step': ms_per_step,
+        'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32',
+        'data': 'synthetic',
+        'config': {'workload': 'C3 rbbox_overlaps: one 8192x8192 block of le90 boxes per GPU '
+                               '(global matrix (8192*G) x 8192 row-sharded, columns replicated), '
+                               'extent 4096, w,h clamp 1e-3 fused',
+                   'rows_per_gpu': N_ROWS, 'cols': N_COLS,
+                   'l2': 'output 268 MB/step exceeds the 126 MB L2; a 512 MB memset flushes L2 '
+                         'between steps, outside the CUDA events',
+                   'timing': 'sum of per-step CUDA-event times on the launching stream, max over ranks'},
+        'gpu_launches': 3 * args.steps,
+        'e2e': {'value': e2e_val, 'unit': 'Gpairs/s',
+                'h2d_bytes_per_step': int(a_host.numel() * 4 + b_host.numel() * 4),
+                'd2h_bytes_per_step': int(N_ROWS * N_COLS * 4), 'steps': e2e_steps,
+                'api': 'orientedobjectdetection_b200.rbbox_overlaps(pinned CPU tensors) -> pinned CPU tensor'},
+        'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
+                     'frac': achieved / peak, 'traffic': None, 'kernel': 'iou_tile_kernel<0,true>',
+                     'kernel_ms': k_ms, 'peak_source': peak_src,
+                     'algorithmic_bytes_per_launch': alg_bytes,
+                     'fp32_view': {'flop_per_pair': FLOP_PER_PAIR,
+                                   'achieved_tflops': pairs_s * FLOP_PER_PAIR / 1e12,
+                                   'peak_tflops_theoretical': FP32_PEAK_TFLOPS,
+                                   'frac': pairs_s * FLOP_PER_PAIR / 1e12 / FP32_PEAK_TFLOPS}},
+        'clocks': clocks,
+    }
+    if rank == 0 and world == 1 and not args.no_secondary:
+        line['secondary'] = secondary_nms(torch, rg, synth)
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        ac, bc = a.copy(), b.copy()
+        ac[:, 2:4] = np.maximum(ac[:, 2:4], 1e-3)
+        bc[:, 2:4] = np.maximum(bc[:, 2:4], 1e-3)
+        from oracle import ref
+        threads = min(ref.max_threads(), len(os.sched_getaffinity(0)))
+        v1, t1 = cpu_iou_sample(ac, bc, 1024, 1)
+        rows_all = min(N_ROWS, max(1024, int(1024 * threads * 0.6)))
+        vN, tN = cpu_iou_sample(ac, bc, rows_all, threads)
+        line['cpu_baseline'] = {
+            'value': vN, 'unit': 'Gpairs/s', 'cores': threads, 'kind': 'port',
+            'sample': '%d-row slice x 8192 columns of the same C3 block, %.1f s' % (rows_all, tN),
+            'single_thread': {'value': v1, 'cores': 1,
+                              'sample': '1024-row slice x 8192 columns, %.1f s' % t1}}
+    if rank == 0:
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse()
+    rank = int(os.environ.get('RANK', 0))
+    world = int(os.environ.get('WORLD_SIZE', 1))
+    local_rank = int(os.environ.get('LOCAL_RANK', 0))
+    if args.impl == 'reference':
+        run_reference(args, rank)
+    else:
+        run_rotgeo(args, rank, world, local_rank)
+
+
+if __name__ == '__main__':
+    main()

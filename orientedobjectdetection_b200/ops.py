@@ -71,8 +71,15 @@ def _overlaps(bboxes1, bboxes2, mode, aligned, min_wh):
                                              cols, b2.stride(0), _MODE[mode], float(min_wh),
                                              out.data_ptr(), cols, ws.data_ptr(), nbytes,
                                              _stream(dev)), 'rotgeo_iou_pairwise')
-    if out.dtype != bboxes1.dtype or out.device != bboxes1.device:
-        out = out.to(device=bboxes1.device, dtype=bboxes1.dtype)
+    if not bboxes1.is_cuda:
+        # CPU caller (eval_map.py:60-62, transforms.py:369-371): result goes back
+        # through a pinned buffer (torch's caching host allocator reuses it)
+        host = torch.empty(out_shape, dtype=torch.float32, pin_memory=True)
+        host.copy_(out, non_blocking=True)
+        torch.cuda.current_stream(dev).synchronize()
+        out = host
+    if out.dtype != bboxes1.dtype:
+        out = out.to(dtype=bboxes1.dtype)
     return out
 
 
