@@ -42,10 +42,12 @@ int rotgeo_version(void);
 const char *rotgeo_last_error(void);
 
 /* ---- packed SoA box layout ------------------------------------------------
- * The kernels read boxes from two float4 planes (plane0 = cx, cy, r, area;
- * plane1 = cos, sin, w/2, h/2), padded to a multiple of 128 boxes.
- * rotgeo_packed_bytes(n) is the size of one packed set; the buffer must be
- * 16-byte aligned. */
+ * The kernels read boxes from two float4 planes (plane0 = cx, cy, xbins, ybins;
+ * plane1 = cos, sin, w/2, h/2), padded to a multiple of 128 boxes.  xbins /
+ * ybins are 32-bit occupancy masks of the box's circumscribed circle over a
+ * modular grid of 32 bins per axis (the first, two-instruction level of the
+ * pair cull).  rotgeo_packed_bytes(n) is the size of one packed set; the
+ * buffer must be 16-byte aligned. */
 size_t rotgeo_packed_bytes(int64_t n);
 
 /* AoS rows -> packed SoA.  `gather` (nullable, int64[n]) selects rows:
@@ -54,9 +56,15 @@ size_t rotgeo_packed_bytes(int64_t n);
  * mmrotate/core/bbox/iou_calculators/rotate_iou2d_calculator.py:84-87);
  * pass 0 for no clamp.  `offsets` (nullable, float[n], indexed like the
  * SOURCE rows) is added to cx and cy before packing — the class/level offset
- * trick of mmrotate/core/post_processing/bbox_nms_rotated.py:73-77. */
+ * trick of mmrotate/core/post_processing/bbox_nms_rotated.py:73-77.
+ * `cull_cell` is the bin width of the cull masks: two packed sets that are
+ * compared with each other MUST be packed with the same positive value
+ * (a good one is the extent of the box centres / 30); <= 0 derives it from this
+ * set alone (fine for a set only ever compared with itself).  The value
+ * affects speed only, never results. */
 int rotgeo_pack_boxes(const float *boxes, int64_t n, int stride, const int64_t *gather,
-                      const float *offsets, float min_wh, void *packed, void *stream);
+                      const float *offsets, float min_wh, float cull_cell, void *packed,
+                      void *stream);
 
 /* ---- rotated IoU -----------------------------------------------------------
  * Replaces ext_module.box_iou_rotated (mmcv.ops.box_iou_rotated), bound by the
@@ -72,7 +80,8 @@ int rotgeo_iou_pairwise(const float *boxes1, int64_t n1, int stride1, const floa
                         int64_t ld_out, void *workspace, size_t workspace_bytes, void *stream);
 
 /* Same on already-packed sets (no workspace; lets a caller keep anchors or
- * ground truth packed across calls). */
+ * ground truth packed across calls).  Both sets must have been packed with the
+ * same positive `cull_cell`. */
 int rotgeo_iou_pairwise_packed(const void *packed1, int64_t n1, const void *packed2, int64_t n2,
                                int mode, float *out, int64_t ld_out, void *stream);
 

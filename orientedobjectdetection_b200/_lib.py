@@ -39,7 +39,7 @@ def load():
     L.rotgeo_last_error.restype = ctypes.c_char_p
     L.rotgeo_packed_bytes.argtypes = [i64]
     L.rotgeo_packed_bytes.restype = sz
-    L.rotgeo_pack_boxes.argtypes = [vp, i64, i32, vp, vp, f32, vp, vp]
+    L.rotgeo_pack_boxes.argtypes = [vp, i64, i32, vp, vp, f32, f32, vp, vp]
     L.rotgeo_pack_boxes.restype = i32
     L.rotgeo_iou_workspace_bytes.argtypes = [i64, i64]
     L.rotgeo_iou_workspace_bytes.restype = sz

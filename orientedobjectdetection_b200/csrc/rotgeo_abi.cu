@@ -43,13 +43,16 @@ size_t rotgeo_packed_bytes(int64_t n) {
 }
 
 int rotgeo_pack_boxes(const float *boxes, int64_t n, int stride, const int64_t *gather,
-                      const float *offsets, float min_wh, void *packed, void *stream) {
+                      const float *offsets, float min_wh, float cull_cell, void *packed,
+                      void *stream) {
     if (n < 0 || stride < 5) return fail(ROTGEO_ERR_ARG, "pack: n=%lld stride=%d", (long long)n, stride);
     if (n == 0) return ROTGEO_OK;
     if (!boxes || !packed) return fail(ROTGEO_ERR_ARG, "pack: null pointer");
     if (!aligned16(packed)) return fail(ROTGEO_ERR_ARG, "pack: packed buffer must be 16-byte aligned");
-    if (rotgeo::launch_pack(boxes, n, stride, gather, offsets, min_wh, packed,
-                            rotgeo::padded_count(n), (cudaStream_t)stream))
+    const rotgeo::PackSet s1 = rotgeo::make_pack_set(boxes, n, stride, gather, offsets, packed,
+                                                     rotgeo::padded_count(n));
+    const rotgeo::PackSet none = rotgeo::make_pack_set(nullptr, 0, 5, nullptr, nullptr, nullptr, 0);
+    if (rotgeo::launch_pack(s1, none, min_wh, cull_cell, (cudaStream_t)stream))
         return cuda_fail("pack launch");
     return ROTGEO_OK;
 }
@@ -88,10 +91,14 @@ int rotgeo_iou_pairwise(const float *boxes1, int64_t n1, int stride1, const floa
     char *ws = reinterpret_cast<char *>(workspace);
     void *pk1 = ws;
     void *pk2 = ws + align_up(rotgeo_packed_bytes(n1), 256);
-    int rc = rotgeo_pack_boxes(boxes1, n1, stride1, nullptr, nullptr, min_wh, pk1, stream);
-    if (rc) return rc;
-    rc = rotgeo_pack_boxes(boxes2, n2, stride2, nullptr, nullptr, min_wh, pk2, stream);
-    if (rc) return rc;
+    if (mode != 0 && mode != 1) return fail(ROTGEO_ERR_ARG, "iou: mode=%d", mode);
+    if (!out || ld_out < n2) return fail(ROTGEO_ERR_ARG, "iou: out=%p ld_out=%lld", (void *)out, (long long)ld_out);
+    // both sets in ONE launch, so they share the automatically chosen bin width
+    const rotgeo::PackSet s1 = rotgeo::make_pack_set(boxes1, n1, stride1, nullptr, nullptr, pk1,
+                                                     rotgeo::padded_count(n1));
+    const rotgeo::PackSet s2 = rotgeo::make_pack_set(boxes2, n2, stride2, nullptr, nullptr, pk2,
+                                                     rotgeo::padded_count(n2));
+    if (rotgeo::launch_pack(s1, s2, min_wh, 0.f, (cudaStream_t)stream)) return cuda_fail("pack launch");
     return rotgeo_iou_pairwise_packed(pk1, n1, pk2, n2, mode, out, ld_out, stream);
 }
 
@@ -162,8 +169,11 @@ int rotgeo_nms(const float *boxes, int64_t n, int stride, const float *offsets,
                         cudaMemcpyHostToDevice, st) != cudaSuccess)
         return cuda_fail("nms segment upload");
     const int64_t *sorder = segmented ? seg_order : order;
-    if (rotgeo::launch_pack(boxes, n, stride, sorder, offsets, 0.f, packed, plan.n_pad, st))
-        return cuda_fail("nms pack launch");
+    {
+        const rotgeo::PackSet s1 = rotgeo::make_pack_set(boxes, n, stride, sorder, offsets, packed, plan.n_pad);
+        const rotgeo::PackSet none = rotgeo::make_pack_set(nullptr, 0, 5, nullptr, nullptr, nullptr, 0);
+        if (rotgeo::launch_pack(s1, none, 0.f, 0.f, st)) return cuda_fail("nms pack launch");
+    }
     const int rc = rotgeo::launch_nms(plan, packed, segs_dev, max_words, order, sorder,
                                       iou_threshold, mask, flags, keep_out, num_keep_out, st);
     if (rc == -1) return fail(ROTGEO_ERR_ARG, "nms: too many tiles");

@@ -21,8 +21,10 @@ __host__ __device__ inline int64_t padded_count(int64_t n) {
     return (n + kPackPad - 1) / kPackPad * kPackPad;
 }
 
-// plane0: (cx, cy, r, area)   r = circumscribed-circle radius, slightly inflated
-// plane1: (cos, sin, a, b)    a = w/2, b = h/2
+// plane0: (cx, cy, xbins, ybins)  xbins / ybins: 32-bit occupancy masks (bit patterns
+//                                 stored in float slots) of the box's circumscribed
+//                                 circle over a modular grid of 32 bins per axis
+// plane1: (cos, sin, a, b)        a = w/2, b = h/2;  area = 4ab, radius = |(a, b)|
 struct PackedView {
     const float4 *p0;
     const float4 *p1;
@@ -37,7 +39,28 @@ __host__ __device__ inline PackedView packed_view(const void *base, int64_t n_pa
     return v;
 }
 
-// Conservative reject: true when the circumscribed circles are disjoint, so the
+// ---- cull level 1: modular bin masks ------------------------------------------
+// The interval [lo, hi] covers the bins floor(lo/cell) .. floor(hi/cell); bin k is
+// bit (k mod 32).  Two intervals that share a point share a bin, hence a bit —
+// whatever the bin width and wherever the boxes are (class-offset coordinates
+// included), so the test `(xa & xb) && (ya & yb)` never rejects a touching pair.
+// Intervals spanning >= 32 bins, or so far out that fp32 no longer resolves bins,
+// get all ones.
+__device__ __forceinline__ uint32_t bin_mask(float lo, float hi, float inv_cell) {
+    const float fl = floorf(lo * inv_cell), fh = floorf(hi * inv_cell);
+    const float span = fh - fl;
+    if (!(span < 31.f) || !(fabsf(fl) < 8388608.f)) return 0xffffffffu;  // also NaN / inf
+    const uint32_t m = (2u << (int)span) - 1u;  // span+1 low bits
+    return __funnelshift_l(m, m, (int)fl & 31);
+}
+
+// circumscribed radius from the half extents, inflated so that every later use
+// (bin masks, circle test) stays conservative under fp32 rounding
+__device__ __forceinline__ float circum_radius(float a, float b) {
+    return sqrtf(fmaf(a, a, b * b)) * 1.000001f + 1e-30f;
+}
+
+// cull level 2: true when the circumscribed circles are disjoint, so the
 // rectangles cannot touch and the reference value is exactly 0.
 __device__ __forceinline__ bool circles_disjoint(float ax, float ay, float ar, float bx, float by,
                                                  float br) {
@@ -66,7 +89,7 @@ __device__ __forceinline__ float fmin3(float a, float b, float c) { return fminf
 // 2*area = sum over the 8 edges of (clipped length) * cross(edge dir, point-origin);
 // the origin is put at the centre of the SMALLER box to limit cancellation.
 __device__ __forceinline__ float rect_intersection_area(float4 A0, float4 A1, float4 B0,
-                                                        float4 B1) {
+                                                        float4 B1, float areaA, float areaB) {
     const float aA = A1.z, bA = A1.w, aB = B1.z, bB = B1.w;
     const float dx = A0.x - B0.x, dy = A0.y - B0.y;
     float c = fmaf(A1.x, B1.x, A1.y * B1.y);
@@ -79,7 +102,7 @@ __device__ __forceinline__ float rect_intersection_area(float4 A0, float4 A1, fl
     s = fmaxf(s, 1e-12f);
     const float rc = __frcp_rn(c), rs = __frcp_rn(s);
     const float n2 = fmaf(c, c, s * s);
-    const bool a_small = A0.w < B0.w;
+    const bool a_small = areaA < areaB;
     // origin O = lam*(X,Y): lam = 1 -> A's centre, 0 -> B's centre
     const float kE = a_small ? 0.f : fmaf(c, Y, -s * X);
     const float kF = a_small ? 0.f : fmaf(c, X, s * Y);
@@ -135,17 +158,27 @@ __device__ __forceinline__ float rect_intersection_area(float4 A0, float4 A1, fl
         }
     }
     float inter = fmaxf(0.5f * acc, 0.f);
-    return fminf(inter, fminf(A0.w, B0.w));
+    return fminf(inter, fminf(areaA, areaB));
 }
 
 // IoU (mode 0) or IoF (mode 1, divide by A's area).  Areas below 1e-14 give 0
-// like the reference's native code (SURVEY.md §8(c) Spec A step 2).
+// like the reference's native code (SURVEY.md §8(c) Spec A step 2).  4ab is
+// bit-identical to the reference's w*h (scaling by powers of two is exact).
 template <int MODE>
 __device__ __forceinline__ float rect_overlap(float4 A0, float4 A1, float4 B0, float4 B1) {
-    const float inter = rect_intersection_area(A0, A1, B0, B1);
-    const float base = MODE == 0 ? (A0.w + B0.w - inter) : A0.w;
+    const float areaA = 4.f * (A1.z * A1.w), areaB = 4.f * (B1.z * B1.w);
+    const float inter = rect_intersection_area(A0, A1, B0, B1, areaA, areaB);
+    const float base = MODE == 0 ? (areaA + areaB - inter) : areaA;
     const float v = __fdividef(inter, base);
-    return (A0.w < 1e-14f || B0.w < 1e-14f) ? 0.f : v;
+    return (areaA < 1e-14f || areaB < 1e-14f) ? 0.f : v;
+}
+
+// level-2 cull + exact value of one queued pair
+template <int MODE>
+__device__ __forceinline__ float pair_value(float4 A0, float4 A1, float4 B0, float4 B1) {
+    const float ra = circum_radius(A1.z, A1.w), rb = circum_radius(B1.z, B1.w);
+    if (circles_disjoint(A0.x, A0.y, ra, B0.x, B0.y, rb)) return 0.f;
+    return rect_overlap<MODE>(A0, A1, B0, B1);
 }
 
 // ---- TMA (bulk async copy) + mbarrier helpers, raw PTX -----------------------

@@ -5,8 +5,22 @@
 
 namespace rotgeo {
 
-int launch_pack(const float *boxes, int64_t n, int stride, const int64_t *gather,
-                const float *offsets, float min_wh, void *packed, int64_t n_pad,
+// One box set to pack: AoS source rows (+ optional gather / centre offsets) and
+// the two destination planes.  n_pad == 0 marks an absent second set.
+struct PackSet {
+    const float *boxes;
+    int64_t n;
+    int stride;
+    const int64_t *gather;   // nullable: packed[i] = boxes[gather[i]]
+    const float *offsets;    // nullable: added to cx, cy, indexed like the source rows
+    float4 *p0, *p1;
+    int64_t n_pad;
+};
+PackSet make_pack_set(const float *boxes, int64_t n, int stride, const int64_t *gather,
+                      const float *offsets, void *packed, int64_t n_pad);
+
+// cell > 0: bin width of the cull masks; cell <= 0: derived from the set(s) in the launch
+int launch_pack(const PackSet &s1, const PackSet &s2, float min_wh, float cell,
                 cudaStream_t stream);
 
 int launch_iou_pairwise(const void *packed1, int64_t n1, const void *packed2, int64_t n2, int mode,

@@ -2,18 +2,18 @@
 //
 // One CTA (256 threads) owns a 64-row x 128-column tile of the output:
 //   0. the tile's row and column boxes (two float4 planes each, 6 KB) are staged
-//      in shared memory by four TMA bulk copies signalled on one mbarrier;
-//   1. cull pass: lane l of warp w tests rows {w, w+8, ...} against its four
-//      columns 4l..4l+3 with the circumscribed-circle test (7 FP32 ops a pair),
-//      stores the row's zeros as one coalesced float4, and remembers survivors
-//      in a 32-bit mask (8 rows x 4 columns);
+//      in shared memory by four TMA bulk copies signalled on one mbarrier; while
+//      they are in flight the CTA streams the tile's zeros to HBM (coalesced
+//      float4 stores, 512 B per warp instruction) — most of the matrix is zero;
+//   1. cull level 1: lane l of warp w tests rows {w, w+8, ...} against its four
+//      columns 4l..4l+3 with the modular bin masks (two ANDs a pair) and
+//      remembers survivors in a 32-bit mask (8 rows x 4 columns);
 //   2. survivors are compacted into a shared-memory queue (one warp scan and one
 //      shared atomic per warp);
-//   3. exact pass: the whole CTA walks the queue with every lane busy on a pair
-//      that really needs the clipper, and scatters the values over the zeros.
-// Disjoint pairs therefore cost a handful of instructions and 4 B of HBM
-// write, overlapping pairs cost the ~170-instruction clipper at full lane
-// occupancy regardless of how sparse they are in the matrix.
+//   3. the whole CTA walks the queue: circumscribed-circle test (cull level 2),
+//      then the exact clipper, and scatters the non-zero values over the zeros.
+// Disjoint pairs therefore cost ~4 instructions and 4 B of HBM write; the
+// kernel is bound by the HBM write stream (DESIGN.md "Kernels").
 #include "rotgeo_device.cuh"
 #include "rotgeo_internal.h"
 
@@ -59,39 +59,52 @@ iou_tile_kernel(const float4 *__restrict__ a0, const float4 *__restrict__ a1, in
         tma_load_1d(sm.col0, b0 + col_base, kTileCols * sizeof(float4), &sm.bar);
         tma_load_1d(sm.col1, b1 + col_base, kTileCols * sizeof(float4), &sm.bar);
     }
+
+    // ---- 0. the tile's zeros, while the TMA copies are in flight ---------------
+    {
+        const int64_t gcol = col_base + 4 * lane;
+        const int cols_here = (int)min((int64_t)4, n2 - gcol);  // <= 0: lane is past the edge
+        const int rows_here = (int)min((int64_t)kTileRows, n1 - row_base);
+        float *dst = out + (row_base + warp) * ld_out + gcol;
+        const int64_t step = (int64_t)kWarps * ld_out;
+        if (VEC) {
+            if (rows_here == kTileRows && cols_here == 4) {   // interior tile: 8 plain stores
+#pragma unroll
+                for (int it = 0; it < kRowsPerWarp; ++it) {
+                    *reinterpret_cast<float4 *>(dst) = make_float4(0.f, 0.f, 0.f, 0.f);
+                    dst += step;
+                }
+            } else if (cols_here > 0) {
+                for (int r = warp; r < rows_here; r += kWarps) {
+                    *reinterpret_cast<float4 *>(dst) = make_float4(0.f, 0.f, 0.f, 0.f);
+                    dst += step;
+                }
+            }
+        } else {
+            for (int it = 0; it < kRowsPerWarp; ++it)
+                if (warp + kWarps * it < rows_here)
+                    for (int k = 0; k < cols_here; ++k) dst[it * step + k] = 0.f;
+        }
+    }
     mbar_wait(&sm.bar, 0);
 
-    // ---- 1. cull pass -------------------------------------------------------
-    float cxs[4], cys[4], crs[4];
+    // ---- 1. cull level 1: bin masks (padding rows / columns carry empty masks) --
+    uint32_t cxm[4], cym[4];
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
         const float4 c = sm.col0[4 * lane + k];
-        cxs[k] = c.x; cys[k] = c.y; crs[k] = c.z;
+        cxm[k] = __float_as_uint(c.z);
+        cym[k] = __float_as_uint(c.w);
     }
-    const int64_t gcol = col_base + 4 * lane;
-    const int cols_here = (int)min((int64_t)4, n2 - gcol);  // <= 0: lane is past the edge
     uint32_t hits = 0;
 #pragma unroll
     for (int it = 0; it < kRowsPerWarp; ++it) {
-        const int r = warp + kWarps * it;
-        const int64_t grow = row_base + r;
-        const float4 R = sm.row0[r];
-        const bool row_ok = grow < n1;
+        const float2 rm = *reinterpret_cast<const float2 *>(&sm.row0[warp + kWarps * it].z);
+        const uint32_t rxm = __float_as_uint(rm.x), rym = __float_as_uint(rm.y);
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
-            const bool hit = row_ok && (k < cols_here) &&
-                             !circles_disjoint(R.x, R.y, R.z, cxs[k], cys[k], crs[k]);
+            const bool hit = ((rxm & cxm[k]) != 0u) & ((rym & cym[k]) != 0u);
             hits |= (hit ? 1u : 0u) << (4 * it + k);
-        }
-        if (row_ok) {
-            float *dst = out + grow * ld_out + gcol;
-            if (VEC) {
-                if (cols_here > 0) *reinterpret_cast<float4 *>(dst) = make_float4(0.f, 0.f, 0.f, 0.f);
-            } else {
-#pragma unroll
-                for (int k = 0; k < 4; ++k)
-                    if (k < cols_here) dst[k] = 0.f;
-            }
         }
     }
 
@@ -117,15 +130,15 @@ iou_tile_kernel(const float4 *__restrict__ a0, const float4 *__restrict__ a1, in
             sm.queue[pos++] = (uint16_t)((r << 7) | c);
         }
     }
-    __syncthreads();
+    __syncthreads();   // also orders the zero stores before the value stores below
 
-    // ---- 3. exact pass over the queue ----------------------------------------
+    // ---- 3. cull level 2 + exact pass over the queue ---------------------------
     const int total = sm.qcount;
     for (int e = tid; e < total; e += kThreads) {
         const int q = sm.queue[e];
         const int r = q >> 7, c = q & 127;
-        const float v = rect_overlap<MODE>(sm.row0[r], sm.row1[r], sm.col0[c], sm.col1[c]);
-        out[(row_base + r) * ld_out + (col_base + c)] = v;
+        const float v = pair_value<MODE>(sm.row0[r], sm.row1[r], sm.col0[c], sm.col1[c]);
+        if (v != 0.f) out[(row_base + r) * ld_out + (col_base + c)] = v;
     }
 }
 
@@ -160,7 +173,7 @@ __device__ __forceinline__ void load_box(const float *b, float min_wh, float4 &p
     }
     double sd, cd;
     sincos((double)b[4], &sd, &cd);
-    p0 = make_float4(b[0], b[1], 0.f, w * h);
+    p0 = make_float4(b[0], b[1], 0.f, 0.f);
     p1 = make_float4((float)cd, (float)sd, 0.5f * w, 0.5f * h);
 }
 

@@ -6,10 +6,11 @@
 //   nms_mask_kernel  one CTA per 128x128 tile of the UPPER TRIANGLE of each
 //                    segment's pair matrix (block-diagonal: pairs from different
 //                    segments are never touched).  Boxes are staged by TMA bulk
-//                    copies; a cull pass (circle test) compacts surviving pairs
-//                    into a shared queue, the exact pass clips them with every
-//                    lane busy and ORs `IoU >= thr` bits into a shared 128x2-word
-//                    tile that is written out once.
+//                    copies; cull level 1 (modular bin masks, two ANDs a pair)
+//                    compacts surviving pairs into a shared queue, the queue pass
+//                    applies the circle test and the exact clipper and ORs
+//                    `IoU >= thr` bits into a shared 128x2-word tile that is
+//                    written out once.
 //   nms_scan_kernel  one CTA per segment walks its 64-box chunks in score order.
 //                    Inside a chunk the kept set is found by peeling (warp
 //                    redux.or rounds, usually 1-3) instead of a 64-step serial
@@ -91,13 +92,18 @@ nms_mask_kernel(const float4 *__restrict__ p0, const float4 *__restrict__ p1,
     }
     mbar_wait(&sm.bar, 0);
 
-    float cxs[4], cys[4], crs[4];
+    // cull level 1 operands: bin masks of this lane's four columns; positions past
+    // the segment's end belong to the next segment (or are padding) -> empty masks
+    uint32_t cxm[4], cym[4];
+    const int cpos = col_base + 4 * lane;
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
         const float4 c = sm.col0[4 * lane + k];
-        cxs[k] = c.x; cys[k] = c.y; crs[k] = c.z;
+        const bool live = cpos + k < L;
+        cxm[k] = live ? __float_as_uint(c.z) : 0u;
+        cym[k] = live ? __float_as_uint(c.w) : 0u;
     }
-    const int cpos = col_base + 4 * lane;
+    const bool diagonal = I == J;   // only there can a column precede its row
 
     for (int half = 0; half < 2; ++half) {
         const int hrow = half * kHalf;
@@ -110,12 +116,13 @@ nms_mask_kernel(const float4 *__restrict__ p0, const float4 *__restrict__ p1,
         for (int it = 0; it < kHalf / kWarps; ++it) {
             const int r = hrow + warp + kWarps * it;
             const int rpos = row_base + r;
-            const float4 R = sm.row0[r];
+            const float2 rm = *reinterpret_cast<const float2 *>(&sm.row0[r].z);
+            const uint32_t rxm = rpos < L ? __float_as_uint(rm.x) : 0u;
+            const uint32_t rym = __float_as_uint(rm.y);
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
-                const int cp = cpos + k;
-                const bool hit = (cp > rpos) && (cp < L) && (rpos < L) &&
-                                 !circles_disjoint(R.x, R.y, R.z, cxs[k], cys[k], crs[k]);
+                bool hit = ((rxm & cxm[k]) != 0u) & ((rym & cym[k]) != 0u);
+                if (diagonal) hit = hit && (cpos + k > rpos);
                 hits |= (hit ? 1u : 0u) << (4 * it + k);
             }
         }
@@ -145,7 +152,7 @@ nms_mask_kernel(const float4 *__restrict__ p0, const float4 *__restrict__ p1,
         for (int e = tid; e < total; e += kThreads) {
             const int q = sm.queue[e];
             const int r = hrow + (q >> 7), c = q & 127;
-            const float v = rect_overlap<0>(sm.row0[r], sm.row1[r], sm.col0[c], sm.col1[c]);
+            const float v = pair_value<0>(sm.row0[r], sm.row1[r], sm.col0[c], sm.col1[c]);
             if (v >= thr) atomicOr(&sm.bits[r][c >> 6], 1ull << (c & 63));
         }
         __syncthreads();

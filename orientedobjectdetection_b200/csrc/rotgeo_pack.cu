@@ -1,32 +1,95 @@
 // AoS (cx, cy, w, h, theta) rows -> packed SoA float4 planes (see rotgeo_device.cuh).
-// One thread per box; the optional gather / centre offset / size clamp are the
-// pieces of the reference's python front-end that would otherwise be separate
-// torch kernels (clone + clamp_ at rotate_iou2d_calculator.py:84-87, the offset
-// add at bbox_nms_rotated.py:73-77, index_select by score order in mmcv's
-// nms_rotated wrapper).
+// One thread per box, one launch for up to two box sets.  The optional gather /
+// centre offset / size clamp are the pieces of the reference's python front-end
+// that would otherwise be separate torch kernels (clone + clamp_ at
+// rotate_iou2d_calculator.py:84-87, the offset add at bbox_nms_rotated.py:73-77,
+// index_select by score order in mmcv's nms_rotated wrapper).
+//
+// The bin width of the cull masks is derived in a prologue every CTA repeats on
+// the same strided sample of <= 256 boxes (so all CTAs agree without a second
+// launch): 32 bins span the sampled extent of the RAW centres — before the class
+// offsets, because a class segment only ever meets itself.  The choice affects
+// speed only; bin_mask() is conservative for any width.
 #include "rotgeo_device.cuh"
 #include "rotgeo_internal.h"
 
 namespace rotgeo {
 
-__global__ void __launch_bounds__(256)
-pack_kernel(const float *__restrict__ boxes, int64_t n, int stride,
-            const int64_t *__restrict__ gather, const float *__restrict__ offsets, float min_wh,
-            float4 *__restrict__ p0, float4 *__restrict__ p1, int64_t n_pad) {
+constexpr int kPackThreads = 256;
+
+__device__ __forceinline__ float warp_min(float v) {
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) v = fminf(v, __shfl_xor_sync(0xffffffffu, v, d));
+    return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, d));
+    return v;
+}
+
+__device__ __forceinline__ const float *src_row(const PackSet &s, int64_t i) {
+    return s.boxes + (s.gather ? s.gather[i] : i) * s.stride;
+}
+
+// 1 / (bin width): identical in every CTA of the launch
+__device__ float sample_inv_cell(const PackSet &s1, const PackSet &s2) {
+    __shared__ float red[4][kPackThreads / 32];
+    const int tid = threadIdx.x;
+    const bool two = s2.n > 0;
+    // first half of the block samples set 1, second half set 2 (all of it set 1 if alone)
+    const PackSet s = (two && tid >= kPackThreads / 2) ? s2 : s1;
+    const int slots = two ? kPackThreads / 2 : kPackThreads;
+    const int t = two ? (tid & (kPackThreads / 2 - 1)) : tid;
+    float lo_x = INFINITY, hi_x = -INFINITY, lo_y = INFINITY, hi_y = -INFINITY;
+    if (s.n > 0) {
+        const int64_t i = (s.n >= slots) ? (int64_t)t * (s.n / slots) : (t % s.n);
+        const float *b = src_row(s, i);
+        const float cx = b[0], cy = b[1];
+        if (fabsf(cx) < 1e30f && fabsf(cy) < 1e30f) {
+            lo_x = hi_x = cx;
+            lo_y = hi_y = cy;
+        }
+    }
+    lo_x = warp_min(lo_x); hi_x = warp_max(hi_x);
+    lo_y = warp_min(lo_y); hi_y = warp_max(hi_y);
+    if ((tid & 31) == 0) {
+        red[0][tid >> 5] = lo_x; red[1][tid >> 5] = hi_x;
+        red[2][tid >> 5] = lo_y; red[3][tid >> 5] = hi_y;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int w = 0; w < kPackThreads / 32; ++w) {
+        lo_x = fminf(lo_x, red[0][w]); hi_x = fmaxf(hi_x, red[1][w]);
+        lo_y = fminf(lo_y, red[2][w]); hi_y = fmaxf(hi_y, red[3][w]);
+    }
+    const float extent = fmaxf(hi_x - lo_x, hi_y - lo_y);
+    // 30 bins across the sampled extent (the sample misses a little at the edges)
+    float cell = extent * (1.f / 30.f);
+    if (!(cell > 1e-30f) || !(cell < 1e30f)) cell = 1.f;
+    return 1.f / cell;
+}
+
+__global__ void __launch_bounds__(kPackThreads)
+pack_kernel(PackSet s1, PackSet s2, float min_wh, float cell) {
+    const float inv_cell = cell > 0.f ? 1.f / cell : sample_inv_cell(s1, s2);
     int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-    if (i >= n_pad) return;
-    if (i >= n) {
-        // padding: a zero-area box very far away; every pair with it is rejected
-        p0[i] = make_float4(1e30f, 1e30f, 0.f, 0.f);
-        p1[i] = make_float4(1.f, 0.f, 0.f, 0.f);
+    const bool second = i >= s1.n_pad;
+    const PackSet s = second ? s2 : s1;
+    if (second) i -= s1.n_pad;
+    if (i >= s.n_pad) return;
+    if (i >= s.n) {
+        // padding: empty bin masks, so no pair with it survives the cull
+        s.p0[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        s.p1[i] = make_float4(1.f, 0.f, 0.f, 0.f);
         return;
     }
-    const int64_t src = gather ? gather[i] : i;
-    const float *b = boxes + src * stride;
+    const int64_t src = s.gather ? s.gather[i] : i;
+    const float *b = s.boxes + src * s.stride;
     float cx = b[0], cy = b[1], w = b[2], h = b[3];
     const float th = b[4];
-    if (offsets) {
-        const float o = offsets[src];
+    if (s.offsets) {
+        const float o = s.offsets[src];
         cx += o;
         cy += o;
     }
@@ -38,23 +101,36 @@ pack_kernel(const float *__restrict__ boxes, int64_t n, int stride,
     double sd, cd;
     sincos((double)th, &sd, &cd);
     const float a = 0.5f * w, hb = 0.5f * h;
-    // circumscribed radius, inflated so the reject test stays conservative
-    const float r = sqrtf(fmaf(a, a, hb * hb)) * 1.000001f + 1e-30f;
-    p0[i] = make_float4(cx, cy, r, w * h);
-    p1[i] = make_float4((float)cd, (float)sd, a, hb);
+    // radius for the masks: the circle-test radius plus the rounding of cx -/+ r
+    const float r = circum_radius(a, hb);
+    const float rx = r + fabsf(cx) * 2.4e-7f, ry = r + fabsf(cy) * 2.4e-7f;
+    const uint32_t xm = bin_mask(cx - rx, cx + rx, inv_cell);
+    const uint32_t ym = bin_mask(cy - ry, cy + ry, inv_cell);
+    s.p0[i] = make_float4(cx, cy, __uint_as_float(xm), __uint_as_float(ym));
+    s.p1[i] = make_float4((float)cd, (float)sd, a, hb);
 }
 
-int launch_pack(const float *boxes, int64_t n, int stride, const int64_t *gather,
-                const float *offsets, float min_wh, void *packed, int64_t n_pad,
+int launch_pack(const PackSet &s1, const PackSet &s2, float min_wh, float cell,
                 cudaStream_t stream) {
-    if (n_pad == 0) return 0;
-    float4 *p0 = reinterpret_cast<float4 *>(packed);
-    float4 *p1 = p0 + n_pad;
-    const int threads = 256;
-    const int64_t blocks = (n_pad + threads - 1) / threads;
-    pack_kernel<<<(unsigned)blocks, threads, 0, stream>>>(boxes, n, stride, gather, offsets, min_wh,
-                                                          p0, p1, n_pad);
+    const int64_t total = s1.n_pad + s2.n_pad;
+    if (total == 0) return 0;
+    const int64_t blocks = (total + kPackThreads - 1) / kPackThreads;
+    pack_kernel<<<(unsigned)blocks, kPackThreads, 0, stream>>>(s1, s2, min_wh, cell);
     return cudaGetLastError() == cudaSuccess ? 0 : -3;
+}
+
+PackSet make_pack_set(const float *boxes, int64_t n, int stride, const int64_t *gather,
+                      const float *offsets, void *packed, int64_t n_pad) {
+    PackSet s;
+    s.boxes = boxes;
+    s.n = n;
+    s.stride = stride;
+    s.gather = gather;
+    s.offsets = offsets;
+    s.p0 = reinterpret_cast<float4 *>(packed);
+    s.p1 = s.p0 ? s.p0 + n_pad : nullptr;
+    s.n_pad = n_pad;
+    return s;
 }
 
 }  // namespace rotgeo
