@@ -42,12 +42,12 @@ int rotgeo_version(void);
 const char *rotgeo_last_error(void);
 
 /* ---- packed SoA box layout ------------------------------------------------
- * The kernels read boxes from two float4 planes (plane0 = cx, cy, xbins, ybins;
- * plane1 = cos, sin, w/2, h/2), padded to a multiple of 128 boxes.  xbins /
- * ybins are 32-bit occupancy masks of the box's circumscribed circle over a
- * modular grid of 32 bins per axis (the first, two-instruction level of the
- * pair cull).  rotgeo_packed_bytes(n) is the size of one packed set; the
- * buffer must be 16-byte aligned. */
+ * The kernels read boxes from three planes, padded to a multiple of 128 boxes:
+ * float4 (cx, cy, r, area), float4 (cos, sin, w/2, h/2) and uint2 (xbins,
+ * ybins) — 32-bit occupancy masks of the box's circumscribed circle over a
+ * modular grid of 32 bins per axis, the first (two-instruction) level of the
+ * pair cull.  rotgeo_packed_bytes(n) is the size of one packed set (40 bytes
+ * a padded box); the buffer must be 16-byte aligned. */
 size_t rotgeo_packed_bytes(int64_t n);
 
 /* AoS rows -> packed SoA.  `gather` (nullable, int64[n]) selects rows:

@@ -39,7 +39,7 @@ const char *rotgeo_last_error(void) { return g_err; }
 
 size_t rotgeo_packed_bytes(int64_t n) {
     if (n < 0) return 0;
-    return (size_t)rotgeo::padded_count(n) * 2 * sizeof(float4);
+    return (size_t)rotgeo::padded_count(n) * rotgeo::kPackedBytesPerBox;
 }
 
 int rotgeo_pack_boxes(const float *boxes, int64_t n, int stride, const int64_t *gather,

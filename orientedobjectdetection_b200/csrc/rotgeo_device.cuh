@@ -21,21 +21,28 @@ __host__ __device__ inline int64_t padded_count(int64_t n) {
     return (n + kPackPad - 1) / kPackPad * kPackPad;
 }
 
-// plane0: (cx, cy, xbins, ybins)  xbins / ybins: 32-bit occupancy masks (bit patterns
-//                                 stored in float slots) of the box's circumscribed
-//                                 circle over a modular grid of 32 bins per axis
-// plane1: (cos, sin, a, b)        a = w/2, b = h/2;  area = 4ab, radius = |(a, b)|
+// A packed set of n_pad slots is three planes, back to back:
+//   plane0 float4 (cx, cy, r, area)   r = circumscribed radius (inflated), area = w*h
+//   plane1 float4 (cos, sin, a, b)    a = w/2, b = h/2
+//   planeM uint2  (xbins, ybins)      32-bit occupancy masks of the circumscribed
+//                                     circle over a modular grid of 32 bins per axis
+// The pair cull reads planeM only (8 B a box, TMA-staged); planes 0/1 are read
+// for the few pairs that survive it.
+constexpr int kPackedBytesPerBox = 2 * 16 + 8;
+
 struct PackedView {
     const float4 *p0;
     const float4 *p1;
+    const uint2 *pm;
 };
 
-// n_pad = number of float4 slots per plane (padded_count(n) for the IoU entry
-// points; the NMS workspace adds slack so tiles may start at any box)
+// n_pad = number of slots per plane (padded_count(n) for the IoU entry points; the
+// NMS workspace adds slack so tiles may start at any box)
 __host__ __device__ inline PackedView packed_view(const void *base, int64_t n_pad) {
     PackedView v;
     v.p0 = reinterpret_cast<const float4 *>(base);
     v.p1 = v.p0 + n_pad;
+    v.pm = reinterpret_cast<const uint2 *>(v.p1 + n_pad);
     return v;
 }
 
@@ -162,22 +169,20 @@ __device__ __forceinline__ float rect_intersection_area(float4 A0, float4 A1, fl
 }
 
 // IoU (mode 0) or IoF (mode 1, divide by A's area).  Areas below 1e-14 give 0
-// like the reference's native code (SURVEY.md §8(c) Spec A step 2).  4ab is
-// bit-identical to the reference's w*h (scaling by powers of two is exact).
+// like the reference's native code (SURVEY.md §8(c) Spec A step 2).
 template <int MODE>
 __device__ __forceinline__ float rect_overlap(float4 A0, float4 A1, float4 B0, float4 B1) {
-    const float areaA = 4.f * (A1.z * A1.w), areaB = 4.f * (B1.z * B1.w);
+    const float areaA = A0.w, areaB = B0.w;
     const float inter = rect_intersection_area(A0, A1, B0, B1, areaA, areaB);
     const float base = MODE == 0 ? (areaA + areaB - inter) : areaA;
     const float v = __fdividef(inter, base);
     return (areaA < 1e-14f || areaB < 1e-14f) ? 0.f : v;
 }
 
-// level-2 cull + exact value of one queued pair
+// level-2 cull + exact value of one pair that survived the bin masks
 template <int MODE>
 __device__ __forceinline__ float pair_value(float4 A0, float4 A1, float4 B0, float4 B1) {
-    const float ra = circum_radius(A1.z, A1.w), rb = circum_radius(B1.z, B1.w);
-    if (circles_disjoint(A0.x, A0.y, ra, B0.x, B0.y, rb)) return 0.f;
+    if (circles_disjoint(A0.x, A0.y, A0.z, B0.x, B0.y, B0.z)) return 0.f;
     return rect_overlap<MODE>(A0, A1, B0, B1);
 }
 
@@ -195,6 +200,9 @@ __device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)),
                  "r"(bytes)
                  : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
     asm volatile(
@@ -217,6 +225,41 @@ __device__ __forceinline__ void tma_load_1d(void *dst_smem, const void *src_gmem
         "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
         ::"r"(smem_u32(dst_smem)), "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
         : "memory");
+}
+
+// ---- cluster launch control (sm_100 work stealing) ------------------------------
+// A running CTA asks the hardware scheduler to cancel the launch of a CTA of the
+// same grid that has not started yet and takes over its blockIdx: persistent CTAs
+// with the hardware's own dynamic load balancing and no global work counter.
+// The 16-byte response lands in shared memory and completes `bar` (16 tx bytes).
+__device__ __forceinline__ void clc_try_cancel(void *resp_smem, uint64_t *bar) {
+    asm volatile(
+        "clusterlaunchcontrol.try_cancel.async.shared::cta.mbarrier::complete_tx::bytes.b128 [%0], [%1];"
+        ::"r"(smem_u32(resp_smem)), "r"(smem_u32(bar))
+        : "memory");
+}
+// true + the cancelled CTA's blockIdx.x, or false when nothing was left to cancel
+__device__ __forceinline__ bool clc_decode(const void *resp_smem, unsigned &ctaid_x) {
+    unsigned ok, x = 0;
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        ".reg .b128 r;\n"
+        "ld.shared.b128 r, [%2];\n"
+        "clusterlaunchcontrol.query_cancel.is_canceled.pred.b128 p, r;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "@p clusterlaunchcontrol.query_cancel.get_first_ctaid::x.b32.b128 %1, r;\n"
+        "}\n"
+        : "=r"(ok), "+r"(x)
+        : "r"(smem_u32(resp_smem))
+        : "memory");
+    ctaid_x = x;
+    return ok != 0;
+}
+// orders this thread's generic-proxy reads of shared memory before later
+// async-proxy writes to it (a response slot about to be reused)
+__device__ __forceinline__ void fence_proxy_async_smem() {
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 }
 
 }  // namespace rotgeo

@@ -14,6 +14,7 @@ struct PackSet {
     const int64_t *gather;   // nullable: packed[i] = boxes[gather[i]]
     const float *offsets;    // nullable: added to cx, cy, indexed like the source rows
     float4 *p0, *p1;
+    uint2 *pm;
     int64_t n_pad;
 };
 PackSet make_pack_set(const float *boxes, int64_t n, int stride, const int64_t *gather,

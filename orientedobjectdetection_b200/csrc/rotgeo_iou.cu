@@ -1,21 +1,30 @@
 // Pairwise rotated IoU / IoF matrix on packed boxes.  sm_100a.
 //
-// One CTA (256 threads) owns a 64-row x 128-column tile of the output:
-//   0. the tile's row and column boxes (two float4 planes each, 6 KB) are staged
-//      in shared memory by four TMA bulk copies signalled on one mbarrier; while
-//      they are in flight the CTA streams the tile's zeros to HBM (coalesced
-//      float4 stores, 512 B per warp instruction) — most of the matrix is zero;
-//   1. cull level 1: lane l of warp w tests rows {w, w+8, ...} against its four
-//      columns 4l..4l+3 with the modular bin masks (two ANDs a pair) and
-//      remembers survivors in a 32-bit mask (8 rows x 4 columns);
-//   2. survivors are compacted into a shared-memory queue (one warp scan and one
-//      shared atomic per warp);
-//   3. the whole CTA walks the queue: circumscribed-circle test (cull level 2),
-//      then the exact clipper, and scatters the non-zero values over the zeros.
-// Disjoint pairs therefore cost ~4 instructions and 4 B of HBM write; the
-// kernel is bound by the HBM write stream (DESIGN.md "Kernels").
+// The grid has one CTA (8 warps) per 64-row x 128-column output tile, but a CTA
+// that is running keeps going: through cluster launch control it cancels the
+// launch of the next not-yet-started CTA and takes over its tile, so the CTAs
+// are persistent (barriers initialised once, masks prefetched, warp queues kept
+// across tiles) while the hardware scheduler still balances the load.  Per tile:
+//   0. the tile's bin masks (64 row + 128 column boxes, 8 B each) arrive in a
+//      4-stage shared-memory ring filled by TMA bulk copies one tile ahead
+//      (full/empty mbarriers; no __syncthreads anywhere in the loop);
+//   1. warp w owns rows {w, w+8, ...}: lane l streams the zeros of its four
+//      columns 4l..4l+3 to HBM (float4, 512 B per warp instruction — most of the
+//      matrix is zero) and tests the same pairs with the masks (two ANDs a pair);
+//   2. surviving pairs go to the warp's private queue (one shared atomic per lane
+//      with hits); whenever >= 32 are queued the warp pops 32 and runs the circle
+//      test + exact clipper with every lane busy, reading the two boxes' geometry
+//      planes through L1/L2, and overwrites the zeros with the non-zero values.
+// A value always lands after its zero: both stores come from the same warp with
+// a __syncwarp between (the same lane when a full queue forces the inline path).
+// Disjoint pairs cost ~5 instructions and 4 B of HBM write; the kernel is bound
+// by the HBM write stream (DESIGN.md "Kernels").
 #include "rotgeo_device.cuh"
 #include "rotgeo_internal.h"
+
+#ifndef ROTGEO_ABLATE
+#define ROTGEO_ABLATE 0   // probe builds (tools/ablate_iou.py): 1 no zero stores, 2 no cull, 4 no exact pass
+#endif
 
 namespace rotgeo {
 
@@ -24,143 +33,213 @@ constexpr int kTileCols = 128;
 constexpr int kThreads = 256;
 constexpr int kWarps = kThreads / 32;
 constexpr int kRowsPerWarp = kTileRows / kWarps;  // 8
+constexpr int kStages = 4;        // mask ring
+constexpr int kRespSlots = 8;     // launch-control responses (> kStages, see the reuse argument below)
+constexpr int kQueueCap = 128;    // pairs per warp queue
 
 struct __align__(16) IouSmem {
-    float4 row0[kTileRows];
-    float4 row1[kTileRows];
-    float4 col0[kTileCols];
-    float4 col1[kTileCols];
-    uint16_t queue[kTileRows * kTileCols];
-    uint64_t bar;
-    int qcount;
+    uint2 rowm[kStages][kTileRows];
+    uint2 colm[kStages][kTileCols];
+    int2 queue[kWarps][kQueueCap];
+    uint4 resp[kRespSlots];
+    uint64_t full[kStages];
+    uint64_t empty[kStages];
+    uint64_t sched[kRespSlots];
+    int qcount[kWarps];
 };
+
+struct IouArgs {
+    const float4 *a0, *a1;
+    const uint2 *am;
+    const float4 *b0, *b1;
+    const uint2 *bm;
+    int64_t n1, n2;
+    float *out;
+    int64_t ld_out;
+    unsigned tiles_x;
+};
+
+template <int MODE>
+__device__ __forceinline__ void emit_pair(const IouArgs &g, int row, int col) {
+    const float v = pair_value<MODE>(__ldg(g.a0 + row), __ldg(g.a1 + row), __ldg(g.b0 + col),
+                                     __ldg(g.b1 + col));
+    if (v != 0.f) g.out[(int64_t)row * g.ld_out + col] = v;
+}
 
 template <int MODE, bool VEC>
 __global__ void __launch_bounds__(kThreads)
-iou_tile_kernel(const float4 *__restrict__ a0, const float4 *__restrict__ a1, int64_t n1,
-                const float4 *__restrict__ b0, const float4 *__restrict__ b1, int64_t n2,
-                float *__restrict__ out, int64_t ld_out, unsigned tiles_x) {
+iou_tile_kernel(const IouArgs g) {
     __shared__ IouSmem sm;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    // 1-D grid, column tiles fastest: neighbouring CTAs share their row boxes
-    const int64_t row_base = (int64_t)(blockIdx.x / tiles_x) * kTileRows;
-    const int64_t col_base = (int64_t)(blockIdx.x % tiles_x) * kTileCols;
 
     if (tid == 0) {
-        sm.qcount = 0;
-        mbar_init(&sm.bar, 1);
+#pragma unroll
+        for (int s = 0; s < kStages; ++s) {
+            mbar_init(&sm.full[s], 1);
+            mbar_init(&sm.empty[s], kWarps);
+        }
+#pragma unroll
+        for (int s = 0; s < kRespSlots; ++s) mbar_init(&sm.sched[s], 1);
         fence_mbar_init();
     }
+    if (tid < kWarps) sm.qcount[tid] = 0;
     __syncthreads();
+
+    auto issue_masks = [&](unsigned k, unsigned t) {   // thread 0: masks of tile t, my k-th
+        const int s = k % kStages;
+        const int64_t rb = (int64_t)(t / g.tiles_x) * kTileRows;
+        const int64_t cb = (int64_t)(t % g.tiles_x) * kTileCols;
+        mbar_expect_tx(&sm.full[s], (kTileRows + kTileCols) * sizeof(uint2));
+        tma_load_1d(sm.rowm[s], g.am + rb, kTileRows * sizeof(uint2), &sm.full[s]);
+        tma_load_1d(sm.colm[s], g.bm + cb, kTileCols * sizeof(uint2), &sm.full[s]);
+    };
+    // the answer for my k-th tile (k >= 1) lives in slot (k-1) % kRespSlots, use (k-1) / kRespSlots
+    auto ask_next = [&](unsigned k) {                  // thread 0: who is my k-th tile?
+        const int slot = (k - 1) % kRespSlots;
+        mbar_expect_tx(&sm.sched[slot], 16);
+        clc_try_cancel(&sm.resp[slot], &sm.sched[slot]);
+    };
+    unsigned t = blockIdx.x;       // my tile k = 0 is my own launch
     if (tid == 0) {
-        mbar_expect_tx(&sm.bar, (2 * kTileRows + 2 * kTileCols) * sizeof(float4));
-        tma_load_1d(sm.row0, a0 + row_base, kTileRows * sizeof(float4), &sm.bar);
-        tma_load_1d(sm.row1, a1 + row_base, kTileRows * sizeof(float4), &sm.bar);
-        tma_load_1d(sm.col0, b0 + col_base, kTileCols * sizeof(float4), &sm.bar);
-        tma_load_1d(sm.col1, b1 + col_base, kTileCols * sizeof(float4), &sm.bar);
+        issue_masks(0, t);
+        ask_next(1);
     }
 
-    // ---- 0. the tile's zeros, while the TMA copies are in flight ---------------
-    {
-        const int64_t gcol = col_base + 4 * lane;
-        const int cols_here = (int)min((int64_t)4, n2 - gcol);  // <= 0: lane is past the edge
-        const int rows_here = (int)min((int64_t)kTileRows, n1 - row_base);
-        float *dst = out + (row_base + warp) * ld_out + gcol;
-        const int64_t step = (int64_t)kWarps * ld_out;
-        if (VEC) {
-            if (rows_here == kTileRows && cols_here == 4) {   // interior tile: 8 plain stores
+    int2 *const wq = sm.queue[warp];
+    int *const wqc = &sm.qcount[warp];
+
+    for (unsigned k = 0;; ++k) {
+        const int s = k % kStages;
+        const int64_t row_base = (int64_t)(t / g.tiles_x) * kTileRows;
+        const int64_t col_base = (int64_t)(t % g.tiles_x) * kTileCols;
+
+        // ---- scheduler (thread 0): learn tile k+1, prefetch its masks, ask for k+2 ---
+        // (the answer was requested a whole tile ago, so this wait is short)
+        if (tid == 0) {
+            const unsigned kn = k + 1;
+            mbar_wait(&sm.sched[k % kRespSlots], (k / kRespSlots) & 1);
+            unsigned tn;
+            if (clc_decode(&sm.resp[k % kRespSlots], tn)) {
+                // ring stage of tile k+1 was last read for tile k+1-kStages: wait until every
+                // warp left it.  That also proves every warp has read the responses up to
+                // that tile, so the slot of tile k+2 (last used kRespSlots tiles ago) is free.
+                if (kn >= kStages) mbar_wait(&sm.empty[kn % kStages], ((kn / kStages) - 1) & 1);
+                issue_masks(kn, tn);
+                fence_proxy_async_smem();
+                ask_next(k + 2);
+            }
+        }
+
+        // ---- zeros of this warp's 8 x 128 strip (independent of the masks) -------
+        if (!(ROTGEO_ABLATE & 1)) {
+            const int64_t gcol = col_base + 4 * lane;
+            const int cols_here = (int)min((int64_t)4, g.n2 - gcol);  // <= 0: lane is past the edge
+            const int rows_here = (int)min((int64_t)kTileRows, g.n1 - row_base);
+            float *dst = g.out + (row_base + warp) * g.ld_out + gcol;
+            const int64_t step = (int64_t)kWarps * g.ld_out;
+            if (VEC) {
+                if (rows_here == kTileRows && cols_here == 4) {   // interior tile: 8 plain stores
 #pragma unroll
-                for (int it = 0; it < kRowsPerWarp; ++it) {
-                    *reinterpret_cast<float4 *>(dst) = make_float4(0.f, 0.f, 0.f, 0.f);
-                    dst += step;
+                    for (int it = 0; it < kRowsPerWarp; ++it) {
+                        *reinterpret_cast<float4 *>(dst) = make_float4(0.f, 0.f, 0.f, 0.f);
+                        dst += step;
+                    }
+                } else if (cols_here > 0) {
+                    for (int r = warp; r < rows_here; r += kWarps) {
+                        *reinterpret_cast<float4 *>(dst) = make_float4(0.f, 0.f, 0.f, 0.f);
+                        dst += step;
+                    }
                 }
-            } else if (cols_here > 0) {
+            } else {
                 for (int r = warp; r < rows_here; r += kWarps) {
-                    *reinterpret_cast<float4 *>(dst) = make_float4(0.f, 0.f, 0.f, 0.f);
+                    for (int k = 0; k < cols_here; ++k) dst[k] = 0.f;
                     dst += step;
                 }
             }
-        } else {
-            for (int it = 0; it < kRowsPerWarp; ++it)
-                if (warp + kWarps * it < rows_here)
-                    for (int k = 0; k < cols_here; ++k) dst[it * step + k] = 0.f;
         }
-    }
-    mbar_wait(&sm.bar, 0);
 
-    // ---- 1. cull level 1: bin masks (padding rows / columns carry empty masks) --
-    uint32_t cxm[4], cym[4];
+        // ---- cull level 1: bin masks (padding rows / columns carry empty masks) ---
+        mbar_wait(&sm.full[s], (k / kStages) & 1);
+        uint32_t hits = 0;
+        if (!(ROTGEO_ABLATE & 2)) {
+            const uint4 c01 = *reinterpret_cast<const uint4 *>(&sm.colm[s][4 * lane]);
+            const uint4 c23 = *reinterpret_cast<const uint4 *>(&sm.colm[s][4 * lane + 2]);
+            const uint32_t cxm[4] = {c01.x, c01.z, c23.x, c23.z};
+            const uint32_t cym[4] = {c01.y, c01.w, c23.y, c23.w};
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
-        const float4 c = sm.col0[4 * lane + k];
-        cxm[k] = __float_as_uint(c.z);
-        cym[k] = __float_as_uint(c.w);
-    }
-    uint32_t hits = 0;
+            for (int it = 0; it < kRowsPerWarp; ++it) {
+                const uint2 rm = sm.rowm[s][warp + kWarps * it];
 #pragma unroll
-    for (int it = 0; it < kRowsPerWarp; ++it) {
-        const float2 rm = *reinterpret_cast<const float2 *>(&sm.row0[warp + kWarps * it].z);
-        const uint32_t rxm = __float_as_uint(rm.x), rym = __float_as_uint(rm.y);
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            const bool hit = ((rxm & cxm[k]) != 0u) & ((rym & cym[k]) != 0u);
-            hits |= (hit ? 1u : 0u) << (4 * it + k);
+                for (int k = 0; k < 4; ++k) {
+                    const bool hit = ((rm.x & cxm[k]) != 0u) & ((rm.y & cym[k]) != 0u);
+                    hits |= (hit ? 1u : 0u) << (4 * it + k);
+                }
+            }
         }
-    }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&sm.empty[s]);   // this warp is done with the stage
 
-    // ---- 2. compact survivors into the queue ---------------------------------
-    if (__any_sync(0xffffffffu, hits != 0)) {
-        const int cnt = __popc(hits);
-        int incl = cnt;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            const int v = __shfl_up_sync(0xffffffffu, incl, d);
-            if (lane >= d) incl += v;
+        // ---- queue the survivors -----------------------------------------------------
+        if (hits) {
+            const int cnt = __popc(hits);
+            int pos = atomicAdd(wqc, cnt);
+            const int row0 = (int)row_base + warp, col0 = (int)col_base + 4 * lane;
+            uint32_t m = hits;
+            while (m) {
+                const int bit = __ffs(m) - 1;
+                m &= m - 1;
+                const int row = row0 + kWarps * (bit >> 2), col = col0 + (bit & 3);
+                if (pos < kQueueCap) wq[pos] = make_int2(row, col);
+                else emit_pair<MODE>(g, row, col);   // queue full: this lane's own zero precedes it
+                ++pos;
+            }
         }
-        int base = 0;
-        if (lane == 31) base = atomicAdd(&sm.qcount, incl);
-        base = __shfl_sync(0xffffffffu, base, 31);
-        int pos = base + incl - cnt;
-        uint32_t m = hits;
-        while (m) {
-            const int bit = __ffs(m) - 1;
-            m &= m - 1;
-            const int r = warp + kWarps * (bit >> 2);
-            const int c = 4 * lane + (bit & 3);
-            sm.queue[pos++] = (uint16_t)((r << 7) | c);
-        }
-    }
-    __syncthreads();   // also orders the zero stores before the value stores below
+        __syncwarp();
 
-    // ---- 3. cull level 2 + exact pass over the queue ---------------------------
-    const int total = sm.qcount;
-    for (int e = tid; e < total; e += kThreads) {
-        const int q = sm.queue[e];
-        const int r = q >> 7, c = q & 127;
-        const float v = pair_value<MODE>(sm.row0[r], sm.row1[r], sm.col0[c], sm.col1[c]);
-        if (v != 0.f) out[(row_base + r) * ld_out + (col_base + c)] = v;
+        // ---- next tile (or none: nothing left to steal) ---------------------------------
+        unsigned tn;
+        mbar_wait(&sm.sched[k % kRespSlots], (k / kRespSlots) & 1);
+        const bool more = clc_decode(&sm.resp[k % kRespSlots], tn);
+        fence_proxy_async_smem();   // my read of the slot precedes its reuse by a later request
+
+        // ---- cull level 2 + exact clipper, 32 queued pairs at a time -----------------
+        int qn = min(*wqc, kQueueCap);
+        while (qn >= 32 || (!more && qn > 0)) {
+            const int take = min(qn, 32);
+            if (lane < take && !(ROTGEO_ABLATE & 4)) {
+                const int2 e = wq[qn - take + lane];
+                emit_pair<MODE>(g, e.x, e.y);
+            }
+            qn -= take;
+        }
+        __syncwarp();
+        if (lane == 0) *wqc = qn;
+        __syncwarp();
+        if (!more) break;
+        t = tn;
     }
 }
 
 int launch_iou_pairwise(const void *packed1, int64_t n1, const void *packed2, int64_t n2, int mode,
                         float *out, int64_t ld_out, cudaStream_t stream) {
     if (n1 == 0 || n2 == 0) return 0;
+    if (n1 > 0x7fffffffLL || n2 > 0x7fffffffLL) return -1;
     const PackedView A = packed_view(packed1, padded_count(n1));
     const PackedView B = packed_view(packed2, padded_count(n2));
     const int64_t tiles_x = (n2 + kTileCols - 1) / kTileCols;
     const int64_t tiles = tiles_x * ((n1 + kTileRows - 1) / kTileRows);
     if (tiles > 0x7fffffffLL) return -1;
-    const unsigned grid = (unsigned)tiles;
     const bool vec = (ld_out % 4 == 0) && (n2 % 4 == 0) && ((reinterpret_cast<uintptr_t>(out) & 15) == 0);
-#define ROTGEO_LAUNCH(M, V)                                                                     \
-    iou_tile_kernel<M, V><<<grid, kThreads, 0, stream>>>(A.p0, A.p1, n1, B.p0, B.p1, n2, out, ld_out, \
-                                                         (unsigned)tiles_x)
-    if (mode == 0) {
-        if (vec) ROTGEO_LAUNCH(0, true); else ROTGEO_LAUNCH(0, false);
-    } else {
-        if (vec) ROTGEO_LAUNCH(1, true); else ROTGEO_LAUNCH(1, false);
-    }
-#undef ROTGEO_LAUNCH
+    void (*kern)(IouArgs) = mode == 0 ? (vec ? iou_tile_kernel<0, true> : iou_tile_kernel<0, false>)
+                                      : (vec ? iou_tile_kernel<1, true> : iou_tile_kernel<1, false>);
+    IouArgs g;
+    g.a0 = A.p0; g.a1 = A.p1; g.am = A.pm;
+    g.b0 = B.p0; g.b1 = B.p1; g.bm = B.pm;
+    g.n1 = n1; g.n2 = n2;
+    g.out = out; g.ld_out = ld_out;
+    g.tiles_x = (unsigned)tiles_x;
+    // one CTA per tile; running CTAs steal the not-yet-launched ones (launch control)
+    kern<<<(unsigned)tiles, kThreads, 0, stream>>>(g);
     return cudaGetLastError() == cudaSuccess ? 0 : -3;
 }
 
@@ -173,7 +252,7 @@ __device__ __forceinline__ void load_box(const float *b, float min_wh, float4 &p
     }
     double sd, cd;
     sincos((double)b[4], &sd, &cd);
-    p0 = make_float4(b[0], b[1], 0.f, 0.f);
+    p0 = make_float4(b[0], b[1], 0.f, w * h);
     p1 = make_float4((float)cd, (float)sd, 0.5f * w, 0.5f * h);
 }
 

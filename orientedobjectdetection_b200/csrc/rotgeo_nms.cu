@@ -41,6 +41,8 @@ struct __align__(16) MaskSmem {
     float4 row1[kTile];
     float4 col0[kTile];
     float4 col1[kTile];
+    uint2 rowm[kTile];
+    uint2 colm[kTile];
     unsigned long long bits[kTile][2];
     uint16_t queue[kHalf * kTile];
     uint64_t bar;
@@ -59,7 +61,7 @@ __device__ __forceinline__ int find_segment(const NmsSegment *__restrict__ segs,
 
 __global__ void __launch_bounds__(kThreads)
 nms_mask_kernel(const float4 *__restrict__ p0, const float4 *__restrict__ p1,
-                const NmsSegment *__restrict__ segs, int nseg, float thr,
+                const uint2 *__restrict__ pm, const NmsSegment *__restrict__ segs, int nseg, float thr,
                 unsigned long long *__restrict__ mask) {
     __shared__ MaskSmem sm;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -90,6 +92,11 @@ nms_mask_kernel(const float4 *__restrict__ p0, const float4 *__restrict__ p1,
         tma_load_1d(sm.col0, p0 + seg.start + col_base, kTile * sizeof(float4), &sm.bar);
         tma_load_1d(sm.col1, p1 + seg.start + col_base, kTile * sizeof(float4), &sm.bar);
     }
+    // bin masks: plain coalesced loads (a segment may start at an odd box, and a
+    // bulk copy needs 16-byte alignment; the float4 geometry planes always have it)
+    if (tid < kTile) sm.rowm[tid] = pm[seg.start + row_base + tid];
+    else sm.colm[tid - kTile] = pm[seg.start + col_base + tid - kTile];
+    __syncthreads();
     mbar_wait(&sm.bar, 0);
 
     // cull level 1 operands: bin masks of this lane's four columns; positions past
@@ -98,10 +105,10 @@ nms_mask_kernel(const float4 *__restrict__ p0, const float4 *__restrict__ p1,
     const int cpos = col_base + 4 * lane;
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-        const float4 c = sm.col0[4 * lane + k];
+        const uint2 c = sm.colm[4 * lane + k];
         const bool live = cpos + k < L;
-        cxm[k] = live ? __float_as_uint(c.z) : 0u;
-        cym[k] = live ? __float_as_uint(c.w) : 0u;
+        cxm[k] = live ? c.x : 0u;
+        cym[k] = live ? c.y : 0u;
     }
     const bool diagonal = I == J;   // only there can a column precede its row
 
@@ -116,9 +123,9 @@ nms_mask_kernel(const float4 *__restrict__ p0, const float4 *__restrict__ p1,
         for (int it = 0; it < kHalf / kWarps; ++it) {
             const int r = hrow + warp + kWarps * it;
             const int rpos = row_base + r;
-            const float2 rm = *reinterpret_cast<const float2 *>(&sm.row0[r].z);
-            const uint32_t rxm = rpos < L ? __float_as_uint(rm.x) : 0u;
-            const uint32_t rym = __float_as_uint(rm.y);
+            const uint2 rm = sm.rowm[r];
+            const uint32_t rxm = rpos < L ? rm.x : 0u;
+            const uint32_t rym = rm.y;
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
                 bool hit = ((rxm & cxm[k]) != 0u) & ((rym & cym[k]) != 0u);
@@ -324,7 +331,7 @@ void nms_plan(int64_t n, const int64_t *seg_offsets_host, int64_t num_segments, 
     plan->total_tiles = tiles;
     plan->mask_words = words;
     size_t off = 0;
-    plan->off_packed = off;   off = align_up(off + (size_t)plan->n_pad * 2 * sizeof(float4), 256);
+    plan->off_packed = off;   off = align_up(off + (size_t)plan->n_pad * kPackedBytesPerBox, 256);
     plan->off_segments = off; off = align_up(off + (size_t)num_segments * sizeof(NmsSegment), 256);
     plan->off_mask = off;     off = align_up(off + (size_t)words * sizeof(uint64_t), 256);
     plan->off_flags = off;    off = align_up(off + (size_t)n, 256);
@@ -340,7 +347,7 @@ int launch_nms(const NmsPlan &plan, const void *packed, const NmsSegment *segmen
     if (plan.total_tiles > 0x7fffffffLL) return -1;
     if (plan.total_tiles > 0)
         nms_mask_kernel<<<(unsigned)plan.total_tiles, kThreads, 0, stream>>>(
-            P.p0, P.p1, segments_dev, (int)plan.num_segments, thr,
+            P.p0, P.p1, P.pm, segments_dev, (int)plan.num_segments, thr,
             reinterpret_cast<unsigned long long *>(mask));
     if (cudaGetLastError() != cudaSuccess) return -3;
     const size_t dyn = (size_t)max_words * sizeof(unsigned long long);

@@ -82,6 +82,7 @@ pack_kernel(PackSet s1, PackSet s2, float min_wh, float cell) {
         // padding: empty bin masks, so no pair with it survives the cull
         s.p0[i] = make_float4(0.f, 0.f, 0.f, 0.f);
         s.p1[i] = make_float4(1.f, 0.f, 0.f, 0.f);
+        s.pm[i] = make_uint2(0u, 0u);
         return;
     }
     const int64_t src = s.gather ? s.gather[i] : i;
@@ -106,8 +107,9 @@ pack_kernel(PackSet s1, PackSet s2, float min_wh, float cell) {
     const float rx = r + fabsf(cx) * 2.4e-7f, ry = r + fabsf(cy) * 2.4e-7f;
     const uint32_t xm = bin_mask(cx - rx, cx + rx, inv_cell);
     const uint32_t ym = bin_mask(cy - ry, cy + ry, inv_cell);
-    s.p0[i] = make_float4(cx, cy, __uint_as_float(xm), __uint_as_float(ym));
+    s.p0[i] = make_float4(cx, cy, r, w * h);
     s.p1[i] = make_float4((float)cd, (float)sd, a, hb);
+    s.pm[i] = make_uint2(xm, ym);
 }
 
 int launch_pack(const PackSet &s1, const PackSet &s2, float min_wh, float cell,
@@ -129,6 +131,7 @@ PackSet make_pack_set(const float *boxes, int64_t n, int stride, const int64_t *
     s.offsets = offsets;
     s.p0 = reinterpret_cast<float4 *>(packed);
     s.p1 = s.p0 ? s.p0 + n_pad : nullptr;
+    s.pm = s.p0 ? reinterpret_cast<uint2 *>(s.p1 + n_pad) : nullptr;
     s.n_pad = n_pad;
     return s;
 }

@@ -177,3 +177,24 @@ def test_merge_results_c5_small():
     # in-place translation of the caller's arrays, like the reference
     assert np.array_equal(mine[1][0][:, 2:], res[1][0][:, 2:])
     assert not np.array_equal(mine[1][0][:, :2], res[1][0][:, :2]) or res[1][0].size == 0
+
+
+# ------------------------------------------------------------------ full-size (BASELINE C3)
+def test_iou_c3_full_size_sample_and_symmetry():
+    """8192 x 8192 (6.7e7 pairs, 8192 tiles: the work-stealing path of the tile
+    kernel): 96 sampled rows against the oracle, and the size-independent
+    property IoU(a, b) == IoU(b, a)^T over the whole matrix."""
+    a, b = synth.c3_iou(seed=0)
+    ad, bd = _cuda(a), _cuda(b)
+    got = rg.rbbox_overlaps(ad, bd)
+    assert got.shape == (8192, 8192)
+    rows = np.random.default_rng(5).choice(8192, 96, replace=False)
+    want = ref_api.rbbox_overlaps(torch.from_numpy(a[rows]), torch.from_numpy(b)).numpy()
+    assert np.abs(got[torch.from_numpy(rows).cuda()].cpu().numpy() - want).max() <= IOU_TOL
+    gt = rg.rbbox_overlaps(bd, ad)
+    assert (got - gt.t()).abs().max().item() <= IOU_TOL
+    nz = int((got > 0).sum().item())
+    assert 20_000 < nz < 400_000          # ~0.06 % of the pairs overlap at this density
+    # ragged full-size shape: no vector stores, partial edge tiles
+    got2 = rg.rbbox_overlaps(ad[:8191], bd[:8189])
+    assert torch.equal(got2, got[:8191, :8189])

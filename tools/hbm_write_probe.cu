@@ -50,6 +50,37 @@ __global__ void fill_wide(float *out, int64_t ld, unsigned chunks_x) {
     for (int it = 0; it < 16; ++it) *reinterpret_cast<float4 *>(dst + it * 128) = make_float4(0.f, 0.f, 0.f, 0.f);
 }
 
+// persistent variant: CTA c fills tiles c, c+G, ...
+__global__ void fill_tiles_persistent(float *out, int64_t ld, unsigned tiles_x, unsigned tiles) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (unsigned t = blockIdx.x; t < tiles; t += gridDim.x) {
+        const int64_t row_base = (int64_t)(t / tiles_x) * 64;
+        const int64_t col_base = (int64_t)(t % tiles_x) * 128;
+        float *dst = out + (row_base + warp) * ld + col_base + 4 * lane;
+#pragma unroll
+        for (int it = 0; it < 8; ++it) {
+            *reinterpret_cast<float4 *>(dst) = make_float4(0.f, 0.f, 0.f, 0.f);
+            dst += 8 * ld;
+        }
+    }
+}
+// persistent, contiguous chunk of tiles per CTA
+__global__ void fill_tiles_persistent_chunk(float *out, int64_t ld, unsigned tiles_x, unsigned tiles) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const unsigned per = (tiles + gridDim.x - 1) / gridDim.x;
+    const unsigned t0 = blockIdx.x * per, t1 = min(tiles, t0 + per);
+    for (unsigned t = t0; t < t1; ++t) {
+        const int64_t row_base = (int64_t)(t / tiles_x) * 64;
+        const int64_t col_base = (int64_t)(t % tiles_x) * 128;
+        float *dst = out + (row_base + warp) * ld + col_base + 4 * lane;
+#pragma unroll
+        for (int it = 0; it < 8; ++it) {
+            *reinterpret_cast<float4 *>(dst) = make_float4(0.f, 0.f, 0.f, 0.f);
+            dst += 8 * ld;
+        }
+    }
+}
+
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
 // TMA bulk stores: one thread per CTA pushes 64 rows x 512 B from a zeroed smem row
@@ -105,6 +136,12 @@ int main() {
     med = time_it([&] { fill_tiles_rowmajor<<<8192, 256>>>(out, M, 64); }, flush, flush_bytes, 20, &best); REPORT("64x128 tiles, rows 8w+k");
     med = time_it([&] { fill_wide<<<8192 / 8 * 4, 256>>>(out, M, 4); }, flush, flush_bytes, 20, &best); REPORT("8 rows x 2048 cols per CTA");
     med = time_it([&] { fill_tiles_tma<<<8192, 128>>>(out, M, 64); }, flush, flush_bytes, 20, &best); REPORT("64x128 tiles, TMA bulk stores");
+    for (int k : {1, 2, 4, 5, 8}) {
+        med = time_it([&] { fill_tiles_persistent<<<148 * k, 256>>>(out, M, 64, 8192); }, flush, flush_bytes, 20, &best);
+        char nm[64]; snprintf(nm, 64, "persistent strided, %d CTA/SM", k); REPORT(nm);
+        med = time_it([&] { fill_tiles_persistent_chunk<<<148 * k, 256>>>(out, M, 64, 8192); }, flush, flush_bytes, 20, &best);
+        snprintf(nm, 64, "persistent chunked, %d CTA/SM", k); REPORT(nm);
+    }
     CK(cudaDeviceSynchronize());
     CK(cudaGetLastError());
     printf("done\n");
