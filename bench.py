@@ -219,7 +219,7 @@ def run_rotgeo(args, rank, world, local_rank):
     def flush():
         flush_buf.zero_()
 
-    def step():      # the C-ABI call rbbox_overlaps makes: pack x2 (clamp 1e-3 fused) + tile kernel
+    def step():      # the C-ABI call rbbox_overlaps makes: pack (both sets, clamp 1e-3 fused) + tile kernel
         _lib.check(L.rotgeo_iou_pairwise(a_dev.data_ptr(), N_ROWS, 5, b_dev.data_ptr(), N_COLS, 5, 0,
                                          1e-3, out.data_ptr(), N_COLS, ws.data_ptr(), nbytes, stream),
                    'rotgeo_iou_pairwise')
@@ -252,14 +252,17 @@ def run_rotgeo(args, rank, world, local_rank):
     kms = timed_steps(torch, kernel_only, args.steps, flush, None)
     clocks = sampler.stop() if rank == 0 else None
     k_ms = float(np.mean(kms))
-    alg_bytes = 4.0 * N_ROWS * N_COLS + 32.0 * (N_ROWS + N_COLS)
+    alg_bytes = 4.0 * N_ROWS * N_COLS + 20.0 * (N_ROWS + N_COLS)   # fp32 matrix out + AoS boxes in
     peak, peak_src = peaks()
     achieved = alg_bytes / (k_ms * 1e-3) / 1e9
     pairs_s = N_ROWS * N_COLS / (k_ms * 1e-3)
 
     # end to end through the public API with HOST buffers (pinned in, pinned out)
     e2e_steps = max(3, min(args.steps, 10))
-    rg.rbbox_overlaps(a_host, b_host)
+    # warm-up with two results alive: the pinned-host caching allocator then owns the two
+    # 268 MB buffers the steady state alternates between (a cold cudaHostAlloc is ~100 ms)
+    keep = [rg.rbbox_overlaps(a_host, b_host), rg.rbbox_overlaps(a_host, b_host)]
+    del keep
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
@@ -285,7 +288,7 @@ def run_rotgeo(args, rank, world, local_rank):
                    'l2': 'output 268 MB/step exceeds the 126 MB L2; a 512 MB memset flushes L2 '
                          'between steps, outside the CUDA events',
                    'timing': 'sum of per-step CUDA-event times on the launching stream, max over ranks'},
-        'gpu_launches': 3 * args.steps,
+        'gpu_launches': 2 * args.steps,   # pack_kernel (both sets) + iou_tile_kernel per step
         'e2e': {'value': e2e_val, 'unit': 'Gpairs/s',
                 'h2d_bytes_per_step': int(a_host.numel() * 4 + b_host.numel() * 4),
                 'd2h_bytes_per_step': int(N_ROWS * N_COLS * 4), 'steps': e2e_steps,

@@ -21,19 +21,32 @@ __host__ __device__ inline int64_t padded_count(int64_t n) {
     return (n + kPackPad - 1) / kPackPad * kPackPad;
 }
 
-// A packed set of n_pad slots is three planes, back to back:
+// A packed set of n_pad slots (n_pad a multiple of 128) is five planes, back to back:
 //   plane0 float4 (cx, cy, r, area)   r = circumscribed radius (inflated), area = w*h
 //   plane1 float4 (cos, sin, a, b)    a = w/2, b = h/2
-//   planeM uint2  (xbins, ybins)      32-bit occupancy masks of the circumscribed
-//                                     circle over a modular grid of 32 bins per axis
-// The pair cull reads planeM only (8 B a box, TMA-staged); planes 0/1 are read
-// for the few pairs that survive it.
-constexpr int kPackedBytesPerBox = 2 * 16 + 8;
+//   planeM uint2  (xbins, ybins)      32-bit occupancy masks of the circumscribed circle
+//                                     over a modular grid of 32 bins per axis
+//   planeR uint32 sx | nx<<8 | sy<<16 | ny<<24: the same occupancy as cyclic bin
+//                                     ranges [s, s+n) per axis (n = 0: padding)
+//   planeT per block of 128 boxes, kTableWords uint32: the block's INVERTED bin
+//          index as a sparse table — T[axis][level j][bin b][word w] has bit c set
+//          iff box 32w+c of the block occupies one of the bins b .. b+2^j-1 (mod 32).
+// The pair cull of the IoU kernel reads planeR of the row boxes and planeT of the
+// column block: the 128-bit set of columns a row can touch is two table lookups
+// per axis (a range OR) and one AND — about one instruction per pair instead of
+// one test per pair.  planes 0/1 are read only for the pairs that survive.
+constexpr int kBlock = 128;                                  // boxes per table block
+constexpr int kTableLevels = 5;                              // run lengths 1, 2, 4, 8, 16
+constexpr int kTableAxisWords = kTableLevels * 32 * (kBlock / 32);   // 640
+constexpr int kTableWords = 2 * kTableAxisWords;             // 1280 (5120 bytes)
+constexpr int kPackedBytesPerBox = 2 * 16 + 8 + 4 + kTableWords * 4 / kBlock;   // 84
 
 struct PackedView {
     const float4 *p0;
     const float4 *p1;
     const uint2 *pm;
+    const uint32_t *pr;
+    const uint32_t *pt;
 };
 
 // n_pad = number of slots per plane (padded_count(n) for the IoU entry points; the
@@ -43,6 +56,8 @@ __host__ __device__ inline PackedView packed_view(const void *base, int64_t n_pa
     v.p0 = reinterpret_cast<const float4 *>(base);
     v.p1 = v.p0 + n_pad;
     v.pm = reinterpret_cast<const uint2 *>(v.p1 + n_pad);
+    v.pr = reinterpret_cast<const uint32_t *>(v.pm + n_pad);
+    v.pt = v.pr + n_pad;
     return v;
 }
 
@@ -52,13 +67,22 @@ __host__ __device__ inline PackedView packed_view(const void *base, int64_t n_pa
 // whatever the bin width and wherever the boxes are (class-offset coordinates
 // included), so the test `(xa & xb) && (ya & yb)` never rejects a touching pair.
 // Intervals spanning >= 32 bins, or so far out that fp32 no longer resolves bins,
-// get all ones.
-__device__ __forceinline__ uint32_t bin_mask(float lo, float hi, float inv_cell) {
+// occupy all 32.
+// cyclic bin range of [lo, hi]: start bin (0..31) and length (1..32)
+__device__ __forceinline__ void bin_range(float lo, float hi, float inv_cell, int &start, int &len) {
     const float fl = floorf(lo * inv_cell), fh = floorf(hi * inv_cell);
     const float span = fh - fl;
-    if (!(span < 31.f) || !(fabsf(fl) < 8388608.f)) return 0xffffffffu;  // also NaN / inf
-    const uint32_t m = (2u << (int)span) - 1u;  // span+1 low bits
-    return __funnelshift_l(m, m, (int)fl & 31);
+    if (!(span < 31.f) || !(fabsf(fl) < 8388608.f)) {  // also NaN / inf
+        start = 0;
+        len = 32;
+    } else {
+        start = (int)fl & 31;
+        len = (int)span + 1;
+    }
+}
+__device__ __forceinline__ uint32_t range_mask(int start, int len) {
+    const uint32_t m = len >= 32 ? 0xffffffffu : ((1u << len) - 1u);
+    return __funnelshift_l(m, m, start);
 }
 
 // circumscribed radius from the half extents, inflated so that every later use

@@ -15,6 +15,7 @@ struct PackSet {
     const float *offsets;    // nullable: added to cx, cy, indexed like the source rows
     float4 *p0, *p1;
     uint2 *pm;
+    uint32_t *pr, *pt;
     int64_t n_pad;
 };
 PackSet make_pack_set(const float *boxes, int64_t n, int stride, const int64_t *gather,

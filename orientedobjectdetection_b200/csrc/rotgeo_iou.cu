@@ -5,25 +5,30 @@
 // launch of the next not-yet-started CTA and takes over its tile, so the CTAs
 // are persistent (barriers initialised once, masks prefetched, warp queues kept
 // across tiles) while the hardware scheduler still balances the load.  Per tile:
-//   0. the tile's bin masks (64 row + 128 column boxes, 8 B each) arrive in a
-//      4-stage shared-memory ring filled by TMA bulk copies one tile ahead
+//   0. the bin ranges of the tile's 64 row boxes (256 B) and the inverted bin index
+//      of its 128-column block (5 KB sparse table, built once at pack time) arrive
+//      in a 4-stage shared-memory ring filled by TMA bulk copies one tile ahead
 //      (full/empty mbarriers; no __syncthreads anywhere in the loop);
 //   1. warp w owns rows {w, w+8, ...}: lane l streams the zeros of its four
 //      columns 4l..4l+3 to HBM (float4, 512 B per warp instruction — most of the
-//      matrix is zero) and tests the same pairs with the masks (two ANDs a pair);
-//   2. surviving pairs go to the warp's private queue (one shared atomic per lane
+//      matrix is zero), always one tile ahead of the cull so that the write stream
+//      never waits for a warp that is busy clipping;
+//   2. cull level 1: lane l takes row l/4 of the warp's eight and column word l%4:
+//      the 32 columns of that word the row can touch = (two table lookups OR-ed
+//      for x) AND (two for y) — ~1 instruction a pair instead of a test a pair;
+//   3. surviving pairs go to the warp's private queue (one shared atomic per lane
 //      with hits); whenever >= 32 are queued the warp pops 32 and runs the circle
 //      test + exact clipper with every lane busy, reading the two boxes' geometry
 //      planes through L1/L2, and overwrites the zeros with the non-zero values.
 // A value always lands after its zero: both stores come from the same warp with
 // a __syncwarp between (the same lane when a full queue forces the inline path).
-// Disjoint pairs cost ~5 instructions and 4 B of HBM write; the kernel is bound
-// by the HBM write stream (DESIGN.md "Kernels").
+// Disjoint pairs cost ~1 instruction and 4 B of HBM write; the kernel is bound by
+// the HBM write stream (DESIGN.md "Kernels").
 #include "rotgeo_device.cuh"
 #include "rotgeo_internal.h"
 
 #ifndef ROTGEO_ABLATE
-#define ROTGEO_ABLATE 0   // probe builds (tools/ablate_iou.py): 1 no zero stores, 2 no cull, 4 no exact pass
+#define ROTGEO_ABLATE 0   // probe builds (tools/ablate_iou.py): 1 no zero stores, 2 no cull, 4 no exact pass, 8 no final drain
 #endif
 
 namespace rotgeo {
@@ -37,9 +42,11 @@ constexpr int kStages = 4;        // mask ring
 constexpr int kRespSlots = 8;     // launch-control responses (> kStages, see the reuse argument below)
 constexpr int kQueueCap = 128;    // pairs per warp queue
 
+static_assert(kTileCols == kBlock, "a column tile is one inverted-index block");
+
 struct __align__(16) IouSmem {
-    uint2 rowm[kStages][kTileRows];
-    uint2 colm[kStages][kTileCols];
+    uint32_t tab[kStages][kTableWords];
+    uint32_t rowr[kStages][kTileRows];
     int2 queue[kWarps][kQueueCap];
     uint4 resp[kRespSlots];
     uint64_t full[kStages];
@@ -50,9 +57,9 @@ struct __align__(16) IouSmem {
 
 struct IouArgs {
     const float4 *a0, *a1;
-    const uint2 *am;
+    const uint32_t *ar;      // row boxes: bin ranges
     const float4 *b0, *b1;
-    const uint2 *bm;
+    const uint32_t *bt;      // column boxes: inverted-index tables, one per 128-block
     int64_t n1, n2;
     float *out;
     int64_t ld_out;
@@ -61,9 +68,19 @@ struct IouArgs {
 
 template <int MODE>
 __device__ __forceinline__ void emit_pair(const IouArgs &g, int row, int col) {
+#if ROTGEO_ABLATE & 32   // probe: no geometry loads
+    const float4 A0 = make_float4((float)row, 1.f, 3.f, 4.f), A1 = make_float4(1.f, 0.f, 1.f, 1.f);
+    const float4 B0 = make_float4((float)col, 1.f, 3.f, 4.f), B1 = make_float4(1.f, 0.f, 1.f, 1.f);
+    const float v = pair_value<MODE>(A0, A1, B0, B1);
+#else
     const float v = pair_value<MODE>(__ldg(g.a0 + row), __ldg(g.a1 + row), __ldg(g.b0 + col),
                                      __ldg(g.b1 + col));
+#endif
+#if ROTGEO_ABLATE & 16   // probe: no value stores (v == 12345 never happens)
+    if (v == 12345.f) g.out[(int64_t)row * g.ld_out + col] = v;
+#else
     if (v != 0.f) g.out[(int64_t)row * g.ld_out + col] = v;
+#endif
 }
 
 template <int MODE, bool VEC>
@@ -85,13 +102,13 @@ iou_tile_kernel(const IouArgs g) {
     if (tid < kWarps) sm.qcount[tid] = 0;
     __syncthreads();
 
-    auto issue_masks = [&](unsigned k, unsigned t) {   // thread 0: masks of tile t, my k-th
+    auto issue_masks = [&](unsigned k, unsigned t) {   // thread 0: cull data of tile t, my k-th
         const int s = k % kStages;
         const int64_t rb = (int64_t)(t / g.tiles_x) * kTileRows;
-        const int64_t cb = (int64_t)(t % g.tiles_x) * kTileCols;
-        mbar_expect_tx(&sm.full[s], (kTileRows + kTileCols) * sizeof(uint2));
-        tma_load_1d(sm.rowm[s], g.am + rb, kTileRows * sizeof(uint2), &sm.full[s]);
-        tma_load_1d(sm.colm[s], g.bm + cb, kTileCols * sizeof(uint2), &sm.full[s]);
+        const int64_t cblk = (int64_t)(t % g.tiles_x);
+        mbar_expect_tx(&sm.full[s], (kTileRows + kTableWords) * sizeof(uint32_t));
+        tma_load_1d(sm.rowr[s], g.ar + rb, kTileRows * sizeof(uint32_t), &sm.full[s]);
+        tma_load_1d(sm.tab[s], g.bt + cblk * kTableWords, kTableWords * sizeof(uint32_t), &sm.full[s]);
     };
     // the answer for my k-th tile (k >= 1) lives in slot (k-1) % kRespSlots, use (k-1) / kRespSlots
     auto ask_next = [&](unsigned k) {                  // thread 0: who is my k-th tile?
@@ -107,6 +124,38 @@ iou_tile_kernel(const IouArgs g) {
 
     int2 *const wq = sm.queue[warp];
     int *const wqc = &sm.qcount[warp];
+
+    // zeros of this warp's 8 x 128 strip of tile tt (independent of the cull data)
+    auto store_zeros = [&](unsigned tt) {
+        if (ROTGEO_ABLATE & 1) return;
+        const int64_t row_base = (int64_t)(tt / g.tiles_x) * kTileRows;
+        const int64_t col_base = (int64_t)(tt % g.tiles_x) * kTileCols;
+        const int64_t gcol = col_base + 4 * lane;
+        const int cols_here = (int)min((int64_t)4, g.n2 - gcol);  // <= 0: lane is past the edge
+        const int rows_here = (int)min((int64_t)kTileRows, g.n1 - row_base);
+        float *dst = g.out + (row_base + warp) * g.ld_out + gcol;
+        const int64_t step = (int64_t)kWarps * g.ld_out;
+        if (VEC) {
+            if (rows_here == kTileRows && cols_here == 4) {   // interior tile: 8 plain stores
+#pragma unroll
+                for (int it = 0; it < kRowsPerWarp; ++it) {
+                    *reinterpret_cast<float4 *>(dst) = make_float4(0.f, 0.f, 0.f, 0.f);
+                    dst += step;
+                }
+            } else if (cols_here > 0) {
+                for (int r = warp; r < rows_here; r += kWarps) {
+                    *reinterpret_cast<float4 *>(dst) = make_float4(0.f, 0.f, 0.f, 0.f);
+                    dst += step;
+                }
+            }
+        } else {
+            for (int r = warp; r < rows_here; r += kWarps) {
+                for (int k = 0; k < cols_here; ++k) dst[k] = 0.f;
+                dst += step;
+            }
+        }
+    };
+    store_zeros(t);   // the zeros always run one tile ahead of the cull
 
     for (unsigned k = 0;; ++k) {
         const int s = k % kStages;
@@ -130,50 +179,21 @@ iou_tile_kernel(const IouArgs g) {
             }
         }
 
-        // ---- zeros of this warp's 8 x 128 strip (independent of the masks) -------
-        if (!(ROTGEO_ABLATE & 1)) {
-            const int64_t gcol = col_base + 4 * lane;
-            const int cols_here = (int)min((int64_t)4, g.n2 - gcol);  // <= 0: lane is past the edge
-            const int rows_here = (int)min((int64_t)kTileRows, g.n1 - row_base);
-            float *dst = g.out + (row_base + warp) * g.ld_out + gcol;
-            const int64_t step = (int64_t)kWarps * g.ld_out;
-            if (VEC) {
-                if (rows_here == kTileRows && cols_here == 4) {   // interior tile: 8 plain stores
-#pragma unroll
-                    for (int it = 0; it < kRowsPerWarp; ++it) {
-                        *reinterpret_cast<float4 *>(dst) = make_float4(0.f, 0.f, 0.f, 0.f);
-                        dst += step;
-                    }
-                } else if (cols_here > 0) {
-                    for (int r = warp; r < rows_here; r += kWarps) {
-                        *reinterpret_cast<float4 *>(dst) = make_float4(0.f, 0.f, 0.f, 0.f);
-                        dst += step;
-                    }
-                }
-            } else {
-                for (int r = warp; r < rows_here; r += kWarps) {
-                    for (int k = 0; k < cols_here; ++k) dst[k] = 0.f;
-                    dst += step;
-                }
-            }
-        }
-
-        // ---- cull level 1: bin masks (padding rows / columns carry empty masks) ---
+        // ---- cull level 1: which of my 32 columns can my row touch? ------------------
+        // (padding rows have empty ranges, padding columns are in no table entry)
         mbar_wait(&sm.full[s], (k / kStages) & 1);
         uint32_t hits = 0;
+        const int rl = lane >> 2, cw = lane & 3;        // row of the warp's eight, column word
         if (!(ROTGEO_ABLATE & 2)) {
-            const uint4 c01 = *reinterpret_cast<const uint4 *>(&sm.colm[s][4 * lane]);
-            const uint4 c23 = *reinterpret_cast<const uint4 *>(&sm.colm[s][4 * lane + 2]);
-            const uint32_t cxm[4] = {c01.x, c01.z, c23.x, c23.z};
-            const uint32_t cym[4] = {c01.y, c01.w, c23.y, c23.w};
-#pragma unroll
-            for (int it = 0; it < kRowsPerWarp; ++it) {
-                const uint2 rm = sm.rowm[s][warp + kWarps * it];
-#pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    const bool hit = ((rm.x & cxm[k]) != 0u) & ((rm.y & cym[k]) != 0u);
-                    hits |= (hit ? 1u : 0u) << (4 * it + k);
-                }
+            const uint32_t rr = sm.rowr[s][warp + kWarps * rl];
+            const int sx = rr & 31, nx = (rr >> 8) & 63, sy = (rr >> 16) & 31, ny = rr >> 24;
+            if (nx != 0) {
+                const int jx = min(31 - __clz(nx), kTableLevels - 1), jy = min(31 - __clz(ny), kTableLevels - 1);
+                const uint32_t *tx = sm.tab[s] + jx * 128 + cw;
+                const uint32_t *ty = sm.tab[s] + kTableAxisWords + jy * 128 + cw;
+                const uint32_t X = tx[sx * 4] | tx[((sx + nx - (1 << jx)) & 31) * 4];
+                const uint32_t Y = ty[sy * 4] | ty[((sy + ny - (1 << jy)) & 31) * 4];
+                hits = X & Y;
             }
         }
         __syncwarp();
@@ -183,14 +203,13 @@ iou_tile_kernel(const IouArgs g) {
         if (hits) {
             const int cnt = __popc(hits);
             int pos = atomicAdd(wqc, cnt);
-            const int row0 = (int)row_base + warp, col0 = (int)col_base + 4 * lane;
+            const int row = (int)row_base + warp + kWarps * rl, col0 = (int)col_base + 32 * cw;
             uint32_t m = hits;
             while (m) {
-                const int bit = __ffs(m) - 1;
+                const int col = col0 + __ffs(m) - 1;
                 m &= m - 1;
-                const int row = row0 + kWarps * (bit >> 2), col = col0 + (bit & 3);
                 if (pos < kQueueCap) wq[pos] = make_int2(row, col);
-                else emit_pair<MODE>(g, row, col);   // queue full: this lane's own zero precedes it
+                else emit_pair<MODE>(g, row, col);   // queue full (its zero was stored before the __syncwarp)
                 ++pos;
             }
         }
@@ -201,10 +220,11 @@ iou_tile_kernel(const IouArgs g) {
         mbar_wait(&sm.sched[k % kRespSlots], (k / kRespSlots) & 1);
         const bool more = clc_decode(&sm.resp[k % kRespSlots], tn);
         fence_proxy_async_smem();   // my read of the slot precedes its reuse by a later request
+        if (more) store_zeros(tn);  // next tile's zeros are in flight while this warp clips
 
         // ---- cull level 2 + exact clipper, 32 queued pairs at a time -----------------
         int qn = min(*wqc, kQueueCap);
-        while (qn >= 32 || (!more && qn > 0)) {
+        while (qn >= 32 || (!more && qn > 0 && !(ROTGEO_ABLATE & 8))) {
             const int take = min(qn, 32);
             if (lane < take && !(ROTGEO_ABLATE & 4)) {
                 const int2 e = wq[qn - take + lane];
@@ -233,8 +253,8 @@ int launch_iou_pairwise(const void *packed1, int64_t n1, const void *packed2, in
     void (*kern)(IouArgs) = mode == 0 ? (vec ? iou_tile_kernel<0, true> : iou_tile_kernel<0, false>)
                                       : (vec ? iou_tile_kernel<1, true> : iou_tile_kernel<1, false>);
     IouArgs g;
-    g.a0 = A.p0; g.a1 = A.p1; g.am = A.pm;
-    g.b0 = B.p0; g.b1 = B.p1; g.bm = B.pm;
+    g.a0 = A.p0; g.a1 = A.p1; g.ar = A.pr;
+    g.b0 = B.p0; g.b1 = B.p1; g.bt = B.pt;
     g.n1 = n1; g.n2 = n2;
     g.out = out; g.ld_out = ld_out;
     g.tiles_x = (unsigned)tiles_x;

@@ -9,7 +9,7 @@
 // the same strided sample of <= 256 boxes (so all CTAs agree without a second
 // launch): 32 bins span the sampled extent of the RAW centres — before the class
 // offsets, because a class segment only ever meets itself.  The choice affects
-// speed only; bin_mask() is conservative for any width.
+// speed only; bin_range() is conservative for any width.
 #include "rotgeo_device.cuh"
 #include "rotgeo_internal.h"
 
@@ -70,46 +70,94 @@ __device__ float sample_inv_cell(const PackSet &s1, const PackSet &s2) {
     return 1.f / cell;
 }
 
+// One CTA packs 256 consecutive slots = two table blocks (slot counts are
+// multiples of 128, so a block never straddles the two sets).
 __global__ void __launch_bounds__(kPackThreads)
 pack_kernel(PackSet s1, PackSet s2, float min_wh, float cell) {
+    __shared__ uint2 s_mask[kPackThreads];
+    __shared__ uint32_t s_tab[2][kTableWords];
+    const int tid = threadIdx.x;
     const float inv_cell = cell > 0.f ? 1.f / cell : sample_inv_cell(s1, s2);
-    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-    const bool second = i >= s1.n_pad;
-    const PackSet s = second ? s2 : s1;
-    if (second) i -= s1.n_pad;
-    if (i >= s.n_pad) return;
-    if (i >= s.n) {
-        // padding: empty bin masks, so no pair with it survives the cull
-        s.p0[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-        s.p1[i] = make_float4(1.f, 0.f, 0.f, 0.f);
-        s.pm[i] = make_uint2(0u, 0u);
-        return;
+    const int64_t g = blockIdx.x * (int64_t)kPackThreads + tid;
+    {
+        const bool second = g >= s1.n_pad;
+        const PackSet s = second ? s2 : s1;
+        const int64_t i = second ? g - s1.n_pad : g;
+        uint2 m = make_uint2(0u, 0u);
+        if (i < s.n_pad) {
+            if (i >= s.n) {
+                // padding: occupies no bin, so no pair with it survives the cull
+                s.p0[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+                s.p1[i] = make_float4(1.f, 0.f, 0.f, 0.f);
+                s.pr[i] = 0u;
+            } else {
+                const int64_t src = s.gather ? s.gather[i] : i;
+                const float *b = s.boxes + src * s.stride;
+                float cx = b[0], cy = b[1], w = b[2], h = b[3];
+                const float th = b[4];
+                if (s.offsets) {
+                    const float o = s.offsets[src];
+                    cx += o;
+                    cy += o;
+                }
+                if (min_wh > 0.f) {
+                    w = fmaxf(w, min_wh);
+                    h = fmaxf(h, min_wh);
+                }
+                // the reference takes cos/sin of theta in double and narrows (Spec A step 3)
+                double sd, cd;
+                sincos((double)th, &sd, &cd);
+                const float a = 0.5f * w, hb = 0.5f * h;
+                // radius for the bins: the circle-test radius plus the rounding of cx -/+ r
+                const float r = circum_radius(a, hb);
+                const float rx = r + fabsf(cx) * 2.4e-7f, ry = r + fabsf(cy) * 2.4e-7f;
+                int sx, nx, sy, ny;
+                bin_range(cx - rx, cx + rx, inv_cell, sx, nx);
+                bin_range(cy - ry, cy + ry, inv_cell, sy, ny);
+                m = make_uint2(range_mask(sx, nx), range_mask(sy, ny));
+                s.p0[i] = make_float4(cx, cy, r, w * h);
+                s.p1[i] = make_float4((float)cd, (float)sd, a, hb);
+                s.pr[i] = (uint32_t)sx | ((uint32_t)nx << 8) | ((uint32_t)sy << 16) | ((uint32_t)ny << 24);
+            }
+            s.pm[i] = m;
+        }
+        s_mask[tid] = m;
     }
-    const int64_t src = s.gather ? s.gather[i] : i;
-    const float *b = s.boxes + src * s.stride;
-    float cx = b[0], cy = b[1], w = b[2], h = b[3];
-    const float th = b[4];
-    if (s.offsets) {
-        const float o = s.offsets[src];
-        cx += o;
-        cy += o;
+    __syncthreads();
+
+    // ---- inverted index of the two blocks: level 0 = transpose of the masks ----------
+    // task (block h, axis a, bin b, word w): bit c <- box 32w+c of block h occupies bin b
+    for (int task = tid; task < 2 * 2 * 32 * 4; task += kPackThreads) {
+        const int w = task & 3, b = (task >> 2) & 31, a = (task >> 7) & 1, h = task >> 8;
+        const uint2 *mm = s_mask + h * kBlock + 32 * w;
+        uint32_t bits = 0;
+#pragma unroll 8
+        for (int c = 0; c < 32; ++c) {
+            const uint32_t v = a ? mm[c].y : mm[c].x;
+            bits |= ((v >> b) & 1u) << c;
+        }
+        s_tab[h][a * kTableAxisWords + b * 4 + w] = bits;
     }
-    if (min_wh > 0.f) {
-        w = fmaxf(w, min_wh);
-        h = fmaxf(h, min_wh);
+    __syncthreads();
+    // level j: bins b .. b+2^j-1  =  level j-1 at b  |  level j-1 at b + 2^(j-1)
+    for (int j = 1; j < kTableLevels; ++j) {
+        for (int task = tid; task < 2 * 2 * 32 * 4; task += kPackThreads) {
+            const int w = task & 3, b = (task >> 2) & 31, a = (task >> 7) & 1, h = task >> 8;
+            const uint32_t *prev = s_tab[h] + a * kTableAxisWords + (j - 1) * 128;
+            s_tab[h][a * kTableAxisWords + j * 128 + b * 4 + w] =
+                prev[b * 4 + w] | prev[((b + (1 << (j - 1))) & 31) * 4 + w];
+        }
+        __syncthreads();
     }
-    // the reference takes cos/sin of theta in double and narrows (Spec A step 3)
-    double sd, cd;
-    sincos((double)th, &sd, &cd);
-    const float a = 0.5f * w, hb = 0.5f * h;
-    // radius for the masks: the circle-test radius plus the rounding of cx -/+ r
-    const float r = circum_radius(a, hb);
-    const float rx = r + fabsf(cx) * 2.4e-7f, ry = r + fabsf(cy) * 2.4e-7f;
-    const uint32_t xm = bin_mask(cx - rx, cx + rx, inv_cell);
-    const uint32_t ym = bin_mask(cy - ry, cy + ry, inv_cell);
-    s.p0[i] = make_float4(cx, cy, r, w * h);
-    s.p1[i] = make_float4((float)cd, (float)sd, a, hb);
-    s.pm[i] = make_uint2(xm, ym);
+    for (int h = 0; h < 2; ++h) {
+        const int64_t g0 = blockIdx.x * (int64_t)kPackThreads + h * kBlock;   // first slot of the block
+        const bool second = g0 >= s1.n_pad;
+        const PackSet s = second ? s2 : s1;
+        const int64_t i0 = second ? g0 - s1.n_pad : g0;
+        if (i0 >= s.n_pad) continue;
+        uint32_t *dst = s.pt + (i0 / kBlock) * kTableWords;
+        for (int k = tid; k < kTableWords; k += kPackThreads) dst[k] = s_tab[h][k];
+    }
 }
 
 int launch_pack(const PackSet &s1, const PackSet &s2, float min_wh, float cell,
@@ -132,6 +180,8 @@ PackSet make_pack_set(const float *boxes, int64_t n, int stride, const int64_t *
     s.p0 = reinterpret_cast<float4 *>(packed);
     s.p1 = s.p0 ? s.p0 + n_pad : nullptr;
     s.pm = s.p0 ? reinterpret_cast<uint2 *>(s.p1 + n_pad) : nullptr;
+    s.pr = s.p0 ? reinterpret_cast<uint32_t *>(s.pm + n_pad) : nullptr;
+    s.pt = s.p0 ? s.pr + n_pad : nullptr;
     s.n_pad = n_pad;
     return s;
 }

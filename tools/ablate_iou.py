@@ -7,16 +7,22 @@ import ctypes, os, subprocess, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 OUT = os.path.join(ROOT, 'tools', '_ablate')
-VARIANTS = {'full': 0, 'no_zero_stores': 1, 'no_cull': 2, 'no_exact': 4, 'stores_only': 6, 'cull_only': 5}
+VARIANTS = {'full': 0, 'no_exact': 4, 'no_value_store': 16, 'no_geom_loads': 32, 'no_loads_no_store': 48}
+if os.environ.get('ABLATE_REGS'):
+    VARIANTS = {'full_r%s' % r: (0, r) for r in os.environ['ABLATE_REGS'].split(',')}
 EXTRA = [a for a in sys.argv[2:]]
 
 def build():
     os.makedirs(OUT, exist_ok=True)
     csrc = os.path.join(ROOT, 'orientedobjectdetection_b200', 'csrc')
     for name, flag in VARIANTS.items():
+        extra = []
+        if isinstance(flag, tuple):
+            flag, regs = flag
+            extra = ['-maxrregcount=%s' % regs]
         so = os.path.join(OUT, 'librotgeo_%s.so' % name)
         cmd = ['/usr/local/cuda/bin/nvcc', '-gencode', 'arch=compute_100a,code=sm_100a', '-O3', '-lineinfo', '-std=c++17',
-               '-DROTGEO_ABLATE=%d' % flag, '-Xcompiler', '-fPIC', '-shared', '-ccbin', '/usr/bin/g++', '-o', so] + EXTRA + \
+               '-DROTGEO_ABLATE=%d' % flag, '-Xcompiler', '-fPIC', '-shared', '-ccbin', '/usr/bin/g++', '-o', so] + EXTRA + extra + \
               [os.path.join(csrc, f) for f in ('rotgeo_abi.cu', 'rotgeo_pack.cu', 'rotgeo_iou.cu', 'rotgeo_nms.cu')]
         subprocess.check_call(cmd)
     print('built', sorted(os.listdir(OUT)))
