@@ -114,3 +114,24 @@ def merge_results(results, offsets, iou_thr=0.1):
         out, _ = _nms(t[:, :-1], t[:, -1], iou_thr)
         merged.append(out.numpy())
     return merged
+
+
+def nms_keep_segmented(boxes, scores, iou_threshold, seg_ids=None, offsets=None):
+    """oracle stand-in for the product's ``ops._nms_keep`` (same signature):
+    greedy NMS inside each segment on boxes whose centres carry ``offsets``,
+    kept indices returned in global score-descending order (ties: lower index)."""
+    b = boxes.detach().cpu().float().clone()
+    s = scores.detach().cpu().float().reshape(-1)
+    if offsets is not None:
+        b[:, :2] = b[:, :2] + offsets.detach().cpu().float()[:, None]
+    seg = torch.zeros(b.shape[0], dtype=torch.long) if seg_ids is None else seg_ids.detach().cpu().long()
+    kept = []
+    for sid in torch.unique(seg).tolist():
+        idx = (seg == sid).nonzero(as_tuple=False).squeeze(1)
+        _, k = ref.nms_rotated(b[idx].numpy(), s[idx].numpy(), iou_threshold)
+        kept.append(idx[torch.from_numpy(k)])
+    kept = torch.cat(kept) if kept else torch.zeros(0, dtype=torch.long)
+    order = torch.from_numpy(ref.stable_desc_order(s.numpy()))
+    rank = torch.empty_like(order)
+    rank[order] = torch.arange(order.numel())
+    return kept[torch.argsort(rank[kept])]
