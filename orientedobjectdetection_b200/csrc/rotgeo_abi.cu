@@ -155,9 +155,9 @@ int rotgeo_nms(const float *boxes, int64_t n, int stride, const float *offsets,
                     workspace_bytes, plan.total_bytes);
     int max_words = 0;
     for (const auto &g : segs) max_words = g.words > max_words ? g.words : max_words;
-    if ((size_t)max_words * 8 > 200 * 1024)
+    if (rotgeo::nms_scan_smem_bytes(max_words) > 224 * 1024)
         return fail(ROTGEO_ERR_ARG, "nms: a segment of more than %d boxes is not supported",
-                    200 * 1024 / 8 * 64);
+                    (224 * 1024 - (int)rotgeo::nms_scan_smem_bytes(0)) / 8 * 64);
     char *ws = reinterpret_cast<char *>(workspace);
     void *packed = ws + plan.off_packed;
     rotgeo::NmsSegment *segs_dev = reinterpret_cast<rotgeo::NmsSegment *>(ws + plan.off_segments);
@@ -170,7 +170,10 @@ int rotgeo_nms(const float *boxes, int64_t n, int stride, const float *offsets,
         return cuda_fail("nms segment upload");
     const int64_t *sorder = segmented ? seg_order : order;
     {
-        const rotgeo::PackSet s1 = rotgeo::make_pack_set(boxes, n, stride, sorder, offsets, packed, plan.n_pad);
+        // slots follow the segment table: every segment starts on a 128-slot boundary
+        rotgeo::PackSet s1 = rotgeo::make_pack_set(boxes, n, stride, sorder, offsets, packed, plan.n_pad);
+        s1.segs = segs_dev;
+        s1.nseg = (int)num_segments;
         const rotgeo::PackSet none = rotgeo::make_pack_set(nullptr, 0, 5, nullptr, nullptr, nullptr, 0);
         if (rotgeo::launch_pack(s1, none, 0.f, 0.f, st)) return cuda_fail("nms pack launch");
     }

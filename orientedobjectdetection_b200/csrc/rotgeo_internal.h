@@ -5,6 +5,19 @@
 
 namespace rotgeo {
 
+// One segment of a segmented NMS.  `start` counts positions in seg_order (boxes in
+// segment-major, score-descending order); `pstart` is the segment's first slot in the
+// packed set, a multiple of 128, so every 128-slot table block lies inside one segment.
+struct NmsSegment {
+    int64_t start;      // first position in seg_order
+    int64_t pstart;     // first packed slot (multiple of 128)
+    int64_t len;        // boxes in the segment
+    int64_t mask_base;  // first u64 word of this segment's suppression mask
+    int64_t tile_base;  // first tile id of this segment in the bitmask grid
+    int32_t words;      // u64 words per mask row (even)
+    int32_t row_blocks; // ceil(len / 64)
+};
+
 // One box set to pack: AoS source rows (+ optional gather / centre offsets) and
 // the two destination planes.  n_pad == 0 marks an absent second set.
 struct PackSet {
@@ -13,6 +26,8 @@ struct PackSet {
     int stride;
     const int64_t *gather;   // nullable: packed[i] = boxes[gather[i]]
     const float *offsets;    // nullable: added to cx, cy, indexed like the source rows
+    const NmsSegment *segs;  // nullable: segmented slot layout (see slot_source)
+    int nseg;
     float4 *p0, *p1;
     uint2 *pm;
     uint32_t *pr, *pt;
@@ -31,19 +46,9 @@ int launch_iou_pairwise(const void *packed1, int64_t n1, const void *packed2, in
 int launch_iou_aligned(const float *boxes1, const float *boxes2, int64_t n, int stride1,
                        int stride2, int mode, float min_wh, float *out, cudaStream_t stream);
 
-// One segment of a segmented NMS, in units of sorted positions.
-struct NmsSegment {
-    int64_t start;      // first sorted position
-    int64_t len;        // boxes in the segment
-    int64_t mask_base;  // first u64 word of this segment's suppression mask
-    int64_t tile_base;  // first tile id of this segment in the bitmask grid
-    int32_t words;      // u64 words per mask row (even)
-    int32_t row_blocks; // ceil(len / 64)
-};
-
 struct NmsPlan {
     int64_t n;
-    int64_t n_pad;       // float4 slots per packed plane (with tile slack)
+    int64_t n_pad;       // packed slots: every segment padded to whole 128-slot blocks
     int64_t num_segments;
     int64_t total_tiles;
     int64_t mask_words;
@@ -53,6 +58,8 @@ struct NmsPlan {
 
 void nms_plan(int64_t n, const int64_t *seg_offsets_host, int64_t num_segments, NmsPlan *plan,
               NmsSegment *segments_out /* nullable, num_segments entries */);
+
+size_t nms_scan_smem_bytes(int max_words);   // dynamic shared memory of nms_scan_kernel
 
 int launch_nms(const NmsPlan &plan, const void *packed, const NmsSegment *segments_dev,
                int max_words, const int64_t *order, const int64_t *seg_order, float thr,

@@ -28,11 +28,28 @@ __device__ __forceinline__ float warp_max(float v) {
     return v;
 }
 
-__device__ __forceinline__ const float *src_row(const PackSet &s, int64_t i) {
-    return s.boxes + (s.gather ? s.gather[i] : i) * s.stride;
+// source row of slot i of a set, or -1 for padding.  Plain sets: slot i = box i
+// (through `gather`).  Segmented sets (NMS): every segment starts at a slot that is
+// a multiple of 128 (so each 128-slot table block lies inside one segment) and is
+// padded up to the next one.
+__device__ __forceinline__ int64_t slot_source(const PackSet &s, int64_t i) {
+    if (s.segs) {
+        int lo = 0, hi = s.nseg - 1;   // last segment with pstart <= i
+        while (lo < hi) {
+            const int mid = (lo + hi + 1) >> 1;
+            if (s.segs[mid].pstart <= i) lo = mid; else hi = mid - 1;
+        }
+        const int64_t pos = i - s.segs[lo].pstart;
+        if (pos >= s.segs[lo].len) return -1;
+        i = s.segs[lo].start + pos;
+    } else if (i >= s.n) {
+        return -1;
+    }
+    return s.gather ? s.gather[i] : i;
 }
 
-// 1 / (bin width): identical in every CTA of the launch
+// 1 / (bin width): identical in every CTA of the launch.  Every CTA reduces the
+// same strided sample of <= 256 raw box centres.
 __device__ float sample_inv_cell(const PackSet &s1, const PackSet &s2) {
     __shared__ float red[4][kPackThreads / 32];
     const int tid = threadIdx.x;
@@ -44,7 +61,7 @@ __device__ float sample_inv_cell(const PackSet &s1, const PackSet &s2) {
     float lo_x = INFINITY, hi_x = -INFINITY, lo_y = INFINITY, hi_y = -INFINITY;
     if (s.n > 0) {
         const int64_t i = (s.n >= slots) ? (int64_t)t * (s.n / slots) : (t % s.n);
-        const float *b = src_row(s, i);
+        const float *b = s.boxes + (s.gather ? s.gather[i] : i) * s.stride;
         const float cx = b[0], cy = b[1];
         if (fabsf(cx) < 1e30f && fabsf(cy) < 1e30f) {
             lo_x = hi_x = cx;
@@ -71,92 +88,96 @@ __device__ float sample_inv_cell(const PackSet &s1, const PackSet &s2) {
 }
 
 // One CTA packs 256 consecutive slots = two table blocks (slot counts are
-// multiples of 128, so a block never straddles the two sets).
+// multiples of 128, so a block never straddles the two sets); warp v packs the 32
+// boxes of word v % 4 of block v / 4.
 __global__ void __launch_bounds__(kPackThreads)
 pack_kernel(PackSet s1, PackSet s2, float min_wh, float cell) {
-    __shared__ uint2 s_mask[kPackThreads];
-    __shared__ uint32_t s_tab[2][kTableWords];
-    const int tid = threadIdx.x;
-    const float inv_cell = cell > 0.f ? 1.f / cell : sample_inv_cell(s1, s2);
+    __shared__ uint32_t s_t0[2][2][32][4];   // level 0: [block][axis][bin][word]
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int64_t g = blockIdx.x * (int64_t)kPackThreads + tid;
-    {
-        const bool second = g >= s1.n_pad;
-        const PackSet s = second ? s2 : s1;
-        const int64_t i = second ? g - s1.n_pad : g;
-        uint2 m = make_uint2(0u, 0u);
-        if (i < s.n_pad) {
-            if (i >= s.n) {
-                // padding: occupies no bin, so no pair with it survives the cull
-                s.p0[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-                s.p1[i] = make_float4(1.f, 0.f, 0.f, 0.f);
-                s.pr[i] = 0u;
-            } else {
-                const int64_t src = s.gather ? s.gather[i] : i;
-                const float *b = s.boxes + src * s.stride;
-                float cx = b[0], cy = b[1], w = b[2], h = b[3];
-                const float th = b[4];
-                if (s.offsets) {
-                    const float o = s.offsets[src];
-                    cx += o;
-                    cy += o;
-                }
-                if (min_wh > 0.f) {
-                    w = fmaxf(w, min_wh);
-                    h = fmaxf(h, min_wh);
-                }
-                // the reference takes cos/sin of theta in double and narrows (Spec A step 3)
-                double sd, cd;
-                sincos((double)th, &sd, &cd);
-                const float a = 0.5f * w, hb = 0.5f * h;
-                // radius for the bins: the circle-test radius plus the rounding of cx -/+ r
-                const float r = circum_radius(a, hb);
-                const float rx = r + fabsf(cx) * 2.4e-7f, ry = r + fabsf(cy) * 2.4e-7f;
-                int sx, nx, sy, ny;
-                bin_range(cx - rx, cx + rx, inv_cell, sx, nx);
-                bin_range(cy - ry, cy + ry, inv_cell, sy, ny);
-                m = make_uint2(range_mask(sx, nx), range_mask(sy, ny));
-                s.p0[i] = make_float4(cx, cy, r, w * h);
-                s.p1[i] = make_float4((float)cd, (float)sd, a, hb);
-                s.pr[i] = (uint32_t)sx | ((uint32_t)nx << 8) | ((uint32_t)sy << 16) | ((uint32_t)ny << 24);
-            }
-            s.pm[i] = m;
-        }
-        s_mask[tid] = m;
-    }
-    __syncthreads();
+    const bool second = g >= s1.n_pad;
+    const PackSet s = second ? s2 : s1;
+    const int64_t i = second ? g - s1.n_pad : g;
+    const bool in_set = i < s.n_pad;
 
-    // ---- inverted index of the two blocks: level 0 = transpose of the masks ----------
-    // task (block h, axis a, bin b, word w): bit c <- box 32w+c of block h occupies bin b
-    for (int task = tid; task < 2 * 2 * 32 * 4; task += kPackThreads) {
-        const int w = task & 3, b = (task >> 2) & 31, a = (task >> 7) & 1, h = task >> 8;
-        const uint2 *mm = s_mask + h * kBlock + 32 * w;
-        uint32_t bits = 0;
-#pragma unroll 8
-        for (int c = 0; c < 32; ++c) {
-            const uint32_t v = a ? mm[c].y : mm[c].x;
-            bits |= ((v >> b) & 1u) << c;
+    // the box first: its loads are in flight while the bin width is being derived
+    const int64_t src = in_set ? slot_source(s, i) : -1;
+    float cx = 0.f, cy = 0.f, w = 0.f, h = 0.f, th = 0.f;
+    if (src >= 0) {
+        const float *b = s.boxes + src * s.stride;
+        cx = b[0]; cy = b[1]; w = b[2]; h = b[3]; th = b[4];
+        if (s.offsets) {
+            const float o = s.offsets[src];
+            cx += o;
+            cy += o;
         }
-        s_tab[h][a * kTableAxisWords + b * 4 + w] = bits;
+    }
+    const float inv_cell = cell > 0.f ? 1.f / cell : sample_inv_cell(s1, s2);
+
+    uint32_t xm = 0u, ym = 0u;
+    if (in_set) {
+        if (src < 0) {
+            // padding: occupies no bin, so no pair with it survives the cull
+            s.p0[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+            s.p1[i] = make_float4(1.f, 0.f, 0.f, 0.f);
+            s.pr[i] = 0u;
+        } else {
+            if (min_wh > 0.f) {
+                w = fmaxf(w, min_wh);
+                h = fmaxf(h, min_wh);
+            }
+            // the reference takes cos/sin of theta in double and narrows (Spec A step 3)
+            double sd, cd;
+            sincos((double)th, &sd, &cd);
+            const float a = 0.5f * w, hb = 0.5f * h;
+            // radius for the bins: the circle-test radius plus the rounding of cx -/+ r
+            const float r = circum_radius(a, hb);
+            const float rx = r + fabsf(cx) * 2.4e-7f, ry = r + fabsf(cy) * 2.4e-7f;
+            int sx, nx, sy, ny;
+            bin_range(cx - rx, cx + rx, inv_cell, sx, nx);
+            bin_range(cy - ry, cy + ry, inv_cell, sy, ny);
+            xm = range_mask(sx, nx);
+            ym = range_mask(sy, ny);
+            s.p0[i] = make_float4(cx, cy, r, w * h);
+            s.p1[i] = make_float4((float)cd, (float)sd, a, hb);
+            s.pr[i] = (uint32_t)sx | ((uint32_t)nx << 8) | ((uint32_t)sy << 16) | ((uint32_t)ny << 24);
+        }
+        s.pm[i] = make_uint2(xm, ym);
+    }
+
+    // ---- inverted index, level 0: transpose the warp's 32 masks with ballots -----------
+    {
+        uint32_t tx = 0u, ty = 0u;
+#pragma unroll
+        for (int b = 0; b < 32; ++b) {
+            const uint32_t bx = __ballot_sync(0xffffffffu, (xm >> b) & 1u);
+            const uint32_t by = __ballot_sync(0xffffffffu, (ym >> b) & 1u);
+            if (lane == b) { tx = bx; ty = by; }
+        }
+        s_t0[warp >> 2][0][lane][warp & 3] = tx;   // bin = lane
+        s_t0[warp >> 2][1][lane][warp & 3] = ty;
     }
     __syncthreads();
-    // level j: bins b .. b+2^j-1  =  level j-1 at b  |  level j-1 at b + 2^(j-1)
-    for (int j = 1; j < kTableLevels; ++j) {
-        for (int task = tid; task < 2 * 2 * 32 * 4; task += kPackThreads) {
-            const int w = task & 3, b = (task >> 2) & 31, a = (task >> 7) & 1, h = task >> 8;
-            const uint32_t *prev = s_tab[h] + a * kTableAxisWords + (j - 1) * 128;
-            s_tab[h][a * kTableAxisWords + j * 128 + b * 4 + w] =
-                prev[b * 4 + w] | prev[((b + (1 << (j - 1))) & 31) * 4 + w];
+    // ---- levels 0..4 by prefix OR over 16 consecutive bins, straight to global ----------
+    // task (block h, axis a, bin b, word w): T[j][b][w] = OR of level 0 at bins b .. b+2^j-1
+    for (int task = tid; task < 2 * 2 * 32 * 4; task += kPackThreads) {
+        const int tw = task & 3, b = (task >> 2) & 31, a = (task >> 7) & 1, hb = task >> 8;
+        const int64_t g0 = blockIdx.x * (int64_t)kPackThreads + hb * kBlock;   // first slot of the block
+        const bool sec = g0 >= s1.n_pad;
+        const PackSet sb = sec ? s2 : s1;
+        const int64_t i0 = sec ? g0 - s1.n_pad : g0;
+        if (i0 >= sb.n_pad) continue;
+        uint32_t *dst = sb.pt + (i0 / kBlock) * kTableWords + a * kTableAxisWords + b * 4 + tw;
+        uint32_t acc = 0u;
+#pragma unroll
+        for (int k = 0; k < 16; ++k) {
+            acc |= s_t0[hb][a][(b + k) & 31][tw];
+            if (k == 0) dst[0] = acc;
+            if (k == 1) dst[128] = acc;
+            if (k == 3) dst[256] = acc;
+            if (k == 7) dst[384] = acc;
+            if (k == 15) dst[512] = acc;
         }
-        __syncthreads();
-    }
-    for (int h = 0; h < 2; ++h) {
-        const int64_t g0 = blockIdx.x * (int64_t)kPackThreads + h * kBlock;   // first slot of the block
-        const bool second = g0 >= s1.n_pad;
-        const PackSet s = second ? s2 : s1;
-        const int64_t i0 = second ? g0 - s1.n_pad : g0;
-        if (i0 >= s.n_pad) continue;
-        uint32_t *dst = s.pt + (i0 / kBlock) * kTableWords;
-        for (int k = tid; k < kTableWords; k += kPackThreads) dst[k] = s_tab[h][k];
     }
 }
 
@@ -172,6 +193,8 @@ int launch_pack(const PackSet &s1, const PackSet &s2, float min_wh, float cell,
 PackSet make_pack_set(const float *boxes, int64_t n, int stride, const int64_t *gather,
                       const float *offsets, void *packed, int64_t n_pad) {
     PackSet s;
+    s.segs = nullptr;
+    s.nseg = 0;
     s.boxes = boxes;
     s.n = n;
     s.stride = stride;

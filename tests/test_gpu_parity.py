@@ -198,3 +198,57 @@ def test_iou_c3_full_size_sample_and_symmetry():
     # ragged full-size shape: no vector stores, partial edge tiles
     got2 = rg.rbbox_overlaps(ad[:8191], bd[:8189])
     assert torch.equal(got2, got[:8191, :8189])
+
+
+# ------------------------------------------------------------------ full-size NMS
+def test_nms_single_segment_12000_vs_oracle():
+    """94 column blocks -> 4465 tiles: the work-stealing path of the mask kernel and
+    24 panels of the blocked scan, keep list compared with the oracle exactly."""
+    n = 12000
+    boxes = synth.le90_boxes(n, 33, 2048.0)
+    scores = synth.unique_scores(n, 33)
+    _, wk = ref.nms_rotated(boxes, scores, 0.3)
+    _, gk = rg.nms_rotated(_cuda(boxes), _cuda(scores), 0.3)
+    _assert_keep(boxes, scores, 0.3, gk.cpu().numpy(), wk)
+
+
+def test_nms_single_segment_30000_greedy_property():
+    """BASELINE C2 worst case as ONE segment (30000 boxes).  The greedy result is the
+    unique set S with: i in S  <=>  no higher-scored j in S has IoU(i, j) >= thr.
+    Checked for every box against the (parity-tested) IoU matrix, with the 1e-5 band."""
+    n, thr = 30000, 0.1
+    boxes = synth.le90_boxes(n, 9, 1024.0)
+    scores = synth.unique_scores(n, 9)
+    bd, sd = _cuda(boxes), _cuda(scores)
+    _, keep = rg.nms_rotated(bd, sd, thr)
+    assert torch.all(sd[keep][:-1] > sd[keep][1:])          # score-descending
+    kept = torch.zeros(n, dtype=torch.bool, device='cuda')
+    kept[keep] = True
+    ious = rg.box_iou_rotated(bd, bd[keep])                 # (n, K)
+    higher = sd[keep][None, :] > sd[:, None]                # kept box has the higher score
+    hit_hi = ((ious >= thr + IOU_TOL) & higher).any(1)      # surely suppressed by a kept box
+    hit_lo = ((ious >= thr - IOU_TOL) & higher).any(1)      # possibly suppressed
+    assert not (kept & hit_hi).any()                        # no kept box is clearly suppressed
+    assert (kept | hit_lo).all()                            # every dropped box has a suppressor
+
+
+@pytest.mark.parametrize('dense', [True])
+def test_multiclass_nms_c2_full_dense(dense):
+    """C2 at full size: 2000 proposals x 15 classes, all classes pass (30000 candidates)."""
+    mb, ms = synth.c2_multiclass(0, n=2000, dense=dense)
+    wd, wl, wk = ref_api.multiclass_nms_rotated(torch.from_numpy(mb), torch.from_numpy(ms), 0.05, 0.1, 2000)
+    gd, gl, gk = rg.multiclass_nms_rotated(_cuda(mb), _cuda(ms), 0.05, dict(iou_thr=0.1), 2000,
+                                           return_inds=True)
+    assert gk.cpu().tolist() == wk.tolist()
+    assert torch.equal(gl.cpu(), wl) and torch.equal(gd.cpu(), wd)
+
+
+def test_batched_nms_c4_full_image():
+    """C4: one image, 5 levels x 2000 proposals, iou_threshold 0.8."""
+    boxes, scores, ids = synth.c4_rpn_image(seed=1)
+    wd, wk = ref_api.batched_nms_rotated(torch.from_numpy(boxes), torch.from_numpy(scores),
+                                         torch.from_numpy(ids), 0.8)
+    gd, gk = rg.batched_nms(_cuda(boxes), _cuda(scores), _cuda(ids),
+                            dict(type='nms_rotated', iou_threshold=0.8))
+    assert gk.cpu().tolist() == wk.tolist()
+    assert torch.equal(gd.cpu(), wd)
