@@ -16,12 +16,14 @@
 //   2. cull level 1: lane l takes row l/4 of the warp's eight and column word l%4:
 //      the 32 columns of that word the row can touch = (two table lookups OR-ed
 //      for x) AND (two for y) — ~1 instruction a pair instead of a test a pair;
-//   3. surviving pairs go to the warp's private queue (one shared atomic per lane
-//      with hits); whenever >= 32 are queued the warp pops 32 and runs the circle
-//      test + exact clipper with every lane busy, reading the two boxes' geometry
-//      planes through L1/L2, and overwrites the zeros with the non-zero values.
+//   3. surviving pairs go to the warp's first queue (ballot ranks, at most one per
+//      lane and round; fill counts are warp-uniform registers); whenever 32 are
+//      queued the warp pops them for the circle test with every lane busy, its
+//      survivors go to a second queue that is popped 32 at a time for the exact
+//      clipper, which reads the geometry planes through L1/L2 and overwrites the
+//      zeros with the non-zero values.
 // A value always lands after its zero: both stores come from the same warp with
-// a __syncwarp between (the same lane when a full queue forces the inline path).
+// a __syncwarp between.
 // Disjoint pairs cost ~1 instruction and 4 B of HBM write; the kernel is bound by
 // the HBM write stream (DESIGN.md "Kernels").
 #include "rotgeo_device.cuh"
@@ -40,19 +42,19 @@ constexpr int kWarps = kThreads / 32;
 constexpr int kRowsPerWarp = kTileRows / kWarps;  // 8
 constexpr int kStages = 4;        // mask ring
 constexpr int kRespSlots = 8;     // launch-control responses (> kStages, see the reuse argument below)
-constexpr int kQueueCap = 128;    // pairs per warp queue
+constexpr int kQueueCap = 64;     // pairs per warp queue (never more than 31 + 32 queued)
 
 static_assert(kTileCols == kBlock, "a column tile is one inverted-index block");
 
 struct __align__(16) IouSmem {
     uint32_t tab[kStages][kTableWords];
     uint32_t rowr[kStages][kTileRows];
-    int2 queue[kWarps][kQueueCap];
+    int2 queue1[kWarps][kQueueCap];   // survived the bin ranges
+    int2 queue2[kWarps][kQueueCap];   // survived the circle test as well
     uint4 resp[kRespSlots];
     uint64_t full[kStages];
     uint64_t empty[kStages];
     uint64_t sched[kRespSlots];
-    int qcount[kWarps];
 };
 
 struct IouArgs {
@@ -66,16 +68,11 @@ struct IouArgs {
     unsigned tiles_x;
 };
 
+// exact value of a pair that passed both culls; non-zero values overwrite the zero
 template <int MODE>
 __device__ __forceinline__ void emit_pair(const IouArgs &g, int row, int col) {
-#if ROTGEO_ABLATE & 32   // probe: no geometry loads
-    const float4 A0 = make_float4((float)row, 1.f, 3.f, 4.f), A1 = make_float4(1.f, 0.f, 1.f, 1.f);
-    const float4 B0 = make_float4((float)col, 1.f, 3.f, 4.f), B1 = make_float4(1.f, 0.f, 1.f, 1.f);
-    const float v = pair_value<MODE>(A0, A1, B0, B1);
-#else
-    const float v = pair_value<MODE>(__ldg(g.a0 + row), __ldg(g.a1 + row), __ldg(g.b0 + col),
-                                     __ldg(g.b1 + col));
-#endif
+    const float v = rect_overlap<MODE>(__ldg(g.a0 + row), __ldg(g.a1 + row), __ldg(g.b0 + col),
+                                       __ldg(g.b1 + col));
 #if ROTGEO_ABLATE & 16   // probe: no value stores (v == 12345 never happens)
     if (v == 12345.f) g.out[(int64_t)row * g.ld_out + col] = v;
 #else
@@ -99,7 +96,6 @@ iou_tile_kernel(const IouArgs g) {
         for (int s = 0; s < kRespSlots; ++s) mbar_init(&sm.sched[s], 1);
         fence_mbar_init();
     }
-    if (tid < kWarps) sm.qcount[tid] = 0;
     __syncthreads();
 
     auto issue_masks = [&](unsigned k, unsigned t) {   // thread 0: cull data of tile t, my k-th
@@ -122,8 +118,33 @@ iou_tile_kernel(const IouArgs g) {
         ask_next(1);
     }
 
-    int2 *const wq = sm.queue[warp];
-    int *const wqc = &sm.qcount[warp];
+    int2 *const q1 = sm.queue1[warp];
+    int2 *const q2 = sm.queue2[warp];
+    int n1 = 0, n2 = 0;                       // warp-uniform fill counts
+    const uint32_t lt = (1u << lane) - 1u;
+    auto clip32 = [&](int take) {             // pop `take` <= 32 entries of queue 2
+        if (lane < take && !(ROTGEO_ABLATE & 4)) {
+            const int2 e = q2[n2 - take + lane];
+            emit_pair<MODE>(g, e.x, e.y);
+        }
+        n2 -= take;
+        __syncwarp();
+    };
+    auto circle32 = [&](int take) {           // pop `take` <= 32 entries of queue 1
+        bool pass = false;
+        int2 e = make_int2(0, 0);
+        if (lane < take) {
+            e = q1[n1 - take + lane];
+            const float4 A0 = __ldg(g.a0 + e.x), B0 = __ldg(g.b0 + e.y);
+            pass = !circles_disjoint(A0.x, A0.y, A0.z, B0.x, B0.y, B0.z);
+        }
+        n1 -= take;
+        const uint32_t b = __ballot_sync(0xffffffffu, pass);
+        if (pass) q2[n2 + __popc(b & lt)] = e;
+        n2 += __popc(b);
+        __syncwarp();
+        if (n2 >= 32) clip32(32);
+    };
 
     // zeros of this warp's 8 x 128 strip of tile tt (independent of the cull data)
     auto store_zeros = [&](unsigned tt) {
@@ -199,21 +220,22 @@ iou_tile_kernel(const IouArgs g) {
         __syncwarp();
         if (lane == 0) mbar_arrive(&sm.empty[s]);   // this warp is done with the stage
 
-        // ---- queue the survivors -----------------------------------------------------
-        if (hits) {
-            const int cnt = __popc(hits);
-            int pos = atomicAdd(wqc, cnt);
+        // ---- survivors -> queue 1, at most one per lane and round ----------------------
+        {
             const int row = (int)row_base + warp + kWarps * rl, col0 = (int)col_base + 32 * cw;
             uint32_t m = hits;
-            while (m) {
-                const int col = col0 + __ffs(m) - 1;
-                m &= m - 1;
-                if (pos < kQueueCap) wq[pos] = make_int2(row, col);
-                else emit_pair<MODE>(g, row, col);   // queue full (its zero was stored before the __syncwarp)
-                ++pos;
+            for (;;) {
+                const uint32_t act = __ballot_sync(0xffffffffu, m != 0u);
+                if (act == 0u) break;
+                if (m) {
+                    q1[n1 + __popc(act & lt)] = make_int2(row, col0 + __ffs(m) - 1);
+                    m &= m - 1;
+                }
+                n1 += __popc(act);
+                __syncwarp();
+                if (n1 >= 32) circle32(32);
             }
         }
-        __syncwarp();
 
         // ---- next tile (or none: nothing left to steal) ---------------------------------
         unsigned tn;
@@ -222,19 +244,12 @@ iou_tile_kernel(const IouArgs g) {
         fence_proxy_async_smem();   // my read of the slot precedes its reuse by a later request
         if (more) store_zeros(tn);  // next tile's zeros are in flight while this warp clips
 
-        // ---- cull level 2 + exact clipper, 32 queued pairs at a time -----------------
-        int qn = min(*wqc, kQueueCap);
-        while (qn >= 32 || (!more && qn > 0 && !(ROTGEO_ABLATE & 8))) {
-            const int take = min(qn, 32);
-            if (lane < take && !(ROTGEO_ABLATE & 4)) {
-                const int2 e = wq[qn - take + lane];
-                emit_pair<MODE>(g, e.x, e.y);
+        if (!more) {            // last tile of this CTA: flush both queues
+            if (!(ROTGEO_ABLATE & 8)) {
+                if (n1 > 0) circle32(n1);
+                if (n2 > 0) clip32(n2);
             }
-            qn -= take;
         }
-        __syncwarp();
-        if (lane == 0) *wqc = qn;
-        __syncwarp();
         if (!more) break;
         t = tn;
     }

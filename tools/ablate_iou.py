@@ -7,7 +7,7 @@ import ctypes, os, subprocess, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 OUT = os.path.join(ROOT, 'tools', '_ablate')
-VARIANTS = {'full': 0, 'no_exact': 4, 'no_value_store': 16, 'no_geom_loads': 32, 'no_loads_no_store': 48}
+VARIANTS = {'full': 0, 'no_exact': 4, 'no_value_store': 16, 'stores_only': 6}
 if os.environ.get('ABLATE_REGS'):
     VARIANTS = {'full_r%s' % r: (0, r) for r in os.environ['ABLATE_REGS'].split(',')}
 EXTRA = [a for a in sys.argv[2:]]
