@@ -102,13 +102,15 @@ int rotgeo_iou_aligned(const float *boxes1, const float *boxes2, int64_t n, int 
  *
  *   boxes / stride    AoS rows as above (n rows)
  *   offsets           nullable float[n]: added to cx, cy (class-offset trick)
- *   order             int64[n]: indices into boxes, score-descending over ALL boxes
+ *   order             int64[n]: indices into boxes, score-descending over ALL boxes;
+ *                     nullable when seg_order is given: kept indices then come out
+ *                     in seg_order order (segment-major) and the caller re-orders
  *   seg_order         nullable int64[n]: the same indices sorted segment-major,
  *                     score-descending inside each segment (null = one segment,
  *                     `order` is used)
  *   seg_offsets_host  HOST int64[num_segments + 1]: segment boundaries in
  *                     seg_order (null when seg_order is null)
- *   keep_out          int64[n]: kept indices into boxes, in `order` order
+ *   keep_out          int64[n]: kept indices into boxes, in `order` order (see above)
  *   num_keep_out      int64[1] (device): how many were kept
  *
  * Workspace: rotgeo_nms_workspace_bytes(n, seg_offsets_host, num_segments). */
@@ -117,6 +119,37 @@ int rotgeo_nms(const float *boxes, int64_t n, int stride, const float *offsets,
                const int64_t *order, const int64_t *seg_order, const int64_t *seg_offsets_host,
                int64_t num_segments, float iou_threshold, int64_t *keep_out,
                int64_t *num_keep_out, void *workspace, size_t workspace_bytes, void *stream);
+
+/* ---- class-batched rotated NMS, fused ----------------------------------------
+ * Replaces the whole body of the reference's multiclass_nms_rotated
+ * (mmrotate/core/post_processing/bbox_nms_rotated.py:33-92, called from the eleven
+ * get_bboxes sites listed in SURVEY.md §3): candidate filter (raw score >
+ * score_thr, tested before the factors), class separation by the reference's own
+ * centre offset  label * (max(cx,cy) + max(w,h) + 1)  in fp32, greedy suppression
+ * per class (IoU >= iou_threshold), global score order, cut to max_num, and the
+ * gather of the output rows — with no device->host read inside the call.
+ *
+ *   multi_bboxes   (rows, 5) when bbox_cols == 5 (one box per row, shared by all
+ *                  classes) or (rows, 5 * num_classes) when bbox_cols == 5 * num_classes;
+ *                  contiguous
+ *   multi_scores   (rows, num_classes + 1) contiguous; the last column (background)
+ *                  is ignored
+ *   score_factors  nullable (rows,): multiplied into the scores after the filter
+ *   cap            rows of the output buffers: max_num if > 0, else rows * num_classes
+ *   dets_out       float (cap, 6): kept boxes + score, score-descending
+ *   labels_out     int64 (cap,)
+ *   keep_flat_out  int64 (cap,): row * num_classes + class of every kept candidate
+ *   num_out        int64[1] (device): how many rows were written (<= cap)
+ *
+ * num_classes <= 64 and rows * num_classes < 2^26.
+ * Workspace: rotgeo_multiclass_nms_workspace_bytes(rows, num_classes) — sized for the
+ * worst case (every class keeps every row), because no count reaches the host. */
+size_t rotgeo_multiclass_nms_workspace_bytes(int64_t rows, int num_classes);
+int rotgeo_multiclass_nms(const float *multi_bboxes, int bbox_cols, const float *multi_scores,
+                          const float *score_factors, int64_t rows, int num_classes,
+                          float score_thr, float iou_threshold, int64_t cap, float *dets_out,
+                          int64_t *labels_out, int64_t *keep_flat_out, int64_t *num_out,
+                          void *workspace, size_t workspace_bytes, void *stream);
 
 #ifdef __cplusplus
 }

@@ -14,6 +14,7 @@ SYMBOLS = (
     'rotgeo_version', 'rotgeo_last_error', 'rotgeo_packed_bytes', 'rotgeo_pack_boxes',
     'rotgeo_iou_workspace_bytes', 'rotgeo_iou_pairwise', 'rotgeo_iou_pairwise_packed',
     'rotgeo_iou_aligned', 'rotgeo_nms_workspace_bytes', 'rotgeo_nms',
+    'rotgeo_multiclass_nms_workspace_bytes', 'rotgeo_multiclass_nms',
 )
 
 _lib = None
@@ -53,6 +54,10 @@ def load():
     L.rotgeo_nms_workspace_bytes.restype = sz
     L.rotgeo_nms.argtypes = [vp, i64, i32, vp, vp, vp, vp, i64, f32, vp, vp, vp, sz, vp]
     L.rotgeo_nms.restype = i32
+    L.rotgeo_multiclass_nms_workspace_bytes.argtypes = [i64, i32]
+    L.rotgeo_multiclass_nms_workspace_bytes.restype = sz
+    L.rotgeo_multiclass_nms.argtypes = [vp, i32, vp, vp, i64, i32, f32, f32, i64, vp, vp, vp, vp, vp, sz, vp]
+    L.rotgeo_multiclass_nms.restype = i32
     _lib = L
     return L
 

@@ -59,6 +59,59 @@ def _iou_thr(nms):
     return nms.iou_thr
 
 
+_FUSED_WS_LIMIT = 2 << 30
+
+
+def _multiclass_nms_fused(multi_bboxes, multi_scores, score_thr, iou_thr, max_num, score_factors,
+                          return_inds):
+    """rotgeo_multiclass_nms; returns None when the shape is outside what it takes."""
+    from . import _lib
+    n, num_classes = multi_scores.size(0), multi_scores.size(1) - 1
+    if n == 0 or num_classes < 1 or num_classes > 64 or n * num_classes >= (1 << 26):
+        return None
+    if multi_bboxes.shape[1] not in (5, 5 * num_classes):
+        return None
+    if not multi_scores.is_cuda and not bool((multi_scores[:, :-1] > score_thr).any()):
+        return None     # host tensors without a candidate: the empty result needs no device
+    L = _lib.load()
+    nbytes = L.rotgeo_multiclass_nms_workspace_bytes(n, num_classes)
+    if nbytes == 0 or nbytes > _FUSED_WS_LIMIT:
+        return None
+    dev = ops._cuda_device(multi_bboxes, multi_scores)
+    mb = multi_bboxes.detach().to(device=dev, dtype=torch.float32).contiguous()
+    ms = multi_scores.detach().to(device=dev, dtype=torch.float32).contiguous()
+    sf = None
+    if score_factors is not None:
+        sf = score_factors.detach().to(device=dev, dtype=torch.float32).reshape(-1).contiguous()
+    cap = min(max_num, n * num_classes) if max_num > 0 else n * num_classes
+    with torch.cuda.device(dev):
+        ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+        dets = torch.empty((cap, 6), dtype=torch.float32, device=dev)
+        labels = torch.empty((cap,), dtype=torch.int64, device=dev)
+        flat = torch.empty((cap,), dtype=torch.int64, device=dev)
+        num = torch.empty(1, dtype=torch.int64, device=dev)
+        _lib.check(L.rotgeo_multiclass_nms(mb.data_ptr(), mb.shape[1], ms.data_ptr(),
+                                           sf.data_ptr() if sf is not None else None, n, num_classes,
+                                           float(score_thr), float(iou_thr), cap, dets.data_ptr(),
+                                           labels.data_ptr(), flat.data_ptr(), num.data_ptr(),
+                                           ws.data_ptr(), nbytes, ops._stream(dev)),
+                   'rotgeo_multiclass_nms')
+        k = int(num.item())        # the one device->host read: sizes the outputs
+    dets, labels = dets[:k], labels[:k]
+    if dets.dtype != multi_bboxes.dtype:
+        dets = dets.to(multi_bboxes.dtype)
+    if dets.device != multi_bboxes.device:
+        dets, labels = dets.to(multi_bboxes.device), labels.to(multi_bboxes.device)
+    if not return_inds:
+        return dets, labels
+    # `keep` of the reference indexes the FILTERED candidate array (row-major order of the
+    # candidates): rank of the kept flat index among the valid ones
+    valid = (ms[:, :-1] > score_thr).reshape(-1)
+    rank = torch.cumsum(valid, 0) - 1
+    keep = rank[flat[:k]].to(multi_bboxes.device)
+    return dets, labels, keep
+
+
 def multiclass_nms_rotated(multi_bboxes, multi_scores, score_thr, nms, max_num=-1,
                            score_factors=None, return_inds=False):
     """Class-batched rotated NMS, same contract as reference
@@ -71,27 +124,41 @@ def multiclass_nms_rotated(multi_bboxes, multi_scores, score_thr, nms, max_num=-
     the reference does — ``label * (max(cx,cy) + max(w,h) + 1)`` added to cx, cy
     in float32 — but the add happens inside the pack kernel and the labels also
     segment the suppression mask, so only same-class tiles are ever computed.
+
+    The whole body runs as ONE C-ABI call (rotgeo_multiclass_nms: candidate filter,
+    sort keys, two radix sorts, device-side plan, pack, mask, scan, emit + output
+    gather) and one device->host read of the kept count; the step-by-step torch
+    version below it is used only for shapes the fused call does not take
+    (more than 64 classes, or a worst-case workspace above 2 GiB).
     """
+    fused = _multiclass_nms_fused(multi_bboxes, multi_scores, score_thr, _iou_thr(nms), max_num,
+                                  score_factors, return_inds)
+    if fused is not None:
+        return fused
+
     num_classes = multi_scores.size(1) - 1
-    if multi_bboxes.shape[1] > 5:
-        bboxes = multi_bboxes.view(multi_scores.size(0), -1, 5)
+    n = multi_scores.size(0)
+    scores2d = multi_scores[:, :-1]
+    # candidates: raw score above the threshold (score_factors are applied afterwards, like
+    # the reference does).  The per-class counts double as the NMS segment sizes, so ONE
+    # device->host read replaces the reference's nonzero() sync and sizes everything.
+    valid_mask = scores2d > score_thr
+    counts_host = valid_mask.sum(0).cpu().numpy().astype(np.int64)
+    total = int(counts_host.sum())
+    flat_valid = valid_mask.reshape(-1)
+    if hasattr(torch, 'nonzero_static'):
+        inds = torch.nonzero_static(flat_valid, size=total).squeeze(1)
     else:
-        bboxes = multi_bboxes[:, None].expand(multi_scores.size(0), num_classes, 5)
-    scores = multi_scores[:, :-1]
-
-    labels = torch.arange(num_classes, dtype=torch.long, device=scores.device)
-    labels = labels.view(1, -1).expand_as(scores)
-    bboxes = bboxes.reshape(-1, 5)
-    scores = scores.reshape(-1)
-    labels = labels.reshape(-1)
-
-    valid_mask = scores > score_thr
+        inds = flat_valid.nonzero(as_tuple=False).squeeze(1)
+    rows = torch.div(inds, num_classes, rounding_mode='floor')
+    labels = inds - rows * num_classes
+    if multi_bboxes.shape[1] > 5:
+        bboxes = multi_bboxes.view(n, -1, 5).reshape(-1, 5)[inds]
+    else:
+        bboxes = multi_bboxes[rows]          # the (n, C, 5) expansion is never materialised
+    scores = scores2d.reshape(-1)[inds]
     if score_factors is not None:
-        score_factors = score_factors.view(-1, 1).expand(multi_scores.size(0), num_classes)
-        scores = scores * score_factors.reshape(-1)
-
-    inds = valid_mask.nonzero(as_tuple=False).squeeze(1)
-    bboxes, scores, labels = bboxes[inds], scores[inds], labels[inds]
+        scores = scores * score_factors.view(-1)[rows]
 
     if bboxes.numel() == 0:
         dets = torch.cat([bboxes, scores[:, None]], -1)
@@ -99,7 +166,8 @@ def multiclass_nms_rotated(multi_bboxes, multi_scores, score_thr, nms, max_num=-
 
     max_coordinate = bboxes[:, :2].max() + bboxes[:, 2:4].max()
     offsets = labels.to(bboxes) * (max_coordinate + 1)
-    keep = ops._nms_keep(bboxes, scores, _iou_thr(nms), seg_ids=labels, offsets=offsets)
+    keep = ops._nms_keep(bboxes, scores, _iou_thr(nms), seg_ids=labels, offsets=offsets,
+                         seg_counts_host=counts_host)
     keep = keep.to(bboxes.device)
 
     if max_num > 0:
@@ -189,7 +257,7 @@ def merge_results(results, offsets, img_shape, iou_thr=0.1, device='cpu'):
         dev = ops._cuda_device()
         d = torch.from_numpy(np.ascontiguousarray(allc)).to(dev)
         s = torch.from_numpy(seg).to(dev)
-        keep = ops._nms_keep(d[:, :5], d[:, 5], iou_thr, seg_ids=s)
+        keep = ops._nms_keep(d[:, :5], d[:, 5], iou_thr, seg_ids=s, seg_counts_host=np.asarray(counts))
         keep = keep[torch.sort(s[keep], stable=True).indices]       # class-major, score-desc inside
         kept = d[keep].cpu().numpy()
         kseg = s[keep].cpu().numpy()

@@ -70,7 +70,7 @@ int rotgeo_iou_pairwise_packed(const void *packed1, int64_t n1, const void *pack
     if (!packed1 || !packed2 || !out) return fail(ROTGEO_ERR_ARG, "iou: null pointer");
     if (!aligned16(packed1) || !aligned16(packed2))
         return fail(ROTGEO_ERR_ARG, "iou: packed buffers must be 16-byte aligned");
-    const int rc = rotgeo::launch_iou_pairwise(packed1, n1, packed2, n2, mode, out, ld_out,
+    const int rc = rotgeo::launch_iou_pairwise(packed1, n1, packed2, n2, mode, out, ld_out, false,
                                                (cudaStream_t)stream);
     if (rc == -1) return fail(ROTGEO_ERR_ARG, "iou: too many tiles");
     if (rc) return cuda_fail("iou launch");
@@ -99,7 +99,12 @@ int rotgeo_iou_pairwise(const float *boxes1, int64_t n1, int stride1, const floa
     const rotgeo::PackSet s2 = rotgeo::make_pack_set(boxes2, n2, stride2, nullptr, nullptr, pk2,
                                                      rotgeo::padded_count(n2));
     if (rotgeo::launch_pack(s1, s2, min_wh, 0.f, (cudaStream_t)stream)) return cuda_fail("pack launch");
-    return rotgeo_iou_pairwise_packed(pk1, n1, pk2, n2, mode, out, ld_out, stream);
+    // the tile kernel starts streaming zeros while the pack kernel is still running
+    const int rc = rotgeo::launch_iou_pairwise(pk1, n1, pk2, n2, mode, out, ld_out, true,
+                                               (cudaStream_t)stream);
+    if (rc == -1) return fail(ROTGEO_ERR_ARG, "iou: too many tiles");
+    if (rc) return cuda_fail("iou launch");
+    return ROTGEO_OK;
 }
 
 int rotgeo_iou_aligned(const float *boxes1, const float *boxes2, int64_t n, int stride1,
@@ -133,7 +138,7 @@ int rotgeo_nms(const float *boxes, int64_t n, int stride, const float *offsets,
             return cuda_fail("nms memset");
         return ROTGEO_OK;
     }
-    if (!boxes || !order || !keep_out) return fail(ROTGEO_ERR_ARG, "nms: null pointer");
+    if (!boxes || !keep_out || (!order && !seg_order)) return fail(ROTGEO_ERR_ARG, "nms: null pointer");
     const bool segmented = seg_order != nullptr;
     if (segmented) {
         if (!seg_offsets_host || num_segments < 1)
@@ -177,10 +182,54 @@ int rotgeo_nms(const float *boxes, int64_t n, int stride, const float *offsets,
         const rotgeo::PackSet none = rotgeo::make_pack_set(nullptr, 0, 5, nullptr, nullptr, nullptr, 0);
         if (rotgeo::launch_pack(s1, none, 0.f, 0.f, st)) return cuda_fail("nms pack launch");
     }
+    // no global order given: kept indices come out segment-major (the caller re-orders)
+    if (!order) order = sorder;
     const int rc = rotgeo::launch_nms(plan, packed, segs_dev, max_words, order, sorder,
                                       iou_threshold, mask, flags, keep_out, num_keep_out, st);
     if (rc == -1) return fail(ROTGEO_ERR_ARG, "nms: too many tiles");
     if (rc) return cuda_fail("nms launch");
+    return ROTGEO_OK;
+}
+
+size_t rotgeo_multiclass_nms_workspace_bytes(int64_t rows, int num_classes) {
+    if (rows <= 0 || num_classes <= 0 || num_classes > rotgeo::kMcMaxClasses) return 0;
+    return rotgeo::multiclass_nms_workspace_bytes(rows, num_classes);
+}
+
+int rotgeo_multiclass_nms(const float *multi_bboxes, int bbox_cols, const float *multi_scores,
+                          const float *score_factors, int64_t rows, int num_classes,
+                          float score_thr, float iou_threshold, int64_t cap, float *dets_out,
+                          int64_t *labels_out, int64_t *keep_flat_out, int64_t *num_out,
+                          void *workspace, size_t workspace_bytes, void *stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    if (rows < 0 || num_classes < 1 || num_classes > rotgeo::kMcMaxClasses ||
+        (bbox_cols != 5 && bbox_cols != 5 * num_classes) || cap < 0)
+        return fail(ROTGEO_ERR_ARG, "multiclass_nms: rows=%lld classes=%d bbox_cols=%d cap=%lld",
+                    (long long)rows, num_classes, bbox_cols, (long long)cap);
+    if (rows * num_classes >= (1ll << 26))
+        return fail(ROTGEO_ERR_ARG, "multiclass_nms: rows * classes must stay below 2^26");
+    if (!num_out) return fail(ROTGEO_ERR_ARG, "multiclass_nms: null num_out");
+    if (rows == 0 || cap == 0) {
+        if (cudaMemsetAsync(num_out, 0, sizeof(int64_t), st) != cudaSuccess)
+            return cuda_fail("multiclass_nms memset");
+        return ROTGEO_OK;
+    }
+    if (!multi_bboxes || !multi_scores || !dets_out || !labels_out || !keep_flat_out)
+        return fail(ROTGEO_ERR_ARG, "multiclass_nms: null pointer");
+    const size_t need = rotgeo::multiclass_nms_workspace_bytes(rows, num_classes);
+    if (!workspace || !aligned16(workspace) || workspace_bytes < need)
+        return fail(ROTGEO_ERR_WORKSPACE, "multiclass_nms: workspace %zu < %zu bytes or misaligned",
+                    workspace_bytes, need);
+    if (rotgeo::nms_scan_smem_bytes((int)(2 * ((rows + 127) / 128))) > 224 * 1024)
+        return fail(ROTGEO_ERR_ARG, "multiclass_nms: too many rows for one segment");
+    const int shared = bbox_cols == 5 ? 1 : 0;   // one box per row, used by every class
+    const int rc = rotgeo::launch_multiclass_nms(multi_bboxes, shared, multi_scores, score_factors,
+                                                 rows, num_classes, score_thr, iou_threshold, cap,
+                                                 dets_out, labels_out, keep_flat_out, num_out,
+                                                 workspace, workspace_bytes, st);
+    if (rc == -1) return fail(ROTGEO_ERR_ARG, "multiclass_nms: too many tiles");
+    if (rc == -2) return fail(ROTGEO_ERR_WORKSPACE, "multiclass_nms: workspace too small");
+    if (rc) return cuda_fail("multiclass_nms launch");
     return ROTGEO_OK;
 }
 

@@ -251,6 +251,18 @@ __device__ __forceinline__ void tma_load_1d(void *dst_smem, const void *src_gmem
         : "memory");
 }
 
+// ---- programmatic dependent launch ---------------------------------------------------
+// A kernel launched with the programmatic-stream-serialization attribute may start
+// while its predecessor in the stream is still running (once every CTA of the
+// predecessor has called pdl_launch_dependents or exited); pdl_wait blocks until the
+// predecessor has completed and its writes are visible.  Both are no-ops otherwise.
+__device__ __forceinline__ void pdl_launch_dependents() {
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+__device__ __forceinline__ void pdl_wait() {
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+
 // ---- cluster launch control (sm_100 work stealing) ------------------------------
 // A running CTA asks the hardware scheduler to cancel the launch of a CTA of the
 // same grid that has not started yet and takes over its blockIdx: persistent CTAs

@@ -28,6 +28,14 @@ struct PackSet {
     const float *offsets;    // nullable: added to cx, cy, indexed like the source rows
     const NmsSegment *segs;  // nullable: segmented slot layout (see slot_source)
     int nseg;
+    // device-planned sets (fused front-ends): the box count lives on the device, and gather[]
+    // holds FLAT candidate indices row * mc_classes + class of a (rows x classes) score matrix
+    const int64_t *n_dev;    // nullable: overrides n
+    int64_t gather_mask;     // gather[] entries are sort keys: index = entry & gather_mask
+    int mc_classes;          // 0: gather[] holds source rows
+    int mc_shared;           // 1: boxes (rows, 5) shared by all classes; 0: (rows * classes, 5)
+    const float *mc_max;     // device float[2]: max(cx, cy), max(w, h) of the candidates; the class
+                             // offset is class * (mc_max[0] + mc_max[1] + 1), bbox_nms_rotated.py:73-77
     float4 *p0, *p1;
     uint2 *pm;
     uint32_t *pr, *pt;
@@ -40,8 +48,9 @@ PackSet make_pack_set(const float *boxes, int64_t n, int stride, const int64_t *
 int launch_pack(const PackSet &s1, const PackSet &s2, float min_wh, float cell,
                 cudaStream_t stream);
 
+// after_pack: the pack kernel of these sets was the previous launch on `stream`
 int launch_iou_pairwise(const void *packed1, int64_t n1, const void *packed2, int64_t n2, int mode,
-                        float *out, int64_t ld_out, cudaStream_t stream);
+                        float *out, int64_t ld_out, bool after_pack, cudaStream_t stream);
 
 int launch_iou_aligned(const float *boxes1, const float *boxes2, int64_t n, int stride1,
                        int stride2, int mode, float min_wh, float *out, cudaStream_t stream);
@@ -59,11 +68,54 @@ struct NmsPlan {
 void nms_plan(int64_t n, const int64_t *seg_offsets_host, int64_t num_segments, NmsPlan *plan,
               NmsSegment *segments_out /* nullable, num_segments entries */);
 
+constexpr int kMcMaxClasses = 64;   // classes the fused multiclass front-end supports
+
+// fused output of the multiclass front-end: rows of (box, score) + labels of the kept candidates
+struct McOut {
+    const float *boxes;      // (rows, 5) if shared else (rows * classes, 5), contiguous
+    const float *scores;     // (rows, score_stride) raw scores
+    const float *factors;    // nullable (rows,)
+    int classes, score_stride, shared;
+    float *dets_out;         // (cap, 6)
+    int64_t *labels_out;     // (cap,)
+    int64_t cap;             // keep at most this many (max_num)
+};
+
 size_t nms_scan_smem_bytes(int max_words);   // dynamic shared memory of nms_scan_kernel
 
 int launch_nms(const NmsPlan &plan, const void *packed, const NmsSegment *segments_dev,
                int max_words, const int64_t *order, const int64_t *seg_order, float thr,
                uint64_t *mask, uint8_t *flags, int64_t *keep_out, int64_t *num_keep_out,
                cudaStream_t stream);
+
+// NMS over a plan made on the DEVICE (fused front-ends): grids and buffers are sized for
+// host-side upper bounds, the kernels read the actual counts from device memory.
+struct NmsDevLaunch {
+    const void *packed;
+    int64_t n_pad_bound;              // packed slots allocated
+    const NmsSegment *segs_dev;
+    int nseg;
+    int64_t tiles_bound;              // mask grid
+    const int64_t *total_tiles_dev;   // actual tile count
+    int max_words_bound;              // mask words per row of the largest possible segment
+    const int64_t *order;             // global score order (entries & idx_mask = box index)
+    const int64_t *seg_order;         // segment-major order (same encoding)
+    int64_t idx_mask;
+    int64_t n_bound;
+    const int64_t *n_dev;             // actual candidate count
+    float thr;
+    uint64_t *mask;
+    uint8_t *flags;
+    int64_t *keep_out, *num_keep_out;
+    McOut mc;
+};
+int launch_nms_device_planned(const NmsDevLaunch &a, cudaStream_t stream);
+
+int launch_multiclass_nms(const float *multi_bboxes, int shared, const float *multi_scores,
+                          const float *score_factors, int64_t rows, int classes, float score_thr,
+                          float iou_threshold, int64_t cap, float *dets_out, int64_t *labels_out,
+                          int64_t *keep_flat_out, int64_t *num_out, void *workspace,
+                          size_t workspace_bytes, cudaStream_t stream);
+size_t multiclass_nms_workspace_bytes(int64_t rows, int classes);
 
 }  // namespace rotgeo

@@ -113,10 +113,6 @@ iou_tile_kernel(const IouArgs g) {
         clc_try_cancel(&sm.resp[slot], &sm.sched[slot]);
     };
     unsigned t = blockIdx.x;       // my tile k = 0 is my own launch
-    if (tid == 0) {
-        issue_masks(0, t);
-        ask_next(1);
-    }
 
     int2 *const q1 = sm.queue1[warp];
     int2 *const q2 = sm.queue2[warp];
@@ -177,6 +173,13 @@ iou_tile_kernel(const IouArgs g) {
         }
     };
     store_zeros(t);   // the zeros always run one tile ahead of the cull
+    // everything below reads the packed sets: when launched as a programmatic dependent of
+    // the pack kernel, the first tile's zeros above overlap it
+    pdl_wait();
+    if (tid == 0) {
+        issue_masks(0, t);
+        ask_next(1);
+    }
 
     for (unsigned k = 0;; ++k) {
         const int s = k % kStages;
@@ -256,7 +259,7 @@ iou_tile_kernel(const IouArgs g) {
 }
 
 int launch_iou_pairwise(const void *packed1, int64_t n1, const void *packed2, int64_t n2, int mode,
-                        float *out, int64_t ld_out, cudaStream_t stream) {
+                        float *out, int64_t ld_out, bool after_pack, cudaStream_t stream) {
     if (n1 == 0 || n2 == 0) return 0;
     if (n1 > 0x7fffffffLL || n2 > 0x7fffffffLL) return -1;
     const PackedView A = packed_view(packed1, padded_count(n1));
@@ -274,7 +277,16 @@ int launch_iou_pairwise(const void *packed1, int64_t n1, const void *packed2, in
     g.out = out; g.ld_out = ld_out;
     g.tiles_x = (unsigned)tiles_x;
     // one CTA per tile; running CTAs steal the not-yet-launched ones (launch control)
-    kern<<<(unsigned)tiles, kThreads, 0, stream>>>(g);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)tiles);
+    cfg.blockDim = dim3(kThreads);
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = after_pack ? 1 : 0;   // overlap with the pack kernel launched just before
+    if (cudaLaunchKernelEx(&cfg, kern, g) != cudaSuccess) return -3;
     return cudaGetLastError() == cudaSuccess ? 0 : -3;
 }
 

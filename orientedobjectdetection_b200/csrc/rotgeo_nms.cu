@@ -76,6 +76,7 @@ struct MaskArgs {
     int nseg;
     float thr;
     unsigned long long *mask;
+    const int64_t *total_tiles;   // nullable: device-planned launch, tile ids >= *total_tiles do not exist
 };
 
 // tile id -> (segment, I, J): tiles of a segment are numbered row block by row block
@@ -137,10 +138,11 @@ nms_mask_kernel(const MaskArgs g) {
         clc_try_cancel(&sm.resp[slot], &sm.sched[slot]);
     };
     if (tid == 0) {
-        const TileInfo t0 = locate_tile(g.segs, g.nseg, blockIdx.x);
+        TileInfo t0;
+        t0.valid = 0; t0.seg = 0; t0.I = 0; t0.J = 0;
+        if (!g.total_tiles || (int64_t)blockIdx.x < *g.total_tiles)
+            t0 = locate_tile(g.segs, g.nseg, blockIdx.x);
         sm.info[0] = t0;
-        issue_cull_data(0, t0);
-        ask_next(1);
         mbar_arrive(&sm.ready[0]);
     }
 
@@ -180,12 +182,30 @@ nms_mask_kernel(const MaskArgs g) {
 
     mbar_wait(&sm.ready[0], 0);
     TileInfo ti = sm.info[0];
+    if (!ti.valid) return;       // launched past the device-side tile count
 
     for (unsigned k = 0;; ++k) {
         const int s = k % kStages;
         const NmsSegment sg = g.segs[ti.seg];
         const int L = (int)sg.len, W = sg.words;
         const int row_base = ti.I * kTile, col_base = ti.J * kTile;   // positions inside the segment
+
+        // ---- zeros of this warp's 16 rows of the tile (two mask words a row) ---------------
+        if (lane < 16) {
+            const int r = row_base + warp + kWarps * lane;
+            if (r < L)
+                *reinterpret_cast<uint4 *>(g.mask + sg.mask_base + (int64_t)r * W + 2 * ti.J) =
+                    make_uint4(0u, 0u, 0u, 0u);
+        }
+        if (k == 0) {
+            // everything below reads the packed set: as a programmatic dependent of the pack
+            // kernel, this CTA's first zeros overlapped it
+            pdl_wait();
+            if (tid == 0) {
+                issue_cull_data(0, ti);
+                ask_next(1);
+            }
+        }
 
         // ---- scheduler: learn tile k+1, prefetch its cull data, ask for k+2, publish ---------
         if (tid == 0) {
@@ -194,7 +214,8 @@ nms_mask_kernel(const MaskArgs g) {
             unsigned tn;
             TileInfo nx;
             nx.valid = 0; nx.seg = 0; nx.I = 0; nx.J = 0;
-            if (clc_decode(&sm.resp[k % kInfoSlots], tn)) {
+            if (clc_decode(&sm.resp[k % kInfoSlots], tn) &&
+                (!g.total_tiles || (int64_t)tn < *g.total_tiles)) {
                 nx = locate_tile(g.segs, g.nseg, tn);
                 // ring stage of tile k+1 was last read for tile k+1-kStages: wait until every
                 // warp left it; they then also left descriptor / response slots that old
@@ -205,14 +226,6 @@ nms_mask_kernel(const MaskArgs g) {
             }
             sm.info[kn % kInfoSlots] = nx;
             mbar_arrive(&sm.ready[kn % kInfoSlots]);
-        }
-
-        // ---- zeros of this warp's 16 rows of the tile (two mask words a row) ---------------
-        if (lane < 16) {
-            const int r = row_base + warp + kWarps * lane;
-            if (r < L)
-                *reinterpret_cast<uint4 *>(g.mask + sg.mask_base + (int64_t)r * W + 2 * ti.J) =
-                    make_uint4(0u, 0u, 0u, 0u);
         }
 
         // ---- cull level 1: per (row, 32-column word) two range-OR lookups per axis -----------
@@ -303,7 +316,7 @@ __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_gr
 template <bool EMIT>
 __global__ void __launch_bounds__(kScanThreads)
 nms_scan_kernel(const NmsSegment *__restrict__ segs, const unsigned long long *__restrict__ mask,
-                const int64_t *__restrict__ seg_order, uint8_t *__restrict__ flags,
+                const int64_t *__restrict__ seg_order, int64_t idx_mask, uint8_t *__restrict__ flags,
                 int64_t *__restrict__ keep_out, int64_t *__restrict__ num_keep_out) {
     extern __shared__ __align__(16) unsigned long long dyn[];
     unsigned long long *const panel0 = dyn;
@@ -379,11 +392,11 @@ nms_scan_kernel(const NmsSegment *__restrict__ segs, const unsigned long long *_
                 if (k0) s_rows[base + rk0] = r0 + q0;
                 if (k1) s_rows[base + rk1] = r0 + q1;
                 if (EMIT) {
-                    if (k0) keep_out[nkeep + rk0] = seg_order[seg.start + r0 + q0];
-                    if (k1) keep_out[nkeep + rk1] = seg_order[seg.start + r0 + q1];
+                    if (k0) keep_out[nkeep + rk0] = seg_order[seg.start + r0 + q0] & idx_mask;
+                    if (k1) keep_out[nkeep + rk1] = seg_order[seg.start + r0 + q1] & idx_mask;
                 } else {
-                    if (r0 + q0 < L) flags[seg_order[seg.start + r0 + q0]] = k0 ? 1 : 0;
-                    if (r0 + q1 < L) flags[seg_order[seg.start + r0 + q1]] = k1 ? 1 : 0;
+                    if (r0 + q0 < L) flags[seg_order[seg.start + r0 + q0] & idx_mask] = k0 ? 1 : 0;
+                    if (r0 + q1 < L) flags[seg_order[seg.start + r0 + q1] & idx_mask] = k1 ? 1 : 0;
                 }
                 __syncwarp();
                 if (lane == 0) {
@@ -430,19 +443,23 @@ nms_scan_kernel(const NmsSegment *__restrict__ segs, const unsigned long long *_
 constexpr int kEmitThreads = 1024;
 constexpr int kEmitItems = 8;
 
+template <bool MC>
 __global__ void __launch_bounds__(kEmitThreads)
 nms_emit_kernel(const int64_t *__restrict__ order, const uint8_t *__restrict__ flags, int64_t n,
-                int64_t *__restrict__ keep_out, int64_t *__restrict__ num_keep_out) {
+                const int64_t *__restrict__ n_dev, int64_t idx_mask, int64_t *__restrict__ keep_out,
+                int64_t *__restrict__ num_keep_out, const McOut mc) {
     __shared__ int warp_cnt[32];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (n_dev) n = *n_dev;
+    const int64_t cap = MC ? mc.cap : n;
     int64_t base = 0;
-    for (int64_t start = 0; start < n; start += kEmitThreads * kEmitItems) {
+    for (int64_t start = 0; start < n && base < cap; start += kEmitThreads * kEmitItems) {
         const int64_t i0 = start + (int64_t)tid * kEmitItems;
         int64_t idx[kEmitItems];
         unsigned f = 0;
 #pragma unroll
         for (int k = 0; k < kEmitItems; ++k) {
-            idx[k] = i0 + k < n ? order[i0 + k] : -1;
+            idx[k] = i0 + k < n ? (order[i0 + k] & idx_mask) : -1;
         }
 #pragma unroll
         for (int k = 0; k < kEmitItems; ++k)
@@ -465,12 +482,27 @@ nms_emit_kernel(const int64_t *__restrict__ order, const uint8_t *__restrict__ f
         }
         int64_t pos = base + before + incl - cnt;
 #pragma unroll
-        for (int k = 0; k < kEmitItems; ++k)
-            if (f & (1u << k)) keep_out[pos++] = idx[k];
+        for (int k = 0; k < kEmitItems; ++k) {
+            if ((f & (1u << k)) && pos < cap) {
+                keep_out[pos] = idx[k];
+                if (MC) {
+                    // the output row of a kept candidate: its box, its (factored) score, its class
+                    const int64_t row = idx[k] / mc.classes;
+                    const int cls = (int)(idx[k] - row * mc.classes);
+                    const float *bx = mc.boxes + (mc.shared ? row : idx[k]) * 5;
+                    float sc = mc.scores[row * mc.score_stride + cls];
+                    if (mc.factors) sc *= mc.factors[row];
+                    float *d = mc.dets_out + pos * 6;
+                    d[0] = bx[0]; d[1] = bx[1]; d[2] = bx[2]; d[3] = bx[3]; d[4] = bx[4]; d[5] = sc;
+                    mc.labels_out[pos] = cls;
+                }
+            }
+            if (f & (1u << k)) ++pos;
+        }
         base += total;
         __syncthreads();
     }
-    if (tid == 0) *num_keep_out = base;
+    if (tid == 0) *num_keep_out = base < cap ? base : cap;
 }
 
 // ---- host-side plan + launch -------------------------------------------------------
@@ -532,8 +564,18 @@ int launch_nms(const NmsPlan &plan, const void *packed, const NmsSegment *segmen
         g.nseg = (int)plan.num_segments;
         g.thr = thr;
         g.mask = reinterpret_cast<unsigned long long *>(mask);
+        g.total_tiles = nullptr;
         // one CTA per tile; running CTAs steal the not-yet-launched ones (launch control)
-        nms_mask_kernel<<<(unsigned)plan.total_tiles, kThreads, 0, stream>>>(g);
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3((unsigned)plan.total_tiles);
+        cfg.blockDim = dim3(kThreads);
+        cfg.stream = stream;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[0].val.programmaticStreamSerializationAllowed = 1;   // overlap with the pack kernel
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        if (cudaLaunchKernelEx(&cfg, nms_mask_kernel, g) != cudaSuccess) return -3;
     }
     if (cudaGetLastError() != cudaSuccess) return -3;
     const size_t dyn = nms_scan_smem_bytes(max_words);
@@ -543,18 +585,59 @@ int launch_nms(const NmsPlan &plan, const void *packed, const NmsSegment *segmen
                                  (int)dyn) != cudaSuccess)
             return -3;
         nms_scan_kernel<true><<<1, kScanThreads, dyn, stream>>>(
-            segments_dev, reinterpret_cast<const unsigned long long *>(mask), seg_order, flags,
+            segments_dev, reinterpret_cast<const unsigned long long *>(mask), seg_order, ~0ll, flags,
             keep_out, num_keep_out);
     } else {
         if (cudaFuncSetAttribute(nms_scan_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)dyn) != cudaSuccess)
             return -3;
         nms_scan_kernel<false><<<(unsigned)plan.num_segments, kScanThreads, dyn, stream>>>(
-            segments_dev, reinterpret_cast<const unsigned long long *>(mask), seg_order, flags,
+            segments_dev, reinterpret_cast<const unsigned long long *>(mask), seg_order, ~0ll, flags,
             keep_out, num_keep_out);
         if (cudaGetLastError() != cudaSuccess) return -3;
-        nms_emit_kernel<<<1, kEmitThreads, 0, stream>>>(order, flags, plan.n, keep_out, num_keep_out);
+        McOut none = {};
+        nms_emit_kernel<false><<<1, kEmitThreads, 0, stream>>>(order, flags, plan.n, nullptr, ~0ll,
+                                                              keep_out, num_keep_out, none);
     }
+    return cudaGetLastError() == cudaSuccess ? 0 : -3;
+}
+
+int launch_nms_device_planned(const NmsDevLaunch &a, cudaStream_t stream) {
+    const PackedView P = packed_view(a.packed, a.n_pad_bound);
+    if (a.tiles_bound > 0x7fffffffLL) return -1;
+    if (a.tiles_bound > 0) {
+        MaskArgs g;
+        g.p0 = P.p0; g.p1 = P.p1; g.pr = P.pr; g.pt = P.pt;
+        g.segs = a.segs_dev;
+        g.nseg = a.nseg;
+        g.thr = a.thr;
+        g.mask = reinterpret_cast<unsigned long long *>(a.mask);
+        g.total_tiles = a.total_tiles_dev;
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3((unsigned)a.tiles_bound);
+        cfg.blockDim = dim3(kThreads);
+        cfg.stream = stream;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[0].val.programmaticStreamSerializationAllowed = 1;   // overlap with the pack kernel
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        if (cudaLaunchKernelEx(&cfg, nms_mask_kernel, g) != cudaSuccess) return -3;
+    }
+    const size_t dyn = nms_scan_smem_bytes(a.max_words_bound);
+    if (cudaFuncSetAttribute(nms_scan_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (int)dyn) != cudaSuccess)
+        return -3;
+    nms_scan_kernel<false><<<(unsigned)a.nseg, kScanThreads, dyn, stream>>>(
+        a.segs_dev, reinterpret_cast<const unsigned long long *>(a.mask), a.seg_order, a.idx_mask,
+        a.flags, a.keep_out, a.num_keep_out);
+    if (cudaGetLastError() != cudaSuccess) return -3;
+    if (a.mc.dets_out)
+        nms_emit_kernel<true><<<1, kEmitThreads, 0, stream>>>(a.order, a.flags, a.n_bound, a.n_dev,
+                                                             a.idx_mask, a.keep_out, a.num_keep_out, a.mc);
+    else
+        nms_emit_kernel<false><<<1, kEmitThreads, 0, stream>>>(a.order, a.flags, a.n_bound, a.n_dev,
+                                                              a.idx_mask, a.keep_out, a.num_keep_out, a.mc);
     return cudaGetLastError() == cudaSuccess ? 0 : -3;
 }
 

@@ -28,11 +28,11 @@ __device__ __forceinline__ float warp_max(float v) {
     return v;
 }
 
-// source row of slot i of a set, or -1 for padding.  Plain sets: slot i = box i
-// (through `gather`).  Segmented sets (NMS): every segment starts at a slot that is
+// position (index into gather[]) of slot i of a set, or -1 for padding.  Plain sets:
+// slot i = position i.  Segmented sets (NMS): every segment starts at a slot that is
 // a multiple of 128 (so each 128-slot table block lies inside one segment) and is
-// padded up to the next one.
-__device__ __forceinline__ int64_t slot_source(const PackSet &s, int64_t i) {
+// padded up to the next one; slots past the last segment are padding too.
+__device__ __forceinline__ int64_t slot_position(const PackSet &s, int64_t i, int64_t n) {
     if (s.segs) {
         int lo = 0, hi = s.nseg - 1;   // last segment with pstart <= i
         while (lo < hi) {
@@ -41,11 +41,23 @@ __device__ __forceinline__ int64_t slot_source(const PackSet &s, int64_t i) {
         }
         const int64_t pos = i - s.segs[lo].pstart;
         if (pos >= s.segs[lo].len) return -1;
-        i = s.segs[lo].start + pos;
-    } else if (i >= s.n) {
-        return -1;
+        return s.segs[lo].start + pos;
     }
-    return s.gather ? s.gather[i] : i;
+    return i < n ? i : -1;
+}
+
+// source row of position `pos` and the centre offset that goes with it
+__device__ __forceinline__ int64_t position_source(const PackSet &s, int64_t pos, float &offset) {
+    const int64_t v = s.gather ? (s.gather[pos] & s.gather_mask) : pos;
+    offset = 0.f;
+    if (s.mc_classes > 0) {
+        const int64_t row = v / s.mc_classes;
+        const int cls = (int)(v - row * s.mc_classes);
+        offset = (float)cls * ((s.mc_max[0] + s.mc_max[1]) + 1.f);
+        return s.mc_shared ? row : v;
+    }
+    if (s.offsets) offset = s.offsets[v];
+    return v;
 }
 
 // 1 / (bin width): identical in every CTA of the launch.  Every CTA reduces the
@@ -54,14 +66,17 @@ __device__ float sample_inv_cell(const PackSet &s1, const PackSet &s2) {
     __shared__ float red[4][kPackThreads / 32];
     const int tid = threadIdx.x;
     const bool two = s2.n > 0;
+    const int64_t n1 = s1.n_dev ? *s1.n_dev : s1.n;
     // first half of the block samples set 1, second half set 2 (all of it set 1 if alone)
     const PackSet s = (two && tid >= kPackThreads / 2) ? s2 : s1;
     const int slots = two ? kPackThreads / 2 : kPackThreads;
     const int t = two ? (tid & (kPackThreads / 2 - 1)) : tid;
     float lo_x = INFINITY, hi_x = -INFINITY, lo_y = INFINITY, hi_y = -INFINITY;
-    if (s.n > 0) {
-        const int64_t i = (s.n >= slots) ? (int64_t)t * (s.n / slots) : (t % s.n);
-        const float *b = s.boxes + (s.gather ? s.gather[i] : i) * s.stride;
+    const int64_t sn = (two && tid >= kPackThreads / 2) ? s2.n : n1;   // only set 1 is ever device-counted
+    if (sn > 0) {
+        const int64_t i = (sn >= slots) ? (int64_t)t * (sn / slots) : (t % sn);
+        float unused;
+        const float *b = s.boxes + position_source(s, i, unused) * s.stride;
         const float cx = b[0], cy = b[1];
         if (fabsf(cx) < 1e30f && fabsf(cy) < 1e30f) {
             lo_x = hi_x = cx;
@@ -94,6 +109,8 @@ __global__ void __launch_bounds__(kPackThreads)
 pack_kernel(PackSet s1, PackSet s2, float min_wh, float cell) {
     __shared__ uint32_t s_t0[2][2][32][4];   // level 0: [block][axis][bin][word]
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    // the consumer kernel may start now: it streams zeros until it needs the packed set
+    pdl_launch_dependents();
     const int64_t g = blockIdx.x * (int64_t)kPackThreads + tid;
     const bool second = g >= s1.n_pad;
     const PackSet s = second ? s2 : s1;
@@ -101,16 +118,14 @@ pack_kernel(PackSet s1, PackSet s2, float min_wh, float cell) {
     const bool in_set = i < s.n_pad;
 
     // the box first: its loads are in flight while the bin width is being derived
-    const int64_t src = in_set ? slot_source(s, i) : -1;
+    const int64_t pos = in_set ? slot_position(s, i, s.n_dev ? *s.n_dev : s.n) : -1;
+    int64_t src = -1;
     float cx = 0.f, cy = 0.f, w = 0.f, h = 0.f, th = 0.f;
-    if (src >= 0) {
+    if (pos >= 0) {
+        float o;
+        src = position_source(s, pos, o);
         const float *b = s.boxes + src * s.stride;
-        cx = b[0]; cy = b[1]; w = b[2]; h = b[3]; th = b[4];
-        if (s.offsets) {
-            const float o = s.offsets[src];
-            cx += o;
-            cy += o;
-        }
+        cx = b[0] + o; cy = b[1] + o; w = b[2]; h = b[3]; th = b[4];
     }
     const float inv_cell = cell > 0.f ? 1.f / cell : sample_inv_cell(s1, s2);
 
@@ -195,6 +210,11 @@ PackSet make_pack_set(const float *boxes, int64_t n, int stride, const int64_t *
     PackSet s;
     s.segs = nullptr;
     s.nseg = 0;
+    s.n_dev = nullptr;
+    s.gather_mask = ~0ll;
+    s.mc_classes = 0;
+    s.mc_shared = 0;
+    s.mc_max = nullptr;
     s.boxes = boxes;
     s.n = n;
     s.stride = stride;

@@ -95,28 +95,49 @@ def box_iou_rotated(bboxes1, bboxes2, mode='iou', aligned=False, clockwise=True)
     return _overlaps(bboxes1, bboxes2, mode, aligned, 0.0)
 
 
-def _nms_keep(boxes, scores, iou_threshold, seg_ids=None, offsets=None):
+def _desc_keys(s):
+    """float32 scores -> int64 keys in [0, 2**32) whose ASCENDING order is the scores'
+    descending order (equal scores give equal keys, so a stable sort breaks ties by
+    lower index first — the reference's sort leaves that order unspecified)."""
+    u = (s + 0.0).view(torch.int32).to(torch.int64) & 0xFFFFFFFF        # +0.0: -0.0 -> 0.0
+    mono = torch.where(u >= 0x80000000, 0xFFFFFFFF - u, u + 0x80000000)  # ascending with the score
+    return 0xFFFFFFFF - mono
+
+
+def _nms_keep(boxes, scores, iou_threshold, seg_ids=None, offsets=None, seg_counts_host=None):
     """kept indices (int64, score-descending, on the CUDA device) of a greedy
-    rotated NMS; ``seg_ids`` (int64/ints per box) restricts suppression to boxes
-    of equal id, ``offsets`` (float per box) is added to cx, cy first."""
+    rotated NMS.
+
+    ``seg_ids`` (non-negative ints per box) restricts suppression to boxes of equal
+    id; ``seg_counts_host`` (optional, host int64 array with one count per id
+    0..S-1) saves the device->host read of the segment sizes when the caller
+    already has them; ``offsets`` (float per box) is added to cx, cy first.
+    One radix sort of (segment, -score) keys, one rotgeo_nms call (pack + mask +
+    scan + emit kernels), one read of the kept count, one small sort of the
+    survivors back into global score order."""
     dev = _cuda_device(boxes, scores)
     n = boxes.size(0)
     b = _rows_f32(boxes, dev)
     s = scores.detach().to(device=dev, dtype=torch.float32).reshape(-1)
     L = _lib.load()
     with torch.cuda.device(dev):
-        # ties: lower index first (the reference's sort is unspecified there)
-        order = torch.sort(s, descending=True, stable=True).indices
-        seg_order_ptr, seg_off_ptr, nseg = None, None, 0
-        seg_off = None
-        if seg_ids is not None:
+        keys = _desc_keys(s)
+        order_ptr, seg_order_ptr, seg_off_ptr, nseg = None, None, None, 0
+        if seg_ids is None:
+            order = torch.sort(keys, stable=True).indices
+            order_ptr = order.data_ptr()
+        else:
             seg = seg_ids.detach().to(device=dev, dtype=torch.int64).reshape(-1)
-            uniq, inv, counts = torch.unique(seg, sorted=True, return_inverse=True,
-                                             return_counts=True)
-            seg_order = order[torch.sort(inv[order], stable=True).indices].contiguous()
-            seg_off = np.zeros(counts.numel() + 1, dtype=np.int64)
-            seg_off[1:] = np.cumsum(counts.cpu().numpy())
-            seg_order_ptr, seg_off_ptr, nseg = seg_order.data_ptr(), seg_off.ctypes.data, counts.numel()
+            if seg_counts_host is None:
+                uniq, seg, counts = torch.unique(seg, sorted=True, return_inverse=True,
+                                                 return_counts=True)
+                seg_counts_host = counts.cpu().numpy()
+            seg_counts_host = np.asarray(seg_counts_host, dtype=np.int64)
+            seg_order = torch.sort((seg << 32) | keys, stable=True).indices
+            seg_off = np.zeros(seg_counts_host.size + 1, dtype=np.int64)
+            np.cumsum(seg_counts_host, out=seg_off[1:])
+            assert seg_off[-1] == n, 'segment counts do not add up to the number of boxes'
+            seg_order_ptr, seg_off_ptr, nseg = seg_order.data_ptr(), seg_off.ctypes.data, seg_counts_host.size
         off_ptr = None
         if offsets is not None:
             offsets = offsets.detach().to(device=dev, dtype=torch.float32).contiguous()
@@ -125,12 +146,16 @@ def _nms_keep(boxes, scores, iou_threshold, seg_ids=None, offsets=None):
         ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
         keep = torch.empty(n, dtype=torch.int64, device=dev)
         nkeep = torch.empty(1, dtype=torch.int64, device=dev)
-        _lib.check(L.rotgeo_nms(b.data_ptr(), n, b.stride(0), off_ptr, order.data_ptr(),
+        _lib.check(L.rotgeo_nms(b.data_ptr(), n, b.stride(0), off_ptr, order_ptr,
                                 seg_order_ptr, seg_off_ptr, nseg, float(iou_threshold),
                                 keep.data_ptr(), nkeep.data_ptr(), ws.data_ptr(), nbytes,
                                 _stream(dev)), 'rotgeo_nms')
-        k = int(nkeep.item())          # the one sync: sizes the output
-    return keep[:k]
+        k = int(nkeep.item())          # the one sync after the launch: sizes the output
+        keep = keep[:k]
+        if seg_ids is not None and k > 1:
+            # segment-major -> global score order (ties: lower index first)
+            keep = keep[torch.sort((keys[keep] << 32) | keep).indices]
+    return keep
 
 
 def nms_rotated(dets, scores, iou_threshold, labels=None, clockwise=True):

@@ -252,3 +252,37 @@ def test_batched_nms_c4_full_image():
                             dict(type='nms_rotated', iou_threshold=0.8))
     assert gk.cpu().tolist() == wk.tolist()
     assert torch.equal(gd.cpu(), wd)
+
+
+def test_multiclass_nms_variants_fused_vs_generic():
+    """fused C-ABI path against the step-by-step torch path of the same package and the
+    oracle: per-class boxes (n, C*5), score_factors, max_num cut, return_inds."""
+    from orientedobjectdetection_b200 import core
+    rng = np.random.default_rng(11)
+    n, C = 700, 7
+    per_cls = np.concatenate([synth.le90_boxes(n, 40 + c, 300.0) for c in range(C)], axis=1)  # (n, C*5)
+    _, ms = synth.c2_multiclass(3, n=n, num_classes=C, extent=300.0)
+    sf = rng.uniform(0.5, 1.0, n).astype(np.float32)
+    for boxes in (per_cls, per_cls[:, :5].copy()):
+        for factors in (None, sf):
+            for max_num in (-1, 150):
+                t_sf = None if factors is None else torch.from_numpy(factors)
+                wd, wl, wk = ref_api.multiclass_nms_rotated(torch.from_numpy(boxes), torch.from_numpy(ms),
+                                                            0.05, 0.1, max_num, t_sf)
+                c_sf = None if factors is None else _cuda(factors)
+                gd, gl, gk = rg.multiclass_nms_rotated(_cuda(boxes), _cuda(ms), 0.05, dict(iou_thr=0.1),
+                                                       max_num, c_sf, return_inds=True)
+                assert gk.cpu().tolist() == wk.tolist()
+                assert torch.equal(gl.cpu(), wl) and torch.equal(gd.cpu(), wd)
+                # the torch path of the package (used for > 64 classes) gives the same
+                saved, core._FUSED_WS_LIMIT = core._FUSED_WS_LIMIT, 0
+                try:
+                    hd, hl, hk = rg.multiclass_nms_rotated(_cuda(boxes), _cuda(ms), 0.05, dict(iou_thr=0.1),
+                                                           max_num, c_sf, return_inds=True)
+                finally:
+                    core._FUSED_WS_LIMIT = saved
+                assert torch.equal(hd, gd) and torch.equal(hl, gl) and torch.equal(hk, gk)
+    # nothing above the threshold
+    d, l = rg.multiclass_nms_rotated(_cuda(per_cls), _cuda(np.zeros((n, C + 1), np.float32)), 0.05,
+                                     dict(iou_thr=0.1), 100)
+    assert d.shape == (0, 6) and l.shape == (0,)
