@@ -158,16 +158,20 @@ int rotgeo_nms(const float *boxes, int64_t n, int stride, const float *offsets,
     if (!workspace || !aligned16(workspace) || workspace_bytes < plan.total_bytes)
         return fail(ROTGEO_ERR_WORKSPACE, "nms: workspace %zu < %zu bytes or misaligned",
                     workspace_bytes, plan.total_bytes);
-    int max_words = 0;
-    for (const auto &g : segs) max_words = g.words > max_words ? g.words : max_words;
-    if (rotgeo::nms_scan_smem_bytes(max_words) > 224 * 1024)
-        return fail(ROTGEO_ERR_ARG, "nms: a segment of more than %d boxes is not supported",
-                    (224 * 1024 - (int)rotgeo::nms_scan_smem_bytes(0)) / 8 * 64);
+    for (const auto &g : segs)
+        if (g.words / 2 >= 65536)     // the mask kernel carries the column block in 16 bits
+            return fail(ROTGEO_ERR_ARG, "nms: a segment of more than %d boxes is not supported", 65535 * 128);
     char *ws = reinterpret_cast<char *>(workspace);
     void *packed = ws + plan.off_packed;
     rotgeo::NmsSegment *segs_dev = reinterpret_cast<rotgeo::NmsSegment *>(ws + plan.off_segments);
     uint64_t *mask = reinterpret_cast<uint64_t *>(ws + plan.off_mask);
     uint8_t *flags = reinterpret_cast<uint8_t *>(ws + plan.off_flags);
+    rotgeo::NmsScratch scratch;
+    scratch.kr = reinterpret_cast<unsigned long long *>(ws + plan.off_kr);
+    scratch.summary = reinterpret_cast<unsigned long long *>(ws + plan.off_summary);
+    scratch.sum_words = plan.sum_words;
+    scratch.sync = reinterpret_cast<unsigned int *>(ws + plan.off_sync);
+    scratch.block_counts = reinterpret_cast<int *>(ws + plan.off_counts);
     // pageable source: the runtime stages the bytes before returning, so `segs`
     // may die at scope exit
     if (cudaMemcpyAsync(segs_dev, segs.data(), segs.size() * sizeof(rotgeo::NmsSegment),
@@ -179,13 +183,17 @@ int rotgeo_nms(const float *boxes, int64_t n, int stride, const float *offsets,
         rotgeo::PackSet s1 = rotgeo::make_pack_set(boxes, n, stride, sorder, offsets, packed, plan.n_pad);
         s1.segs = segs_dev;
         s1.nseg = (int)num_segments;
+        s1.z_kr = scratch.kr;
+        s1.z_summary = scratch.summary;
+        s1.z_sum_words = scratch.sum_words;
+        s1.z_sync = scratch.sync;
         const rotgeo::PackSet none = rotgeo::make_pack_set(nullptr, 0, 5, nullptr, nullptr, nullptr, 0);
         if (rotgeo::launch_pack(s1, none, 0.f, 0.f, st)) return cuda_fail("nms pack launch");
     }
     // no global order given: kept indices come out segment-major (the caller re-orders)
     if (!order) order = sorder;
-    const int rc = rotgeo::launch_nms(plan, packed, segs_dev, max_words, order, sorder,
-                                      iou_threshold, mask, flags, keep_out, num_keep_out, st);
+    const int rc = rotgeo::launch_nms(plan, packed, segs_dev, order, sorder, iou_threshold, mask,
+                                      flags, scratch, keep_out, num_keep_out, st);
     if (rc == -1) return fail(ROTGEO_ERR_ARG, "nms: too many tiles");
     if (rc) return cuda_fail("nms launch");
     return ROTGEO_OK;
@@ -220,8 +228,6 @@ int rotgeo_multiclass_nms(const float *multi_bboxes, int bbox_cols, const float 
     if (!workspace || !aligned16(workspace) || workspace_bytes < need)
         return fail(ROTGEO_ERR_WORKSPACE, "multiclass_nms: workspace %zu < %zu bytes or misaligned",
                     workspace_bytes, need);
-    if (rotgeo::nms_scan_smem_bytes((int)(2 * ((rows + 127) / 128))) > 224 * 1024)
-        return fail(ROTGEO_ERR_ARG, "multiclass_nms: too many rows for one segment");
     const int shared = bbox_cols == 5 ? 1 : 0;   // one box per row, used by every class
     const int rc = rotgeo::launch_multiclass_nms(multi_bboxes, shared, multi_scores, score_factors,
                                                  rows, num_classes, score_thr, iou_threshold, cap,

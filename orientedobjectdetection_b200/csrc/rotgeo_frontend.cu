@@ -5,16 +5,21 @@
 // (n*C, 5), threshold the scores, nonzero() (a host sync), three gathers, two
 // global max reductions for the class offset, the sort inside mmcv.ops.nms_rotated
 // and the final gathers/cat — a dozen small launches and several device->host
-// round trips.  Here the whole call is eight launches and NO device->host read:
+// round trips.  Here the whole call is a fixed sequence of launches and NO
+// device->host read:
 //
-//   mc_keys_kernel   one thread per (row, class): candidate test, 64-bit sort keys
-//                    (class | descending score | flat index), per-class counts,
+//   mc_keys_kernel   one thread per (row, class): candidate test, 32-bit key (image of
+//                    the score, descending) + flat index, per-class counts,
 //                    max(cx,cy) / max(w,h) of the candidates
-//   cub radix sort   twice, keys only: segment-major order and global score order
-//   mc_plan_kernel   segment table and tile count from the class counts (the plan
-//                    the host makes in rotgeo_nms, made on the device)
-//   pack / mask / scan kernels of rotgeo_nms, launched over host-side upper bounds
-//   nms_emit_kernel  global score order, writes (box, score) rows and labels directly
+//   cub radix sort   stable pairs sort on the 32 key bits (4 passes): global score order
+//   mc_class_kernel  class of every entry of that order (1 byte); thread 0 also makes the
+//                    segment table and tile count from the class counts (the plan the
+//                    host makes in rotgeo_nms, made on the device)
+//   cub radix sort   one stable 8-bit pass on the class: segment-major order, score
+//                    order preserved inside a class
+//   pack / mask / resolve kernels of rotgeo_nms, launched over host-side upper bounds;
+//                    the resolve kernel's compaction runs in global score order and writes
+//                    the (box, score) rows and labels directly
 //
 // Sizes that depend on the data (candidates, tiles, mask words) never reach the host:
 // grids and workspace are sized for the worst case (every class keeps all n rows)
@@ -26,9 +31,8 @@
 
 namespace rotgeo {
 
-constexpr int kIdxBits = 26;                       // flat index row * C + class
-constexpr unsigned long long kIdxMask = (1ull << kIdxBits) - 1ull;
 constexpr int kTile = 128;
+constexpr uint32_t kInvalidKey = 0xffffffffu;   // behind every candidate (their keys are < 2^31)
 
 struct McHeader {
     long long n_valid;        // candidates (score > score_thr)
@@ -47,22 +51,10 @@ __device__ __forceinline__ float ordered_float(unsigned int o) {
     return __uint_as_float((o & 0x80000000u) ? (o & 0x7fffffffu) : ~o);
 }
 
-__global__ void mc_init_kernel(McHeader *h) {
-    const int t = threadIdx.x;
-    if (t == 0) {
-        h->n_valid = 0;
-        h->total_tiles = 0;
-        h->max_xy = 0u;     // below the image of every float
-        h->max_wh = 0u;
-    }
-    if (t < kMcMaxClasses) h->counts[t] = 0;
-}
-
 __global__ void __launch_bounds__(256)
 mc_keys_kernel(const float *__restrict__ boxes, int shared, const float *__restrict__ scores,
                const float *__restrict__ factors, int64_t rows, int classes, float score_thr,
-               unsigned long long *__restrict__ keys_seg, unsigned long long *__restrict__ keys_glob,
-               McHeader *__restrict__ hdr) {
+               uint32_t *__restrict__ keys, uint32_t *__restrict__ vals, McHeader *__restrict__ hdr) {
     __shared__ int s_cnt[kMcMaxClasses];
     __shared__ unsigned int s_max[2];
     const int tid = threadIdx.x;
@@ -75,21 +67,21 @@ mc_keys_kernel(const float *__restrict__ boxes, int shared, const float *__restr
         const int64_t row = f / classes;
         const int cls = (int)(f - row * classes);
         const float raw = scores[row * (classes + 1) + cls];
-        unsigned long long ks = ~0ull, kg = ~0ull;
+        uint32_t key = kInvalidKey;
         if (raw > score_thr) {                       // tested BEFORE the factors, like the reference
             float sc = raw;
             if (factors) sc *= factors[row];
-            // descending score: complement of the order-preserving image (+0.0f: -0 -> +0)
-            const unsigned long long desc = 0xffffffffu - ordered_bits(sc + 0.0f);
-            kg = (desc << kIdxBits) | (unsigned long long)f;
-            ks = ((unsigned long long)cls << (32 + kIdxBits)) | kg;
+            // descending score: complement of the order-preserving image (+0.0f: -0 -> +0);
+            // equal scores keep their flat-index order because the sort is stable
+            key = 0xffffffffu - ordered_bits(sc + 0.0f);
+            if (key == kInvalidKey) key = kInvalidKey - 1u;   // -NaN payloads only
             atomicAdd(&s_cnt[cls], 1);
             const float *b = boxes + (shared ? row : f) * 5;
             atomicMax(&s_max[0], ordered_bits(fmaxf(b[0], b[1])));
             atomicMax(&s_max[1], ordered_bits(fmaxf(b[2], b[3])));
         }
-        keys_seg[f] = ks;
-        keys_glob[f] = kg;
+        keys[f] = key;
+        vals[f] = (uint32_t)f;
     }
     __syncthreads();
     if (tid < classes && s_cnt[tid]) atomicAdd(&hdr->counts[tid], s_cnt[tid]);
@@ -97,9 +89,16 @@ mc_keys_kernel(const float *__restrict__ boxes, int shared, const float *__restr
     if (tid == 1 && s_max[1]) atomicMax(&hdr->max_wh, s_max[1]);
 }
 
-// the plan nms_plan() makes on the host, on the device (one thread: <= 64 segments)
-__global__ void mc_plan_kernel(McHeader *hdr, NmsSegment *segs, int classes) {
-    if (threadIdx.x != 0) return;
+// class byte of every entry of the global score order (255 behind the candidates); thread 0
+// of the grid also makes the plan nms_plan() makes on the host (<= 64 segments)
+__global__ void __launch_bounds__(256)
+mc_class_kernel(const uint32_t *__restrict__ keys_sorted, const uint32_t *__restrict__ vals_sorted,
+                int64_t total, int classes, uint8_t *__restrict__ cls_out, McHeader *hdr,
+                NmsSegment *segs) {
+    const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i < total)
+        cls_out[i] = keys_sorted[i] == kInvalidKey ? (uint8_t)255 : (uint8_t)(vals_sorted[i] % (uint32_t)classes);
+    if (i != 0) return;
     long long start = 0, slots = 0, words = 0, tiles = 0;
     for (int c = 0; c < classes; ++c) {
         const long long len = hdr->counts[c];
@@ -131,15 +130,10 @@ struct McLayout {
     int64_t blocks_per_cls;  // ceil(rows / 128)
     int64_t slots_bound, tiles_bound, words_bound;
     size_t cub_bytes;
-    size_t off_hdr, off_segs, off_keys_seg, off_keys_seg2, off_keys_glob, off_keys_glob2, off_cub,
-        off_packed, off_mask, off_flags, total_bytes;
+    size_t off_hdr, off_segs, off_keys, off_keys2, off_vals, off_vals2, off_cls, off_cls2, off_segvals,
+        off_cub, off_packed, off_mask, off_flags, off_kr, off_summary, off_sync, off_counts, total_bytes;
+    int sum_words;
 };
-
-static int sort_end_bit(int classes) {
-    int cbits = 0;
-    while ((1 << cbits) < classes) ++cbits;
-    return 32 + kIdxBits + cbits;
-}
 
 static void mc_layout(int64_t rows, int classes, McLayout *l) {
     l->total = rows * classes;
@@ -148,21 +142,31 @@ static void mc_layout(int64_t rows, int classes, McLayout *l) {
     l->slots_bound = classes * l->blocks_per_cls * kTile;
     l->tiles_bound = classes * (l->blocks_per_cls * (l->blocks_per_cls + 1) / 2);
     l->words_bound = (int64_t)classes * rows * 2 * l->blocks_per_cls;
-    size_t cub = 0;
-    cub::DoubleBuffer<unsigned long long> db(nullptr, nullptr);
-    cub::DeviceRadixSort::SortKeys(nullptr, cub, db, (int)l->total, 0, sort_end_bit(classes));
-    l->cub_bytes = cub;
+    size_t cub1 = 0, cub2 = 0;
+    cub::DoubleBuffer<uint32_t> dk(nullptr, nullptr), dv(nullptr, nullptr);
+    cub::DeviceRadixSort::SortPairs(nullptr, cub1, dk, dv, (int)l->total, 0, 32);
+    cub::DeviceRadixSort::SortPairs(nullptr, cub2, (const uint8_t *)nullptr, (uint8_t *)nullptr,
+                                    (const uint32_t *)nullptr, (uint32_t *)nullptr, (int)l->total, 0, 8);
+    l->cub_bytes = cub1 > cub2 ? cub1 : cub2;
     size_t off = 0;
     l->off_hdr = off;        off = align_up(off + sizeof(McHeader), 256);
     l->off_segs = off;       off = align_up(off + (size_t)classes * sizeof(NmsSegment), 256);
-    l->off_keys_seg = off;   off = align_up(off + (size_t)l->total * 8, 256);
-    l->off_keys_seg2 = off;  off = align_up(off + (size_t)l->total * 8, 256);
-    l->off_keys_glob = off;  off = align_up(off + (size_t)l->total * 8, 256);
-    l->off_keys_glob2 = off; off = align_up(off + (size_t)l->total * 8, 256);
-    l->off_cub = off;        off = align_up(off + cub, 256);
+    l->off_keys = off;       off = align_up(off + (size_t)l->total * 4, 256);
+    l->off_keys2 = off;      off = align_up(off + (size_t)l->total * 4, 256);
+    l->off_vals = off;       off = align_up(off + (size_t)l->total * 4, 256);
+    l->off_vals2 = off;      off = align_up(off + (size_t)l->total * 4, 256);
+    l->off_cls = off;        off = align_up(off + (size_t)l->total, 256);
+    l->off_cls2 = off;       off = align_up(off + (size_t)l->total, 256);
+    l->off_segvals = off;    off = align_up(off + (size_t)l->total * 4, 256);
+    l->off_cub = off;        off = align_up(off + l->cub_bytes, 256);
     l->off_packed = off;     off = align_up(off + (size_t)l->slots_bound * kPackedBytesPerBox, 256);
     l->off_mask = off;       off = align_up(off + (size_t)l->words_bound * 8, 256);
     l->off_flags = off;      off = align_up(off + (size_t)l->total, 256);
+    l->sum_words = nms_sum_words(l->blocks_per_cls);
+    l->off_kr = off;         off = align_up(off + (size_t)(l->slots_bound / 64) * 16, 256);
+    l->off_summary = off;    off = align_up(off + (size_t)l->slots_bound * l->sum_words * 8, 256);
+    l->off_sync = off;       off = align_up(off + kNmsSyncWords * sizeof(unsigned int), 256);
+    l->off_counts = off;     off = align_up(off + kNmsMaxBlocks * sizeof(int), 256);
     l->total_bytes = off;
 }
 
@@ -184,38 +188,52 @@ int launch_multiclass_nms(const float *multi_bboxes, int shared, const float *mu
     char *ws = reinterpret_cast<char *>(workspace);
     McHeader *hdr = reinterpret_cast<McHeader *>(ws + l.off_hdr);
     NmsSegment *segs = reinterpret_cast<NmsSegment *>(ws + l.off_segs);
-    unsigned long long *ks = reinterpret_cast<unsigned long long *>(ws + l.off_keys_seg);
-    unsigned long long *ks2 = reinterpret_cast<unsigned long long *>(ws + l.off_keys_seg2);
-    unsigned long long *kg = reinterpret_cast<unsigned long long *>(ws + l.off_keys_glob);
-    unsigned long long *kg2 = reinterpret_cast<unsigned long long *>(ws + l.off_keys_glob2);
+    uint32_t *keys = reinterpret_cast<uint32_t *>(ws + l.off_keys);
+    uint32_t *keys2 = reinterpret_cast<uint32_t *>(ws + l.off_keys2);
+    uint32_t *vals = reinterpret_cast<uint32_t *>(ws + l.off_vals);
+    uint32_t *vals2 = reinterpret_cast<uint32_t *>(ws + l.off_vals2);
+    uint8_t *cls = reinterpret_cast<uint8_t *>(ws + l.off_cls);
+    uint8_t *cls2 = reinterpret_cast<uint8_t *>(ws + l.off_cls2);
+    uint32_t *segvals = reinterpret_cast<uint32_t *>(ws + l.off_segvals);
+    const unsigned grid = (unsigned)((l.total + 255) / 256);
 
-    mc_init_kernel<<<1, 64, 0, stream>>>(hdr);
-    mc_keys_kernel<<<(unsigned)((l.total + 255) / 256), 256, 0, stream>>>(
-        multi_bboxes, shared, multi_scores, score_factors, rows, classes, score_thr, ks, kg, hdr);
+    // zero bits: no candidates, no tiles, maxima below the image of every float
+    if (cudaMemsetAsync(hdr, 0, sizeof(McHeader), stream) != cudaSuccess) return -3;
+    mc_keys_kernel<<<grid, 256, 0, stream>>>(multi_bboxes, shared, multi_scores, score_factors, rows,
+                                             classes, score_thr, keys, vals, hdr);
     if (cudaGetLastError() != cudaSuccess) return -3;
-    // invalid entries are all ones and sort behind every candidate
-    cub::DoubleBuffer<unsigned long long> dbs(ks, ks2), dbg(kg, kg2);
+    cub::DoubleBuffer<uint32_t> dk(keys, keys2), dv(vals, vals2);
     size_t cub_bytes = l.cub_bytes;
-    if (cub::DeviceRadixSort::SortKeys(ws + l.off_cub, cub_bytes, dbs, (int)l.total, 0,
-                                       sort_end_bit(classes), stream) != cudaSuccess)
+    if (cub::DeviceRadixSort::SortPairs(ws + l.off_cub, cub_bytes, dk, dv, (int)l.total, 0, 32,
+                                        stream) != cudaSuccess)
         return -3;
-    cub_bytes = l.cub_bytes;
-    if (cub::DeviceRadixSort::SortKeys(ws + l.off_cub, cub_bytes, dbg, (int)l.total, 0,
-                                       32 + kIdxBits, stream) != cudaSuccess)
-        return -3;
-    mc_plan_kernel<<<1, 32, 0, stream>>>(hdr, segs, classes);
+    const uint32_t *order32 = dv.Current();
+    mc_class_kernel<<<grid, 256, 0, stream>>>(dk.Current(), order32, l.total, classes, cls, hdr, segs);
     if (cudaGetLastError() != cudaSuccess) return -3;
+    cub_bytes = l.cub_bytes;
+    if (cub::DeviceRadixSort::SortPairs(ws + l.off_cub, cub_bytes, (const uint8_t *)cls, cls2, order32,
+                                        segvals, (int)l.total, 0, 8, stream) != cudaSuccess)
+        return -3;
 
-    // pack: slots follow the device-made segment table; gather[] = sorted keys (index in the low bits)
-    PackSet s1 = make_pack_set(multi_bboxes, l.total, 5, reinterpret_cast<const int64_t *>(dbs.Current()),
-                               nullptr, ws + l.off_packed, l.slots_bound);
+    // pack: slots follow the device-made segment table; the gather list is the segment-major order
+    PackSet s1 = make_pack_set(multi_bboxes, l.total, 5, nullptr, nullptr, ws + l.off_packed, l.slots_bound);
     s1.segs = segs;
     s1.nseg = classes;
     s1.n_dev = reinterpret_cast<const int64_t *>(&hdr->n_valid);
-    s1.gather_mask = (int64_t)kIdxMask;
+    s1.gather32 = segvals;
     s1.mc_classes = classes;
     s1.mc_shared = shared;
     s1.mc_max = hdr->mc_max;
+    NmsScratch scratch;
+    scratch.kr = reinterpret_cast<unsigned long long *>(ws + l.off_kr);
+    scratch.summary = reinterpret_cast<unsigned long long *>(ws + l.off_summary);
+    scratch.sum_words = l.sum_words;
+    scratch.sync = reinterpret_cast<unsigned int *>(ws + l.off_sync);
+    scratch.block_counts = reinterpret_cast<int *>(ws + l.off_counts);
+    s1.z_kr = scratch.kr;
+    s1.z_summary = scratch.summary;
+    s1.z_sum_words = scratch.sum_words;
+    s1.z_sync = scratch.sync;
     const PackSet none = make_pack_set(nullptr, 0, 5, nullptr, nullptr, nullptr, 0);
     if (launch_pack(s1, none, 0.f, 0.f, stream)) return -3;
 
@@ -226,10 +244,10 @@ int launch_multiclass_nms(const float *multi_bboxes, int shared, const float *mu
     a.nseg = classes;
     a.tiles_bound = l.tiles_bound;
     a.total_tiles_dev = reinterpret_cast<const int64_t *>(&hdr->total_tiles);
-    a.max_words_bound = (int)(2 * l.blocks_per_cls);
-    a.order = reinterpret_cast<const int64_t *>(dbg.Current());
-    a.seg_order = reinterpret_cast<const int64_t *>(dbs.Current());
-    a.idx_mask = (int64_t)kIdxMask;
+    a.scratch = scratch;
+    a.max_chunks_bound = 2 * l.blocks_per_cls;
+    a.order32 = order32;
+    a.seg_order32 = segvals;
     a.n_bound = l.total;
     a.n_dev = reinterpret_cast<const int64_t *>(&hdr->n_valid);
     a.thr = iou_threshold;

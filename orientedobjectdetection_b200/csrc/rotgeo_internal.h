@@ -28,19 +28,25 @@ struct PackSet {
     const float *offsets;    // nullable: added to cx, cy, indexed like the source rows
     const NmsSegment *segs;  // nullable: segmented slot layout (see slot_source)
     int nseg;
-    // device-planned sets (fused front-ends): the box count lives on the device, and gather[]
+    // device-planned sets (fused front-ends): the box count lives on the device, and gather32[]
     // holds FLAT candidate indices row * mc_classes + class of a (rows x classes) score matrix
     const int64_t *n_dev;    // nullable: overrides n
-    int64_t gather_mask;     // gather[] entries are sort keys: index = entry & gather_mask
-    int mc_classes;          // 0: gather[] holds source rows
+    const uint32_t *gather32;  // nullable: 32-bit gather list, used instead of gather
+    int mc_classes;          // 0: the gather list holds source rows
     int mc_shared;           // 1: boxes (rows, 5) shared by all classes; 0: (rows * classes, 5)
     const float *mc_max;     // device float[2]: max(cx, cy), max(w, h) of the candidates; the class
                              // offset is class * (mc_max[0] + mc_max[1] + 1), bbox_nms_rotated.py:73-77
+    // NMS only: scratch of the resolve stage, zeroed here so that no extra launch is needed
+    unsigned long long *z_kr;       // nullable: n_pad / 64 (kept, removed) word pairs
+    unsigned long long *z_summary;  // n_pad * z_sum_words row summaries
+    int z_sum_words;
+    unsigned int *z_sync;           // kNmsSyncWords words of barrier / round state
     float4 *p0, *p1;
     uint2 *pm;
     uint32_t *pr, *pt;
     int64_t n_pad;
 };
+constexpr int kNmsSyncWords = 16;
 PackSet make_pack_set(const float *boxes, int64_t n, int stride, const int64_t *gather,
                       const float *offsets, void *packed, int64_t n_pad);
 
@@ -61,9 +67,25 @@ struct NmsPlan {
     int64_t num_segments;
     int64_t total_tiles;
     int64_t mask_words;
+    int64_t max_chunks;  // 64-box chunks of the largest segment (upper bound)
+    int sum_words;       // u64 words of a row summary: ceil(column blocks of the largest segment / 64)
     // workspace layout (byte offsets)
-    size_t off_packed, off_segments, off_mask, off_flags, off_seg_keep, total_bytes;
+    size_t off_packed, off_segments, off_mask, off_flags, off_kr, off_summary, off_sync, off_counts,
+        total_bytes;
 };
+
+// scratch of the resolve stage (rotgeo_nms.cu); kr / summary / sync are zeroed by the pack kernel
+struct NmsScratch {
+    unsigned long long *kr;        // per 64-slot word: kept bits, removed bits
+    unsigned long long *summary;   // per slot: bit J set = the row has a bit in column block J
+    int sum_words;
+    unsigned int *sync;
+    int *block_counts;             // kNmsMaxBlocks entries
+};
+constexpr int kNmsMaxBlocks = 1024;
+static inline int nms_sum_words(int64_t max_col_blocks) {
+    return (int)((max_col_blocks + 63) / 64 > 0 ? (max_col_blocks + 63) / 64 : 1);
+}
 
 void nms_plan(int64_t n, const int64_t *seg_offsets_host, int64_t num_segments, NmsPlan *plan,
               NmsSegment *segments_out /* nullable, num_segments entries */);
@@ -81,11 +103,9 @@ struct McOut {
     int64_t cap;             // keep at most this many (max_num)
 };
 
-size_t nms_scan_smem_bytes(int max_words);   // dynamic shared memory of nms_scan_kernel
-
 int launch_nms(const NmsPlan &plan, const void *packed, const NmsSegment *segments_dev,
-               int max_words, const int64_t *order, const int64_t *seg_order, float thr,
-               uint64_t *mask, uint8_t *flags, int64_t *keep_out, int64_t *num_keep_out,
+               const int64_t *order, const int64_t *seg_order, float thr, uint64_t *mask,
+               uint8_t *flags, const NmsScratch &scratch, int64_t *keep_out, int64_t *num_keep_out,
                cudaStream_t stream);
 
 // NMS over a plan made on the DEVICE (fused front-ends): grids and buffers are sized for
@@ -97,10 +117,10 @@ struct NmsDevLaunch {
     int nseg;
     int64_t tiles_bound;              // mask grid
     const int64_t *total_tiles_dev;   // actual tile count
-    int max_words_bound;              // mask words per row of the largest possible segment
-    const int64_t *order;             // global score order (entries & idx_mask = box index)
-    const int64_t *seg_order;         // segment-major order (same encoding)
-    int64_t idx_mask;
+    NmsScratch scratch;
+    int64_t max_chunks_bound;         // 64-box chunks of the largest possible segment
+    const uint32_t *order32;          // global score order (flat candidate indices)
+    const uint32_t *seg_order32;      // segment-major order
     int64_t n_bound;
     const int64_t *n_dev;             // actual candidate count
     float thr;

@@ -2,29 +2,39 @@
 //
 // Input: boxes packed in SEGMENT-MAJOR order (segment = class / FPN level /
 // image x level ...), score-descending inside each segment, every segment
-// starting at a packed slot that is a multiple of 128.  Three kernels:
+// starting at a packed slot that is a multiple of 128.  Two kernels:
 //
-//   nms_mask_kernel  the suppression bit matrix, block-diagonal and upper-triangular:
-//                    one work item per 128x128 tile of the upper triangle of each
-//                    segment's pair matrix (pairs from different segments are never
-//                    touched).  Same machinery as the IoU kernel: CTAs made persistent
-//                    by cluster-launch-control work stealing, cull data (row bin
-//                    ranges + the column block's inverted bin index) TMA-staged in a
-//                    shared-memory ring, tile zeros stored first, surviving pairs
-//                    queued per warp, circle-tested 32 at a time, re-queued and clipped
-//                    32 at a time; `IoU >= thr` becomes an atomicOr into the (already
-//                    zeroed) mask word.
-//   nms_scan_kernel  one CTA per segment, blocked right-looking greedy scan.  A panel
-//                    of 512 rows x 8 words around the diagonal is staged in shared
-//                    memory (cp.async, double-buffered); its eight 64-box chunks are
-//                    resolved there — inside a chunk the kept set is found by peeling
-//                    (warp redux.or rounds, usually 1-3) instead of a 64-step serial
-//                    loop — and only then are the kept rows OR-ed into the `removed`
-//                    bitmap right of the panel in one bulk pass over global memory.
-//                    The mask never leaves the GPU.
-//   nms_emit_kernel  (several segments only) compacts the kept flags in GLOBAL score
-//                    order into keep_out — the order mmcv.ops.nms_rotated returns and
-//                    every reference caller slices with [:max_num].
+//   nms_mask_kernel     the suppression relation as a bit matrix, block-diagonal and
+//                       LOWER-triangular: bit i of row j (i < j in score order) says
+//                       "i suppresses j if i is kept" — a row lists the earlier boxes
+//                       its own fate depends on.  One work item per 128x128 tile of the
+//                       lower triangle of each segment's pair matrix (pairs of different
+//                       segments are never touched).  Same machinery as the IoU kernel:
+//                       CTAs made persistent by cluster-launch-control work stealing,
+//                       cull data (row bin ranges + the column block's inverted bin
+//                       index) TMA-staged in a shared-memory ring, tile zeros stored
+//                       first, surviving pairs queued per warp, circle-tested 32 at a
+//                       time, re-queued and clipped 32 at a time; `IoU >= thr` becomes an
+//                       atomicOr into the (already zeroed) mask word plus one into the
+//                       row's SUMMARY (one bit per 128-column block that holds a bit).
+//   nms_resolve_kernel  the greedy decision as a data-parallel fixed point instead of a
+//                       serial scan.  State: two monotone bitmaps, kept and removed.  A
+//                       box is removed as soon as one earlier neighbour is kept, and kept
+//                       as soon as all earlier neighbours are removed — exactly the
+//                       greedy result, whatever the evaluation order.  One cooperative
+//                       persistent grid; a round gives every 64-box chunk that still has
+//                       undecided boxes to one warp, which walks the set summary bits of
+//                       each undecided row (16 B of mask per bit), tests them against
+//                       the bitmaps, and settles the chunk's internal chains by peeling
+//                       (ballots, usually 1-3 iterations).  Rounds are separated by a
+//                       grid barrier and stop when nothing is undecided: 1-2 rounds for
+//                       sparse scenes, ~10 for dense ones, at worst one per chunk of the
+//                       largest segment (the length of the old serial scan).  The same
+//                       grid then writes the per-box flags and compacts them in GLOBAL
+//                       score order into keep_out (and, for the fused multiclass call,
+//                       the (box, score) rows and labels) — the order
+//                       mmcv.ops.nms_rotated returns and every reference caller slices
+//                       with [:max_num].  The mask never leaves the GPU.
 //
 // Replaces mmcv's nms_rotated (64x64 bitmask over the full square + D2H copy of
 // the mask + serial host scan; reference call sites
@@ -48,13 +58,15 @@ static_assert(kTile == kBlock, "a tile column is one inverted-index block");
 struct TileInfo {
     int valid;        // 0: nothing left to steal
     int seg;          // segment index
-    int I, J;         // row / column block inside the segment (I <= J)
+    int I, J;         // row / column block inside the segment (J <= I)
 };
 
 struct QEntry {       // one pair that survived cull level 1
     int prow, pcol;               // packed slots
-    unsigned long long word;      // index of the mask word holding its bit
+    unsigned long long word;      // low 48 bits: index of the mask word holding its bit;
+                                  // high 16 bits: column block J (its summary bit)
 };
+constexpr unsigned long long kWordMask = (1ull << 48) - 1ull;
 
 struct __align__(16) MaskSmem {
     uint32_t tab[kStages][kTableWords];
@@ -75,11 +87,15 @@ struct MaskArgs {
     const NmsSegment *segs;
     int nseg;
     float thr;
+    float area_ratio;             // pairs with min(area) < area_ratio * max(area) cannot reach thr
     unsigned long long *mask;
+    unsigned long long *summary;  // per packed slot: sum_words words, zeroed by the pack kernel
+    int sum_words;
     const int64_t *total_tiles;   // nullable: device-planned launch, tile ids >= *total_tiles do not exist
 };
 
-// tile id -> (segment, I, J): tiles of a segment are numbered row block by row block
+// tile id -> (segment, I, J): tiles of a segment are numbered row block by row block,
+// row block I holding the I + 1 tiles J = 0 .. I
 __device__ TileInfo locate_tile(const NmsSegment *__restrict__ segs, int nseg, unsigned tile) {
     int lo = 0, hi = nseg - 1;  // last segment with tile_base <= tile
     while (lo < hi) {
@@ -87,17 +103,16 @@ __device__ TileInfo locate_tile(const NmsSegment *__restrict__ segs, int nseg, u
         if (segs[mid].tile_base <= (int64_t)tile) lo = mid; else hi = mid - 1;
     }
     const int64_t t = (int64_t)tile - segs[lo].tile_base;
-    const int C = segs[lo].words >> 1;  // 128-box column blocks
-    // tiles before block-row i: i*C - i*(i-1)/2
-    int I = (int)(((2.0 * C + 1.0) - sqrt((2.0 * C + 1.0) * (2.0 * C + 1.0) - 8.0 * (double)t)) * 0.5);
-    I = max(0, min(I, C - 1));
-    while (I + 1 < C && (int64_t)(I + 1) * C - (int64_t)(I + 1) * I / 2 <= t) ++I;
-    while (I > 0 && (int64_t)I * C - (int64_t)I * (I - 1) / 2 > t) --I;
+    // tiles before block-row i: i (i + 1) / 2
+    int64_t I = (int64_t)((sqrt(8.0 * (double)t + 1.0) - 1.0) * 0.5);
+    if (I < 0) I = 0;
+    while ((I + 1) * (I + 2) / 2 <= t) ++I;
+    while (I > 0 && I * (I + 1) / 2 > t) --I;
     TileInfo ti;
     ti.valid = 1;
     ti.seg = lo;
-    ti.I = I;
-    ti.J = I + (int)(t - ((int64_t)I * C - (int64_t)I * (I - 1) / 2));
+    ti.I = (int)I;
+    ti.J = (int)(t - I * (I + 1) / 2);
     return ti;
 }
 
@@ -159,7 +174,11 @@ nms_mask_kernel(const MaskArgs g) {
             const QEntry e = q2[n2 - take + lane];
             const float v = rect_overlap<0>(__ldg(g.p0 + e.prow), __ldg(g.p1 + e.prow),
                                             __ldg(g.p0 + e.pcol), __ldg(g.p1 + e.pcol));
-            if (v >= g.thr) atomicOr(g.mask + e.word, 1ull << (e.pcol & 63));
+            if (v >= g.thr) {
+                const int J = (int)(e.word >> 48);
+                atomicOr(g.mask + (e.word & kWordMask), 1ull << (e.pcol & 63));
+                atomicOr(g.summary + (int64_t)e.prow * g.sum_words + (J >> 6), 1ull << (J & 63));
+            }
         }
         n2 -= take;
         __syncwarp();
@@ -170,7 +189,10 @@ nms_mask_kernel(const MaskArgs g) {
         if (lane < take) {
             e = q1[n1 - take + lane];
             const float4 A0 = __ldg(g.p0 + e.prow), B0 = __ldg(g.p0 + e.pcol);
-            pass = !circles_disjoint(A0.x, A0.y, A0.z, B0.x, B0.y, B0.z);
+            // IoU <= min(area) / max(area): with a high threshold (RPN: 0.8) most pairs of
+            // different sizes end here, 1e-4 below the threshold to stay clear of rounding
+            pass = !circles_disjoint(A0.x, A0.y, A0.z, B0.x, B0.y, B0.z) &&
+                   fminf(A0.w, B0.w) >= g.area_ratio * fmaxf(A0.w, B0.w);
         }
         n1 -= take;
         const uint32_t b = __ballot_sync(0xffffffffu, pass);
@@ -245,10 +267,10 @@ nms_mask_kernel(const MaskArgs g) {
                 const uint32_t X = tx[sx * 4] | tx[((sx + nx - (1 << jx)) & 31) * 4];
                 const uint32_t Y = ty[sy * 4] | ty[((sy + ny - (1 << jy)) & 31) * 4];
                 h = X & Y;
-                if (ti.I == ti.J) {                                  // keep columns after the row only
+                if (ti.I == ti.J) {                                  // keep columns before the row only
                     const int d = rloc - 32 * cw;                    // row's bit inside this word
-                    if (d >= 31) h = 0u;
-                    else if (d >= 0) h &= ~((2u << d) - 1u);
+                    if (d <= 0) h = 0u;
+                    else if (d < 32) h &= (1u << d) - 1u;
                 }
             }
             hits[p] = h;
@@ -263,7 +285,8 @@ nms_mask_kernel(const MaskArgs g) {
             const int rloc = warp + kWarps * (rl + 8 * p);
             QEntry e;
             e.prow = (int)sg.pstart + row_base + rloc;
-            e.word = (unsigned long long)(sg.mask_base + (int64_t)(row_base + rloc) * W + 2 * ti.J + (cw >> 1));
+            e.word = (unsigned long long)(sg.mask_base + (int64_t)(row_base + rloc) * W + 2 * ti.J + (cw >> 1)) |
+                     ((unsigned long long)ti.J << 48);
             const int pcol0 = (int)sg.pstart + col_base + 32 * cw;
             for (;;) {
                 const uint32_t act = __ballot_sync(0xffffffffu, m != 0u);
@@ -293,177 +316,286 @@ nms_mask_kernel(const MaskArgs g) {
     }
 }
 
-// ---- greedy scan -----------------------------------------------------------------
-constexpr int kScanThreads = 512;
-constexpr int kPanelChunks = 8;                       // 64-box chunks per panel
-constexpr int kPanelRows = 64 * kPanelChunks;         // 512
-constexpr int kPanelWords = kPanelRows * kPanelChunks;  // u64 words per panel buffer (32 KB)
 
-__device__ __forceinline__ unsigned long long warp_or64(unsigned long long v) {
-    const unsigned lo = __reduce_or_sync(0xffffffffu, (unsigned)v);
-    const unsigned hi = __reduce_or_sync(0xffffffffu, (unsigned)(v >> 32));
-    return ((unsigned long long)hi << 32) | lo;
+// ---- greedy decision: parallel fixed point over (kept, removed) bitmaps -------------
+constexpr int kResThreads = 1024;
+constexpr int kResWarps = kResThreads / 32;
+constexpr int kLocalChunks = 64;                       // segments of <= 4096 boxes are settled by ONE CTA,
+                                                       // state in shared memory, __syncthreads between rounds
+constexpr int kEmitItems = 8;                          // positions of `order` per thread and tile
+constexpr int kEmitTile = kResThreads * kEmitItems;
+
+struct ResolveArgs {
+    const NmsSegment *segs;
+    int nseg;
+    int has_large;                // some segment may have more than kLocalChunks chunks
+    const unsigned long long *mask;
+    NmsScratch sc;
+    int64_t chunks;               // 64-slot words to visit (an upper bound when device-planned)
+    const int64_t *order;         // global score order: box indices ...
+    const int64_t *seg_order;     // ... and segment-major order
+    const uint32_t *order32;      // the same as 32-bit indices (fused front-ends); used when non-null
+    const uint32_t *seg_order32;
+    int64_t n;
+    const int64_t *n_dev;         // nullable: overrides n
+    uint8_t *flags;
+    int64_t *keep_out, *num_keep_out;
+    McOut mc;
+};
+
+__device__ __forceinline__ int64_t order_at(const ResolveArgs &a, int64_t i) {
+    return a.order32 ? (int64_t)a.order32[i] : a.order[i];
+}
+__device__ __forceinline__ int64_t seg_order_at(const ResolveArgs &a, int64_t i) {
+    return a.seg_order32 ? (int64_t)a.seg_order32[i] : a.seg_order[i];
 }
 
-__device__ __forceinline__ void cp_async16(void *dst_smem, const void *src) {
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(dst_smem)), "l"(src) : "memory");
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
-
-// dynamic shared memory: two panel buffers, then the `removed` bitmap (seg.words entries)
-template <bool EMIT>
-__global__ void __launch_bounds__(kScanThreads)
-nms_scan_kernel(const NmsSegment *__restrict__ segs, const unsigned long long *__restrict__ mask,
-                const int64_t *__restrict__ seg_order, int64_t idx_mask, uint8_t *__restrict__ flags,
-                int64_t *__restrict__ keep_out, int64_t *__restrict__ num_keep_out) {
-    extern __shared__ __align__(16) unsigned long long dyn[];
-    unsigned long long *const panel0 = dyn;
-    unsigned long long *const removed = dyn + 2 * kPanelWords;
-    __shared__ int s_rows[kPanelRows];   // kept rows of the current panel (segment positions)
-    __shared__ int s_nk_chunk, s_nk_panel;
-
-    const NmsSegment seg = segs[blockIdx.x];
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int W = seg.words;
-    const int L = (int)seg.len;
-    const unsigned long long *__restrict__ M = mask + seg.mask_base;
-    const int panels = (seg.row_blocks + kPanelChunks - 1) / kPanelChunks;
-
-    // panel P: rows [512 P, 512 P + 512) x words [8 P, 8 P + 8), 64 B per row
-    auto load_panel = [&](int P, unsigned long long *buf) {
-        const int r0 = P * kPanelRows, w0 = P * kPanelChunks;
-        for (int idx = tid; idx < kPanelRows * 4; idx += kScanThreads) {
-            const int r = idx >> 2, q = idx & 3;           // row, 16-byte quarter
-            if (r0 + r < L && w0 + 2 * q < W)
-                cp_async16(buf + r * kPanelChunks + 2 * q, M + (int64_t)(r0 + r) * W + w0 + 2 * q);
-        }
-        cp_async_commit();
-    };
-    load_panel(0, panel0);
-
-    for (int w = tid; w < W; w += kScanThreads) {
-        // positions >= L do not exist: mark them removed
-        const int first = w * 64;
-        unsigned long long v = 0ull;
-        if (first >= L) v = ~0ull;
-        else if (first + 64 > L) v = ~0ull << (L - first);
-        removed[w] = v;
-    }
-
-    int64_t nkeep = 0;
-    for (int P = 0; P < panels; ++P) {
-        unsigned long long *const buf = panel0 + (P & 1) * kPanelWords;
-        if (P + 1 < panels) {
-            load_panel(P + 1, panel0 + ((P + 1) & 1) * kPanelWords);
-            cp_async_wait<1>();
+// sync[0] arrival count, sync[1] generation, sync[2..4] "something is still undecided" per round % 3
+__device__ __forceinline__ void grid_barrier(unsigned int *sync, unsigned int nblocks) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        volatile unsigned int *gen = sync + 1;
+        const unsigned int g = *gen;
+        __threadfence();
+        if (atomicAdd(sync, 1u) == nblocks - 1u) {
+            *(volatile unsigned int *)sync = 0u;
+            __threadfence();
+            *gen = g + 1u;
         } else {
-            cp_async_wait<0>();
+            while (*gen == g) {}
         }
-        if (tid == 0) s_nk_panel = 0;
-        __syncthreads();
-
-        const int r0 = P * kPanelRows, w0 = P * kPanelChunks;
-        const int chunks_here = min(kPanelChunks, seg.row_blocks - w0);
-        for (int cl = 0; cl < chunks_here; ++cl) {
-            const int c = w0 + cl;
-            if (warp == 0) {
-                // lane holds the diagonal words of rows c*64+lane and c*64+32+lane
-                const int q0 = cl * 64 + lane, q1 = q0 + 32;       // rows inside the panel
-                const unsigned long long d0 = r0 + q0 < L ? buf[q0 * kPanelChunks + cl] : 0ull;
-                const unsigned long long d1 = r0 + q1 < L ? buf[q1 * kPanelChunks + cl] : 0ull;
-                unsigned long long cand = ~removed[c];
-                unsigned long long kept = 0ull;
-                while (cand) {
-                    const bool in0 = (cand >> lane) & 1ull, in1 = (cand >> (lane + 32)) & 1ull;
-                    // everything some undecided box could still suppress
-                    const unsigned long long threat = warp_or64((in0 ? d0 : 0ull) | (in1 ? d1 : 0ull));
-                    const unsigned long long safe = cand & ~threat;   // nobody left can suppress these
-                    kept |= safe;
-                    const bool s0 = (safe >> lane) & 1ull, s1 = (safe >> (lane + 32)) & 1ull;
-                    const unsigned long long killed = warp_or64((s0 ? d0 : 0ull) | (s1 ? d1 : 0ull));
-                    cand &= ~(safe | killed);
-                }
-                const bool k0 = (kept >> lane) & 1ull, k1 = (kept >> (lane + 32)) & 1ull;
-                const int rk0 = __popcll(kept & ((1ull << lane) - 1ull));
-                const int rk1 = __popcll(kept & ((1ull << (lane + 32)) - 1ull));
-                const int base = s_nk_panel;
-                if (k0) s_rows[base + rk0] = r0 + q0;
-                if (k1) s_rows[base + rk1] = r0 + q1;
-                if (EMIT) {
-                    if (k0) keep_out[nkeep + rk0] = seg_order[seg.start + r0 + q0] & idx_mask;
-                    if (k1) keep_out[nkeep + rk1] = seg_order[seg.start + r0 + q1] & idx_mask;
-                } else {
-                    if (r0 + q0 < L) flags[seg_order[seg.start + r0 + q0] & idx_mask] = k0 ? 1 : 0;
-                    if (r0 + q1 < L) flags[seg_order[seg.start + r0 + q1] & idx_mask] = k1 ? 1 : 0;
-                }
-                __syncwarp();
-                if (lane == 0) {
-                    s_nk_chunk = __popcll(kept);
-                    s_nk_panel = base + __popcll(kept);
-                }
-            }
-            __syncthreads();
-            const int nk = s_nk_chunk;
-            nkeep += nk;
-            // kept rows of this chunk -> removed bits of the panel's remaining words (shared memory only)
-            const int wrem = chunks_here - (cl + 1);
-            if (wrem > 0 && nk > 0) {
-                const int base = s_nk_panel - nk;
-                for (int it = tid; it < nk * wrem; it += kScanThreads) {
-                    const int kk = it / wrem, j = cl + 1 + (it - kk * wrem);
-                    const unsigned long long v = buf[(s_rows[base + kk] - r0) * kPanelChunks + j];
-                    if (v) atomicOr(&removed[w0 + j], v);
-                }
-            }
-            __syncthreads();
-        }
-        // kept rows of the whole panel -> removed bits right of the panel, from global memory:
-        // every thread takes (kept row, word) items, a row's words by consecutive threads
-        const int wfar0 = w0 + kPanelChunks, wfar = W - wfar0;
-        const int nkp = s_nk_panel;
-        if (wfar > 0 && nkp > 0) {
-            const int items = nkp * wfar;
-#pragma unroll 4
-            for (int it = tid; it < items; it += kScanThreads) {
-                const int kk = it / wfar, wi = it - kk * wfar;
-                const unsigned long long v = M[(int64_t)s_rows[kk] * W + wfar0 + wi];
-                if (v) atomicOr(&removed[wfar0 + wi], v);
-            }
-        }
-        __syncthreads();
+        __threadfence();
     }
-    if (EMIT && tid == 0) *num_keep_out = nkeep;
+    __syncthreads();
 }
 
-// ---- ordered compaction of the kept flags (several segments) ---------------------
-// One CTA; each thread takes 8 consecutive positions of `order` per round, so a
-// round covers 8192 boxes with two block-wide barriers.
-constexpr int kEmitThreads = 1024;
-constexpr int kEmitItems = 8;
+__device__ __forceinline__ ulonglong2 ldcg_u64x2(const unsigned long long *p) {
+    ulonglong2 v;
+    asm volatile("ld.global.cg.v2.u64 {%0, %1}, [%2];" : "=l"(v.x), "=l"(v.y) : "l"(p));
+    return v;
+}
+// (kept, removed) words of one chunk: shared memory (LOCAL) or global memory through L2
+template <bool LOCAL>
+__device__ __forceinline__ ulonglong2 kr_load(const unsigned long long *p) {
+    if (LOCAL) {
+        const volatile unsigned long long *v = p;
+        return make_ulonglong2(v[0], v[1]);
+    }
+    return ldcg_u64x2(p);
+}
+template <bool LOCAL>
+__device__ __forceinline__ void kr_store(unsigned long long *p, unsigned long long k, unsigned long long r) {
+    if (LOCAL) {
+        volatile unsigned long long *v = p;
+        v[0] = k;
+        v[1] = r;
+    } else {
+        asm volatile("st.global.cg.v2.u64 [%0], {%1, %2};" ::"l"(p), "l"(k), "l"(r) : "memory");
+    }
+}
+__device__ __forceinline__ unsigned long long ballot64(bool lo, bool hi) {
+    return (unsigned long long)__ballot_sync(0xffffffffu, lo) |
+           ((unsigned long long)__ballot_sync(0xffffffffu, hi) << 32);
+}
+
+// segment that owns packed slot `slot` (last one with pstart <= slot)
+__device__ __forceinline__ int segment_of_slot(const NmsSegment *__restrict__ segs, int nseg, int64_t slot) {
+    int lo = 0, hi = nseg - 1;
+    while (lo < hi) {
+        const int mid = (lo + hi + 1) >> 1;
+        if (segs[mid].pstart <= slot) lo = mid; else hi = mid - 1;
+    }
+    return lo;
+}
+
+// One warp, one 64-box chunk (word c of its segment's mask rows), one round.  Lane l owns rows
+// l and l + 32.  kr_seg: the segment's (kept, removed) word pairs.  Returns true while the chunk
+// still has an undecided box.
+// Both bitmaps only ever gain bits, and a reader that sees an old word merely treats a decided
+// box as undecided for one more round: chunks can be settled concurrently, in any order.
+template <bool LOCAL>
+__device__ bool resolve_chunk(const ResolveArgs &a, const NmsSegment &sg, int c,
+                              unsigned long long *kr_seg, int lane) {
+    const int64_t pos0 = (int64_t)c * 64, len = sg.len;
+    const unsigned long long valid = len - pos0 >= 64 ? ~0ull : ((1ull << (len - pos0)) - 1ull);
+    const ulonglong2 kr0 = kr_load<LOCAL>(kr_seg + 2 * c);
+    unsigned long long Kc = kr0.x, Rc = kr0.y;
+    const unsigned long long und = valid & ~(Kc | Rc);
+    if (und == 0ull) return false;
+
+    const int W = sg.words;
+    const unsigned long long *const M = a.mask + sg.mask_base;
+    const unsigned long long *const S = a.sc.summary + (sg.pstart + pos0) * a.sc.sum_words;
+    unsigned long long D[2];
+    bool exK[2], exU[2];
+#pragma unroll
+    for (int p = 0; p < 2; ++p) {
+        const int q = lane + 32 * p;
+        D[p] = 0ull;
+        exK[p] = exU[p] = false;
+        if ((und >> q) & 1ull) {
+            const int64_t row = pos0 + q;
+            const unsigned long long *mrow = M + row * W;
+            const unsigned long long *srow = S + q * a.sc.sum_words;
+            const int kmax = (int)(row >> 13);           // summary words that can hold a bit: column blocks 0 .. row / 128
+            for (int k = 0; k <= kmax && !exK[p]; ++k) {
+                unsigned long long sb = __ldg(srow + k);
+                while (sb) {
+                    const int J = (k << 6) + __ffsll((long long)sb) - 1;
+                    sb &= sb - 1ull;
+                    const ulonglong2 m = __ldg(reinterpret_cast<const ulonglong2 *>(mrow + 2 * J));
+#pragma unroll
+                    for (int h = 0; h < 2; ++h) {
+                        const unsigned long long mv = h ? m.y : m.x;
+                        const int w = 2 * J + h;
+                        if (mv == 0ull) continue;
+                        if (w < c) {                      // earlier chunk: its current state
+                            const ulonglong2 o = kr_load<LOCAL>(kr_seg + 2 * w);
+                            if (mv & o.x) exK[p] = true;
+                            if (mv & ~(o.x | o.y)) exU[p] = true;
+                        } else if (w == c) {
+                            D[p] = mv;                    // earlier boxes of this chunk
+                        }
+                    }
+                    if (exK[p]) break;
+                }
+            }
+        }
+    }
+    const unsigned long long EXK = ballot64(exK[0], exK[1]);
+    const unsigned long long EXU = ballot64(exU[0], exU[1]);
+    Rc |= und & EXK;
+    unsigned long long cand = und & ~EXK;
+    // chains inside the chunk: peel until nothing changes
+    for (;;) {
+        bool rm[2], kp[2];
+#pragma unroll
+        for (int p = 0; p < 2; ++p) {
+            const int q = lane + 32 * p;
+            const bool in = (cand >> q) & 1ull;
+            rm[p] = in && (D[p] & Kc) != 0ull;
+            kp[p] = in && !rm[p] && (D[p] & cand) == 0ull && !((EXU >> q) & 1ull);
+        }
+        const unsigned long long REM = ballot64(rm[0], rm[1]);
+        const unsigned long long KEEP = ballot64(kp[0], kp[1]);
+        if ((REM | KEEP) == 0ull) break;
+        Kc |= KEEP;
+        Rc |= REM;
+        cand &= ~(REM | KEEP);
+    }
+    if (lane == 0 && (Kc != kr0.x || Rc != kr0.y)) kr_store<LOCAL>(kr_seg + 2 * c, Kc, Rc);
+    return cand != 0ull;
+}
+
+// kept bits of one chunk -> per-box flags (indexed like the caller's boxes)
+__device__ __forceinline__ void write_flags(const ResolveArgs &a, const NmsSegment &sg, int c,
+                                            unsigned long long K, int lane) {
+#pragma unroll
+    for (int p = 0; p < 2; ++p) {
+        const int q = lane + 32 * p;
+        const int64_t pos = (int64_t)c * 64 + q;
+        if (pos < sg.len) a.flags[seg_order_at(a, sg.start + pos)] = (uint8_t)((K >> q) & 1ull);
+    }
+}
+
+__device__ __forceinline__ int block_sum(int v, int *s_red /* kResWarps */) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
+    __syncthreads();
+    if (lane == 0) s_red[warp] = v;
+    __syncthreads();
+    int t = 0;
+#pragma unroll
+    for (int w = 0; w < kResWarps; ++w) t += s_red[w];
+    return t;
+}
 
 template <bool MC>
-__global__ void __launch_bounds__(kEmitThreads)
-nms_emit_kernel(const int64_t *__restrict__ order, const uint8_t *__restrict__ flags, int64_t n,
-                const int64_t *__restrict__ n_dev, int64_t idx_mask, int64_t *__restrict__ keep_out,
-                int64_t *__restrict__ num_keep_out, const McOut mc) {
-    __shared__ int warp_cnt[32];
+__global__ void __launch_bounds__(kResThreads, 1)
+nms_resolve_kernel(const ResolveArgs a) {
+    __shared__ __align__(16) unsigned long long s_kr[2 * kLocalChunks];
+    __shared__ int s_red[kResWarps];
+    __shared__ int s_warp_cnt[kResWarps];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    if (n_dev) n = *n_dev;
-    const int64_t cap = MC ? mc.cap : n;
-    int64_t base = 0;
-    for (int64_t start = 0; start < n && base < cap; start += kEmitThreads * kEmitItems) {
+    const unsigned int G = gridDim.x;
+
+    // ---- small segments: one CTA each, rounds separated by __syncthreads ------------------
+    for (int s = blockIdx.x; s < a.nseg; s += G) {
+        const NmsSegment sg = a.segs[s];
+        const int nch = sg.row_blocks;
+        if (sg.len <= 0 || nch > kLocalChunks) continue;
+        for (int i = tid; i < 2 * nch; i += kResThreads) s_kr[i] = 0ull;
+        __syncthreads();
+        for (;;) {
+            bool left = false;
+            for (int c = warp; c < nch; c += kResWarps) left |= resolve_chunk<true>(a, sg, c, s_kr, lane);
+            if (!__syncthreads_or(left)) break;
+        }
+        for (int c = warp; c < nch; c += kResWarps) write_flags(a, sg, c, s_kr[2 * c], lane);
+        __syncthreads();
+    }
+
+    // ---- large segments: the whole grid, rounds separated by a grid barrier -------------------
+    if (a.has_large) {
+        const int64_t gwarp = (int64_t)blockIdx.x * kResWarps + warp, nwarps = (int64_t)G * kResWarps;
+        volatile unsigned int *pend = a.sc.sync + 2;
+        for (unsigned int round = 0;; ++round) {
+            // slot (round + 1) % 3 was last read after the barrier of round - 2; every CTA has passed
+            // the barrier of round - 1 since, so it can be cleared for the next round now
+            if (blockIdx.x == 0 && tid == 0) pend[(round + 1) % 3] = 0u;
+            bool left = false;
+            for (int64_t gw = gwarp; gw < a.chunks; gw += nwarps) {
+                const NmsSegment &sg = a.segs[segment_of_slot(a.segs, a.nseg, gw * 64)];
+                const int64_t c = gw - (sg.pstart >> 6);
+                if (sg.row_blocks <= kLocalChunks || c >= sg.row_blocks) continue;
+                left |= resolve_chunk<false>(a, sg, (int)c, a.sc.kr + 2 * (sg.pstart >> 6), lane);
+            }
+            if (left && lane == 0) pend[round % 3] = 1u;
+            grid_barrier(a.sc.sync, G);
+            if (pend[round % 3] == 0u) break;
+        }
+        for (int64_t gw = gwarp; gw < a.chunks; gw += nwarps) {
+            const NmsSegment &sg = a.segs[segment_of_slot(a.segs, a.nseg, gw * 64)];
+            const int64_t c = gw - (sg.pstart >> 6);
+            if (sg.row_blocks <= kLocalChunks || c >= sg.row_blocks) continue;
+            write_flags(a, sg, (int)c, ldcg_u64x2(a.sc.kr + 2 * gw).x, lane);
+        }
+    }
+    grid_barrier(a.sc.sync, G);
+
+    // ---- ordered compaction in global score order: count, barrier, write ----------------------
+    const int64_t n = a.n_dev ? *a.n_dev : a.n;
+    const int64_t cap = MC ? a.mc.cap : n;
+    const int64_t per = ((n + G - 1) / G + kEmitTile - 1) / kEmitTile * kEmitTile;
+    const int64_t lo = min(n, (int64_t)blockIdx.x * per), hi = min(n, lo + per);
+    {
+        int cnt = 0;
+        for (int64_t i = lo + tid; i < hi; i += kResThreads) cnt += __ldcg(a.flags + order_at(a, i)) != 0;
+        cnt = block_sum(cnt, s_red);
+        if (tid == 0) a.sc.block_counts[blockIdx.x] = cnt;
+    }
+    grid_barrier(a.sc.sync, G);
+    int before = 0, total = 0;
+    for (unsigned int b = tid; b < G; b += kResThreads) {
+        const int cb = __ldcg(a.sc.block_counts + b);
+        total += cb;
+        if (b < blockIdx.x) before += cb;
+    }
+    before = block_sum(before, s_red);
+    total = block_sum(total, s_red);
+    if (blockIdx.x == 0 && tid == 0) *a.num_keep_out = (int64_t)total < cap ? (int64_t)total : cap;
+
+    int64_t base = before;
+    for (int64_t start = lo; start < hi && base < cap; start += kEmitTile) {
         const int64_t i0 = start + (int64_t)tid * kEmitItems;
         int64_t idx[kEmitItems];
         unsigned f = 0;
 #pragma unroll
-        for (int k = 0; k < kEmitItems; ++k) {
-            idx[k] = i0 + k < n ? (order[i0 + k] & idx_mask) : -1;
-        }
+        for (int k = 0; k < kEmitItems; ++k) idx[k] = i0 + k < hi ? order_at(a, i0 + k) : -1;
 #pragma unroll
         for (int k = 0; k < kEmitItems; ++k)
-            if (idx[k] >= 0 && flags[idx[k]] != 0) f |= 1u << k;
+            if (idx[k] >= 0 && __ldcg(a.flags + idx[k]) != 0) f |= 1u << k;
         const int cnt = __popc(f);
         int incl = cnt;
 #pragma unroll
@@ -471,38 +603,37 @@ nms_emit_kernel(const int64_t *__restrict__ order, const uint8_t *__restrict__ f
             const int v = __shfl_up_sync(0xffffffffu, incl, d);
             if (lane >= d) incl += v;
         }
-        if (lane == 31) warp_cnt[warp] = incl;
         __syncthreads();
-        int before = 0, total = 0;
+        if (lane == 31) s_warp_cnt[warp] = incl;
+        __syncthreads();
+        int wbefore = 0, wtotal = 0;
 #pragma unroll
-        for (int w = 0; w < 32; ++w) {
-            const int c = warp_cnt[w];
-            before += (w < warp) ? c : 0;
-            total += c;
+        for (int w = 0; w < kResWarps; ++w) {
+            const int cw = s_warp_cnt[w];
+            wbefore += (w < warp) ? cw : 0;
+            wtotal += cw;
         }
-        int64_t pos = base + before + incl - cnt;
+        int64_t pos = base + wbefore + incl - cnt;
 #pragma unroll
         for (int k = 0; k < kEmitItems; ++k) {
             if ((f & (1u << k)) && pos < cap) {
-                keep_out[pos] = idx[k];
+                a.keep_out[pos] = idx[k];
                 if (MC) {
                     // the output row of a kept candidate: its box, its (factored) score, its class
-                    const int64_t row = idx[k] / mc.classes;
-                    const int cls = (int)(idx[k] - row * mc.classes);
-                    const float *bx = mc.boxes + (mc.shared ? row : idx[k]) * 5;
-                    float sc = mc.scores[row * mc.score_stride + cls];
-                    if (mc.factors) sc *= mc.factors[row];
-                    float *d = mc.dets_out + pos * 6;
+                    const int64_t row = idx[k] / a.mc.classes;
+                    const int cls = (int)(idx[k] - row * a.mc.classes);
+                    const float *bx = a.mc.boxes + (a.mc.shared ? row : idx[k]) * 5;
+                    float sc = a.mc.scores[row * a.mc.score_stride + cls];
+                    if (a.mc.factors) sc *= a.mc.factors[row];
+                    float *d = a.mc.dets_out + pos * 6;
                     d[0] = bx[0]; d[1] = bx[1]; d[2] = bx[2]; d[3] = bx[3]; d[4] = bx[4]; d[5] = sc;
-                    mc.labels_out[pos] = cls;
+                    a.mc.labels_out[pos] = cls;
                 }
             }
             if (f & (1u << k)) ++pos;
         }
-        base += total;
-        __syncthreads();
+        base += wtotal;
     }
-    if (tid == 0) *num_keep_out = base < cap ? base : cap;
 }
 
 // ---- host-side plan + launch -------------------------------------------------------
@@ -517,7 +648,7 @@ void nms_plan(int64_t n, const int64_t *seg_offsets_host, int64_t num_segments, 
         num_segments = 1;
     }
     plan->num_segments = num_segments;
-    int64_t tiles = 0, words = 0, slots = 0;
+    int64_t tiles = 0, words = 0, slots = 0, max_blocks = 0;
     for (int64_t s = 0; s < num_segments; ++s) {
         const int64_t start = seg_offsets_host[s], len = seg_offsets_host[s + 1] - start;
         const int64_t C = (len + kTile - 1) / kTile;
@@ -534,111 +665,144 @@ void nms_plan(int64_t n, const int64_t *seg_offsets_host, int64_t num_segments, 
         slots += C * kTile;
         tiles += C * (C + 1) / 2;
         words += len * 2 * C;
+        max_blocks = C > max_blocks ? C : max_blocks;
     }
     plan->n_pad = slots > 0 ? slots : kTile;   // every segment padded to whole 128-slot blocks
     plan->total_tiles = tiles;
     plan->mask_words = words;
+    plan->sum_words = nms_sum_words(max_blocks);
+    plan->max_chunks = 2 * max_blocks;
     size_t off = 0;
     plan->off_packed = off;   off = align_up(off + (size_t)plan->n_pad * kPackedBytesPerBox, 256);
     plan->off_segments = off; off = align_up(off + (size_t)num_segments * sizeof(NmsSegment), 256);
     plan->off_mask = off;     off = align_up(off + (size_t)words * sizeof(uint64_t), 256);
     plan->off_flags = off;    off = align_up(off + (size_t)n, 256);
-    plan->off_seg_keep = off;
+    plan->off_kr = off;       off = align_up(off + (size_t)(plan->n_pad / 64) * 16, 256);
+    plan->off_summary = off;  off = align_up(off + (size_t)plan->n_pad * plan->sum_words * 8, 256);
+    plan->off_sync = off;     off = align_up(off + kNmsSyncWords * sizeof(unsigned int), 256);
+    plan->off_counts = off;   off = align_up(off + kNmsMaxBlocks * sizeof(int), 256);
     plan->total_bytes = off;
 }
 
-size_t nms_scan_smem_bytes(int max_words) {
-    return (size_t)(2 * kPanelWords + max_words) * sizeof(unsigned long long);
+// CTAs of the resolve grid: all co-resident (cooperative launch), at most one per SM
+static int resolve_grid_limit(bool mc) {
+    static int limit[2] = {0, 0};
+    if (limit[mc] == 0) {
+        int dev = 0, sms = 0, per_sm = 0;
+        if (cudaGetDevice(&dev) != cudaSuccess ||
+            cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess)
+            return -1;
+        const cudaError_t e = mc
+            ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, nms_resolve_kernel<true>, kResThreads, 0)
+            : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, nms_resolve_kernel<false>, kResThreads, 0);
+        if (e != cudaSuccess || per_sm < 1) return -1;
+        limit[mc] = sms < kNmsMaxBlocks ? sms : kNmsMaxBlocks;   // one 1024-thread CTA per SM
+    }
+    return limit[mc];
+}
+
+static int launch_mask(const MaskArgs &g, int64_t tiles, cudaStream_t stream) {
+    if (tiles > 0x7fffffffLL) return -1;
+    if (tiles <= 0) return 0;
+    // one CTA per tile; running CTAs steal the not-yet-launched ones (launch control)
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)tiles);
+    cfg.blockDim = dim3(kThreads);
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;   // overlap with the pack kernel
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, nms_mask_kernel, g) == cudaSuccess ? 0 : -3;
+}
+
+static int launch_resolve(const ResolveArgs &a, cudaStream_t stream) {
+    const bool mc = a.mc.dets_out != nullptr;
+    const int limit = resolve_grid_limit(mc);
+    if (limit < 1) return -3;
+    // one chunk per warp in the first round, one small segment per CTA
+    int64_t want = (a.chunks + kResWarps - 1) / kResWarps;
+    if (want < a.nseg) want = a.nseg;
+    if (want < 1) want = 1;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)(want < limit ? want : limit));
+    cfg.blockDim = dim3(kResThreads);
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeCooperative;              // the grid barrier needs every CTA resident
+    attr[0].val.cooperative = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    const cudaError_t e = mc ? cudaLaunchKernelEx(&cfg, nms_resolve_kernel<true>, a)
+                             : cudaLaunchKernelEx(&cfg, nms_resolve_kernel<false>, a);
+    return e == cudaSuccess ? 0 : -3;
 }
 
 int launch_nms(const NmsPlan &plan, const void *packed, const NmsSegment *segments_dev,
-               int max_words, const int64_t *order, const int64_t *seg_order, float thr,
-               uint64_t *mask, uint8_t *flags, int64_t *keep_out, int64_t *num_keep_out,
+               const int64_t *order, const int64_t *seg_order, float thr, uint64_t *mask,
+               uint8_t *flags, const NmsScratch &scratch, int64_t *keep_out, int64_t *num_keep_out,
                cudaStream_t stream) {
     const PackedView P = packed_view(packed, plan.n_pad);
-    if (plan.total_tiles > 0x7fffffffLL) return -1;
-    if (plan.total_tiles > 0) {
-        MaskArgs g;
-        g.p0 = P.p0; g.p1 = P.p1; g.pr = P.pr; g.pt = P.pt;
-        g.segs = segments_dev;
-        g.nseg = (int)plan.num_segments;
-        g.thr = thr;
-        g.mask = reinterpret_cast<unsigned long long *>(mask);
-        g.total_tiles = nullptr;
-        // one CTA per tile; running CTAs steal the not-yet-launched ones (launch control)
-        cudaLaunchConfig_t cfg = {};
-        cfg.gridDim = dim3((unsigned)plan.total_tiles);
-        cfg.blockDim = dim3(kThreads);
-        cfg.stream = stream;
-        cudaLaunchAttribute attr[1];
-        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-        attr[0].val.programmaticStreamSerializationAllowed = 1;   // overlap with the pack kernel
-        cfg.attrs = attr;
-        cfg.numAttrs = 1;
-        if (cudaLaunchKernelEx(&cfg, nms_mask_kernel, g) != cudaSuccess) return -3;
-    }
-    if (cudaGetLastError() != cudaSuccess) return -3;
-    const size_t dyn = nms_scan_smem_bytes(max_words);
-    const bool single = plan.num_segments == 1;
-    if (single) {
-        if (cudaFuncSetAttribute(nms_scan_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 (int)dyn) != cudaSuccess)
-            return -3;
-        nms_scan_kernel<true><<<1, kScanThreads, dyn, stream>>>(
-            segments_dev, reinterpret_cast<const unsigned long long *>(mask), seg_order, ~0ll, flags,
-            keep_out, num_keep_out);
-    } else {
-        if (cudaFuncSetAttribute(nms_scan_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 (int)dyn) != cudaSuccess)
-            return -3;
-        nms_scan_kernel<false><<<(unsigned)plan.num_segments, kScanThreads, dyn, stream>>>(
-            segments_dev, reinterpret_cast<const unsigned long long *>(mask), seg_order, ~0ll, flags,
-            keep_out, num_keep_out);
-        if (cudaGetLastError() != cudaSuccess) return -3;
-        McOut none = {};
-        nms_emit_kernel<false><<<1, kEmitThreads, 0, stream>>>(order, flags, plan.n, nullptr, ~0ll,
-                                                              keep_out, num_keep_out, none);
-    }
-    return cudaGetLastError() == cudaSuccess ? 0 : -3;
+    MaskArgs g;
+    g.p0 = P.p0; g.p1 = P.p1; g.pr = P.pr; g.pt = P.pt;
+    g.segs = segments_dev;
+    g.nseg = (int)plan.num_segments;
+    g.thr = thr;
+    g.area_ratio = thr - 1e-4f;
+    g.mask = reinterpret_cast<unsigned long long *>(mask);
+    g.summary = scratch.summary;
+    g.sum_words = scratch.sum_words;
+    g.total_tiles = nullptr;
+    int rc = launch_mask(g, plan.total_tiles, stream);
+    if (rc) return rc;
+    ResolveArgs a = {};
+    a.segs = segments_dev;
+    a.nseg = (int)plan.num_segments;
+    a.mask = g.mask;
+    a.sc = scratch;
+    a.has_large = plan.max_chunks > kLocalChunks;
+    a.chunks = plan.n_pad / 64;
+    a.order = order;
+    a.seg_order = seg_order;
+    a.n = plan.n;
+    a.n_dev = nullptr;
+    a.flags = flags;
+    a.keep_out = keep_out;
+    a.num_keep_out = num_keep_out;
+    return launch_resolve(a, stream);
 }
 
-int launch_nms_device_planned(const NmsDevLaunch &a, cudaStream_t stream) {
-    const PackedView P = packed_view(a.packed, a.n_pad_bound);
-    if (a.tiles_bound > 0x7fffffffLL) return -1;
-    if (a.tiles_bound > 0) {
-        MaskArgs g;
-        g.p0 = P.p0; g.p1 = P.p1; g.pr = P.pr; g.pt = P.pt;
-        g.segs = a.segs_dev;
-        g.nseg = a.nseg;
-        g.thr = a.thr;
-        g.mask = reinterpret_cast<unsigned long long *>(a.mask);
-        g.total_tiles = a.total_tiles_dev;
-        cudaLaunchConfig_t cfg = {};
-        cfg.gridDim = dim3((unsigned)a.tiles_bound);
-        cfg.blockDim = dim3(kThreads);
-        cfg.stream = stream;
-        cudaLaunchAttribute attr[1];
-        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-        attr[0].val.programmaticStreamSerializationAllowed = 1;   // overlap with the pack kernel
-        cfg.attrs = attr;
-        cfg.numAttrs = 1;
-        if (cudaLaunchKernelEx(&cfg, nms_mask_kernel, g) != cudaSuccess) return -3;
-    }
-    const size_t dyn = nms_scan_smem_bytes(a.max_words_bound);
-    if (cudaFuncSetAttribute(nms_scan_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             (int)dyn) != cudaSuccess)
-        return -3;
-    nms_scan_kernel<false><<<(unsigned)a.nseg, kScanThreads, dyn, stream>>>(
-        a.segs_dev, reinterpret_cast<const unsigned long long *>(a.mask), a.seg_order, a.idx_mask,
-        a.flags, a.keep_out, a.num_keep_out);
-    if (cudaGetLastError() != cudaSuccess) return -3;
-    if (a.mc.dets_out)
-        nms_emit_kernel<true><<<1, kEmitThreads, 0, stream>>>(a.order, a.flags, a.n_bound, a.n_dev,
-                                                             a.idx_mask, a.keep_out, a.num_keep_out, a.mc);
-    else
-        nms_emit_kernel<false><<<1, kEmitThreads, 0, stream>>>(a.order, a.flags, a.n_bound, a.n_dev,
-                                                              a.idx_mask, a.keep_out, a.num_keep_out, a.mc);
-    return cudaGetLastError() == cudaSuccess ? 0 : -3;
+int launch_nms_device_planned(const NmsDevLaunch &d, cudaStream_t stream) {
+    const PackedView P = packed_view(d.packed, d.n_pad_bound);
+    MaskArgs g;
+    g.p0 = P.p0; g.p1 = P.p1; g.pr = P.pr; g.pt = P.pt;
+    g.segs = d.segs_dev;
+    g.nseg = d.nseg;
+    g.thr = d.thr;
+    g.area_ratio = d.thr - 1e-4f;
+    g.mask = reinterpret_cast<unsigned long long *>(d.mask);
+    g.summary = d.scratch.summary;
+    g.sum_words = d.scratch.sum_words;
+    g.total_tiles = d.total_tiles_dev;
+    int rc = launch_mask(g, d.tiles_bound, stream);
+    if (rc) return rc;
+    ResolveArgs a = {};
+    a.segs = d.segs_dev;
+    a.nseg = d.nseg;
+    a.mask = g.mask;
+    a.sc = d.scratch;
+    a.has_large = d.max_chunks_bound > kLocalChunks;
+    a.chunks = d.n_pad_bound / 64;
+    a.order32 = d.order32;
+    a.seg_order32 = d.seg_order32;
+    a.n = d.n_bound;
+    a.n_dev = d.n_dev;
+    a.flags = d.flags;
+    a.keep_out = d.keep_out;
+    a.num_keep_out = d.num_keep_out;
+    a.mc = d.mc;
+    return launch_resolve(a, stream);
 }
 
 }  // namespace rotgeo

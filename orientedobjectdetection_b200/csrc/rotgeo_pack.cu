@@ -48,7 +48,7 @@ __device__ __forceinline__ int64_t slot_position(const PackSet &s, int64_t i, in
 
 // source row of position `pos` and the centre offset that goes with it
 __device__ __forceinline__ int64_t position_source(const PackSet &s, int64_t pos, float &offset) {
-    const int64_t v = s.gather ? (s.gather[pos] & s.gather_mask) : pos;
+    const int64_t v = s.gather32 ? (int64_t)s.gather32[pos] : (s.gather ? s.gather[pos] : pos);
     offset = 0.f;
     if (s.mc_classes > 0) {
         const int64_t row = v / s.mc_classes;
@@ -128,6 +128,17 @@ pack_kernel(PackSet s1, PackSet s2, float min_wh, float cell) {
         cx = b[0] + o; cy = b[1] + o; w = b[2]; h = b[3]; th = b[4];
     }
     const float inv_cell = cell > 0.f ? 1.f / cell : sample_inv_cell(s1, s2);
+
+    // NMS: scratch of the resolve stage starts from zero (the mask kernel only touches it
+    // after its griddepcontrol.wait, i.e. after this grid has completed)
+    if (in_set && !second && s1.z_kr) {
+        for (int k = 0; k < s1.z_sum_words; ++k) s1.z_summary[i * s1.z_sum_words + k] = 0ull;
+        if ((i & 63) == 0) {
+            s1.z_kr[2 * (i >> 6)] = 0ull;
+            s1.z_kr[2 * (i >> 6) + 1] = 0ull;
+        }
+        if (i < kNmsSyncWords) s1.z_sync[i] = 0u;
+    }
 
     uint32_t xm = 0u, ym = 0u;
     if (in_set) {
@@ -211,10 +222,14 @@ PackSet make_pack_set(const float *boxes, int64_t n, int stride, const int64_t *
     s.segs = nullptr;
     s.nseg = 0;
     s.n_dev = nullptr;
-    s.gather_mask = ~0ll;
+    s.gather32 = nullptr;
     s.mc_classes = 0;
     s.mc_shared = 0;
     s.mc_max = nullptr;
+    s.z_kr = nullptr;
+    s.z_summary = nullptr;
+    s.z_sum_words = 0;
+    s.z_sync = nullptr;
     s.boxes = boxes;
     s.n = n;
     s.stride = stride;

@@ -286,3 +286,19 @@ def test_multiclass_nms_variants_fused_vs_generic():
     d, l = rg.multiclass_nms_rotated(_cuda(per_cls), _cuda(np.zeros((n, C + 1), np.float32)), 0.05,
                                      dict(iou_thr=0.1), 100)
     assert d.shape == (0, 6) and l.shape == (0,)
+
+
+@pytest.mark.parametrize('n', [1500, 9000])
+def test_nms_chain_needs_many_rounds(n):
+    """a chain of boxes, each suppressing the next one, scores descending along the chain:
+    the decision of box i depends on all i-1 before it (the worst case for the round-based
+    resolve kernel, both the one-CTA path and the grid path)."""
+    b = np.zeros((n, 5), np.float32)
+    b[:, 0] = np.arange(n) * 6.0
+    b[:, 2] = 10.0
+    b[:, 3] = 10.0
+    s = np.linspace(1.0, 0.1, n).astype(np.float32)
+    _, want = ref.nms_rotated(b, s, 0.1)
+    _, keep = rg.nms_rotated(_cuda(b), _cuda(s), 0.1)
+    assert keep.cpu().tolist() == want.tolist()
+    assert want.tolist() == list(range(0, n, 2))
