@@ -31,6 +31,7 @@ extern "C" {
 #define ROTGEO_ERR_ARG (-1)        /* bad argument (null pointer, negative size, bad mode) */
 #define ROTGEO_ERR_WORKSPACE (-2)  /* workspace too small / misaligned */
 #define ROTGEO_ERR_CUDA (-3)       /* a CUDA runtime call or launch failed */
+#define ROTGEO_ERR_RANGE (-4)      /* rotgeo_nms_prepare: ids span >= 2^16 values / too many segments */
 
 #define ROTGEO_MODE_IOU 0
 #define ROTGEO_MODE_IOF 1          /* intersection / area(first box) */
@@ -119,6 +120,45 @@ int rotgeo_nms(const float *boxes, int64_t n, int stride, const float *offsets,
                const int64_t *order, const int64_t *seg_order, const int64_t *seg_offsets_host,
                int64_t num_segments, float iou_threshold, int64_t *keep_out,
                int64_t *num_keep_out, void *workspace, size_t workspace_bytes, void *stream);
+
+/* ---- rotated NMS front-end: orders and segment sizes ----------------------------
+ * What the reference does in python/ATen around the native op
+ * (mmcv/ops/nms.py nms_rotated: scores.sort(0, descending=True) + index_select;
+ * mmcv/ops/nms.py batched_nms: boxes.max(), the id * (max + 1) offsets, the add),
+ * in two calls:
+ *
+ *   rotgeo_nms_prepare   stable descending score order of scores (n,); with seg_ids
+ *                        (n,) int64 also the segment-major order (ascending id, score
+ *                        order inside an id) and the size of every segment present.
+ *                        The sizes are returned to the HOST (seg_counts_host[0 ..
+ *                        *num_segments_host), ascending id) because the host lays out
+ *                        the suppression mask from them: with seg_ids this call
+ *                        synchronises `stream` (the one device->host read of the whole
+ *                        NMS); without seg_ids it does not.  ROTGEO_ERR_RANGE when the
+ *                        ids span 65536 values or more, or more than seg_cap segments
+ *                        are present (callers then split the job).
+ *   rotgeo_nms_prepared  pack + mask + resolve over the orders left in `prep`.  Centre
+ *                        offsets: `offsets` (n,) float added to cx, cy, or, with
+ *                        id_offsets != 0, mmcv.batched_nms's own
+ *                        float(id) * (max(cx,cy) + max(w,h) + 1) computed in fp32 on the
+ *                        device (the maxima were reduced by rotgeo_nms_prepare).
+ *                        keep_out (n,) receives the kept indices in GLOBAL descending
+ *                        score order; workspace: rotgeo_nms_workspace_bytes() of the
+ *                        prefix sums of seg_counts_host.
+ *
+ * prep: device buffer of rotgeo_nms_prepare_bytes(n) bytes, 16-byte aligned; it must stay
+ * untouched between the two calls.  seg_ids must be the same pointer in both calls
+ * (nullptr = one segment). */
+size_t rotgeo_nms_prepare_bytes(int64_t n);
+int rotgeo_nms_prepare(const float *boxes, int64_t n, int stride, const float *scores,
+                       const int64_t *seg_ids, void *prep, size_t prep_bytes,
+                       int64_t *seg_counts_host, int64_t seg_cap, int64_t *num_segments_host,
+                       void *stream);
+int rotgeo_nms_prepared(const float *boxes, int64_t n, int stride, const float *offsets,
+                        const int64_t *seg_ids, int id_offsets, const void *prep,
+                        const int64_t *seg_counts_host, int64_t num_segments, float iou_threshold,
+                        int64_t *keep_out, int64_t *num_keep_out, void *workspace,
+                        size_t workspace_bytes, void *stream);
 
 /* ---- class-batched rotated NMS, fused ----------------------------------------
  * Replaces the whole body of the reference's multiclass_nms_rotated

@@ -14,8 +14,10 @@ SYMBOLS = (
     'rotgeo_version', 'rotgeo_last_error', 'rotgeo_packed_bytes', 'rotgeo_pack_boxes',
     'rotgeo_iou_workspace_bytes', 'rotgeo_iou_pairwise', 'rotgeo_iou_pairwise_packed',
     'rotgeo_iou_aligned', 'rotgeo_nms_workspace_bytes', 'rotgeo_nms',
+    'rotgeo_nms_prepare_bytes', 'rotgeo_nms_prepare', 'rotgeo_nms_prepared',
     'rotgeo_multiclass_nms_workspace_bytes', 'rotgeo_multiclass_nms',
 )
+ERR_RANGE = -4
 
 _lib = None
 
@@ -54,6 +56,12 @@ def load():
     L.rotgeo_nms_workspace_bytes.restype = sz
     L.rotgeo_nms.argtypes = [vp, i64, i32, vp, vp, vp, vp, i64, f32, vp, vp, vp, sz, vp]
     L.rotgeo_nms.restype = i32
+    L.rotgeo_nms_prepare_bytes.argtypes = [i64]
+    L.rotgeo_nms_prepare_bytes.restype = sz
+    L.rotgeo_nms_prepare.argtypes = [vp, i64, i32, vp, vp, vp, sz, vp, i64, vp, vp]
+    L.rotgeo_nms_prepare.restype = i32
+    L.rotgeo_nms_prepared.argtypes = [vp, i64, i32, vp, vp, i32, vp, vp, i64, f32, vp, vp, vp, sz, vp]
+    L.rotgeo_nms_prepared.restype = i32
     L.rotgeo_multiclass_nms_workspace_bytes.argtypes = [i64, i32]
     L.rotgeo_multiclass_nms_workspace_bytes.restype = sz
     L.rotgeo_multiclass_nms.argtypes = [vp, i32, vp, vp, i64, i32, f32, f32, i64, vp, vp, vp, vp, vp, sz, vp]

@@ -140,11 +140,9 @@ def multiclass_nms_rotated(multi_bboxes, multi_scores, score_thr, nms, max_num=-
     n = multi_scores.size(0)
     scores2d = multi_scores[:, :-1]
     # candidates: raw score above the threshold (score_factors are applied afterwards, like
-    # the reference does).  The per-class counts double as the NMS segment sizes, so ONE
-    # device->host read replaces the reference's nonzero() sync and sizes everything.
+    # the reference does)
     valid_mask = scores2d > score_thr
-    counts_host = valid_mask.sum(0).cpu().numpy().astype(np.int64)
-    total = int(counts_host.sum())
+    total = int(valid_mask.sum())
     flat_valid = valid_mask.reshape(-1)
     if hasattr(torch, 'nonzero_static'):
         inds = torch.nonzero_static(flat_valid, size=total).squeeze(1)
@@ -164,10 +162,8 @@ def multiclass_nms_rotated(multi_bboxes, multi_scores, score_thr, nms, max_num=-
         dets = torch.cat([bboxes, scores[:, None]], -1)
         return (dets, labels, inds) if return_inds else (dets, labels)
 
-    max_coordinate = bboxes[:, :2].max() + bboxes[:, 2:4].max()
-    offsets = labels.to(bboxes) * (max_coordinate + 1)
-    keep = ops._nms_keep(bboxes, scores, _iou_thr(nms), seg_ids=labels, offsets=offsets,
-                         seg_counts_host=counts_host)
+    # class separation: label * (max(cx,cy) + max(w,h) + 1) added to cx, cy (id_offsets)
+    keep = ops._nms_keep(bboxes, scores, _iou_thr(nms), seg_ids=labels, id_offsets=True)
     keep = keep.to(bboxes.device)
 
     if max_num > 0:
@@ -257,7 +253,7 @@ def merge_results(results, offsets, img_shape, iou_thr=0.1, device='cpu'):
         dev = ops._cuda_device()
         d = torch.from_numpy(np.ascontiguousarray(allc)).to(dev)
         s = torch.from_numpy(seg).to(dev)
-        keep = ops._nms_keep(d[:, :5], d[:, 5], iou_thr, seg_ids=s, seg_counts_host=np.asarray(counts))
+        keep = ops._nms_keep(d[:, :5], d[:, 5], iou_thr, seg_ids=s)
         keep = keep[torch.sort(s[keep], stable=True).indices]       # class-major, score-desc inside
         kept = d[keep].cpu().numpy()
         kseg = s[keep].cpu().numpy()

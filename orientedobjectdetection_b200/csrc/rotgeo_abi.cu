@@ -192,8 +192,79 @@ int rotgeo_nms(const float *boxes, int64_t n, int stride, const float *offsets,
     }
     // no global order given: kept indices come out segment-major (the caller re-orders)
     if (!order) order = sorder;
-    const int rc = rotgeo::launch_nms(plan, packed, segs_dev, order, sorder, iou_threshold, mask,
-                                      flags, scratch, keep_out, num_keep_out, st);
+    const int rc = rotgeo::launch_nms(plan, packed, segs_dev, order, sorder, nullptr, nullptr,
+                                      iou_threshold, mask, flags, scratch, keep_out, num_keep_out, st);
+    if (rc == -1) return fail(ROTGEO_ERR_ARG, "nms: too many tiles");
+    if (rc) return cuda_fail("nms launch");
+    return ROTGEO_OK;
+}
+
+size_t rotgeo_nms_prepare_bytes(int64_t n) { return rotgeo::nms_prepare_bytes(n); }
+
+int rotgeo_nms_prepare(const float *boxes, int64_t n, int stride, const float *scores,
+                       const int64_t *seg_ids, void *prep, size_t prep_bytes,
+                       int64_t *seg_counts_host, int64_t seg_cap, int64_t *num_segments_host,
+                       void *stream) {
+    if (n <= 0 || n > 0x7fffffffLL || stride < 5)
+        return fail(ROTGEO_ERR_ARG, "nms_prepare: n=%lld stride=%d", (long long)n, stride);
+    if (!boxes || !scores || !prep || !seg_counts_host || seg_cap < 1 || !num_segments_host)
+        return fail(ROTGEO_ERR_ARG, "nms_prepare: null pointer");
+    if (!aligned16(prep) || prep_bytes < rotgeo::nms_prepare_bytes(n))
+        return fail(ROTGEO_ERR_WORKSPACE, "nms_prepare: buffer %zu < %zu bytes or misaligned", prep_bytes,
+                    rotgeo::nms_prepare_bytes(n));
+    const int rc = rotgeo::nms_prepare(boxes, n, stride, scores, seg_ids, prep, seg_counts_host, seg_cap,
+                                       num_segments_host, (cudaStream_t)stream);
+    if (rc == -4) return fail(ROTGEO_ERR_RANGE, "nms_prepare: segment ids span 65536 values or more");
+    if (rc == -5) return fail(ROTGEO_ERR_RANGE, "nms_prepare: more than %lld segments", (long long)seg_cap);
+    if (rc) return cuda_fail("nms_prepare");
+    return ROTGEO_OK;
+}
+
+int rotgeo_nms_prepared(const float *boxes, int64_t n, int stride, const float *offsets,
+                        const int64_t *seg_ids, int id_offsets, const void *prep,
+                        const int64_t *seg_counts_host, int64_t num_segments, float iou_threshold,
+                        int64_t *keep_out, int64_t *num_keep_out, void *workspace,
+                        size_t workspace_bytes, void *stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    if (n <= 0 || stride < 5 || num_segments < 1)
+        return fail(ROTGEO_ERR_ARG, "nms_prepared: n=%lld stride=%d segments=%lld", (long long)n, stride,
+                    (long long)num_segments);
+    if (!boxes || !prep || !seg_counts_host || !keep_out || !num_keep_out)
+        return fail(ROTGEO_ERR_ARG, "nms_prepared: null pointer");
+    if (id_offsets && !seg_ids) return fail(ROTGEO_ERR_ARG, "nms_prepared: id_offsets without seg_ids");
+    if (!seg_ids && num_segments != 1)
+        return fail(ROTGEO_ERR_ARG, "nms_prepared: several segments need the seg_ids given to prepare");
+    std::vector<int64_t> seg_off((size_t)num_segments + 1, 0);
+    for (int64_t s = 0; s < num_segments; ++s) {
+        if (seg_counts_host[s] < 0) return fail(ROTGEO_ERR_ARG, "nms_prepared: negative segment size");
+        seg_off[(size_t)s + 1] = seg_off[(size_t)s] + seg_counts_host[s];
+    }
+    if (seg_off[(size_t)num_segments] != n)
+        return fail(ROTGEO_ERR_ARG, "nms_prepared: segment sizes do not add up to n");
+    rotgeo::NmsPlan plan;
+    std::vector<rotgeo::NmsSegment> segs((size_t)num_segments);
+    rotgeo::nms_plan(n, seg_off.data(), num_segments, &plan, segs.data());
+    if (!workspace || !aligned16(workspace) || workspace_bytes < plan.total_bytes)
+        return fail(ROTGEO_ERR_WORKSPACE, "nms_prepared: workspace %zu < %zu bytes or misaligned",
+                    workspace_bytes, plan.total_bytes);
+    for (const auto &g : segs)
+        if (g.words / 2 >= 65536)
+            return fail(ROTGEO_ERR_ARG, "nms: a segment of more than %d boxes is not supported", 65535 * 128);
+    char *ws = reinterpret_cast<char *>(workspace);
+    rotgeo::NmsSegment *segs_dev = reinterpret_cast<rotgeo::NmsSegment *>(ws + plan.off_segments);
+    rotgeo::NmsScratch scratch;
+    scratch.kr = reinterpret_cast<unsigned long long *>(ws + plan.off_kr);
+    scratch.summary = reinterpret_cast<unsigned long long *>(ws + plan.off_summary);
+    scratch.sum_words = plan.sum_words;
+    scratch.sync = reinterpret_cast<unsigned int *>(ws + plan.off_sync);
+    scratch.block_counts = reinterpret_cast<int *>(ws + plan.off_counts);
+    if (cudaMemcpyAsync(segs_dev, segs.data(), segs.size() * sizeof(rotgeo::NmsSegment),
+                        cudaMemcpyHostToDevice, st) != cudaSuccess)
+        return cuda_fail("nms segment upload");
+    const int rc = rotgeo::launch_nms_prepared(
+        boxes, n, stride, offsets, id_offsets ? seg_ids : nullptr, seg_ids != nullptr, prep, plan, segs_dev,
+        iou_threshold, ws + plan.off_packed, reinterpret_cast<uint64_t *>(ws + plan.off_mask),
+        reinterpret_cast<uint8_t *>(ws + plan.off_flags), scratch, keep_out, num_keep_out, st);
     if (rc == -1) return fail(ROTGEO_ERR_ARG, "nms: too many tiles");
     if (rc) return cuda_fail("nms launch");
     return ROTGEO_OK;

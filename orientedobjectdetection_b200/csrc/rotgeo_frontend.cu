@@ -24,7 +24,10 @@
 // Sizes that depend on the data (candidates, tiles, mask words) never reach the host:
 // grids and workspace are sized for the worst case (every class keeps all n rows)
 // and the kernels read the actual counts from the device-side header.
+#include <vector>
+
 #include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_run_length_encode.cuh>
 
 #include "rotgeo_device.cuh"
 #include "rotgeo_internal.h"
@@ -265,6 +268,204 @@ int launch_multiclass_nms(const float *multi_bboxes, int shared, const float *mu
     a.mc.labels_out = labels_out;
     a.mc.cap = cap;
     return launch_nms_device_planned(a, stream);
+}
+
+
+// ============================================================================================
+// Generic front-end: score order and segment order of (scores[, ids]) for rotgeo_nms_prepared.
+// Replaces what the reference does around mmcv.ops.nms_rotated / batched_nms
+// (mmcv/ops/nms.py: scores.sort(descending=True), the per-id loop or the offset trick) and
+// what this package used to do with a dozen torch launches: key transform, one 64-bit sort,
+// unique() for the segment sizes.  The ONE device->host read of the call sequence — the
+// sizes of the segments, which the host needs to lay out the mask — happens here.
+//
+//   prep_keys_kernel    32-bit key (descending image of the score) + index; extremes of the
+//                       ids; max(cx,cy) / max(w,h) for the id-derived centre offsets
+//   cub radix sort      stable pairs sort on the 32 key bits: global score order
+//   prep_segkey_kernel  16-bit segment key (id - min id) of every entry of that order
+//   cub radix sort      stable 16-bit pairs sort: segment-major order
+//   cub run-length      sizes of the segments present, ascending id
+// ============================================================================================
+struct PrepHeader {
+    unsigned long long id_max_u, id_min_inv_u;   // images of the extreme ids (atomicMax from zero)
+    unsigned int max_xy, max_wh;
+    float mc_max[2];
+    int range_bad;                               // ids span 2^16 or more
+    int n_runs;
+};
+
+struct PrepLayout {
+    size_t off_hdr, off_keys, off_keys2, off_vals, off_order, off_segkey, off_segkey2, off_seg_order,
+        off_runs_unique, off_runs_count, off_cub, total_bytes;
+    size_t cub_bytes;
+};
+
+static void prep_layout(int64_t n, PrepLayout *l) {
+    size_t c1 = 0, c2 = 0, c3 = 0;
+    cub::DeviceRadixSort::SortPairs(nullptr, c1, (const uint32_t *)nullptr, (uint32_t *)nullptr,
+                                    (const uint32_t *)nullptr, (uint32_t *)nullptr, (int)n, 0, 32);
+    cub::DeviceRadixSort::SortPairs(nullptr, c2, (const uint16_t *)nullptr, (uint16_t *)nullptr,
+                                    (const uint32_t *)nullptr, (uint32_t *)nullptr, (int)n, 0, 16);
+    cub::DeviceRunLengthEncode::Encode(nullptr, c3, (const uint16_t *)nullptr, (uint16_t *)nullptr,
+                                       (int *)nullptr, (int *)nullptr, (int)n);
+    l->cub_bytes = c1 > c2 ? c1 : c2;
+    if (c3 > l->cub_bytes) l->cub_bytes = c3;
+    size_t off = 0;
+    l->off_hdr = off;         off = align_up(off + sizeof(PrepHeader), 256);
+    l->off_keys = off;        off = align_up(off + (size_t)n * 4, 256);
+    l->off_keys2 = off;       off = align_up(off + (size_t)n * 4, 256);
+    l->off_vals = off;        off = align_up(off + (size_t)n * 4, 256);
+    l->off_order = off;       off = align_up(off + (size_t)n * 4, 256);
+    l->off_segkey = off;      off = align_up(off + (size_t)n * 2, 256);
+    l->off_segkey2 = off;     off = align_up(off + (size_t)n * 2, 256);
+    l->off_seg_order = off;   off = align_up(off + (size_t)n * 4, 256);
+    l->off_runs_unique = off; off = align_up(off + (size_t)n * 2, 256);
+    l->off_runs_count = off;  off = align_up(off + (size_t)n * 4, 256);
+    l->off_cub = off;         off = align_up(off + l->cub_bytes, 256);
+    l->total_bytes = off;
+}
+
+size_t nms_prepare_bytes(int64_t n) {
+    if (n <= 0) return 0;
+    PrepLayout l;
+    prep_layout(n, &l);
+    return l.total_bytes;
+}
+
+__device__ __forceinline__ unsigned long long id_image(int64_t id) {   // order-preserving
+    return (unsigned long long)id ^ 0x8000000000000000ull;
+}
+
+__global__ void __launch_bounds__(256)
+prep_keys_kernel(const float *__restrict__ boxes, int stride, const float *__restrict__ scores,
+                 const int64_t *__restrict__ ids, int64_t n, uint32_t *__restrict__ keys,
+                 uint32_t *__restrict__ vals, PrepHeader *__restrict__ hdr) {
+    __shared__ unsigned long long s_id[2];
+    __shared__ unsigned int s_max[2];
+    const int tid = threadIdx.x;
+    if (tid < 2) { s_id[tid] = 0ull; s_max[tid] = 0u; }
+    __syncthreads();
+    const int64_t i = blockIdx.x * (int64_t)blockDim.x + tid;
+    if (i < n) {
+        // descending score: complement of the order-preserving image (+0.0f: -0 -> +0); equal
+        // scores keep their index order because the sort is stable
+        keys[i] = 0xffffffffu - ordered_bits(scores[i] + 0.0f);
+        vals[i] = (uint32_t)i;
+        if (ids) {
+            const unsigned long long u = id_image(ids[i]);
+            atomicMax(&s_id[0], u);
+            atomicMax(&s_id[1], ~u);
+            const float *b = boxes + i * stride;
+            atomicMax(&s_max[0], ordered_bits(fmaxf(b[0], b[1])));
+            atomicMax(&s_max[1], ordered_bits(fmaxf(b[2], b[3])));
+        }
+    }
+    __syncthreads();
+    if (ids && tid == 0) {
+        atomicMax(&hdr->id_max_u, s_id[0]);
+        atomicMax(&hdr->id_min_inv_u, s_id[1]);
+        atomicMax(&hdr->max_xy, s_max[0]);
+        atomicMax(&hdr->max_wh, s_max[1]);
+    }
+}
+
+__global__ void __launch_bounds__(256)
+prep_segkey_kernel(const int64_t *__restrict__ ids, const uint32_t *__restrict__ order, int64_t n,
+                   uint16_t *__restrict__ segkey, PrepHeader *hdr) {
+    const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    const unsigned long long lo = ~hdr->id_min_inv_u;
+    if (i == 0) {
+        if (hdr->id_max_u - lo >= 65536ull) hdr->range_bad = 1;
+        hdr->mc_max[0] = ordered_float(hdr->max_xy);
+        hdr->mc_max[1] = ordered_float(hdr->max_wh);
+    }
+    if (i < n) segkey[i] = (uint16_t)(id_image(ids[order[i]]) - lo);
+}
+
+// returns 0, -3 (CUDA), -4 (ids span >= 2^16 values), -5 (more segments than seg_cap)
+int nms_prepare(const float *boxes, int64_t n, int stride, const float *scores, const int64_t *ids,
+                void *prep, int64_t *seg_counts_host, int64_t seg_cap, int64_t *num_segments_host,
+                cudaStream_t stream) {
+    PrepLayout l;
+    prep_layout(n, &l);
+    char *ws = reinterpret_cast<char *>(prep);
+    PrepHeader *hdr = reinterpret_cast<PrepHeader *>(ws + l.off_hdr);
+    uint32_t *keys = reinterpret_cast<uint32_t *>(ws + l.off_keys);
+    uint32_t *keys2 = reinterpret_cast<uint32_t *>(ws + l.off_keys2);
+    uint32_t *vals = reinterpret_cast<uint32_t *>(ws + l.off_vals);
+    uint32_t *order = reinterpret_cast<uint32_t *>(ws + l.off_order);
+    const unsigned grid = (unsigned)((n + 255) / 256);
+    if (cudaMemsetAsync(hdr, 0, sizeof(PrepHeader), stream) != cudaSuccess) return -3;
+    prep_keys_kernel<<<grid, 256, 0, stream>>>(boxes, stride, scores, ids, n, keys, vals, hdr);
+    if (cudaGetLastError() != cudaSuccess) return -3;
+    size_t cub_bytes = l.cub_bytes;
+    if (cub::DeviceRadixSort::SortPairs(ws + l.off_cub, cub_bytes, (const uint32_t *)keys, keys2,
+                                        (const uint32_t *)vals, order, (int)n, 0, 32, stream) != cudaSuccess)
+        return -3;
+    if (!ids) {
+        seg_counts_host[0] = n;
+        *num_segments_host = 1;
+        return 0;
+    }
+    uint16_t *segkey = reinterpret_cast<uint16_t *>(ws + l.off_segkey);
+    uint16_t *segkey2 = reinterpret_cast<uint16_t *>(ws + l.off_segkey2);
+    uint32_t *seg_order = reinterpret_cast<uint32_t *>(ws + l.off_seg_order);
+    uint16_t *runs_unique = reinterpret_cast<uint16_t *>(ws + l.off_runs_unique);
+    int *runs_count = reinterpret_cast<int *>(ws + l.off_runs_count);
+    prep_segkey_kernel<<<grid, 256, 0, stream>>>(ids, order, n, segkey, hdr);
+    if (cudaGetLastError() != cudaSuccess) return -3;
+    cub_bytes = l.cub_bytes;
+    if (cub::DeviceRadixSort::SortPairs(ws + l.off_cub, cub_bytes, (const uint16_t *)segkey, segkey2,
+                                        (const uint32_t *)order, seg_order, (int)n, 0, 16, stream) != cudaSuccess)
+        return -3;
+    cub_bytes = l.cub_bytes;
+    if (cub::DeviceRunLengthEncode::Encode(ws + l.off_cub, cub_bytes, (const uint16_t *)segkey2, runs_unique,
+                                           runs_count, &hdr->n_runs, (int)n, stream) != cudaSuccess)
+        return -3;
+    // the one device->host read: header + the first seg_cap run lengths
+    PrepHeader h;
+    const int64_t ncopy = n < seg_cap ? n : seg_cap;
+    std::vector<int> counts((size_t)ncopy);
+    if (cudaMemcpyAsync(&h, hdr, sizeof(PrepHeader), cudaMemcpyDeviceToHost, stream) != cudaSuccess ||
+        cudaMemcpyAsync(counts.data(), runs_count, (size_t)ncopy * sizeof(int), cudaMemcpyDeviceToHost,
+                        stream) != cudaSuccess ||
+        cudaStreamSynchronize(stream) != cudaSuccess)
+        return -3;
+    if (h.range_bad) return -4;
+    if (h.n_runs > seg_cap) return -5;
+    for (int r = 0; r < h.n_runs; ++r) seg_counts_host[r] = counts[(size_t)r];
+    *num_segments_host = h.n_runs;
+    return 0;
+}
+
+int launch_nms_prepared(const float *boxes, int64_t n, int stride, const float *offsets,
+                        const int64_t *offset_ids, bool segmented, const void *prep, const NmsPlan &plan,
+                        const NmsSegment *segs_dev, float thr, void *packed, uint64_t *mask,
+                        uint8_t *flags, const NmsScratch &scratch, int64_t *keep_out,
+                        int64_t *num_keep_out, cudaStream_t stream) {
+    PrepLayout l;
+    prep_layout(n, &l);
+    const char *ws = reinterpret_cast<const char *>(prep);
+    const PrepHeader *hdr = reinterpret_cast<const PrepHeader *>(ws + l.off_hdr);
+    const uint32_t *order = reinterpret_cast<const uint32_t *>(ws + l.off_order);
+    // prepared without ids: one segment, the segment-major order is the score order
+    const uint32_t *seg_order = segmented ? reinterpret_cast<const uint32_t *>(ws + l.off_seg_order) : order;
+    PackSet s1 = make_pack_set(boxes, n, stride, nullptr, offsets, packed, plan.n_pad);
+    s1.gather32 = seg_order;
+    s1.segs = segs_dev;
+    s1.nseg = (int)plan.num_segments;
+    if (offset_ids) {
+        s1.offset_ids = offset_ids;
+        s1.mc_max = hdr->mc_max;
+    }
+    s1.z_kr = scratch.kr;
+    s1.z_summary = scratch.summary;
+    s1.z_sum_words = scratch.sum_words;
+    s1.z_sync = scratch.sync;
+    const PackSet none = make_pack_set(nullptr, 0, 5, nullptr, nullptr, nullptr, 0);
+    if (launch_pack(s1, none, 0.f, 0.f, stream)) return -3;
+    return launch_nms(plan, packed, segs_dev, nullptr, nullptr, order, seg_order, thr, mask, flags,
+                      scratch, keep_out, num_keep_out, stream);
 }
 
 }  // namespace rotgeo

@@ -26,6 +26,7 @@ struct PackSet {
     int stride;
     const int64_t *gather;   // nullable: packed[i] = boxes[gather[i]]
     const float *offsets;    // nullable: added to cx, cy, indexed like the source rows
+    const int64_t *offset_ids;  // nullable: centre offset = id * (mc_max[0] + mc_max[1] + 1) instead
     const NmsSegment *segs;  // nullable: segmented slot layout (see slot_source)
     int nseg;
     // device-planned sets (fused front-ends): the box count lives on the device, and gather32[]
@@ -103,10 +104,23 @@ struct McOut {
     int64_t cap;             // keep at most this many (max_num)
 };
 
+// orders: either the 64-bit pair or the 32-bit pair is given
 int launch_nms(const NmsPlan &plan, const void *packed, const NmsSegment *segments_dev,
-               const int64_t *order, const int64_t *seg_order, float thr, uint64_t *mask,
-               uint8_t *flags, const NmsScratch &scratch, int64_t *keep_out, int64_t *num_keep_out,
+               const int64_t *order, const int64_t *seg_order, const uint32_t *order32,
+               const uint32_t *seg_order32, float thr, uint64_t *mask, uint8_t *flags,
+               const NmsScratch &scratch, int64_t *keep_out, int64_t *num_keep_out,
                cudaStream_t stream);
+
+// generic front-end (rotgeo_frontend.cu)
+size_t nms_prepare_bytes(int64_t n);
+int nms_prepare(const float *boxes, int64_t n, int stride, const float *scores, const int64_t *ids,
+                void *prep, int64_t *seg_counts_host, int64_t seg_cap, int64_t *num_segments_host,
+                cudaStream_t stream);
+int launch_nms_prepared(const float *boxes, int64_t n, int stride, const float *offsets,
+                        const int64_t *offset_ids, bool segmented, const void *prep, const NmsPlan &plan,
+                        const NmsSegment *segs_dev, float thr, void *packed, uint64_t *mask,
+                        uint8_t *flags, const NmsScratch &scratch, int64_t *keep_out,
+                        int64_t *num_keep_out, cudaStream_t stream);
 
 // NMS over a plan made on the DEVICE (fused front-ends): grids and buffers are sized for
 // host-side upper bounds, the kernels read the actual counts from device memory.

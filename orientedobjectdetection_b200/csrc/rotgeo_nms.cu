@@ -740,8 +740,9 @@ static int launch_resolve(const ResolveArgs &a, cudaStream_t stream) {
 }
 
 int launch_nms(const NmsPlan &plan, const void *packed, const NmsSegment *segments_dev,
-               const int64_t *order, const int64_t *seg_order, float thr, uint64_t *mask,
-               uint8_t *flags, const NmsScratch &scratch, int64_t *keep_out, int64_t *num_keep_out,
+               const int64_t *order, const int64_t *seg_order, const uint32_t *order32,
+               const uint32_t *seg_order32, float thr, uint64_t *mask, uint8_t *flags,
+               const NmsScratch &scratch, int64_t *keep_out, int64_t *num_keep_out,
                cudaStream_t stream) {
     const PackedView P = packed_view(packed, plan.n_pad);
     MaskArgs g;
@@ -765,6 +766,8 @@ int launch_nms(const NmsPlan &plan, const void *packed, const NmsSegment *segmen
     a.chunks = plan.n_pad / 64;
     a.order = order;
     a.seg_order = seg_order;
+    a.order32 = order32;
+    a.seg_order32 = seg_order32;
     a.n = plan.n;
     a.n_dev = nullptr;
     a.flags = flags;

@@ -53,10 +53,14 @@ __device__ __forceinline__ int64_t position_source(const PackSet &s, int64_t pos
     if (s.mc_classes > 0) {
         const int64_t row = v / s.mc_classes;
         const int cls = (int)(v - row * s.mc_classes);
-        offset = (float)cls * ((s.mc_max[0] + s.mc_max[1]) + 1.f);
+        offset = __fmul_rn((float)cls, __fadd_rn(__fadd_rn(s.mc_max[0], s.mc_max[1]), 1.f));
         return s.mc_shared ? row : v;
     }
     if (s.offsets) offset = s.offsets[v];
+    // mmcv.ops.batched_nms: id * (max(cx,cy) + max(w,h) + 1), all in fp32
+    // (no fused multiply-add anywhere here: torch rounds the product, then the sum)
+    if (s.offset_ids)
+        offset = __fmul_rn((float)s.offset_ids[v], __fadd_rn(__fadd_rn(s.mc_max[0], s.mc_max[1]), 1.f));
     return v;
 }
 
@@ -125,7 +129,7 @@ pack_kernel(PackSet s1, PackSet s2, float min_wh, float cell) {
         float o;
         src = position_source(s, pos, o);
         const float *b = s.boxes + src * s.stride;
-        cx = b[0] + o; cy = b[1] + o; w = b[2]; h = b[3]; th = b[4];
+        cx = __fadd_rn(b[0], o); cy = __fadd_rn(b[1], o); w = b[2]; h = b[3]; th = b[4];
     }
     const float inv_cell = cell > 0.f ? 1.f / cell : sample_inv_cell(s1, s2);
 
@@ -223,6 +227,7 @@ PackSet make_pack_set(const float *boxes, int64_t n, int stride, const int64_t *
     s.nseg = 0;
     s.n_dev = nullptr;
     s.gather32 = nullptr;
+    s.offset_ids = nullptr;
     s.mc_classes = 0;
     s.mc_shared = 0;
     s.mc_max = nullptr;

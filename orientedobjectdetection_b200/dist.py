@@ -124,33 +124,32 @@ def nms_images(images, iou_threshold, max_per_img=-1, keep_fn=None):
     sizes = [int(b.shape[0]) for b, _, _ in images]
     if sum(sizes) == 0:
         return [torch.zeros(0, dtype=torch.int64) for _ in images]
+    dev = images[0][0].device
     boxes = torch.cat([b for b, _, _ in images], dim=0)
     scores = torch.cat([s for _, s, _ in images], dim=0)
-    offs, segs, img_of = [], [], []
-    seg_base = 0
-    for i, (b, s, ids) in enumerate(images):
-        if b.shape[0] == 0:
-            continue
-        ids = ids.to(torch.int64)
-        # per-image offset trick, same float arithmetic as mmcv.ops.batched_nms
-        max_coordinate = b[..., :2].max() + b[..., 2:4].max()
-        offs.append(ids.to(b) * (max_coordinate + torch.tensor(1).to(b)))
-        segs.append(ids - ids.min() + seg_base)
-        seg_base = int(segs[-1].max()) + 1
-        img_of.append(torch.full((b.shape[0],), i, dtype=torch.int64, device=b.device))
-    offsets, seg, img_of = torch.cat(offs), torch.cat(segs), torch.cat(img_of)
-    keep = keep_fn(boxes, scores, iou_threshold, seg_ids=seg, offsets=offsets).to(boxes.device)
+    ids = torch.cat([i.to(torch.int64) for _, _, i in images], dim=0)
+    nimg = len(images)
+    sizes_t = torch.tensor(sizes, dtype=torch.int64)
+    img_of = torch.repeat_interleave(torch.arange(nimg, dtype=torch.int64), sizes_t).to(dev)
+    # per-image offset trick, same float arithmetic as mmcv.ops.batched_nms on every image:
+    # id * (max(cx,cy) + max(w,h) + 1) with the maxima of THAT image
+    neg = torch.full((nimg,), float('-inf'), dtype=boxes.dtype, device=dev)
+    m_xy = neg.clone().scatter_reduce_(0, img_of, boxes[:, :2].max(dim=1).values, 'amax')
+    m_wh = neg.clone().scatter_reduce_(0, img_of, boxes[:, 2:4].max(dim=1).values, 'amax')
+    offsets = ids.to(boxes) * ((m_xy + m_wh)[img_of] + torch.tensor(1).to(boxes))
+    # one segment per (image, id)
+    id_lo = ids.min()
+    seg = img_of * (ids.max() - id_lo + 1) + (ids - id_lo)
+    keep = keep_fn(boxes, scores, iou_threshold, seg_ids=seg, offsets=offsets).to(dev)
     # global score order -> per image (stable: score order survives inside an image)
     kimg = img_of[keep]
-    keep = keep[torch.sort(kimg, stable=True).indices]
-    counts = torch.bincount(img_of[keep], minlength=len(images)).tolist()
-    starts = np.concatenate([[0], np.cumsum(sizes)])
-    out, pos = [], 0
-    for i, c in enumerate(counts):
-        k = keep[pos:pos + c] - int(starts[i])
-        pos += c
-        out.append(k[:max_per_img] if max_per_img > 0 else k)
-    return out
+    perm = torch.sort(kimg, stable=True).indices
+    keep, kimg = keep[perm], kimg[perm]
+    starts = torch.cat([torch.zeros(1, dtype=torch.int64), torch.cumsum(sizes_t, 0)[:-1]]).to(dev)
+    local = keep - starts[kimg]
+    counts = torch.bincount(kimg, minlength=nimg).tolist()
+    out = list(torch.split(local, counts))
+    return [k[:max_per_img] for k in out] if max_per_img > 0 else out
 
 
 def nms_images_sharded(images, iou_threshold, max_per_img=-1, group=None, keep_fn=None):

@@ -13,6 +13,8 @@ merge_results.py:115 with device='cpu') are moved to the current CUDA device
 and the result is returned on the caller's device — a transfer, never a CPU
 implementation.  No GPU or no library => RuntimeError.
 """
+import ctypes
+
 import numpy as np
 import torch
 
@@ -95,67 +97,79 @@ def box_iou_rotated(bboxes1, bboxes2, mode='iou', aligned=False, clockwise=True)
     return _overlaps(bboxes1, bboxes2, mode, aligned, 0.0)
 
 
-def _desc_keys(s):
-    """float32 scores -> int64 keys in [0, 2**32) whose ASCENDING order is the scores'
-    descending order (equal scores give equal keys, so a stable sort breaks ties by
-    lower index first — the reference's sort leaves that order unspecified)."""
-    u = (s + 0.0).view(torch.int32).to(torch.int64) & 0xFFFFFFFF        # +0.0: -0.0 -> 0.0
-    mono = torch.where(u >= 0x80000000, 0xFFFFFFFF - u, u + 0x80000000)  # ascending with the score
-    return 0xFFFFFFFF - mono
+_SEG_CAP = 16384     # segments one call handles (ids must also span fewer than 2**16 values)
 
 
-def _nms_keep(boxes, scores, iou_threshold, seg_ids=None, offsets=None, seg_counts_host=None):
+def _nms_keep(boxes, scores, iou_threshold, seg_ids=None, offsets=None, id_offsets=False):
     """kept indices (int64, score-descending, on the CUDA device) of a greedy
     rotated NMS.
 
-    ``seg_ids`` (non-negative ints per box) restricts suppression to boxes of equal
-    id; ``seg_counts_host`` (optional, host int64 array with one count per id
-    0..S-1) saves the device->host read of the segment sizes when the caller
-    already has them; ``offsets`` (float per box) is added to cx, cy first.
-    One radix sort of (segment, -score) keys, one rotgeo_nms call (pack + mask +
-    scan + emit kernels), one read of the kept count, one small sort of the
-    survivors back into global score order."""
+    ``seg_ids`` (ints per box) restricts suppression to boxes of equal id.  Centre
+    offsets (added to cx, cy before the geometry, as the reference's class
+    separation does): ``offsets`` (float per box), or ``id_offsets=True`` for
+    mmcv.batched_nms's own ``id * (max(cx,cy) + max(w,h) + 1)``, computed on the
+    device.  Two C-ABI calls: rotgeo_nms_prepare (key transform, radix sorts,
+    segment sizes -> host: the one sync before the launch) and rotgeo_nms_prepared
+    (pack + mask + resolve kernels), then one read of the kept count."""
     dev = _cuda_device(boxes, scores)
     n = boxes.size(0)
     b = _rows_f32(boxes, dev)
-    s = scores.detach().to(device=dev, dtype=torch.float32).reshape(-1)
+    s = scores.detach().to(device=dev, dtype=torch.float32).reshape(-1).contiguous()
     L = _lib.load()
     with torch.cuda.device(dev):
-        keys = _desc_keys(s)
-        order_ptr, seg_order_ptr, seg_off_ptr, nseg = None, None, None, 0
-        if seg_ids is None:
-            order = torch.sort(keys, stable=True).indices
-            order_ptr = order.data_ptr()
-        else:
-            seg = seg_ids.detach().to(device=dev, dtype=torch.int64).reshape(-1)
-            if seg_counts_host is None:
-                uniq, seg, counts = torch.unique(seg, sorted=True, return_inverse=True,
-                                                 return_counts=True)
-                seg_counts_host = counts.cpu().numpy()
-            seg_counts_host = np.asarray(seg_counts_host, dtype=np.int64)
-            seg_order = torch.sort((seg << 32) | keys, stable=True).indices
-            seg_off = np.zeros(seg_counts_host.size + 1, dtype=np.int64)
-            np.cumsum(seg_counts_host, out=seg_off[1:])
-            assert seg_off[-1] == n, 'segment counts do not add up to the number of boxes'
-            seg_order_ptr, seg_off_ptr, nseg = seg_order.data_ptr(), seg_off.ctypes.data, seg_counts_host.size
+        seg_ptr = None
+        if seg_ids is not None:
+            seg = seg_ids.detach().to(device=dev, dtype=torch.int64).reshape(-1).contiguous()
+            seg_ptr = seg.data_ptr()
         off_ptr = None
         if offsets is not None:
             offsets = offsets.detach().to(device=dev, dtype=torch.float32).contiguous()
             off_ptr = offsets.data_ptr()
-        nbytes = L.rotgeo_nms_workspace_bytes(n, seg_off_ptr, nseg)
+        stream = _stream(dev)
+        pbytes = L.rotgeo_nms_prepare_bytes(n)
+        prep = torch.empty(pbytes, dtype=torch.uint8, device=dev)
+        cap = min(n, _SEG_CAP)
+        counts = np.empty(cap, dtype=np.int64)
+        nseg = ctypes.c_int64(0)
+        rc = L.rotgeo_nms_prepare(b.data_ptr(), n, b.stride(0), s.data_ptr(), seg_ptr, prep.data_ptr(),
+                                  pbytes, counts.ctypes.data, cap, ctypes.byref(nseg), stream)
+        if rc == _lib.ERR_RANGE:
+            return _nms_keep_split(b, s, iou_threshold, seg, offsets, id_offsets)
+        _lib.check(rc, 'rotgeo_nms_prepare')
+        nseg = nseg.value
+        seg_off = np.zeros(nseg + 1, dtype=np.int64)
+        np.cumsum(counts[:nseg], out=seg_off[1:])
+        nbytes = L.rotgeo_nms_workspace_bytes(n, seg_off.ctypes.data, nseg)
         ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
         keep = torch.empty(n, dtype=torch.int64, device=dev)
         nkeep = torch.empty(1, dtype=torch.int64, device=dev)
-        _lib.check(L.rotgeo_nms(b.data_ptr(), n, b.stride(0), off_ptr, order_ptr,
-                                seg_order_ptr, seg_off_ptr, nseg, float(iou_threshold),
-                                keep.data_ptr(), nkeep.data_ptr(), ws.data_ptr(), nbytes,
-                                _stream(dev)), 'rotgeo_nms')
+        _lib.check(L.rotgeo_nms_prepared(b.data_ptr(), n, b.stride(0), off_ptr, seg_ptr,
+                                         1 if id_offsets else 0, prep.data_ptr(), counts.ctypes.data,
+                                         nseg, float(iou_threshold), keep.data_ptr(), nkeep.data_ptr(),
+                                         ws.data_ptr(), nbytes, stream), 'rotgeo_nms_prepared')
         k = int(nkeep.item())          # the one sync after the launch: sizes the output
-        keep = keep[:k]
-        if seg_ids is not None and k > 1:
-            # segment-major -> global score order (ties: lower index first)
-            keep = keep[torch.sort((keys[keep] << 32) | keep).indices]
-    return keep
+    return keep[:k]
+
+
+def _nms_keep_split(b, s, iou_threshold, seg, offsets, id_offsets):
+    """segment ids too spread out / too many segments for one call: renumber them
+    densely (torch.unique) and run chunks of _SEG_CAP segments; the centre offsets
+    are materialised first so that every chunk sees the same values."""
+    if id_offsets:
+        max_coordinate = b[:, :2].max() + b[:, 2:4].max()
+        offsets = seg.to(b.dtype) * (max_coordinate + torch.tensor(1).to(b))
+    dense = torch.unique(seg, sorted=True, return_inverse=True)[1]
+    nseg = int(dense.max().item()) + 1
+    keeps = []
+    for lo in range(0, nseg, _SEG_CAP):
+        sel = torch.nonzero((dense >= lo) & (dense < lo + _SEG_CAP)).squeeze(1)
+        k = _nms_keep(b[sel], s[sel], iou_threshold, seg_ids=dense[sel] - lo,
+                      offsets=None if offsets is None else offsets[sel])
+        keeps.append(sel[k])
+    keep = torch.cat(keeps)
+    # chunks -> global score order (ties: lower index first)
+    order = torch.sort(keep).values
+    return order[torch.sort(s[order], descending=True, stable=True).indices]
 
 
 def nms_rotated(dets, scores, iou_threshold, labels=None, clockwise=True):
@@ -222,13 +236,10 @@ def batched_nms(boxes, scores, idxs, nms_cfg, class_agnostic=False):
         return torch.cat([boxes, scores[:, None]], -1), boxes.new_zeros((0,), dtype=torch.long)
 
     if nms_type == 'nms_rotated' and boxes.size(-1) == 5:
-        offsets, seg = None, None
-        if not class_agnostic:
-            # same float arithmetic as mmcv: max(cx,cy) + max(w,h) + 1, times the id
-            max_coordinate = boxes[..., :2].max() + boxes[..., 2:4].max()
-            offsets = idxs.to(boxes) * (max_coordinate + torch.tensor(1).to(boxes))
-            seg = idxs
-        keep = _nms_keep(boxes, scores, thr, seg_ids=seg, offsets=offsets).to(boxes.device)
+        # not class_agnostic: the centre offset  id * (max(cx,cy) + max(w,h) + 1)  of mmcv, same
+        # fp32 arithmetic, derived on the device
+        keep = _nms_keep(boxes, scores, thr, seg_ids=None if class_agnostic else idxs,
+                         id_offsets=not class_agnostic).to(boxes.device)
     else:
         if class_agnostic:
             b = boxes

@@ -302,3 +302,62 @@ def test_nms_chain_needs_many_rounds(n):
     _, keep = rg.nms_rotated(_cuda(b), _cuda(s), 0.1)
     assert keep.cpu().tolist() == want.tolist()
     assert want.tolist() == list(range(0, n, 2))
+
+
+def test_batched_nms_id_ranges_and_split_path(monkeypatch):
+    """ids of batched_nms are arbitrary integers: negative, sparse, spread over more than
+    2**16 values (rotgeo_nms_prepare reports ROTGEO_ERR_RANGE and the caller splits), and
+    more segments than one call takes."""
+    from orientedobjectdetection_b200 import ops
+    n = 3000
+    boxes = synth.le90_boxes(n, 21, 400.0)
+    scores = synth.unique_scores(n, 21)
+    rng = np.random.default_rng(21)
+    cfg = dict(type='nms_rotated', iou_threshold=0.3)
+    tb, ts = torch.from_numpy(boxes), torch.from_numpy(scores)
+    for ids in (rng.integers(-3, 4, n), rng.integers(0, 5, n) * 1000 - 7,
+                rng.integers(0, 6, n) * 100000, rng.integers(0, 40, n)):
+        ids = ids.astype(np.int64)
+        ti = torch.from_numpy(ids)
+        if np.abs(ids).max() < 10000:
+            _, wk = ref_api.batched_nms_rotated(tb, ts, ti, 0.3)
+            wk = wk.tolist()
+        else:
+            # offsets of 1e8: fp32 no longer resolves the boxes, and the reference arithmetic
+            # returns garbage "IoU" (in the thousands) for boxes of DIFFERENT ids that are 1e8
+            # apart, i.e. spurious cross-id suppression.  This implementation never pairs boxes
+            # of different ids; inside an id it reproduces the reference on the same rounded
+            # coordinates (DESIGN.md "Deviations").
+            maxc = tb[:, :2].max() + tb[:, 2:4].max()
+            off = ti.to(tb) * (maxc + torch.tensor(1).to(tb))
+            shifted = torch.cat([tb[:, :2] + off[:, None], tb[:, 2:5]], -1).numpy()
+            wk = []
+            for u in np.unique(ids):
+                sel = np.nonzero(ids == u)[0]
+                wk += sel[ref.nms_rotated(shifted[sel], scores[sel], 0.3)[1]].tolist()
+            wk.sort(key=lambda i: -scores[i])
+        for cap in (16384, 8):
+            monkeypatch.setattr(ops, '_SEG_CAP', cap)
+            gd, gk = rg.batched_nms(_cuda(boxes), _cuda(scores), ti.cuda(), cfg)
+            assert gk.cpu().tolist() == wk
+            assert torch.equal(gd.cpu(), torch.cat([tb[wk], ts[wk][:, None]], -1))
+    # class_agnostic: one segment, no offsets
+    wd, wk = ref_api.batched_nms_rotated(torch.from_numpy(boxes), torch.from_numpy(scores),
+                                         torch.zeros(n, dtype=torch.int64), 0.3, class_agnostic=True)
+    gd, gk = rg.batched_nms(_cuda(boxes), _cuda(scores), torch.zeros(n, dtype=torch.int64).cuda(), cfg,
+                            class_agnostic=True)
+    assert gk.cpu().tolist() == wk.tolist()
+
+
+def test_nms_images_c4_batch_vs_per_image_calls():
+    from orientedobjectdetection_b200 import dist as rdist
+    imgs = [synth.c4_rpn_image(seed=s, per_level=300 + 50 * s) for s in range(5)]
+    imgs.insert(2, (np.zeros((0, 5), np.float32), np.zeros(0, np.float32), np.zeros(0, np.int64)))
+    dev_imgs = [(_cuda(b), _cuda(s), torch.from_numpy(i).cuda()) for b, s, i in imgs]
+    got = rdist.nms_images(dev_imgs, 0.8, 500)
+    for (b, s, i), g in zip(imgs, got):
+        if b.shape[0] == 0:
+            assert g.numel() == 0
+            continue
+        _, wk = ref_api.batched_nms_rotated(torch.from_numpy(b), torch.from_numpy(s), torch.from_numpy(i), 0.8)
+        assert g.cpu().tolist() == wk[:500].tolist()
