@@ -115,8 +115,8 @@ def run_reference(args, rank):
     a, b = synth.c3_iou(0, N_ROWS, N_COLS, EXTENT)
     a[:, 2:4] = np.maximum(a[:, 2:4], 1e-3)
     b[:, 2:4] = np.maximum(b[:, 2:4], 1e-3)
-    threads = min(ref.max_threads(), len(os.sched_getaffinity(0)))
-    rows = 1024
+    threads = min(ref.max_threads(), len(os.sched_getaffinity(0)))   # not OMP_NUM_THREADS (torchrun sets 1)
+    rows = min(N_ROWS, max(1024, 256 * threads))
     for _ in range(max(1, min(args.warmup, 2))):
         ref.box_iou_rotated(a[:rows], b, threads=threads)
     times = []
@@ -157,11 +157,13 @@ def timed_steps(torch, fn, steps, flush, stream_sync):
 
 
 def secondary_nms(torch, rg, synth, reps=5):
-    """rotated-NMS boxes/s on one GPU, device-resident inputs, through the public
-    python API (includes its single D2H sync)."""
+    """rotated-NMS boxes/s on one GPU through the public python API, wall clock incl. the
+    call's own device->host reads.  C2/C4: inputs resident on the device (as the detector
+    heads have them); C5: host numpy lists in, numpy out (as huge_image_demo.py has them)."""
+    from orientedobjectdetection_b200 import dist as rdist
     res = {}
 
-    def best(fn):
+    def best(fn, reps=reps):
         fn()
         ts = []
         for _ in range(reps):
@@ -178,16 +180,53 @@ def secondary_nms(torch, rg, synth, reps=5):
         ncand = int((ms[:, :-1] > 0.05).sum())
         t = best(lambda: rg.multiclass_nms_rotated(mbd, msd, 0.05, dict(iou_thr=0.1), 2000))
         res[name] = {'boxes': ncand, 'ms': 1e3 * t, 'boxes_per_s': ncand / t}
-    boxes, scores, ids = synth.c4_rpn_image(0)
-    bd, sd, idd = (torch.from_numpy(x).cuda() for x in (boxes, scores, ids))
-    t = best(lambda: rg.batched_nms(bd, sd, idd, dict(type='nms_rotated', iou_threshold=0.8)))
-    res['c4_batched_nms_1img_5x2000'] = {'boxes': len(boxes), 'ms': 1e3 * t, 'boxes_per_s': len(boxes) / t}
+    imgs = [tuple(torch.from_numpy(x).cuda() for x in synth.c4_rpn_image(s)) for s in range(64)]
+    bd, sd, idd = imgs[0]
+    cfg = dict(type='nms_rotated', iou_threshold=0.8)
+    t = best(lambda: rg.batched_nms(bd, sd, idd, cfg))
+    res['c4_batched_nms_1img_5x2000'] = {'boxes': int(bd.shape[0]), 'ms': 1e3 * t, 'boxes_per_s': bd.shape[0] / t}
+    nb = sum(int(b.shape[0]) for b, _, _ in imgs)
+    t = best(lambda: [rg.batched_nms(b, s, i, cfg)[1][:2000] for b, s, i in imgs], 2)
+    res['c4_64img_per_image_calls'] = {'boxes': nb, 'ms': 1e3 * t, 'boxes_per_s': nb / t}
+    t = best(lambda: rdist.nms_images(imgs, 0.8, 2000), 3)
+    res['c4_64img_one_segmented_launch'] = {'boxes': nb, 'ms': 1e3 * t, 'boxes_per_s': nb / t}
+    del imgs
     n = 30000
     b1 = torch.from_numpy(synth.le90_boxes(n, 9, 1024.0)).cuda()
     s1 = torch.from_numpy(synth.unique_scores(n, 9)).cuda()
     t = best(lambda: rg.nms_rotated(b1, s1, 0.1))
     res['nms_rotated_single_segment_30000'] = {'boxes': n, 'ms': 1e3 * t, 'boxes_per_s': n / t}
+    # C5: ~200k detections of 400 overlapping patches, 15 Zipf-skewed classes
+    patches, offs, shape = synth.c5_patch_results(0)
+    nd = sum(a.shape[0] for p in patches for a in p)
+    ts = []
+    for _ in range(3):
+        cp = [[a.copy() for a in p] for p in patches]     # merge_results shifts its input in place
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        rg.merge_results(cp, offs, shape, 0.1)
+        ts.append(time.perf_counter() - t0)
+    res['c5_merge_results_200k_host_lists'] = {'boxes': nd, 'ms': 1e3 * min(ts), 'boxes_per_s': nd / min(ts)}
+    # `cp` was shifted to image coordinates in place by the last merge_results call
+    allc = np.concatenate([a for p in cp for a in p], axis=0)
+    seg = np.concatenate([np.full(a.shape[0], c, np.int64) for p in cp for c, a in enumerate(p)])
+    dd, sg = torch.from_numpy(allc).cuda(), torch.from_numpy(seg).cuda()
+    from orientedobjectdetection_b200 import ops
+    t = best(lambda: ops._nms_keep(dd[:, :5], dd[:, 5], 0.1, seg_ids=sg), 3)
+    res['c5_class_batched_nms_200k_device_resident'] = {'boxes': nd, 'ms': 1e3 * t, 'boxes_per_s': nd / t}
     return res
+
+
+def measured_traffic():
+    """DRAM bytes per launch of the dominant kernel from the committed ncu --set full capture
+    (profiles/r01_iou_tile_kernel_traffic.json, written from the .ncu-rep by tools/ncu_traffic.py)"""
+    p = os.path.join(ROOT, 'profiles', 'r01_iou_tile_kernel_traffic.json')
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))['dram_bytes_per_launch'])
+        except Exception:
+            return None
+    return None
 
 
 def run_rotgeo(args, rank, world, local_rank):
@@ -294,7 +333,7 @@ def run_rotgeo(args, rank, world, local_rank):
                 'd2h_bytes_per_step': int(N_ROWS * N_COLS * 4), 'steps': e2e_steps,
                 'api': 'orientedobjectdetection_b200.rbbox_overlaps(pinned CPU tensors) -> pinned CPU tensor'},
         'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
-                     'frac': achieved / peak, 'traffic': None, 'kernel': 'iou_tile_kernel<0,true>',
+                     'frac': achieved / peak, 'traffic': measured_traffic(), 'kernel': 'iou_tile_kernel<0,true>',
                      'kernel_ms': k_ms, 'peak_source': peak_src,
                      'algorithmic_bytes_per_launch': alg_bytes,
                      'fp32_view': {'flop_per_pair': FLOP_PER_PAIR,

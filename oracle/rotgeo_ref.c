@@ -29,7 +29,9 @@
 
 #ifdef _OPENMP
 #include <omp.h>
-int rotgeo_ref_max_threads(void) { return omp_get_max_threads(); }
+/* processors available to this process (affinity-aware); deliberately not omp_get_max_threads(): launchers
+   such as torchrun export OMP_NUM_THREADS=1, and the callers pass an explicit thread count anyway */
+int rotgeo_ref_max_threads(void) { return omp_get_num_procs(); }
 #else
 int rotgeo_ref_max_threads(void) { return 1; }
 #endif

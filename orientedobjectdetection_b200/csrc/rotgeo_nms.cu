@@ -329,6 +329,7 @@ struct ResolveArgs {
     const NmsSegment *segs;
     int nseg;
     int has_large;                // some segment may have more than kLocalChunks chunks
+    int snapshot;                 // grid path: the state of all chunks fits the dynamic shared memory
     const unsigned long long *mask;
     NmsScratch sc;
     int64_t chunks;               // 64-slot words to visit (an upper bound when device-planned)
@@ -374,18 +375,18 @@ __device__ __forceinline__ ulonglong2 ldcg_u64x2(const unsigned long long *p) {
     asm volatile("ld.global.cg.v2.u64 {%0, %1}, [%2];" : "=l"(v.x), "=l"(v.y) : "l"(p));
     return v;
 }
-// (kept, removed) words of one chunk: shared memory (LOCAL) or global memory through L2
-template <bool LOCAL>
+// (kept, removed) words of one chunk: shared memory (SMEM) or global memory through L2
+template <bool SMEM>
 __device__ __forceinline__ ulonglong2 kr_load(const unsigned long long *p) {
-    if (LOCAL) {
+    if (SMEM) {
         const volatile unsigned long long *v = p;
         return make_ulonglong2(v[0], v[1]);
     }
     return ldcg_u64x2(p);
 }
-template <bool LOCAL>
+template <bool SMEM>
 __device__ __forceinline__ void kr_store(unsigned long long *p, unsigned long long k, unsigned long long r) {
-    if (LOCAL) {
+    if (SMEM) {
         volatile unsigned long long *v = p;
         v[0] = k;
         v[1] = r;
@@ -409,16 +410,18 @@ __device__ __forceinline__ int segment_of_slot(const NmsSegment *__restrict__ se
 }
 
 // One warp, one 64-box chunk (word c of its segment's mask rows), one round.  Lane l owns rows
-// l and l + 32.  kr_seg: the segment's (kept, removed) word pairs.  Returns true while the chunk
-// still has an undecided box.
+// l and l + 32.  kr_others: where the state of the segment's OTHER chunks is read (shared
+// memory when RD_SMEM: the one-CTA path, or the grid path's per-round snapshot); kr_mine: the
+// live (kept, removed) pairs of the segment, read and written for chunk c only.  Returns true
+// while the chunk still has an undecided box.
 // Both bitmaps only ever gain bits, and a reader that sees an old word merely treats a decided
 // box as undecided for one more round: chunks can be settled concurrently, in any order.
-template <bool LOCAL>
+template <bool RD_SMEM, bool WR_SMEM>
 __device__ bool resolve_chunk(const ResolveArgs &a, const NmsSegment &sg, int c,
-                              unsigned long long *kr_seg, int lane) {
+                              const unsigned long long *kr_others, unsigned long long *kr_mine, int lane) {
     const int64_t pos0 = (int64_t)c * 64, len = sg.len;
     const unsigned long long valid = len - pos0 >= 64 ? ~0ull : ((1ull << (len - pos0)) - 1ull);
-    const ulonglong2 kr0 = kr_load<LOCAL>(kr_seg + 2 * c);
+    const ulonglong2 kr0 = kr_load<WR_SMEM>(kr_mine + 2 * c);
     unsigned long long Kc = kr0.x, Rc = kr0.y;
     const unsigned long long und = valid & ~(Kc | Rc);
     if (und == 0ull) return false;
@@ -440,24 +443,35 @@ __device__ bool resolve_chunk(const ResolveArgs &a, const NmsSegment &sg, int c,
             const int kmax = (int)(row >> 13);           // summary words that can hold a bit: column blocks 0 .. row / 128
             for (int k = 0; k <= kmax && !exK[p]; ++k) {
                 unsigned long long sb = __ldg(srow + k);
-                while (sb) {
-                    const int J = (k << 6) + __ffsll((long long)sb) - 1;
-                    sb &= sb - 1ull;
-                    const ulonglong2 m = __ldg(reinterpret_cast<const ulonglong2 *>(mrow + 2 * J));
+                while (sb != 0ull && !exK[p]) {
+                    // four column blocks at a time: their mask loads are in flight together
+                    int J[4];
+                    ulonglong2 m[4];
 #pragma unroll
-                    for (int h = 0; h < 2; ++h) {
-                        const unsigned long long mv = h ? m.y : m.x;
-                        const int w = 2 * J + h;
-                        if (mv == 0ull) continue;
-                        if (w < c) {                      // earlier chunk: its current state
-                            const ulonglong2 o = kr_load<LOCAL>(kr_seg + 2 * w);
-                            if (mv & o.x) exK[p] = true;
-                            if (mv & ~(o.x | o.y)) exU[p] = true;
-                        } else if (w == c) {
-                            D[p] = mv;                    // earlier boxes of this chunk
+                    for (int t = 0; t < 4; ++t) {
+                        J[t] = sb ? (k << 6) + __ffsll((long long)sb) - 1 : -1;
+                        sb &= sb - 1ull;     // 0 stays 0
+                    }
+#pragma unroll
+                    for (int t = 0; t < 4; ++t)
+                        m[t] = J[t] >= 0 ? __ldg(reinterpret_cast<const ulonglong2 *>(mrow + 2 * J[t]))
+                                         : make_ulonglong2(0ull, 0ull);
+#pragma unroll
+                    for (int t = 0; t < 4; ++t) {
+#pragma unroll
+                        for (int h = 0; h < 2; ++h) {
+                            const unsigned long long mv = h ? m[t].y : m[t].x;
+                            const int w = 2 * J[t] + h;
+                            if (mv == 0ull) continue;
+                            if (w < c) {                      // earlier chunk: its state
+                                const ulonglong2 o = kr_load<RD_SMEM>(kr_others + 2 * w);
+                                if (mv & o.x) exK[p] = true;
+                                if (mv & ~(o.x | o.y)) exU[p] = true;
+                            } else if (w == c) {
+                                D[p] = mv;                    // earlier boxes of this chunk
+                            }
                         }
                     }
-                    if (exK[p]) break;
                 }
             }
         }
@@ -483,7 +497,7 @@ __device__ bool resolve_chunk(const ResolveArgs &a, const NmsSegment &sg, int c,
         Rc |= REM;
         cand &= ~(REM | KEEP);
     }
-    if (lane == 0 && (Kc != kr0.x || Rc != kr0.y)) kr_store<LOCAL>(kr_seg + 2 * c, Kc, Rc);
+    if (lane == 0 && (Kc != kr0.x || Rc != kr0.y)) kr_store<WR_SMEM>(kr_mine + 2 * c, Kc, Rc);
     return cand != 0ull;
 }
 
@@ -514,7 +528,9 @@ __device__ __forceinline__ int block_sum(int v, int *s_red /* kResWarps */) {
 template <bool MC>
 __global__ void __launch_bounds__(kResThreads, 1)
 nms_resolve_kernel(const ResolveArgs a) {
-    __shared__ __align__(16) unsigned long long s_kr[2 * kLocalChunks];
+    // dynamic shared memory: the (kept, removed) pairs of one small segment, or (grid path,
+    // a.snapshot) this round's copy of the pairs of ALL chunks
+    extern __shared__ __align__(16) unsigned long long s_kr[];
     __shared__ int s_red[kResWarps];
     __shared__ int s_warp_cnt[kResWarps];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -529,7 +545,8 @@ nms_resolve_kernel(const ResolveArgs a) {
         __syncthreads();
         for (;;) {
             bool left = false;
-            for (int c = warp; c < nch; c += kResWarps) left |= resolve_chunk<true>(a, sg, c, s_kr, lane);
+            for (int c = warp; c < nch; c += kResWarps)
+                left |= resolve_chunk<true, true>(a, sg, c, s_kr, s_kr, lane);
             if (!__syncthreads_or(left)) break;
         }
         for (int c = warp; c < nch; c += kResWarps) write_flags(a, sg, c, s_kr[2 * c], lane);
@@ -538,18 +555,31 @@ nms_resolve_kernel(const ResolveArgs a) {
 
     // ---- large segments: the whole grid, rounds separated by a grid barrier -------------------
     if (a.has_large) {
-        const int64_t gwarp = (int64_t)blockIdx.x * kResWarps + warp, nwarps = (int64_t)G * kResWarps;
+        // consecutive chunks go to different CTAs: a mid-size segment is spread over every SM
+        const int64_t gwarp = (int64_t)blockIdx.x + (int64_t)G * warp, nwarps = (int64_t)G * kResWarps;
         volatile unsigned int *pend = a.sc.sync + 2;
         for (unsigned int round = 0;; ++round) {
             // slot (round + 1) % 3 was last read after the barrier of round - 2; every CTA has passed
             // the barrier of round - 1 since, so it can be cleared for the next round now
             if (blockIdx.x == 0 && tid == 0) pend[(round + 1) % 3] = 0u;
+            if (a.snapshot) {
+                // every row test below reads the state of earlier chunks: from shared memory
+                // instead of one L2 round trip each
+                for (int64_t i = tid; i < a.chunks; i += kResThreads) {
+                    const ulonglong2 v = ldcg_u64x2(a.sc.kr + 2 * i);
+                    s_kr[2 * i] = v.x;
+                    s_kr[2 * i + 1] = v.y;
+                }
+                __syncthreads();
+            }
             bool left = false;
             for (int64_t gw = gwarp; gw < a.chunks; gw += nwarps) {
                 const NmsSegment &sg = a.segs[segment_of_slot(a.segs, a.nseg, gw * 64)];
-                const int64_t c = gw - (sg.pstart >> 6);
+                const int64_t c = gw - (sg.pstart >> 6), w0 = 2 * (sg.pstart >> 6);
                 if (sg.row_blocks <= kLocalChunks || c >= sg.row_blocks) continue;
-                left |= resolve_chunk<false>(a, sg, (int)c, a.sc.kr + 2 * (sg.pstart >> 6), lane);
+                left |= a.snapshot
+                    ? resolve_chunk<true, false>(a, sg, (int)c, s_kr + w0, a.sc.kr + w0, lane)
+                    : resolve_chunk<false, false>(a, sg, (int)c, a.sc.kr + w0, a.sc.kr + w0, lane);
             }
             if (left && lane == 0) pend[round % 3] = 1u;
             grid_barrier(a.sc.sync, G);
@@ -684,6 +714,8 @@ void nms_plan(int64_t n, const int64_t *seg_offsets_host, int64_t num_segments, 
     plan->total_bytes = off;
 }
 
+constexpr size_t kSnapshotBytes = 160 * 1024;   // chunks * 16 B: up to 655k boxes in one launch
+
 // CTAs of the resolve grid: all co-resident (cooperative launch), at most one per SM
 static int resolve_grid_limit(bool mc) {
     static int limit[2] = {0, 0};
@@ -692,9 +724,13 @@ static int resolve_grid_limit(bool mc) {
         if (cudaGetDevice(&dev) != cudaSuccess ||
             cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess)
             return -1;
-        const cudaError_t e = mc
-            ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, nms_resolve_kernel<true>, kResThreads, 0)
-            : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, nms_resolve_kernel<false>, kResThreads, 0);
+        cudaError_t e = mc
+            ? cudaFuncSetAttribute(nms_resolve_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSnapshotBytes)
+            : cudaFuncSetAttribute(nms_resolve_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSnapshotBytes);
+        if (e != cudaSuccess) return -1;
+        e = mc
+            ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, nms_resolve_kernel<true>, kResThreads, kSnapshotBytes)
+            : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, nms_resolve_kernel<false>, kResThreads, kSnapshotBytes);
         if (e != cudaSuccess || per_sm < 1) return -1;
         limit[mc] = sms < kNmsMaxBlocks ? sms : kNmsMaxBlocks;   // one 1024-thread CTA per SM
     }
@@ -717,17 +753,26 @@ static int launch_mask(const MaskArgs &g, int64_t tiles, cudaStream_t stream) {
     return cudaLaunchKernelEx(&cfg, nms_mask_kernel, g) == cudaSuccess ? 0 : -3;
 }
 
-static int launch_resolve(const ResolveArgs &a, cudaStream_t stream) {
-    const bool mc = a.mc.dets_out != nullptr;
+static int launch_resolve(const ResolveArgs &a_in, cudaStream_t stream) {
+    const bool mc = a_in.mc.dets_out != nullptr;
     const int limit = resolve_grid_limit(mc);
     if (limit < 1) return -3;
-    // one chunk per warp in the first round, one small segment per CTA
-    int64_t want = (a.chunks + kResWarps - 1) / kResWarps;
-    if (want < a.nseg) want = a.nseg;
+    // one small segment per CTA; with large segments, their chunks spread over every SM (the row
+    // tests are latency-bound: more SMs, more loads in flight)
+    int64_t want = a_in.has_large ? a_in.chunks : a_in.nseg;
     if (want < 1) want = 1;
+    // dynamic shared memory: one small segment's state, or a snapshot of every chunk's
+    ResolveArgs a = a_in;
+    size_t dyn = 2 * kLocalChunks * sizeof(unsigned long long);
+    a.snapshot = 0;
+    if (a.has_large && (size_t)a.chunks * 16 <= kSnapshotBytes) {
+        a.snapshot = 1;
+        if ((size_t)a.chunks * 16 > dyn) dyn = (size_t)a.chunks * 16;
+    }
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)(want < limit ? want : limit));
     cfg.blockDim = dim3(kResThreads);
+    cfg.dynamicSmemBytes = dyn;
     cfg.stream = stream;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeCooperative;              // the grid barrier needs every CTA resident
