@@ -196,6 +196,18 @@ def secondary_nms(torch, rg, synth, reps=5):
     s1 = torch.from_numpy(synth.unique_scores(n, 9)).cuda()
     t = best(lambda: rg.nms_rotated(b1, s1, 0.1))
     res['nms_rotated_single_segment_30000'] = {'boxes': n, 'ms': 1e3 * t, 'boxes_per_s': n / t}
+    # C3 (iii): the assigner's reductions of the 8192 x 8192 matrix without the matrix
+    a3, b3 = synth.c3_iou(0)
+    a3d, b3d = torch.from_numpy(a3).cuda(), torch.from_numpy(b3).cuda()
+    t = best(lambda: rg.rbbox_overlaps_max(a3d, b3d))
+    res['c3_rowcol_max_8192x8192_fused'] = {'pairs': a3.shape[0] * b3.shape[0], 'ms': 1e3 * t,
+                                            'gpairs_per_s': a3.shape[0] * b3.shape[0] / t / 1e9}
+    anchors = torch.from_numpy(synth.le90_boxes(196416, 5, 1024.0)).cuda()
+    gtb = torch.from_numpy(synth.le90_boxes(100, 6, 1024.0)).cuda()
+    asg = rg.MaxIoUAssigner(0.5, 0.4, min_pos_iou=0.0)
+    t = best(lambda: asg.assign(anchors, gtb))
+    res['retinanet_max_iou_assign_100gt_x_196416_anchors'] = {'pairs': 100 * 196416, 'ms': 1e3 * t,
+                                                              'gpairs_per_s': 100 * 196416 / t / 1e9}
     # C5: ~200k detections of 400 overlapping patches, 15 Zipf-skewed classes
     patches, offs, shape = synth.c5_patch_results(0)
     nd = sum(a.shape[0] for p in patches for a in p)

@@ -121,6 +121,41 @@ int rotgeo_nms(const float *boxes, int64_t n, int stride, const float *offsets,
                int64_t num_segments, float iou_threshold, int64_t *keep_out,
                int64_t *num_keep_out, void *workspace, size_t workspace_bytes, void *stream);
 
+/* ---- fused assigner reductions ------------------------------------------------
+ * What every caller of the reference's IoU calculator does with the matrix, without the
+ * matrix.  boxes1 = the rows (ground truth in the assigners),
+ * boxes2 = the columns (anchors / proposals); mode, min_wh as in rotgeo_iou_pairwise.
+ *
+ * rotgeo_iou_rowcol_max: row_max[i], row_argmax[i] = max / first argmax over the columns of
+ *   overlap(boxes1[i], boxes2[:]) and col_max[j], col_argmax[j] likewise over the rows — the
+ *   pair of `overlaps.max(dim=1)` / `overlaps.max(dim=0)` every assigner starts with
+ *   (mmdet MaxIoUAssigner.assign_wrt_overlaps; mmrotate/core/bbox/assigners/
+ *   atss_obb_assigner.py:118-145; obb_label_assigner.py:128-143 per gt).  Any output may be
+ *   null.  A line without a positive value reports 0 at index 0.
+ *
+ * rotgeo_max_iou_assign: the whole of MaxIoUAssigner.assign_wrt_overlaps after
+ *   `overlaps = self.iou_calculator(gt_bboxes, bboxes)` (reference call:
+ *   rotate_iou2d_calculator.py:44 <- mmdet max_iou_assigner.py): per box j
+ *     -1, then 0 where neg_iou_lo <= max_j < neg_iou_hi (a float neg_iou_thr t is the
+ *     interval [0, t)), then argmax_j + 1 where max_j >= pos_iou_thr; with
+ *     match_low_quality, every gt i with gt_max_i >= min_pos_iou claims (ascending i, later
+ *     wins) box gt_argmax_i, or with gt_max_assign_all every box whose overlap with i equals
+ *     gt_max_i — including, as in mmdet, all boxes when gt_max_i == 0 >= min_pos_iou.
+ *   assigned_gt_inds (num_boxes,) int64, max_overlaps (num_boxes,) float (nullable).
+ *   gt_bboxes_ignore / ignore_iof_thr / gpu_assign_thr are not part of this entry.
+ *
+ * workspace: rotgeo_iou_max_workspace_bytes(n1, n2) bytes, 16-byte aligned. */
+size_t rotgeo_iou_max_workspace_bytes(int64_t n1, int64_t n2);
+int rotgeo_iou_rowcol_max(const float *boxes1, int64_t n1, int stride1, const float *boxes2, int64_t n2,
+                          int stride2, int mode, float min_wh, float *row_max, int64_t *row_argmax,
+                          float *col_max, int64_t *col_argmax, void *workspace, size_t workspace_bytes,
+                          void *stream);
+int rotgeo_max_iou_assign(const float *gt_boxes, int64_t num_gts, int stride_g, const float *boxes,
+                          int64_t num_boxes, int stride_b, int mode, float min_wh, float pos_iou_thr,
+                          float neg_iou_lo, float neg_iou_hi, float min_pos_iou, int match_low_quality,
+                          int gt_max_assign_all, int64_t *assigned_gt_inds, float *max_overlaps,
+                          void *workspace, size_t workspace_bytes, void *stream);
+
 /* ---- rotated NMS front-end: orders and segment sizes ----------------------------
  * What the reference does in python/ATen around the native op
  * (mmcv/ops/nms.py nms_rotated: scores.sort(0, descending=True) + index_select;

@@ -135,3 +135,35 @@ def nms_keep_segmented(boxes, scores, iou_threshold, seg_ids=None, offsets=None)
     rank = torch.empty_like(order)
     rank[order] = torch.arange(order.numel())
     return kept[torch.argsort(rank[kept])]
+
+
+def max_iou_assign(overlaps, pos_iou_thr, neg_iou_thr, min_pos_iou=0., gt_max_assign_all=True,
+                   match_low_quality=True):
+    """mmdet 2.x ``MaxIoUAssigner.assign_wrt_overlaps`` (mmdet/core/bbox/assigners/
+    max_iou_assigner.py — external dependency of the reference, pinned by
+    mmrotate/__init__.py; the assigner named by the fork's RetinaNet / RPN / R-CNN configs),
+    restated on a given (num_gts, num_bboxes) overlap matrix.  Returns (assigned_gt_inds,
+    max_overlaps)."""
+    num_gts, num_bboxes = overlaps.size(0), overlaps.size(1)
+    assigned = overlaps.new_full((num_bboxes,), -1, dtype=torch.long)
+    if num_gts == 0 or num_bboxes == 0:
+        max_overlaps = overlaps.new_zeros((num_bboxes,))
+        if num_gts == 0:
+            assigned[:] = 0
+        return assigned, max_overlaps
+    max_overlaps, argmax_overlaps = overlaps.max(dim=0)
+    gt_max_overlaps, gt_argmax_overlaps = overlaps.max(dim=1)
+    if isinstance(neg_iou_thr, float):
+        assigned[(max_overlaps >= 0) & (max_overlaps < neg_iou_thr)] = 0
+    else:
+        assigned[(max_overlaps >= neg_iou_thr[0]) & (max_overlaps < neg_iou_thr[1])] = 0
+    pos_inds = max_overlaps >= pos_iou_thr
+    assigned[pos_inds] = argmax_overlaps[pos_inds] + 1
+    if match_low_quality:
+        for i in range(num_gts):
+            if gt_max_overlaps[i] >= min_pos_iou:
+                if gt_max_assign_all:
+                    assigned[overlaps[i, :] == gt_max_overlaps[i]] = i + 1
+                else:
+                    assigned[gt_argmax_overlaps[i]] = i + 1
+    return assigned, max_overlaps

@@ -14,6 +14,7 @@ SYMBOLS = (
     'rotgeo_version', 'rotgeo_last_error', 'rotgeo_packed_bytes', 'rotgeo_pack_boxes',
     'rotgeo_iou_workspace_bytes', 'rotgeo_iou_pairwise', 'rotgeo_iou_pairwise_packed',
     'rotgeo_iou_aligned', 'rotgeo_nms_workspace_bytes', 'rotgeo_nms',
+    'rotgeo_iou_max_workspace_bytes', 'rotgeo_iou_rowcol_max', 'rotgeo_max_iou_assign',
     'rotgeo_nms_prepare_bytes', 'rotgeo_nms_prepare', 'rotgeo_nms_prepared',
     'rotgeo_multiclass_nms_workspace_bytes', 'rotgeo_multiclass_nms',
 )
@@ -56,6 +57,13 @@ def load():
     L.rotgeo_nms_workspace_bytes.restype = sz
     L.rotgeo_nms.argtypes = [vp, i64, i32, vp, vp, vp, vp, i64, f32, vp, vp, vp, sz, vp]
     L.rotgeo_nms.restype = i32
+    L.rotgeo_iou_max_workspace_bytes.argtypes = [i64, i64]
+    L.rotgeo_iou_max_workspace_bytes.restype = sz
+    L.rotgeo_iou_rowcol_max.argtypes = [vp, i64, i32, vp, i64, i32, i32, f32, vp, vp, vp, vp, vp, sz, vp]
+    L.rotgeo_iou_rowcol_max.restype = i32
+    L.rotgeo_max_iou_assign.argtypes = [vp, i64, i32, vp, i64, i32, i32, f32, f32, f32, f32, f32, i32, i32,
+                                        vp, vp, vp, sz, vp]
+    L.rotgeo_max_iou_assign.restype = i32
     L.rotgeo_nms_prepare_bytes.argtypes = [i64]
     L.rotgeo_nms_prepare_bytes.restype = sz
     L.rotgeo_nms_prepare.argtypes = [vp, i64, i32, vp, vp, vp, sz, vp, i64, vp, vp]

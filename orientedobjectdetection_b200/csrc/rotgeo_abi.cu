@@ -119,6 +119,74 @@ int rotgeo_iou_aligned(const float *boxes1, const float *boxes2, int64_t n, int 
     return ROTGEO_OK;
 }
 
+size_t rotgeo_iou_max_workspace_bytes(int64_t n1, int64_t n2) {
+    return rotgeo::iou_max_workspace_bytes(n1, n2);
+}
+
+static int fill_async(void *dst, int value, size_t bytes, cudaStream_t st) {
+    return bytes == 0 || cudaMemsetAsync(dst, value, bytes, st) == cudaSuccess ? 0 : -1;
+}
+
+int rotgeo_iou_rowcol_max(const float *boxes1, int64_t n1, int stride1, const float *boxes2, int64_t n2,
+                          int stride2, int mode, float min_wh, float *row_max, int64_t *row_argmax,
+                          float *col_max, int64_t *col_argmax, void *workspace, size_t workspace_bytes,
+                          void *stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    if (n1 < 0 || n2 < 0 || stride1 < 5 || stride2 < 5 || (mode != 0 && mode != 1))
+        return fail(ROTGEO_ERR_ARG, "iou_rowcol_max: n1=%lld n2=%lld mode=%d", (long long)n1, (long long)n2, mode);
+    if (n1 == 0 || n2 == 0) {
+        // an empty line has maximum 0 at index 0 here (torch.max raises on an empty dimension)
+        if ((n1 && row_max && fill_async(row_max, 0, (size_t)n1 * 4, st)) ||
+            (n1 && row_argmax && fill_async(row_argmax, 0, (size_t)n1 * 8, st)) ||
+            (n2 && col_max && fill_async(col_max, 0, (size_t)n2 * 4, st)) ||
+            (n2 && col_argmax && fill_async(col_argmax, 0, (size_t)n2 * 8, st)))
+            return cuda_fail("iou_rowcol_max memset");
+        return ROTGEO_OK;
+    }
+    if (!boxes1 || !boxes2) return fail(ROTGEO_ERR_ARG, "iou_rowcol_max: null pointer");
+    const size_t need = rotgeo::iou_max_workspace_bytes(n1, n2);
+    if (!workspace || !aligned16(workspace) || workspace_bytes < need)
+        return fail(ROTGEO_ERR_WORKSPACE, "iou_rowcol_max: workspace %zu < %zu bytes or misaligned",
+                    workspace_bytes, need);
+    const int rc = rotgeo::launch_iou_rowcol_max(boxes1, n1, stride1, boxes2, n2, stride2, mode, min_wh,
+                                                 row_max, row_argmax, col_max, col_argmax, workspace, st);
+    if (rc == -1) return fail(ROTGEO_ERR_ARG, "iou_rowcol_max: too many tiles");
+    if (rc) return cuda_fail("iou_rowcol_max launch");
+    return ROTGEO_OK;
+}
+
+int rotgeo_max_iou_assign(const float *gt_boxes, int64_t num_gts, int stride_g, const float *boxes,
+                          int64_t num_boxes, int stride_b, int mode, float min_wh, float pos_iou_thr,
+                          float neg_iou_lo, float neg_iou_hi, float min_pos_iou, int match_low_quality,
+                          int gt_max_assign_all, int64_t *assigned_gt_inds, float *max_overlaps,
+                          void *workspace, size_t workspace_bytes, void *stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    if (num_gts < 0 || num_boxes < 0 || stride_g < 5 || stride_b < 5 || (mode != 0 && mode != 1) ||
+        num_gts >= 0x7fffffffLL)
+        return fail(ROTGEO_ERR_ARG, "max_iou_assign: gts=%lld boxes=%lld mode=%d", (long long)num_gts,
+                    (long long)num_boxes, mode);
+    if (num_boxes == 0) return ROTGEO_OK;
+    if (!assigned_gt_inds) return fail(ROTGEO_ERR_ARG, "max_iou_assign: null assigned_gt_inds");
+    if (num_gts == 0) {   // no ground truth: everything is background (max_iou_assigner.py, empty branch)
+        if (fill_async(assigned_gt_inds, 0, (size_t)num_boxes * 8, st) ||
+            (max_overlaps && fill_async(max_overlaps, 0, (size_t)num_boxes * 4, st)))
+            return cuda_fail("max_iou_assign memset");
+        return ROTGEO_OK;
+    }
+    if (!gt_boxes || !boxes) return fail(ROTGEO_ERR_ARG, "max_iou_assign: null pointer");
+    const size_t need = rotgeo::iou_max_workspace_bytes(num_gts, num_boxes);
+    if (!workspace || !aligned16(workspace) || workspace_bytes < need)
+        return fail(ROTGEO_ERR_WORKSPACE, "max_iou_assign: workspace %zu < %zu bytes or misaligned",
+                    workspace_bytes, need);
+    const int rc = rotgeo::launch_max_iou_assign(gt_boxes, num_gts, stride_g, boxes, num_boxes, stride_b, mode,
+                                                 min_wh, pos_iou_thr, neg_iou_lo, neg_iou_hi, min_pos_iou,
+                                                 match_low_quality, gt_max_assign_all, assigned_gt_inds,
+                                                 max_overlaps, workspace, st);
+    if (rc == -1) return fail(ROTGEO_ERR_ARG, "max_iou_assign: too many tiles");
+    if (rc) return cuda_fail("max_iou_assign launch");
+    return ROTGEO_OK;
+}
+
 size_t rotgeo_nms_workspace_bytes(int64_t n, const int64_t *seg_offsets_host, int64_t num_segments) {
     if (n <= 0) return 0;
     rotgeo::NmsPlan plan;

@@ -59,6 +59,24 @@ int launch_pack(const PackSet &s1, const PackSet &s2, float min_wh, float cell,
 int launch_iou_pairwise(const void *packed1, int64_t n1, const void *packed2, int64_t n2, int mode,
                         float *out, int64_t ld_out, bool after_pack, cudaStream_t stream);
 
+// reductions instead of the matrix (rotgeo_assign.cu): keys = float bits << 32 | ~index, 0 = none
+int launch_iou_max(const void *packed1, int64_t n1, const void *packed2, int64_t n2, int mode,
+                   unsigned long long *row_key, unsigned long long *col_key, bool after_pack,
+                   cudaStream_t stream);
+int launch_iou_row_max_hits(const void *packed1, int64_t n1, const void *packed2, int64_t n2, int mode,
+                            const float *row_max, float min_pos_iou, int *col_lowq, cudaStream_t stream);
+
+// fused assigner path (rotgeo_assign.cu)
+size_t iou_max_workspace_bytes(int64_t n1, int64_t n2);
+int launch_iou_rowcol_max(const float *boxes1, int64_t n1, int stride1, const float *boxes2, int64_t n2,
+                          int stride2, int mode, float min_wh, float *row_max, int64_t *row_argmax,
+                          float *col_max, int64_t *col_argmax, void *workspace, cudaStream_t stream);
+int launch_max_iou_assign(const float *gts, int64_t num_gts, int stride_g, const float *boxes,
+                          int64_t num_boxes, int stride_b, int mode, float min_wh, float pos_iou_thr,
+                          float neg_lo, float neg_hi, float min_pos_iou, int match_low_quality,
+                          int gt_max_assign_all, int64_t *assigned, float *max_overlaps, void *workspace,
+                          cudaStream_t stream);
+
 int launch_iou_aligned(const float *boxes1, const float *boxes2, int64_t n, int stride1,
                        int stride2, int mode, float min_wh, float *out, cudaStream_t stream);
 

