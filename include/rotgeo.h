@@ -156,6 +156,26 @@ int rotgeo_max_iou_assign(const float *gt_boxes, int64_t num_gts, int stride_g, 
                           int gt_max_assign_all, int64_t *assigned_gt_inds, float *max_overlaps,
                           void *workspace, size_t workspace_bytes, void *stream);
 
+/* ---- mAP evaluation: true / false positives -------------------------------------
+ * The per-image body of the reference's tpfp_default (mmrotate/core/evaluation/
+ * eval_map.py:12-94) for ALL (class, image) pairs of eval_rbbox_map (eval_map.py:126-246)
+ * in one launch.  Detections (rows of det_stride >= 6 floats:
+ * box + score) and ground truths (rows of gt_stride >= 5 floats) are grouped by segment;
+ * segment s owns dets [det_seg_offsets[s], det_seg_offsets[s+1]) and gts likewise (device
+ * arrays of num_segments + 1 int64).  Inside a segment the ignored ground truths come after
+ * the others, flagged in gt_ignore (nullable).  Per detection, as in the reference: IoU
+ * (raw box_iou_rotated, no clamp) against the segment's gts, max and first argmax; then in
+ * descending score order (ties: lower index first) tp = 1 if max >= iou_thr and the argmax
+ * gt is neither ignored nor claimed yet, fp = 1 if it was claimed already or max < iou_thr,
+ * both 0 if the argmax gt is an ignored one; a segment without gts is all fp.
+ * tp_out, fp_out: (num_dets,) bytes; iou_max_out (num_dets,) float, nullable. */
+size_t rotgeo_eval_tpfp_workspace_bytes(int64_t num_dets, int64_t num_gts);
+int rotgeo_eval_tpfp(const float *dets, int64_t num_dets, int det_stride, const int64_t *det_seg_offsets,
+                     const float *gts, int64_t num_gts, int gt_stride, const int64_t *gt_seg_offsets,
+                     const uint8_t *gt_ignore, int64_t num_segments, float iou_thr, uint8_t *tp_out,
+                     uint8_t *fp_out, float *iou_max_out, void *workspace, size_t workspace_bytes,
+                     void *stream);
+
 /* ---- rotated NMS front-end: orders and segment sizes ----------------------------
  * What the reference does in python/ATen around the native op
  * (mmcv/ops/nms.py nms_rotated: scores.sort(0, descending=True) + index_select;

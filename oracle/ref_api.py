@@ -167,3 +167,80 @@ def max_iou_assign(overlaps, pos_iou_thr, neg_iou_thr, min_pos_iou=0., gt_max_as
                 else:
                     assigned[gt_argmax_overlaps[i]] = i + 1
     return assigned, max_overlaps
+
+
+def tpfp_default(det_bboxes, gt_bboxes, gt_bboxes_ignore, iou_thr=0.5):
+    """reference mmrotate/core/evaluation/eval_map.py:12-94 without area ranges (which the
+    reference itself leaves NotImplemented); ties in the score order: lower index first"""
+    det_bboxes = np.array(det_bboxes)
+    gt_ignore_inds = np.concatenate((np.zeros(gt_bboxes.shape[0], dtype=bool),
+                                     np.ones(gt_bboxes_ignore.shape[0], dtype=bool)))
+    gt_bboxes = np.vstack((gt_bboxes, gt_bboxes_ignore))
+    num_dets, num_gts = det_bboxes.shape[0], gt_bboxes.shape[0]
+    tp = np.zeros(num_dets, dtype=np.float32)
+    fp = np.zeros(num_dets, dtype=np.float32)
+    if num_gts == 0:
+        fp[...] = 1
+        return tp, fp
+    if num_dets == 0:
+        return tp, fp
+    ious = ref.box_iou_rotated(det_bboxes[:, :5].astype(np.float32), gt_bboxes.astype(np.float32))
+    ious_max, ious_argmax = ious.max(axis=1), ious.argmax(axis=1)
+    sort_inds = np.argsort(-det_bboxes[:, -1], kind='stable')
+    gt_covered = np.zeros(num_gts, dtype=bool)
+    for i in sort_inds:
+        if ious_max[i] >= iou_thr:
+            matched_gt = ious_argmax[i]
+            if not gt_ignore_inds[matched_gt]:
+                if not gt_covered[matched_gt]:
+                    gt_covered[matched_gt] = True
+                    tp[i] = 1
+                else:
+                    fp[i] = 1
+        else:
+            fp[i] = 1
+    return tp, fp
+
+
+def eval_rbbox_map(det_results, annotations, iou_thr=0.5, use_07_metric=True):
+    """reference eval_map.py:126-246 (scale_ranges=None) with mmdet's average_precision
+    restated; returns (mean_ap, per-class dicts, per-class (tp, fp) before sorting)"""
+    num_imgs, num_classes = len(det_results), len(det_results[0])
+    results, flags = [], []
+    eps = np.finfo(np.float32).eps
+    for c in range(num_classes):
+        cls_dets = [np.asarray(r[c], dtype=np.float32).reshape(-1, 6) for r in det_results]
+        tps, fps, num_gts = [], [], 0
+        for i, ann in enumerate(annotations):
+            g = np.asarray(ann['bboxes'], np.float32).reshape(-1, 5)[np.asarray(ann['labels']) == c]
+            if ann.get('labels_ignore', None) is not None:
+                gi = np.asarray(ann['bboxes_ignore'], np.float32).reshape(-1, 5)[np.asarray(ann['labels_ignore']) == c]
+            else:
+                gi = np.zeros((0, 5), np.float32)
+            t, f = tpfp_default(cls_dets[i], g, gi, iou_thr)
+            tps.append(t)
+            fps.append(f)
+            num_gts += g.shape[0]
+        alld = np.vstack(cls_dets)
+        tp_raw, fp_raw = np.hstack(tps), np.hstack(fps)
+        flags.append((tp_raw, fp_raw))
+        order = np.argsort(-alld[:, -1], kind='stable')
+        tp, fp = np.cumsum(tp_raw[order]), np.cumsum(fp_raw[order])
+        rec = tp / np.maximum(num_gts, eps)
+        prec = tp / np.maximum(tp + fp, eps)
+        if use_07_metric:
+            ap = 0.0
+            for thr in np.arange(0, 1 + 1e-3, 0.1):
+                p = prec[rec >= thr]
+                ap += p.max() if p.size else 0.0
+            ap /= 11
+        else:
+            mrec = np.concatenate([[0.], rec, [1.]])
+            mpre = np.concatenate([[0.], prec, [0.]])
+            for k in range(mpre.size - 1, 0, -1):
+                mpre[k - 1] = max(mpre[k - 1], mpre[k])
+            ind = np.where(mrec[1:] != mrec[:-1])[0]
+            ap = float(np.sum((mrec[ind + 1] - mrec[ind]) * mpre[ind + 1]))
+        results.append({'num_gts': num_gts, 'num_dets': alld.shape[0], 'recall': rec, 'precision': prec, 'ap': ap})
+    aps = [r['ap'] for r in results if r['num_gts'] > 0]
+    return (float(np.mean(aps)) if aps else 0.0), results, flags

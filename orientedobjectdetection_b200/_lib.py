@@ -15,6 +15,7 @@ SYMBOLS = (
     'rotgeo_iou_workspace_bytes', 'rotgeo_iou_pairwise', 'rotgeo_iou_pairwise_packed',
     'rotgeo_iou_aligned', 'rotgeo_nms_workspace_bytes', 'rotgeo_nms',
     'rotgeo_iou_max_workspace_bytes', 'rotgeo_iou_rowcol_max', 'rotgeo_max_iou_assign',
+    'rotgeo_eval_tpfp_workspace_bytes', 'rotgeo_eval_tpfp',
     'rotgeo_nms_prepare_bytes', 'rotgeo_nms_prepare', 'rotgeo_nms_prepared',
     'rotgeo_multiclass_nms_workspace_bytes', 'rotgeo_multiclass_nms',
 )
@@ -64,6 +65,10 @@ def load():
     L.rotgeo_max_iou_assign.argtypes = [vp, i64, i32, vp, i64, i32, i32, f32, f32, f32, f32, f32, i32, i32,
                                         vp, vp, vp, sz, vp]
     L.rotgeo_max_iou_assign.restype = i32
+    L.rotgeo_eval_tpfp_workspace_bytes.argtypes = [i64, i64]
+    L.rotgeo_eval_tpfp_workspace_bytes.restype = sz
+    L.rotgeo_eval_tpfp.argtypes = [vp, i64, i32, vp, vp, i64, i32, vp, vp, i64, f32, vp, vp, vp, vp, sz, vp]
+    L.rotgeo_eval_tpfp.restype = i32
     L.rotgeo_nms_prepare_bytes.argtypes = [i64]
     L.rotgeo_nms_prepare_bytes.restype = sz
     L.rotgeo_nms_prepare.argtypes = [vp, i64, i32, vp, vp, vp, sz, vp, i64, vp, vp]

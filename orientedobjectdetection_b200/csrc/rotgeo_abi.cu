@@ -187,6 +187,32 @@ int rotgeo_max_iou_assign(const float *gt_boxes, int64_t num_gts, int stride_g, 
     return ROTGEO_OK;
 }
 
+size_t rotgeo_eval_tpfp_workspace_bytes(int64_t num_dets, int64_t num_gts) {
+    return rotgeo::eval_tpfp_workspace_bytes(num_dets, num_gts);
+}
+
+int rotgeo_eval_tpfp(const float *dets, int64_t num_dets, int det_stride, const int64_t *det_seg_offsets,
+                     const float *gts, int64_t num_gts, int gt_stride, const int64_t *gt_seg_offsets,
+                     const uint8_t *gt_ignore, int64_t num_segments, float iou_thr, uint8_t *tp_out,
+                     uint8_t *fp_out, float *iou_max_out, void *workspace, size_t workspace_bytes,
+                     void *stream) {
+    if (num_dets < 0 || num_gts < 0 || num_segments < 0 || det_stride < 6 || gt_stride < 5 ||
+        num_dets > 0x7fffffffLL || num_gts > 0x7fffffffLL)
+        return fail(ROTGEO_ERR_ARG, "eval_tpfp: dets=%lld gts=%lld segments=%lld det_stride=%d gt_stride=%d",
+                    (long long)num_dets, (long long)num_gts, (long long)num_segments, det_stride, gt_stride);
+    if (num_dets == 0 || num_segments == 0) return ROTGEO_OK;
+    if (!dets || !det_seg_offsets || !gt_seg_offsets || !tp_out || !fp_out || (num_gts > 0 && !gts))
+        return fail(ROTGEO_ERR_ARG, "eval_tpfp: null pointer");
+    const size_t need = rotgeo::eval_tpfp_workspace_bytes(num_dets, num_gts);
+    if (!workspace || !aligned16(workspace) || workspace_bytes < need)
+        return fail(ROTGEO_ERR_WORKSPACE, "eval_tpfp: workspace %zu < %zu bytes or misaligned", workspace_bytes, need);
+    if (rotgeo::launch_eval_tpfp(dets, num_dets, det_stride, det_seg_offsets, gts, num_gts, gt_stride,
+                                 gt_seg_offsets, gt_ignore, num_segments, iou_thr, tp_out, fp_out, iou_max_out,
+                                 workspace, (cudaStream_t)stream))
+        return cuda_fail("eval_tpfp launch");
+    return ROTGEO_OK;
+}
+
 size_t rotgeo_nms_workspace_bytes(int64_t n, const int64_t *seg_offsets_host, int64_t num_segments) {
     if (n <= 0) return 0;
     rotgeo::NmsPlan plan;

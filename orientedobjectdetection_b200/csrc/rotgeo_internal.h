@@ -77,6 +77,13 @@ int launch_max_iou_assign(const float *gts, int64_t num_gts, int stride_g, const
                           int gt_max_assign_all, int64_t *assigned, float *max_overlaps, void *workspace,
                           cudaStream_t stream);
 
+// mAP evaluation: TP / FP of every detection, all (class, image) segments at once (rotgeo_eval.cu)
+size_t eval_tpfp_workspace_bytes(int64_t num_dets, int64_t num_gts);
+int launch_eval_tpfp(const float *dets, int64_t num_dets, int det_stride, const int64_t *det_off,
+                     const float *gts, int64_t num_gts, int gt_stride, const int64_t *gt_off,
+                     const uint8_t *gt_ignore, int64_t num_segments, float iou_thr, uint8_t *tp,
+                     uint8_t *fp, float *iou_max_out, void *workspace, cudaStream_t stream);
+
 int launch_iou_aligned(const float *boxes1, const float *boxes2, int64_t n, int stride1,
                        int stride2, int mode, float min_wh, float *out, cudaStream_t stream);
 

@@ -157,3 +157,37 @@ def stress_boxes(seed=0):
     far = base.copy()
     far[:, :2] += 3.0e4
     return dict(base=base, dup=dup, axis=axis, tiny=tiny, huge=huge, far=far)
+
+
+def eval_dataset(seed=0, num_imgs=40, num_classes=15, gts_per_img=60, extent=1024.0, with_ignore=True):
+    """detections + annotations in the layout of the reference's eval_rbbox_map
+    (mmrotate/core/evaluation/eval_map.py:136-150): per image, ground truths with labels
+    (a few of them in the ignore lists) and per class (m, 6) detections made of jittered
+    copies of ground truths (some duplicated: the greedy claim matters), wrong-class copies
+    and random false alarms."""
+    rng = np.random.default_rng(seed + 9001)
+    dets, anns = [], []
+    for i in range(num_imgs):
+        n = int(rng.integers(0, gts_per_img + 1))
+        g = le90_boxes(n, seed * 1000 + i, extent, w_lo=12.0, w_hi=160.0)
+        lab = rng.integers(0, num_classes, n)
+        ign = rng.random(n) < (0.1 if with_ignore else 0.0)
+        ann = dict(bboxes=g[~ign], labels=lab[~ign])
+        if with_ignore:
+            ann['bboxes_ignore'] = g[ign]
+            ann['labels_ignore'] = lab[ign]
+        anns.append(ann)
+        per = []
+        for c in range(num_classes):
+            src = g[lab == c]
+            rep = np.repeat(src, rng.integers(0, 3, src.shape[0]), axis=0)     # 0-2 detections per gt
+            jit = rep + rng.normal(0, 1.0, rep.shape).astype(np.float32) * np.array([2, 2, 2, 1, 0.03], np.float32)
+            other = g[lab != c][: int(rng.integers(0, 3))]                        # wrong-class hits
+            fa = le90_boxes(int(rng.integers(0, 4)), seed * 77 + i * 31 + c, extent)
+            b = np.concatenate([jit, other, fa], axis=0).astype(np.float32)
+            sc = rng.uniform(0.05, 1.0, b.shape[0]).astype(np.float32)
+            if b.shape[0] > 3:
+                sc[1] = sc[0]                                                    # a score tie
+            per.append(np.concatenate([b, sc[:, None]], axis=1).astype(np.float32))
+        dets.append(per)
+    return dets, anns

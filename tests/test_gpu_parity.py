@@ -434,3 +434,52 @@ def test_max_iou_assigner_edge_cases():
     m = rg.rbbox_overlaps(gts, boxes).cpu()
     want, _ = ref_api.max_iou_assign(m, 0.5, 0.4)
     assert torch.equal(r.gt_inds.cpu(), want) and int((want == 2).sum()) == 100 - int((m[0] > 0).sum() * 0 + 0) - int(((want != 2)).sum())
+
+
+# ---------------------------------------------------------------- mAP evaluation on the GPU
+def test_eval_map_golden_p0004(golden_dir):
+    """reference tests/test_data/test_datasets/test_dota.py:51-55: mAP == 0.7272727"""
+    import json
+    import os
+    from orientedobjectdetection_b200 import evaluation
+    g = json.load(open(os.path.join(golden_dir, 'dota_p0004_golden.json')))
+    dets = np.array(g['dets'], dtype=np.float64)                 # (3, 5): the last column doubles as score
+    gts = np.array(g['gt_obbs_oc_f32'], dtype=np.float32)
+    det6 = np.concatenate([dets, dets[:, -1:]], axis=1).astype(np.float32)
+    mean_ap, res = evaluation.eval_rbbox_map([[det6]], [dict(bboxes=gts, labels=np.zeros(4, np.int64))],
+                                             iou_thr=0.5, use_07_metric=True)
+    np.testing.assert_almost_equal(mean_ap, g['expected_mAP'], decimal=g['decimals'])
+    assert res[0]['num_gts'] == 4 and res[0]['num_dets'] == 3
+
+
+@pytest.mark.parametrize('use_07', [True, False])
+def test_eval_map_vs_restated_reference(use_07):
+    from orientedobjectdetection_b200 import evaluation
+    dets, anns = synth.eval_dataset(seed=1, num_imgs=40, num_classes=15)
+    mean_ap, res = evaluation.eval_rbbox_map(dets, anns, iou_thr=0.5, use_07_metric=use_07)
+    want_ap, want, flags = ref_api.eval_rbbox_map(dets, anns, 0.5, use_07)
+    # tp / fp of every detection
+    d, doff, g, goff, ign = evaluation._flatten(dets, anns, 15)
+    tp, fp = evaluation.tpfp_segments(d, doff, g, goff, ign, 0.5)
+    n_img = len(dets)
+    for c in range(15):
+        lo, hi = doff[c * n_img], doff[(c + 1) * n_img]
+        assert np.array_equal(tp[lo:hi], flags[c][0].astype(np.uint8))
+        assert np.array_equal(fp[lo:hi], flags[c][1].astype(np.uint8))
+        assert res[c]['num_gts'] == want[c]['num_gts'] and res[c]['num_dets'] == want[c]['num_dets']
+        np.testing.assert_allclose(res[c]['ap'], want[c]['ap'], rtol=0, atol=1e-6)
+    np.testing.assert_allclose(mean_ap, want_ap, rtol=0, atol=1e-6)
+    assert 0.05 < mean_ap < 0.95
+
+
+def test_eval_map_empty_cases():
+    from orientedobjectdetection_b200 import evaluation
+    none = np.zeros((0, 6), np.float32)
+    some = np.concatenate([synth.le90_boxes(5, 3, 200.0), np.linspace(0.9, 0.5, 5, dtype=np.float32)[:, None]], 1)
+    anns = [dict(bboxes=np.zeros((0, 5), np.float32), labels=np.zeros(0, np.int64)),
+            dict(bboxes=synth.le90_boxes(3, 4, 200.0), labels=np.array([0, 0, 1]))]
+    mean_ap, res = evaluation.eval_rbbox_map([[some, none], [none, none]], anns)
+    want_ap, want, _ = ref_api.eval_rbbox_map([[some, none], [none, none]], anns)
+    assert mean_ap == want_ap == 0.0 and res[0]['num_dets'] == 5 and res[1]['num_dets'] == 0
+    with pytest.raises(NotImplementedError):
+        evaluation.eval_rbbox_map([[some, none]], anns[:1], scale_ranges=[(0, 32)])
