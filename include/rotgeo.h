@@ -176,6 +176,17 @@ int rotgeo_eval_tpfp(const float *dets, int64_t num_dets, int det_stride, const 
                      uint8_t *fp_out, float *iou_max_out, void *workspace, size_t workspace_bytes,
                      void *stream);
 
+/* ---- differentiable aligned IoU ------------------------------------------------
+ * Replaces mmcv.ops.diff_iou_rotated_2d as the reference's RotatedIoULoss calls it
+ * (mmrotate/models/losses/rotated_iou_loss.py:47):
+ * iou_out[i] = IoU(boxes1[i], boxes2[i]) and, when the pointers are not null,
+ * grad1_out[i, :] = d iou_out[i] / d (cx, cy, w, h, theta) of boxes1[i] and grad2_out
+ * likewise for boxes2[i] ((n, 5) contiguous).  The gradient is analytic (boundary
+ * integrals over the clipped edges), not autograd through a vertex list; it is 0 where the
+ * boxes do not intersect and where an area is below 1e-14. */
+int rotgeo_diff_iou_aligned(const float *boxes1, const float *boxes2, int64_t n, int stride1, int stride2,
+                            float *iou_out, float *grad1_out, float *grad2_out, void *stream);
+
 /* ---- rotated NMS front-end: orders and segment sizes ----------------------------
  * What the reference does in python/ATen around the native op
  * (mmcv/ops/nms.py nms_rotated: scores.sort(0, descending=True) + index_select;

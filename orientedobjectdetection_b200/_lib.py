@@ -16,6 +16,7 @@ SYMBOLS = (
     'rotgeo_iou_aligned', 'rotgeo_nms_workspace_bytes', 'rotgeo_nms',
     'rotgeo_iou_max_workspace_bytes', 'rotgeo_iou_rowcol_max', 'rotgeo_max_iou_assign',
     'rotgeo_eval_tpfp_workspace_bytes', 'rotgeo_eval_tpfp',
+    'rotgeo_diff_iou_aligned',
     'rotgeo_nms_prepare_bytes', 'rotgeo_nms_prepare', 'rotgeo_nms_prepared',
     'rotgeo_multiclass_nms_workspace_bytes', 'rotgeo_multiclass_nms',
 )
@@ -69,6 +70,8 @@ def load():
     L.rotgeo_eval_tpfp_workspace_bytes.restype = sz
     L.rotgeo_eval_tpfp.argtypes = [vp, i64, i32, vp, vp, i64, i32, vp, vp, i64, f32, vp, vp, vp, vp, sz, vp]
     L.rotgeo_eval_tpfp.restype = i32
+    L.rotgeo_diff_iou_aligned.argtypes = [vp, vp, i64, i32, i32, vp, vp, vp, vp]
+    L.rotgeo_diff_iou_aligned.restype = i32
     L.rotgeo_nms_prepare_bytes.argtypes = [i64]
     L.rotgeo_nms_prepare_bytes.restype = sz
     L.rotgeo_nms_prepare.argtypes = [vp, i64, i32, vp, vp, vp, sz, vp, i64, vp, vp]

@@ -213,6 +213,18 @@ int rotgeo_eval_tpfp(const float *dets, int64_t num_dets, int det_stride, const 
     return ROTGEO_OK;
 }
 
+int rotgeo_diff_iou_aligned(const float *boxes1, const float *boxes2, int64_t n, int stride1, int stride2,
+                            float *iou_out, float *grad1_out, float *grad2_out, void *stream) {
+    if (n < 0 || stride1 < 5 || stride2 < 5)
+        return fail(ROTGEO_ERR_ARG, "diff_iou_aligned: n=%lld stride1=%d stride2=%d", (long long)n, stride1, stride2);
+    if (n == 0) return ROTGEO_OK;
+    if (!boxes1 || !boxes2 || !iou_out) return fail(ROTGEO_ERR_ARG, "diff_iou_aligned: null pointer");
+    if (rotgeo::launch_diff_iou(boxes1, boxes2, n, stride1, stride2, iou_out, grad1_out, grad2_out,
+                                (cudaStream_t)stream))
+        return cuda_fail("diff_iou_aligned launch");
+    return ROTGEO_OK;
+}
+
 size_t rotgeo_nms_workspace_bytes(int64_t n, const int64_t *seg_offsets_host, int64_t num_segments) {
     if (n <= 0) return 0;
     rotgeo::NmsPlan plan;

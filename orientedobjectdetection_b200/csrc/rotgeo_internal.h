@@ -84,6 +84,10 @@ int launch_eval_tpfp(const float *dets, int64_t num_dets, int det_stride, const 
                      const uint8_t *gt_ignore, int64_t num_segments, float iou_thr, uint8_t *tp,
                      uint8_t *fp, float *iou_max_out, void *workspace, cudaStream_t stream);
 
+// differentiable aligned IoU (rotgeo_diff.cu): value + gradient w.r.t. both boxes, (n, 5) each, nullable
+int launch_diff_iou(const float *boxes1, const float *boxes2, int64_t n, int stride1, int stride2,
+                    float *iou_out, float *grad1, float *grad2, cudaStream_t stream);
+
 int launch_iou_aligned(const float *boxes1, const float *boxes2, int64_t n, int stride1,
                        int stride2, int mode, float min_wh, float *out, cudaStream_t stream);
 

@@ -483,3 +483,73 @@ def test_eval_map_empty_cases():
     assert mean_ap == want_ap == 0.0 and res[0]['num_dets'] == 5 and res[1]['num_dets'] == 0
     with pytest.raises(NotImplementedError):
         evaluation.eval_rbbox_map([[some, none]], anns[:1], scale_ranges=[(0, 32)])
+
+
+# ---------------------------------------------------------------- differentiable aligned IoU
+def _overlapping_pairs(n, seed):
+    rng = np.random.default_rng(seed)
+    a = synth.le90_boxes(n, seed, 300.0, w_lo=20.0, w_hi=120.0, aspect_hi=4.0)
+    b = a.copy()
+    b[:, :2] += rng.normal(0, 12.0, (n, 2)).astype(np.float32)
+    b[:, 2:4] *= rng.uniform(0.6, 1.5, (n, 2)).astype(np.float32)
+    b[:, 4] += rng.normal(0, 0.5, n).astype(np.float32)
+    a[:, 4] = rng.uniform(-3.5, 3.5, n).astype(np.float32)          # all four quadrants of the relative angle
+    return a, b
+
+
+def test_diff_iou_forward_matches_oracle_and_gradient_matches_float64_differences():
+    from tests import _geom64
+    from orientedobjectdetection_b200 import losses
+    n = 400
+    a, b = _overlapping_pairs(n, 5)
+    ta = torch.from_numpy(a).cuda().requires_grad_(True)
+    tb = torch.from_numpy(b).cuda().requires_grad_(True)
+    iou = losses.diff_iou_rotated_2d(ta[None], tb[None])[0]
+    want = ref.box_iou_rotated(a, b, aligned=True)
+    assert np.abs(iou.detach().cpu().numpy() - want).max() <= 1e-5
+    iou.sum().backward()
+    ga, gb = ta.grad.cpu().numpy(), tb.grad.cpu().numpy()
+    # central differences of the independent float64 clipper
+    steps = np.array([1e-3, 1e-3, 1e-3, 1e-3, 1e-5])
+    checked = 0
+    for i in range(n):
+        if not (0.05 < want[i] < 0.95):
+            continue
+        for which, g in ((0, ga), (1, gb)):
+            for p in range(5):
+                hi_a, hi_b = a[i].astype(np.float64), b[i].astype(np.float64)
+                lo_a, lo_b = hi_a.copy(), hi_b.copy()
+                (hi_a if which == 0 else hi_b)[p] += steps[p]
+                (lo_a if which == 0 else lo_b)[p] -= steps[p]
+                num = (_geom64.iou(hi_a, hi_b) - _geom64.iou(lo_a, lo_b)) / (2 * steps[p])
+                assert abs(g[i, p] - num) <= 2e-3 * max(1.0, abs(num)) + 2e-4, (i, which, p, g[i, p], num)
+        checked += 1
+    assert checked > 200
+    # translating both boxes together changes nothing
+    assert np.abs(ga[:, :2] + gb[:, :2]).max() <= 1e-4
+
+
+def test_diff_iou_zero_gradient_cases_and_loss_api():
+    from orientedobjectdetection_b200 import losses
+    a = torch.tensor([[0., 0., 10., 4., 0.3], [0., 0., 10., 4., 0.3], [5., 5., 0., 3., 0.]]).cuda().requires_grad_(True)
+    b = torch.tensor([[100., 0., 10., 4., 0.1], [0., 0., 10., 4., 0.3], [5., 5., 2., 3., 0.]]).cuda()
+    iou = losses.diff_iou_rotated_2d(a[None], b[None])[0]
+    iou.sum().backward()
+    assert iou[0].item() == 0.0 and abs(iou[1].item() - 1.0) < 1e-6 and iou[2].item() == 0.0
+    assert bool((a.grad[0] == 0).all()) and bool((a.grad[2] == 0).all()) and bool(torch.isfinite(a.grad).all())
+    # the reference's own loss test (tests/test_models/test_loss.py:142-175): every call returns a tensor
+    torch.manual_seed(0)
+    pred = torch.rand((10, 5)).cuda().requires_grad_(True)
+    target = torch.rand((10, 5)).cuda()
+    weight = torch.rand((10,)).cuda()
+    L = losses.RotatedIoULoss
+    outs = [L(linear=True)(pred, target), L(mode='linear')(pred, target), L(mode='log')(pred, target),
+            L(mode='square')(pred, target), L()(pred, target), L()(pred, target, weight),
+            L()(pred, target, reduction_override='mean'), L()(pred, target, avg_factor=10)]
+    assert all(isinstance(o, torch.Tensor) and o.dim() == 0 and bool(torch.isfinite(o)) for o in outs)
+    outs[2].backward()
+    assert bool(torch.isfinite(pred.grad).all()) and float(pred.grad.abs().sum()) > 0
+    # values: -log(clamp(iou)) averaged
+    want = ref.box_iou_rotated(pred.detach().cpu().numpy(), target.cpu().numpy(), aligned=True)
+    assert abs(float(outs[2]) - float(np.mean(-np.log(np.maximum(want, 1e-6))))) < 1e-4
+    assert float(L()(pred, target, torch.zeros(10).cuda())) == 0.0
