@@ -244,3 +244,38 @@ def eval_rbbox_map(det_results, annotations, iou_thr=0.5, use_07_metric=True):
         results.append({'num_gts': num_gts, 'num_dets': alld.shape[0], 'recall': rec, 'precision': prec, 'ap': ap})
     aps = [r['ap'] for r in results if r['num_gts'] > 0]
     return (float(np.mean(aps)) if aps else 0.0), results, flags
+
+
+def merge_det(results, img_ids, num_classes, iou_thr=0.1):
+    """reference mmrotate/datasets/dota.py:216-276 + _merge_func :358-382 with the oracle NMS:
+    float64 rows (label, box, score) exactly as the reference builds them, nms_rotated in the
+    dtype it is handed (float64)."""
+    import re
+    from collections import defaultdict
+    collector = defaultdict(list)
+    for idx, img_id in enumerate(img_ids):
+        oriname = img_id.split('__', maxsplit=1)[0]
+        m = re.compile(r'__(\d+)___(\d+)').search(img_id)
+        x, y = (int(m.group(1)), int(m.group(2))) if m else (0, 0)
+        new_result = []
+        for i, dets in enumerate(results[idx]):
+            bboxes, scores = dets[:, :-1], dets[:, [-1]]
+            ori = bboxes.copy()
+            ori[..., :2] = ori[..., :2] + np.array([x, y], dtype=np.float32)
+            new_result.append(np.concatenate([np.zeros((bboxes.shape[0], 1)) + i, ori, scores], axis=1))
+        collector[oriname].append(np.concatenate(new_result, axis=0))
+    ids, out = [], []
+    for img_id, label_dets in collector.items():
+        label_dets = np.concatenate(label_dets, axis=0)
+        labels, dets = label_dets[:, 0], label_dets[:, 1:]
+        per = []
+        for i in range(num_classes):
+            d = dets[labels == i]
+            if len(d) == 0:
+                per.append(d)
+            else:
+                nms_dets, _ = ref.nms_rotated(d[:, :5], d[:, -1], iou_thr)
+                per.append(nms_dets)
+        ids.append(img_id)
+        out.append(per)
+    return tuple(ids), tuple(out)

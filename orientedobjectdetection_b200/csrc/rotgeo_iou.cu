@@ -9,7 +9,7 @@
 //      of its 128-column block (5 KB sparse table, built once at pack time) arrive
 //      in a 4-stage shared-memory ring filled by TMA bulk copies one tile ahead
 //      (full/empty mbarriers; no __syncthreads anywhere in the loop);
-//   1. warp w owns rows {w, w+8, ...}: lane l streams the zeros of its four
+//   1. warp w owns rows 8w .. 8w+7: lane l streams the zeros of its four
 //      columns 4l..4l+3 to HBM (float4, 512 B per warp instruction — most of the
 //      matrix is zero), always one tile ahead of the cull so that the write stream
 //      never waits for a warp that is busy clipping;
@@ -173,23 +173,25 @@ iou_tile_kernel(const IouArgs g) {
         const int64_t gcol = col_base + 4 * lane;
         const int cols_here = (int)min((int64_t)4, g.n2 - gcol);  // <= 0: lane is past the edge
         const int rows_here = (int)min((int64_t)kTileRows, g.n1 - row_base);
-        float *dst = g.out + (row_base + warp) * g.ld_out + gcol;
-        const int64_t step = (int64_t)kWarps * g.ld_out;
+        // warp w owns the 8 CONSECUTIVE rows 8w .. 8w+7 of the tile (measured faster for the write
+        // stream than rows w, w+8, ...: profiles/r01_hbm_write_probe.txt)
+        float *dst = g.out + (row_base + kRowsPerWarp * warp) * g.ld_out + gcol;
+        const int64_t step = g.ld_out;
         if (VEC) {
             if (rows_here == kTileRows && cols_here == 4) {   // interior tile: 8 plain stores
 #pragma unroll
                 for (int it = 0; it < kRowsPerWarp; ++it) {
-                    *reinterpret_cast<float4 *>(dst) = make_float4(0.f, 0.f, 0.f, 0.f);
+                    __stcs(reinterpret_cast<float4 *>(dst), make_float4(0.f, 0.f, 0.f, 0.f));
                     dst += step;
                 }
             } else if (cols_here > 0) {
-                for (int r = warp; r < rows_here; r += kWarps) {
+                for (int r = kRowsPerWarp * warp; r < min(rows_here, kRowsPerWarp * (warp + 1)); ++r) {
                     *reinterpret_cast<float4 *>(dst) = make_float4(0.f, 0.f, 0.f, 0.f);
                     dst += step;
                 }
             }
         } else {
-            for (int r = warp; r < rows_here; r += kWarps) {
+            for (int r = kRowsPerWarp * warp; r < min(rows_here, kRowsPerWarp * (warp + 1)); ++r) {
                 for (int k = 0; k < cols_here; ++k) dst[k] = 0.f;
                 dst += step;
             }
@@ -232,7 +234,7 @@ iou_tile_kernel(const IouArgs g) {
         uint32_t hits = 0;
         const int rl = lane >> 2, cw = lane & 3;        // row of the warp's eight, column word
         if (!(ROTGEO_ABLATE & 2)) {
-            const uint32_t rr = sm.rowr[s][warp + kWarps * rl];
+            const uint32_t rr = sm.rowr[s][kRowsPerWarp * warp + rl];
             const int sx = rr & 31, nx = (rr >> 8) & 63, sy = (rr >> 16) & 31, ny = rr >> 24;
             if (nx != 0) {
                 const int jx = min(31 - __clz(nx), kTableLevels - 1), jy = min(31 - __clz(ny), kTableLevels - 1);
@@ -248,7 +250,7 @@ iou_tile_kernel(const IouArgs g) {
 
         // ---- survivors -> queue 1, at most one per lane and round ----------------------
         {
-            const int row = (int)row_base + warp + kWarps * rl, col0 = (int)col_base + 32 * cw;
+            const int row = (int)row_base + kRowsPerWarp * warp + rl, col0 = (int)col_base + 32 * cw;
             uint32_t m = hits;
             for (;;) {
                 const uint32_t act = __ballot_sync(0xffffffffu, m != 0u);

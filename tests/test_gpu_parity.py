@@ -553,3 +553,28 @@ def test_diff_iou_zero_gradient_cases_and_loss_api():
     want = ref.box_iou_rotated(pred.detach().cpu().numpy(), target.cpu().numpy(), aligned=True)
     assert abs(float(outs[2]) - float(np.mean(-np.log(np.maximum(want, 1e-6))))) < 1e-4
     assert float(L()(pred, target, torch.zeros(10).cuda())) == 0.0
+
+
+def test_merge_det_dota_submission_path():
+    """a11: DOTADataset.merge_det (dota.py:216-276, 358-382): patches named
+    <image>__<scale>__<x>___<y>, float64 rows, one NMS per (image, class)"""
+    from orientedobjectdetection_b200 import datasets
+    results, img_ids = [], []
+    for k, name in enumerate(['P0001', 'P0002', 'P0777']):
+        res, offs, _ = synth.c5_patch_results(seed=10 + k, width=2400, height=2400, dets_per_patch=120,
+                                              num_classes=6)
+        for p, (x, y) in enumerate(offs):
+            results.append(res[p])
+            img_ids.append('%s__1__%d___%d' % (name, x, y))
+    gi, gd = datasets.merge_det(results, img_ids, CLASSES=tuple('abcdef'))
+    wi, wd = ref_api.merge_det(results, img_ids, 6)
+    assert gi == wi and len(gd) == len(wd) == 3
+    for a, b in zip(gd, wd):
+        for ca, cb in zip(a, b):
+            assert ca.dtype == np.float64 and ca.shape == cb.shape
+            assert np.array_equal(ca, cb)
+    # the single-image function of the reference
+    info = ('P0001', [np.concatenate([np.concatenate([np.zeros((d.shape[0], 1)) + c, d], axis=1)
+                                      for c, d in enumerate(results[0])], axis=0)])
+    img, per = datasets._merge_func(info, tuple('abcdef'), 0.1)
+    assert img == 'P0001' and len(per) == 6 and all(p.shape[1] == 6 for p in per)
