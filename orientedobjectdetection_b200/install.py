@@ -4,10 +4,10 @@ nine modules that bind the names at import time are listed in SURVEY.md §8(b).
 """
 import importlib
 
-from . import core, ops
+from . import assign, core, datasets, evaluation, losses, ops
 
 _L1 = {'box_iou_rotated': ops.box_iou_rotated, 'nms_rotated': ops.nms_rotated,
-       'batched_nms': ops.batched_nms}
+       'batched_nms': ops.batched_nms, 'diff_iou_rotated_2d': losses.diff_iou_rotated_2d}
 _L1_MODULES = (
     'mmcv.ops',
     'mmrotate.core.bbox.iou_calculators.rotate_iou2d_calculator',
@@ -18,6 +18,7 @@ _L1_MODULES = (
     'mmrotate.datasets.dota',
     'mmrotate.models.dense_heads.rotated_rpn_head',
     'mmrotate.models.dense_heads.oriented_rpn_head',
+    'mmrotate.models.losses.rotated_iou_loss',
 )
 _L2 = {
     'mmrotate.core.bbox.iou_calculators.rotate_iou2d_calculator':
@@ -32,10 +33,15 @@ _L2 = {
          'aug_multiclass_nms_rotated': core.aug_multiclass_nms_rotated},
     'mmrotate.core.patch.merge_results': {'merge_results': core.merge_results},
     'mmrotate.core.patch': {'merge_results': core.merge_results},
+    'mmrotate.core.evaluation.eval_map': {'eval_rbbox_map': evaluation.eval_rbbox_map},
+    'mmrotate.core.evaluation': {'eval_rbbox_map': evaluation.eval_rbbox_map},
+    'mmrotate.datasets.dota': {'_merge_func': datasets._merge_func, 'eval_rbbox_map': evaluation.eval_rbbox_map},
+    'mmrotate.datasets.hrsc': {'eval_rbbox_map': evaluation.eval_rbbox_map},
     'mmrotate.core': {'rbbox_overlaps': core.rbbox_overlaps,
                       'multiclass_nms_rotated': core.multiclass_nms_rotated,
                       'aug_multiclass_nms_rotated': core.aug_multiclass_nms_rotated,
-                      'merge_results': core.merge_results},
+                      'merge_results': core.merge_results,
+                      'eval_rbbox_map': evaluation.eval_rbbox_map},
 }
 
 
@@ -70,6 +76,13 @@ def patch(strict=False):
         IOU_CALCULATORS.register_module(name='RBboxOverlaps2D', force=True,
                                         module=core.RBboxOverlaps2D)
         done.append(('mmdet IOU_CALCULATORS', 'RBboxOverlaps2D'))
+    except Exception:
+        if strict:
+            raise
+    try:   # opt-in by name: assigner=dict(type='FusedMaxIoUAssigner', ...) in a config
+        from mmdet.core.bbox.builder import BBOX_ASSIGNERS
+        BBOX_ASSIGNERS.register_module(name='FusedMaxIoUAssigner', force=True, module=assign.MaxIoUAssigner)
+        done.append(('mmdet BBOX_ASSIGNERS', 'FusedMaxIoUAssigner'))
     except Exception:
         if strict:
             raise
