@@ -129,13 +129,16 @@ def nms_images(images, iou_threshold, max_per_img=-1, keep_fn=None):
     scores = torch.cat([s for _, s, _ in images], dim=0)
     ids = torch.cat([i.to(torch.int64) for _, _, i in images], dim=0)
     nimg = len(images)
+    total = sum(sizes)
     sizes_t = torch.tensor(sizes, dtype=torch.int64)
-    img_of = torch.repeat_interleave(torch.arange(nimg, dtype=torch.int64), sizes_t).to(dev)
+    sizes_d = sizes_t.to(dev)
+    img_of = torch.repeat_interleave(torch.arange(nimg, dtype=torch.int64, device=dev), sizes_d,
+                                     output_size=total)
     # per-image offset trick, same float arithmetic as mmcv.ops.batched_nms on every image:
-    # id * (max(cx,cy) + max(w,h) + 1) with the maxima of THAT image
-    neg = torch.full((nimg,), float('-inf'), dtype=boxes.dtype, device=dev)
-    m_xy = neg.clone().scatter_reduce_(0, img_of, boxes[:, :2].max(dim=1).values, 'amax')
-    m_wh = neg.clone().scatter_reduce_(0, img_of, boxes[:, 2:4].max(dim=1).values, 'amax')
+    # id * (max(cx,cy) + max(w,h) + 1) with the maxima of THAT image (images are contiguous
+    # row ranges: one segmented max per term; empty images never index the result)
+    m_xy = torch.segment_reduce(boxes[:, :2].max(dim=1).values, 'max', lengths=sizes_d, unsafe=True)
+    m_wh = torch.segment_reduce(boxes[:, 2:4].max(dim=1).values, 'max', lengths=sizes_d, unsafe=True)
     offsets = ids.to(boxes) * ((m_xy + m_wh)[img_of] + torch.tensor(1).to(boxes))
     # one segment per (image, id)
     id_lo = ids.min()
@@ -145,7 +148,7 @@ def nms_images(images, iou_threshold, max_per_img=-1, keep_fn=None):
     kimg = img_of[keep]
     perm = torch.sort(kimg, stable=True).indices
     keep, kimg = keep[perm], kimg[perm]
-    starts = torch.cat([torch.zeros(1, dtype=torch.int64), torch.cumsum(sizes_t, 0)[:-1]]).to(dev)
+    starts = (torch.cumsum(sizes_t, 0) - sizes_t).to(dev)
     local = keep - starts[kimg]
     counts = torch.bincount(kimg, minlength=nimg).tolist()
     out = list(torch.split(local, counts))
