@@ -172,6 +172,37 @@ def _nms_keep_split(b, s, iou_threshold, seg, offsets, id_offsets):
     return order[torch.sort(s[order], descending=True, stable=True).indices]
 
 
+def nms_threshold_band(boxes, iou_threshold, seg_ids=None, offsets=None, tol=1e-5, chunk=4096):
+    """Pairs whose IoU lies within ``tol`` of ``iou_threshold`` — the only pairs at which the
+    kept set may legitimately differ from the reference's (BASELINE.json north_star: "keep
+    indices identical except at pairs whose IoU lies within 1e-5 of the threshold, which are
+    listed").  Returns ``(pairs (k, 2) int64 with i < j, ious (k,))`` on the CUDA device;
+    pairs of different ``seg_ids`` are not listed.  ``offsets`` as in ``_nms_keep``.  Diagnostic
+    helper: the (chunk x n) IoU blocks are materialised, sizes of tests and audits only."""
+    dev = _cuda_device(boxes)
+    b = _rows_f32(boxes, dev).clone()
+    if offsets is not None:
+        b[:, :2] += offsets.to(device=dev, dtype=torch.float32)[:, None]
+    n = b.shape[0]
+    seg = None if seg_ids is None else seg_ids.to(device=dev, dtype=torch.int64).reshape(-1)
+    pairs, vals = [], []
+    for lo in range(0, n, chunk):
+        hi = min(n, lo + chunk)
+        iou = _overlaps(b[lo:hi], b, 'iou', False, 0.0)
+        near = (iou - float(iou_threshold)).abs() <= tol
+        near &= torch.arange(lo, hi, device=dev)[:, None] < torch.arange(n, device=dev)[None, :]
+        if seg is not None:
+            near &= seg[lo:hi, None] == seg[None, :]
+        ij = near.nonzero(as_tuple=False)
+        if ij.numel():
+            vals.append(iou[ij[:, 0], ij[:, 1]])
+            ij[:, 0] += lo
+            pairs.append(ij)
+    if not pairs:
+        return torch.zeros((0, 2), dtype=torch.int64, device=dev), torch.zeros(0, device=dev)
+    return torch.cat(pairs), torch.cat(vals)
+
+
 def nms_rotated(dets, scores, iou_threshold, labels=None, clockwise=True):
     """Drop-in for ``mmcv.ops.nms_rotated``.
 
