@@ -52,7 +52,7 @@ int rotgeo_pack_boxes(const float *boxes, int64_t n, int stride, const int64_t *
     const rotgeo::PackSet s1 = rotgeo::make_pack_set(boxes, n, stride, gather, offsets, packed,
                                                      rotgeo::padded_count(n));
     const rotgeo::PackSet none = rotgeo::make_pack_set(nullptr, 0, 5, nullptr, nullptr, nullptr, 0);
-    if (rotgeo::launch_pack(s1, none, min_wh, cull_cell, (cudaStream_t)stream))
+    if (rotgeo::launch_pack(s1, none, min_wh, cull_cell, 0.f, (cudaStream_t)stream))
         return cuda_fail("pack launch");
     return ROTGEO_OK;
 }
@@ -98,7 +98,7 @@ int rotgeo_iou_pairwise(const float *boxes1, int64_t n1, int stride1, const floa
                                                      rotgeo::padded_count(n1));
     const rotgeo::PackSet s2 = rotgeo::make_pack_set(boxes2, n2, stride2, nullptr, nullptr, pk2,
                                                      rotgeo::padded_count(n2));
-    if (rotgeo::launch_pack(s1, s2, min_wh, 0.f, (cudaStream_t)stream)) return cuda_fail("pack launch");
+    if (rotgeo::launch_pack(s1, s2, min_wh, 0.f, 0.f, (cudaStream_t)stream)) return cuda_fail("pack launch");
     // the tile kernel starts streaming zeros while the pack kernel is still running
     const int rc = rotgeo::launch_iou_pairwise(pk1, n1, pk2, n2, mode, out, ld_out, true,
                                                (cudaStream_t)stream);
@@ -294,7 +294,7 @@ int rotgeo_nms(const float *boxes, int64_t n, int stride, const float *offsets,
         s1.z_sum_words = scratch.sum_words;
         s1.z_sync = scratch.sync;
         const rotgeo::PackSet none = rotgeo::make_pack_set(nullptr, 0, 5, nullptr, nullptr, nullptr, 0);
-        if (rotgeo::launch_pack(s1, none, 0.f, 0.f, st)) return cuda_fail("nms pack launch");
+        if (rotgeo::launch_pack(s1, none, 0.f, 0.f, iou_threshold - 1e-4f, st)) return cuda_fail("nms pack launch");
     }
     // no global order given: kept indices come out segment-major (the caller re-orders)
     if (!order) order = sorder;

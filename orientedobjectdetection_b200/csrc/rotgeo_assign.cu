@@ -107,7 +107,7 @@ static int pack_and_reduce(const float *boxes1, int64_t n1, int stride1, const f
     if (cudaMemsetAsync(ws + l.off_row_key, 0, l.off_all + 4 - l.off_row_key, stream) != cudaSuccess) return -3;
     const PackSet s1 = make_pack_set(boxes1, n1, stride1, nullptr, nullptr, ws + l.off_pk1, padded_count(n1));
     const PackSet s2 = make_pack_set(boxes2, n2, stride2, nullptr, nullptr, ws + l.off_pk2, padded_count(n2));
-    if (launch_pack(s1, s2, min_wh, 0.f, stream)) return -3;
+    if (launch_pack(s1, s2, min_wh, 0.f, 0.f, stream)) return -3;
     return launch_iou_max(ws + l.off_pk1, n1, ws + l.off_pk2, n2, mode,
                           reinterpret_cast<unsigned long long *>(ws + l.off_row_key),
                           reinterpret_cast<unsigned long long *>(ws + l.off_col_key), true, stream);

@@ -21,44 +21,59 @@ __host__ __device__ inline int64_t padded_count(int64_t n) {
     return (n + kPackPad - 1) / kPackPad * kPackPad;
 }
 
-// A packed set of n_pad slots (n_pad a multiple of 128) is five planes, back to back:
+// A packed set of n_pad slots (n_pad a multiple of 128) is four planes, back to back:
 //   plane0 float4 (cx, cy, r, area)   r = circumscribed radius (inflated), area = w*h
 //   plane1 float4 (cos, sin, a, b)    a = w/2, b = h/2
-//   planeM uint2  (xbins, ybins)      32-bit occupancy masks of the circumscribed circle
-//                                     over a modular grid of 32 bins per axis
-//   planeR uint32 sx | nx<<8 | sy<<16 | ny<<24: the same occupancy as cyclic bin
-//                                     ranges [s, s+n) per axis (n = 0: padding)
+//   planeR uint32 the box's occupancy as bin ranges [s, s+n): x and y cyclic over a modular
+//                                     grid of 32 bins per axis (n = 0: padding), plus, for
+//                                     NMS packs, the range of AREA bins a partner must fall in
+//                                     to reach the IoU threshold (pack_ranges below)
 //   planeT per block of 128 boxes, kTableWords uint32: the block's INVERTED bin
 //          index as a sparse table — T[axis][level j][bin b][word w] has bit c set
-//          iff box 32w+c of the block occupies one of the bins b .. b+2^j-1 (mod 32).
-// The pair cull of the IoU kernel reads planeR of the row boxes and planeT of the
-// column block: the 128-bit set of columns a row can touch is two table lookups
-// per axis (a range OR) and one AND — about one instruction per pair instead of
-// one test per pair.  planes 0/1 are read only for the pairs that survive.
+//          iff box 32w+c of the block occupies one of the bins b .. b+2^j-1 (mod 32);
+//          axes x, y and (NMS packs) log-area, where a box occupies exactly one bin.
+// The pair cull reads planeR of the row boxes and planeT of the column block: the
+// 128-bit set of columns a row can touch is two table lookups per axis (a range OR)
+// and one AND — about one instruction per pair instead of one test per pair.
+// planes 0/1 are read only for the pairs that survive.
 constexpr int kBlock = 128;                                  // boxes per table block
 constexpr int kTableLevels = 5;                              // run lengths 1, 2, 4, 8, 16
 constexpr int kTableAxisWords = kTableLevels * 32 * (kBlock / 32);   // 640
-constexpr int kTableWords = 2 * kTableAxisWords;             // 1280 (5120 bytes)
-constexpr int kPackedBytesPerBox = 2 * 16 + 8 + 4 + kTableWords * 4 / kBlock;   // 84
+constexpr int kTableXYWords = 2 * kTableAxisWords;           // 1280: what the IoU kernel stages (5 KB)
+constexpr int kTableWords = 3 * kTableAxisWords;             // 1920 (7680 bytes)
+constexpr int kPackedBytesPerBox = 2 * 16 + 4 + kTableWords * 4 / kBlock;   // 96
 
 struct PackedView {
     const float4 *p0;
     const float4 *p1;
-    const uint2 *pm;
     const uint32_t *pr;
     const uint32_t *pt;
 };
 
 // n_pad = number of slots per plane (padded_count(n) for the IoU entry points; the
-// NMS workspace adds slack so tiles may start at any box)
+// NMS packs pad every segment to whole blocks)
 __host__ __device__ inline PackedView packed_view(const void *base, int64_t n_pad) {
     PackedView v;
     v.p0 = reinterpret_cast<const float4 *>(base);
     v.p1 = v.p0 + n_pad;
-    v.pm = reinterpret_cast<const uint2 *>(v.p1 + n_pad);
-    v.pr = reinterpret_cast<const uint32_t *>(v.pm + n_pad);
+    v.pr = reinterpret_cast<const uint32_t *>(v.p1 + n_pad);
     v.pt = v.pr + n_pad;
     return v;
+}
+
+// planeR: sx:5 | nx:6 | sy:5 | ny:6 | sa:5 | na:5  (na = 0: no area constraint)
+__host__ __device__ inline uint32_t pack_ranges(int sx, int nx, int sy, int ny, int sa, int na) {
+    return (uint32_t)sx | ((uint32_t)nx << 5) | ((uint32_t)sy << 11) | ((uint32_t)ny << 16) |
+           ((uint32_t)sa << 22) | ((uint32_t)na << 27);
+}
+struct BinRanges {
+    int sx, nx, sy, ny, sa, na;
+};
+__host__ __device__ inline BinRanges unpack_ranges(uint32_t rr) {
+    BinRanges r;
+    r.sx = rr & 31; r.nx = (rr >> 5) & 63; r.sy = (rr >> 11) & 31; r.ny = (rr >> 16) & 63;
+    r.sa = (rr >> 22) & 31; r.na = rr >> 27;
+    return r;
 }
 
 // ---- cull level 1: modular bin masks ------------------------------------------

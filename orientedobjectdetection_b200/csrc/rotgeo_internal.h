@@ -43,7 +43,6 @@ struct PackSet {
     int z_sum_words;
     unsigned int *z_sync;           // kNmsSyncWords words of barrier / round state
     float4 *p0, *p1;
-    uint2 *pm;
     uint32_t *pr, *pt;
     int64_t n_pad;
 };
@@ -51,8 +50,10 @@ constexpr int kNmsSyncWords = 16;
 PackSet make_pack_set(const float *boxes, int64_t n, int stride, const int64_t *gather,
                       const float *offsets, void *packed, int64_t n_pad);
 
-// cell > 0: bin width of the cull masks; cell <= 0: derived from the set(s) in the launch
-int launch_pack(const PackSet &s1, const PackSet &s2, float min_wh, float cell,
+// cell > 0: bin width of the cull masks; cell <= 0: derived from the set(s) in the launch.
+// area_ratio in (0, 1): NMS pack, also builds the area axis for pairs that need
+// min(area) >= area_ratio * max(area); otherwise 0
+int launch_pack(const PackSet &s1, const PackSet &s2, float min_wh, float cell, float area_ratio,
                 cudaStream_t stream);
 
 // after_pack: the pack kernel of these sets was the previous launch on `stream`

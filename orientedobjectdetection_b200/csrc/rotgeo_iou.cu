@@ -47,7 +47,7 @@ constexpr int kQueueCap = 64;     // pairs per warp queue (never more than 31 + 
 static_assert(kTileCols == kBlock, "a column tile is one inverted-index block");
 
 struct __align__(16) IouSmem {
-    uint32_t tab[kStages][kTableWords];
+    uint32_t tab[kStages][kTableXYWords];   // x and y axes of the column block's index
     uint32_t rowr[kStages][kTileRows];
     int2 queue1[kWarps][kQueueCap];   // survived the bin ranges
     int2 queue2[kWarps][kQueueCap];   // survived the circle test as well
@@ -125,9 +125,9 @@ iou_tile_kernel(const IouArgs g) {
         const int s = k % kStages;
         const int64_t rb = (int64_t)(t / g.tiles_x) * kTileRows;
         const int64_t cblk = (int64_t)(t % g.tiles_x);
-        mbar_expect_tx(&sm.full[s], (kTileRows + kTableWords) * sizeof(uint32_t));
+        mbar_expect_tx(&sm.full[s], (kTileRows + kTableXYWords) * sizeof(uint32_t));
         tma_load_1d(sm.rowr[s], g.ar + rb, kTileRows * sizeof(uint32_t), &sm.full[s]);
-        tma_load_1d(sm.tab[s], g.bt + cblk * kTableWords, kTableWords * sizeof(uint32_t), &sm.full[s]);
+        tma_load_1d(sm.tab[s], g.bt + cblk * kTableWords, kTableXYWords * sizeof(uint32_t), &sm.full[s]);
     };
     // the answer for my k-th tile (k >= 1) lives in slot (k-1) % kRespSlots, use (k-1) / kRespSlots
     auto ask_next = [&](unsigned k) {                  // thread 0: who is my k-th tile?
@@ -235,7 +235,8 @@ iou_tile_kernel(const IouArgs g) {
         const int rl = lane >> 2, cw = lane & 3;        // row of the warp's eight, column word
         if (!(ROTGEO_ABLATE & 2)) {
             const uint32_t rr = sm.rowr[s][kRowsPerWarp * warp + rl];
-            const int sx = rr & 31, nx = (rr >> 8) & 63, sy = (rr >> 16) & 31, ny = rr >> 24;
+            const BinRanges br = unpack_ranges(rr);
+            const int sx = br.sx, nx = br.nx, sy = br.sy, ny = br.ny;
             if (nx != 0) {
                 const int jx = min(31 - __clz(nx), kTableLevels - 1), jy = min(31 - __clz(ny), kTableLevels - 1);
                 const uint32_t *tx = sm.tab[s] + jx * 128 + cw;

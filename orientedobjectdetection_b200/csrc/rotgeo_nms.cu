@@ -50,7 +50,7 @@ namespace rotgeo {
 constexpr int kTile = 128;      // tile edge in boxes = one inverted-index block = two mask words
 constexpr int kThreads = 256;
 constexpr int kWarps = kThreads / 32;
-constexpr int kStages = 4;      // cull-data ring
+constexpr int kStages = 3;      // cull-data ring (3 x 7.7 KB of index + row ranges)
 constexpr int kInfoSlots = 8;   // tile descriptors / launch-control responses (> kStages)
 constexpr int kQueueCap = 64;   // pairs per warp queue (never more than 31 + 32 queued)
 static_assert(kTile == kBlock, "a tile column is one inverted-index block");
@@ -258,7 +258,8 @@ nms_mask_kernel(const MaskArgs g) {
         for (int p = 0; p < 2; ++p) {
             const int rloc = warp + kWarps * (rl + 8 * p);          // row inside the tile
             const uint32_t rr = sm.rowr[s][rloc];
-            const int sx = rr & 31, nx = (rr >> 8) & 63, sy = (rr >> 16) & 31, ny = rr >> 24;
+            const BinRanges br = unpack_ranges(rr);
+            const int sx = br.sx, nx = br.nx, sy = br.sy, ny = br.ny;
             uint32_t h = 0;
             if (nx != 0) {
                 const int jx = min(31 - __clz(nx), kTableLevels - 1), jy = min(31 - __clz(ny), kTableLevels - 1);
@@ -267,6 +268,13 @@ nms_mask_kernel(const MaskArgs g) {
                 const uint32_t X = tx[sx * 4] | tx[((sx + nx - (1 << jx)) & 31) * 4];
                 const uint32_t Y = ty[sy * 4] | ty[((sy + ny - (1 << jy)) & 31) * 4];
                 h = X & Y;
+                if (br.na != 0) {
+                    // third axis: only columns whose area lies within the ratio that can still
+                    // reach the threshold (IoU <= min(area) / max(area))
+                    const int ja = min(31 - __clz(br.na), kTableLevels - 1);
+                    const uint32_t *ta = sm.tab[s] + 2 * kTableAxisWords + ja * 128 + cw;
+                    h &= ta[br.sa * 4] | ta[((br.sa + br.na - (1 << ja)) & 31) * 4];
+                }
                 if (ti.I == ti.J) {                                  // keep columns before the row only
                     const int d = rloc - 32 * cw;                    // row's bit inside this word
                     if (d <= 0) h = 0u;

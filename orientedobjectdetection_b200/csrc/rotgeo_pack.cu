@@ -8,8 +8,9 @@
 // The bin width of the cull masks is derived in a prologue every CTA repeats on
 // the same strided sample of <= 256 boxes (so all CTAs agree without a second
 // launch): 32 bins span the sampled extent of the RAW centres — before the class
-// offsets, because a class segment only ever meets itself.  The choice affects
-// speed only; bin_range() is conservative for any width.
+// offsets, because a class segment only ever meets itself — and, for NMS packs, 30 of
+// the 32 area bins span the sampled range of log2(area).  The choices affect speed
+// only; bin_range() and area_bin() are conservative for any width.
 #include "rotgeo_device.cuh"
 #include "rotgeo_internal.h"
 
@@ -64,10 +65,15 @@ __device__ __forceinline__ int64_t position_source(const PackSet &s, int64_t pos
     return v;
 }
 
-// 1 / (bin width): identical in every CTA of the launch.  Every CTA reduces the
-// same strided sample of <= 256 raw box centres.
-__device__ float sample_inv_cell(const PackSet &s1, const PackSet &s2) {
-    __shared__ float red[4][kPackThreads / 32];
+struct BinScale {
+    float inv_cell;          // 1 / (spatial bin width)
+    float a_lo, a_inv;       // area bin = floor((log2(area) - a_lo) * a_inv) + 1, clamped to 0 .. 31
+};
+
+// identical in every CTA of the launch: every CTA reduces the same strided sample of <= 256
+// raw boxes (centres and log2 areas)
+__device__ BinScale sample_bin_scale(const PackSet &s1, const PackSet &s2) {
+    __shared__ float red[6][kPackThreads / 32];
     const int tid = threadIdx.x;
     const bool two = s2.n > 0;
     const int64_t n1 = s1.n_dev ? *s1.n_dev : s1.n;
@@ -76,6 +82,7 @@ __device__ float sample_inv_cell(const PackSet &s1, const PackSet &s2) {
     const int slots = two ? kPackThreads / 2 : kPackThreads;
     const int t = two ? (tid & (kPackThreads / 2 - 1)) : tid;
     float lo_x = INFINITY, hi_x = -INFINITY, lo_y = INFINITY, hi_y = -INFINITY;
+    float lo_a = INFINITY, hi_a = -INFINITY;
     const int64_t sn = (two && tid >= kPackThreads / 2) ? s2.n : n1;   // only set 1 is ever device-counted
     if (sn > 0) {
         const int64_t i = (sn >= slots) ? (int64_t)t * (sn / slots) : (t % sn);
@@ -86,32 +93,48 @@ __device__ float sample_inv_cell(const PackSet &s1, const PackSet &s2) {
             lo_x = hi_x = cx;
             lo_y = hi_y = cy;
         }
+        const float la = __log2f(b[2] * b[3]);
+        if (fabsf(la) < 1e30f) lo_a = hi_a = la;     // also rejects NaN / -inf (zero area)
     }
     lo_x = warp_min(lo_x); hi_x = warp_max(hi_x);
     lo_y = warp_min(lo_y); hi_y = warp_max(hi_y);
+    lo_a = warp_min(lo_a); hi_a = warp_max(hi_a);
     if ((tid & 31) == 0) {
         red[0][tid >> 5] = lo_x; red[1][tid >> 5] = hi_x;
         red[2][tid >> 5] = lo_y; red[3][tid >> 5] = hi_y;
+        red[4][tid >> 5] = lo_a; red[5][tid >> 5] = hi_a;
     }
     __syncthreads();
 #pragma unroll
     for (int w = 0; w < kPackThreads / 32; ++w) {
         lo_x = fminf(lo_x, red[0][w]); hi_x = fmaxf(hi_x, red[1][w]);
         lo_y = fminf(lo_y, red[2][w]); hi_y = fmaxf(hi_y, red[3][w]);
+        lo_a = fminf(lo_a, red[4][w]); hi_a = fmaxf(hi_a, red[5][w]);
     }
+    BinScale sc;
     const float extent = fmaxf(hi_x - lo_x, hi_y - lo_y);
     // 30 bins across the sampled extent (the sample misses a little at the edges)
     float cell = extent * (1.f / 30.f);
     if (!(cell > 1e-30f) || !(cell < 1e30f)) cell = 1.f;
-    return 1.f / cell;
+    sc.inv_cell = 1.f / cell;
+    const float span = hi_a - lo_a;
+    sc.a_lo = (span >= 0.f) ? lo_a : 0.f;
+    sc.a_inv = (span > 1e-6f && span < 1e30f) ? 30.f / span : 1.f;
+    return sc;
+}
+
+// area bin of log2(area) value `la` (monotone, clamped; NaN -> 0)
+__device__ __forceinline__ int area_bin(float la, const BinScale &sc) {
+    const float t = floorf((la - sc.a_lo) * sc.a_inv) + 1.f;
+    return (int)fminf(fmaxf(t, 0.f), 31.f);
 }
 
 // One CTA packs 256 consecutive slots = two table blocks (slot counts are
 // multiples of 128, so a block never straddles the two sets); warp v packs the 32
 // boxes of word v % 4 of block v / 4.
 __global__ void __launch_bounds__(kPackThreads)
-pack_kernel(PackSet s1, PackSet s2, float min_wh, float cell) {
-    __shared__ uint32_t s_t0[2][2][32][4];   // level 0: [block][axis][bin][word]
+pack_kernel(PackSet s1, PackSet s2, float min_wh, float cell, float area_ratio) {
+    __shared__ uint32_t s_t0[2][3][32][4];   // level 0: [block][axis x, y, area][bin][word]
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     // the consumer kernel may start now: it streams zeros until it needs the packed set
     pdl_launch_dependents();
@@ -131,7 +154,15 @@ pack_kernel(PackSet s1, PackSet s2, float min_wh, float cell) {
         const float *b = s.boxes + src * s.stride;
         cx = __fadd_rn(b[0], o); cy = __fadd_rn(b[1], o); w = b[2]; h = b[3]; th = b[4];
     }
-    const float inv_cell = cell > 0.f ? 1.f / cell : sample_inv_cell(s1, s2);
+    BinScale sc;
+    if (cell > 0.f) {
+        sc.inv_cell = 1.f / cell;
+        sc.a_lo = 0.f;
+        sc.a_inv = 1.f;
+    } else {
+        sc = sample_bin_scale(s1, s2);
+    }
+    const float inv_cell = sc.inv_cell;
 
     // NMS: scratch of the resolve stage starts from zero (the mask kernel only touches it
     // after its griddepcontrol.wait, i.e. after this grid has completed)
@@ -144,7 +175,7 @@ pack_kernel(PackSet s1, PackSet s2, float min_wh, float cell) {
         if (i < kNmsSyncWords) s1.z_sync[i] = 0u;
     }
 
-    uint32_t xm = 0u, ym = 0u;
+    uint32_t xm = 0u, ym = 0u, am = 0u;
     if (in_set) {
         if (src < 0) {
             // padding: occupies no bin, so no pair with it survives the cull
@@ -168,11 +199,20 @@ pack_kernel(PackSet s1, PackSet s2, float min_wh, float cell) {
             bin_range(cy - ry, cy + ry, inv_cell, sy, ny);
             xm = range_mask(sx, nx);
             ym = range_mask(sy, ny);
+            // area axis (NMS): the box sits in one bin; a partner can reach the IoU threshold only
+            // with an area inside [area * ratio, area / ratio] (IoU <= min(area) / max(area))
+            int sa = 0, na = 0;
+            if (area_ratio > 0.f && area_ratio < 1.f) {
+                const float la = __log2f(w * h), dl = -__log2f(area_ratio);
+                am = 1u << area_bin(la, sc);
+                sa = area_bin(la - dl, sc);
+                na = area_bin(la + dl, sc) - sa + 1;
+                if (na >= 32 || !(fabsf(la) < 1e30f)) { sa = 0; na = 0; }     // no constraint
+            }
             s.p0[i] = make_float4(cx, cy, r, w * h);
             s.p1[i] = make_float4((float)cd, (float)sd, a, hb);
-            s.pr[i] = (uint32_t)sx | ((uint32_t)nx << 8) | ((uint32_t)sy << 16) | ((uint32_t)ny << 24);
+            s.pr[i] = pack_ranges(sx, nx, sy, ny, sa, na);
         }
-        s.pm[i] = make_uint2(xm, ym);
     }
 
     // ---- inverted index, level 0: transpose the warp's 32 masks with ballots -----------
@@ -186,12 +226,22 @@ pack_kernel(PackSet s1, PackSet s2, float min_wh, float cell) {
         }
         s_t0[warp >> 2][0][lane][warp & 3] = tx;   // bin = lane
         s_t0[warp >> 2][1][lane][warp & 3] = ty;
+        if (area_ratio > 0.f && area_ratio < 1.f) {   // NMS packs only (launch-uniform)
+            uint32_t ta = 0u;
+#pragma unroll
+            for (int b = 0; b < 32; ++b) {
+                const uint32_t ba = __ballot_sync(0xffffffffu, (am >> b) & 1u);
+                if (lane == b) ta = ba;
+            }
+            s_t0[warp >> 2][2][lane][warp & 3] = ta;
+        }
     }
     __syncthreads();
     // ---- levels 0..4 by prefix OR over 16 consecutive bins, straight to global ----------
     // task (block h, axis a, bin b, word w): T[j][b][w] = OR of level 0 at bins b .. b+2^j-1
-    for (int task = tid; task < 2 * 2 * 32 * 4; task += kPackThreads) {
-        const int tw = task & 3, b = (task >> 2) & 31, a = (task >> 7) & 1, hb = task >> 8;
+    const int axes = (area_ratio > 0.f && area_ratio < 1.f) ? 3 : 2;   // IoU packs: the area axis is never read
+    for (int task = tid; task < 2 * axes * 32 * 4; task += kPackThreads) {
+        const int tw = task & 3, b = (task >> 2) & 31, hb = (task >> 7) & 1, a = task >> 8;
         const int64_t g0 = blockIdx.x * (int64_t)kPackThreads + hb * kBlock;   // first slot of the block
         const bool sec = g0 >= s1.n_pad;
         const PackSet sb = sec ? s2 : s1;
@@ -211,12 +261,12 @@ pack_kernel(PackSet s1, PackSet s2, float min_wh, float cell) {
     }
 }
 
-int launch_pack(const PackSet &s1, const PackSet &s2, float min_wh, float cell,
+int launch_pack(const PackSet &s1, const PackSet &s2, float min_wh, float cell, float area_ratio,
                 cudaStream_t stream) {
     const int64_t total = s1.n_pad + s2.n_pad;
     if (total == 0) return 0;
     const int64_t blocks = (total + kPackThreads - 1) / kPackThreads;
-    pack_kernel<<<(unsigned)blocks, kPackThreads, 0, stream>>>(s1, s2, min_wh, cell);
+    pack_kernel<<<(unsigned)blocks, kPackThreads, 0, stream>>>(s1, s2, min_wh, cell, area_ratio);
     return cudaGetLastError() == cudaSuccess ? 0 : -3;
 }
 
@@ -242,8 +292,7 @@ PackSet make_pack_set(const float *boxes, int64_t n, int stride, const int64_t *
     s.offsets = offsets;
     s.p0 = reinterpret_cast<float4 *>(packed);
     s.p1 = s.p0 ? s.p0 + n_pad : nullptr;
-    s.pm = s.p0 ? reinterpret_cast<uint2 *>(s.p1 + n_pad) : nullptr;
-    s.pr = s.p0 ? reinterpret_cast<uint32_t *>(s.pm + n_pad) : nullptr;
+    s.pr = s.p0 ? reinterpret_cast<uint32_t *>(s.p1 + n_pad) : nullptr;
     s.pt = s.p0 ? s.pr + n_pad : nullptr;
     s.n_pad = n_pad;
     return s;

@@ -33,9 +33,9 @@ def test_exports_match_header(lib):
 
 def test_size_queries_without_gpu(lib):
     assert lib.rotgeo_packed_bytes(0) == 0
-    assert lib.rotgeo_packed_bytes(1) == 128 * 84
-    assert lib.rotgeo_packed_bytes(129) == 256 * 84
-    assert lib.rotgeo_iou_workspace_bytes(8192, 8192) == 2 * 8192 * 84
+    assert lib.rotgeo_packed_bytes(1) == 128 * 96
+    assert lib.rotgeo_packed_bytes(129) == 256 * 96
+    assert lib.rotgeo_iou_workspace_bytes(8192, 8192) == 2 * 8192 * 96
     assert lib.rotgeo_nms_workspace_bytes(0, None, 0) == 0
     one = lib.rotgeo_nms_workspace_bytes(2000, None, 0)
     offs = np.array([0, 500, 500, 2000], dtype=np.int64)
