@@ -294,7 +294,7 @@ int rotgeo_nms(const float *boxes, int64_t n, int stride, const float *offsets,
         s1.z_sum_words = scratch.sum_words;
         s1.z_sync = scratch.sync;
         const rotgeo::PackSet none = rotgeo::make_pack_set(nullptr, 0, 5, nullptr, nullptr, nullptr, 0);
-        if (rotgeo::launch_pack(s1, none, 0.f, 0.f, iou_threshold - 1e-4f, st)) return cuda_fail("nms pack launch");
+        if (rotgeo::launch_pack(s1, none, 0.f, 0.f, rotgeo::nms_area_axis_ratio(iou_threshold), st)) return cuda_fail("nms pack launch");
     }
     // no global order given: kept indices come out segment-major (the caller re-orders)
     if (!order) order = sorder;

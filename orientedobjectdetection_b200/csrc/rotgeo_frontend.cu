@@ -238,7 +238,7 @@ int launch_multiclass_nms(const float *multi_bboxes, int shared, const float *mu
     s1.z_sum_words = scratch.sum_words;
     s1.z_sync = scratch.sync;
     const PackSet none = make_pack_set(nullptr, 0, 5, nullptr, nullptr, nullptr, 0);
-    if (launch_pack(s1, none, 0.f, 0.f, iou_threshold - 1e-4f, stream)) return -3;
+    if (launch_pack(s1, none, 0.f, 0.f, nms_area_axis_ratio(iou_threshold), stream)) return -3;
 
     NmsDevLaunch a;
     a.packed = ws + l.off_packed;
@@ -463,7 +463,7 @@ int launch_nms_prepared(const float *boxes, int64_t n, int stride, const float *
     s1.z_sum_words = scratch.sum_words;
     s1.z_sync = scratch.sync;
     const PackSet none = make_pack_set(nullptr, 0, 5, nullptr, nullptr, nullptr, 0);
-    if (launch_pack(s1, none, 0.f, 0.f, thr - 1e-4f, stream)) return -3;
+    if (launch_pack(s1, none, 0.f, 0.f, nms_area_axis_ratio(thr), stream)) return -3;
     return launch_nms(plan, packed, segs_dev, nullptr, nullptr, order, seg_order, thr, mask, flags,
                       scratch, keep_out, num_keep_out, stream);
 }

@@ -47,6 +47,14 @@ struct PackSet {
     int64_t n_pad;
 };
 constexpr int kNmsSyncWords = 16;
+
+// The area axis of the inverted index pays off when the threshold is high enough for the
+// admissible area range to be narrow (RPN: 0.8 -> a few of the 32 bins); at the usual 0.1 of
+// the detection heads it would admit half of the bins and cost more than it removes.
+static inline float nms_area_axis_ratio(float iou_threshold) {
+    const float r = iou_threshold - 1e-4f;
+    return (r >= 0.25f && r < 1.f) ? r : 0.f;
+}
 PackSet make_pack_set(const float *boxes, int64_t n, int stride, const int64_t *gather,
                       const float *offsets, void *packed, int64_t n_pad);
 

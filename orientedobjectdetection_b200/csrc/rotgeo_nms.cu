@@ -50,7 +50,8 @@ namespace rotgeo {
 constexpr int kTile = 128;      // tile edge in boxes = one inverted-index block = two mask words
 constexpr int kThreads = 256;
 constexpr int kWarps = kThreads / 32;
-constexpr int kStages = 3;      // cull-data ring (3 x 7.7 KB of index + row ranges)
+constexpr int kMaxStages = 4;   // cull-data ring: 4 stages of the x/y index (5 KB), or 3 with the area axis (7.7 KB)
+constexpr int kTabWords = 3 * kTableWords;   // 5760 words >= 4 * kTableXYWords
 constexpr int kInfoSlots = 8;   // tile descriptors / launch-control responses (> kStages)
 constexpr int kQueueCap = 64;   // pairs per warp queue (never more than 31 + 32 queued)
 static_assert(kTile == kBlock, "a tile column is one inverted-index block");
@@ -69,14 +70,14 @@ struct QEntry {       // one pair that survived cull level 1
 constexpr unsigned long long kWordMask = (1ull << 48) - 1ull;
 
 struct __align__(16) MaskSmem {
-    uint32_t tab[kStages][kTableWords];
-    uint32_t rowr[kStages][kTile];
+    uint32_t tab[kTabWords];
+    uint32_t rowr[kMaxStages][kTile];
     QEntry queue1[kWarps][kQueueCap];   // survived the bin ranges
     QEntry queue2[kWarps][kQueueCap];   // survived the circle test as well
     uint4 resp[kInfoSlots];
     TileInfo info[kInfoSlots];
-    uint64_t full[kStages];
-    uint64_t empty[kStages];
+    uint64_t full[kMaxStages];
+    uint64_t empty[kMaxStages];
     uint64_t sched[kInfoSlots];
     uint64_t ready[kInfoSlots];
 };
@@ -88,6 +89,7 @@ struct MaskArgs {
     int nseg;
     float thr;
     float area_ratio;             // pairs with min(area) < area_ratio * max(area) cannot reach thr
+    int area_axis;                // the packed set carries the area axis of the index (launch-uniform)
     unsigned long long *mask;
     unsigned long long *summary;  // per packed slot: sum_words words, zeroed by the pack kernel
     int sum_words;
@@ -116,14 +118,19 @@ __device__ TileInfo locate_tile(const NmsSegment *__restrict__ segs, int nseg, u
     return ti;
 }
 
+// AREA: the packed set carries the area axis of the index (high thresholds, see
+// nms_area_axis_ratio): 3 ring stages of 7.7 KB instead of 4 of 5 KB, one more range lookup
+template <bool AREA>
 __global__ void __launch_bounds__(kThreads)
 nms_mask_kernel(const MaskArgs g) {
     __shared__ MaskSmem sm;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    constexpr int kStages = AREA ? 3 : 4;
+    constexpr uint32_t tab_words = AREA ? kTableWords : kTableXYWords;
 
     if (tid == 0) {
 #pragma unroll
-        for (int s = 0; s < kStages; ++s) {
+        for (int s = 0; s < kMaxStages; ++s) {
             mbar_init(&sm.full[s], 1);
             mbar_init(&sm.empty[s], kWarps);
         }
@@ -141,11 +148,11 @@ nms_mask_kernel(const MaskArgs g) {
     auto issue_cull_data = [&](unsigned k, const TileInfo &ti) {
         const int s = k % kStages;
         const NmsSegment &sg = g.segs[ti.seg];
-        mbar_expect_tx(&sm.full[s], (kTile + kTableWords) * sizeof(uint32_t));
+        mbar_expect_tx(&sm.full[s], (kTile + tab_words) * sizeof(uint32_t));
         tma_load_1d(sm.rowr[s], g.pr + sg.pstart + (int64_t)ti.I * kTile, kTile * sizeof(uint32_t),
                     &sm.full[s]);
-        tma_load_1d(sm.tab[s], g.pt + (sg.pstart / kBlock + ti.J) * kTableWords,
-                    kTableWords * sizeof(uint32_t), &sm.full[s]);
+        tma_load_1d(sm.tab + s * tab_words, g.pt + (sg.pstart / kBlock + ti.J) * kTableWords,
+                    tab_words * sizeof(uint32_t), &sm.full[s]);
     };
     auto ask_next = [&](unsigned k) {
         const int slot = (k - 1) % kInfoSlots;
@@ -263,16 +270,17 @@ nms_mask_kernel(const MaskArgs g) {
             uint32_t h = 0;
             if (nx != 0) {
                 const int jx = min(31 - __clz(nx), kTableLevels - 1), jy = min(31 - __clz(ny), kTableLevels - 1);
-                const uint32_t *tx = sm.tab[s] + jx * 128 + cw;
-                const uint32_t *ty = sm.tab[s] + kTableAxisWords + jy * 128 + cw;
+                const uint32_t *const tab = sm.tab + s * tab_words;
+                const uint32_t *tx = tab + jx * 128 + cw;
+                const uint32_t *ty = tab + kTableAxisWords + jy * 128 + cw;
                 const uint32_t X = tx[sx * 4] | tx[((sx + nx - (1 << jx)) & 31) * 4];
                 const uint32_t Y = ty[sy * 4] | ty[((sy + ny - (1 << jy)) & 31) * 4];
                 h = X & Y;
-                if (br.na != 0) {
+                if (AREA && br.na != 0) {
                     // third axis: only columns whose area lies within the ratio that can still
                     // reach the threshold (IoU <= min(area) / max(area))
                     const int ja = min(31 - __clz(br.na), kTableLevels - 1);
-                    const uint32_t *ta = sm.tab[s] + 2 * kTableAxisWords + ja * 128 + cw;
+                    const uint32_t *ta = tab + 2 * kTableAxisWords + ja * 128 + cw;
                     h &= ta[br.sa * 4] | ta[((br.sa + br.na - (1 << ja)) & 31) * 4];
                 }
                 if (ti.I == ti.J) {                                  // keep columns before the row only
@@ -758,7 +766,9 @@ static int launch_mask(const MaskArgs &g, int64_t tiles, cudaStream_t stream) {
     attr[0].val.programmaticStreamSerializationAllowed = 1;   // overlap with the pack kernel
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    return cudaLaunchKernelEx(&cfg, nms_mask_kernel, g) == cudaSuccess ? 0 : -3;
+    const cudaError_t e = g.area_axis ? cudaLaunchKernelEx(&cfg, nms_mask_kernel<true>, g)
+                                      : cudaLaunchKernelEx(&cfg, nms_mask_kernel<false>, g);
+    return e == cudaSuccess ? 0 : -3;
 }
 
 static int launch_resolve(const ResolveArgs &a_in, cudaStream_t stream) {
@@ -804,6 +814,7 @@ int launch_nms(const NmsPlan &plan, const void *packed, const NmsSegment *segmen
     g.nseg = (int)plan.num_segments;
     g.thr = thr;
     g.area_ratio = thr - 1e-4f;
+    g.area_axis = nms_area_axis_ratio(thr) > 0.f;
     g.mask = reinterpret_cast<unsigned long long *>(mask);
     g.summary = scratch.summary;
     g.sum_words = scratch.sum_words;
@@ -837,6 +848,7 @@ int launch_nms_device_planned(const NmsDevLaunch &d, cudaStream_t stream) {
     g.nseg = d.nseg;
     g.thr = d.thr;
     g.area_ratio = d.thr - 1e-4f;
+    g.area_axis = nms_area_axis_ratio(d.thr) > 0.f;
     g.mask = reinterpret_cast<unsigned long long *>(d.mask);
     g.summary = d.scratch.summary;
     g.sum_words = d.scratch.sum_words;
