@@ -235,6 +235,56 @@ def secondary_nms(torch, rg, synth, reps=5):
     return res
 
 
+def secondary_sharded(torch, dist, rg, synth, dev):
+    """N > 1: the NMS workloads that shard (BASELINE C4: images over ranks, C5: classes over
+    ranks) and C3 as ONE global matrix row-sharded (strong scaling), wall clock, max over ranks.
+    Every rank builds the same synthetic inputs; results are all-gathered (dist.py)."""
+    from orientedobjectdetection_b200 import dist as rdist
+    import copy
+    res = {}
+
+    def timed(fn, reps=3):
+        fn()
+        ts = []
+        for _ in range(reps):
+            torch.cuda.synchronize()
+            dist.barrier()
+            t0 = time.perf_counter()
+            fn()
+            torch.cuda.synchronize()
+            t = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ts.append(float(t))
+        return min(ts)
+
+    imgs = [tuple(torch.from_numpy(x).to(dev) for x in synth.c4_rpn_image(s)) for s in range(64)]
+    nb = sum(int(b.shape[0]) for b, _, _ in imgs)
+    t = timed(lambda: rdist.nms_images_sharded(imgs, 0.8, 2000))
+    res['c4_64img_sharded_over_ranks'] = {'boxes': nb, 'ms': 1e3 * t, 'boxes_per_s': nb / t}
+    del imgs
+    patches, offs, shape = synth.c5_patch_results(0)
+    nd = sum(a.shape[0] for p in patches for a in p)
+    ts = []
+    for _ in range(2):
+        cp = copy.deepcopy(patches)
+        torch.cuda.synchronize()
+        dist.barrier()
+        t0 = time.perf_counter()
+        rdist.merge_results_sharded(cp, offs, shape, 0.1)
+        tt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        ts.append(float(tt))
+    res['c5_merge_results_classes_sharded_over_ranks'] = {'boxes': nd, 'ms': 1e3 * min(ts), 'boxes_per_s': nd / min(ts)}
+    a3, b3 = synth.c3_iou(0)
+    ad, bd = torch.from_numpy(a3).to(dev), torch.from_numpy(b3).to(dev)
+    pairs = a3.shape[0] * b3.shape[0]
+    t = timed(lambda: rdist.rbbox_overlaps_sharded(ad, bd, gather=False), 5)
+    res['c3_one_8192x8192_matrix_row_sharded_compute_only'] = {'pairs': pairs, 'ms': 1e3 * t, 'gpairs_per_s': pairs / t / 1e9}
+    t = timed(lambda: rdist.rbbox_overlaps_sharded(ad, bd), 5)
+    res['c3_one_8192x8192_matrix_row_sharded_plus_allgather'] = {'pairs': pairs, 'ms': 1e3 * t, 'gpairs_per_s': pairs / t / 1e9}
+    return res
+
+
 def measured_traffic():
     """DRAM bytes per launch of the dominant kernel from the committed ncu --set full capture
     (profiles/r01_iou_tile_kernel_traffic.json, written from the .ncu-rep by tools/ncu_traffic.py)"""
@@ -362,6 +412,14 @@ def run_rotgeo(args, rank, world, local_rank):
     }
     if rank == 0 and world == 1 and not args.no_secondary:
         line['secondary'] = secondary_nms(torch, rg, synth)
+    if world > 1 and not args.no_secondary:
+        try:
+            sec = secondary_sharded(torch, dist, rg, synth, dev)
+            if rank == 0:
+                line['secondary'] = sec
+        except Exception as exc:      # the headline line must survive a failure here
+            if rank == 0:
+                line['secondary'] = {'error': repr(exc)[:300]}
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         ac, bc = a.copy(), b.copy()
         ac[:, 2:4] = np.maximum(ac[:, 2:4], 1e-3)
