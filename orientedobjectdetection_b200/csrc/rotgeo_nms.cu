@@ -41,6 +41,7 @@
 // mmrotate/core/post_processing/bbox_nms_rotated.py:80,122,
 // mmrotate/core/patch/merge_results.py:116-118, mmrotate/datasets/dota.py:379).
 #include <math.h>
+#include <stdlib.h>
 
 #include "rotgeo_device.cuh"
 #include "rotgeo_internal.h"
@@ -54,6 +55,7 @@ constexpr int kMaxStages = 4;   // cull-data ring: 4 stages of the x/y index (5 
 constexpr int kTabWords = 3 * kTableWords;   // 5760 words >= 4 * kTableXYWords
 constexpr int kInfoSlots = 8;   // tile descriptors / launch-control responses (> kStages)
 constexpr int kQueueCap = 64;   // pairs per warp queue (never more than 31 + 32 queued)
+constexpr int64_t kAheadMinTiles = 148 * 4 * 8;   // smaller grids: scheduler look-ahead 1 (see MaskArgs::ahead)
 static_assert(kTile == kBlock, "a tile column is one inverted-index block");
 
 struct TileInfo {
@@ -80,6 +82,14 @@ struct __align__(16) MaskSmem {
     uint64_t empty[kMaxStages];
     uint64_t sched[kInfoSlots];
     uint64_t ready[kInfoSlots];
+    // thread 0's scheduler state (kept here, not in registers that every thread would carry)
+    struct Sched {
+        unsigned next_ask, next_resp;   // launch-control requests issued / answers consumed, from 1
+        unsigned grp_next, grp_left;    // rest of the tile group in hand
+        int alive;                      // no request has failed yet
+        int cur_nb;                     // 128-row blocks of cur's segment
+        TileInfo cur;                   // the tile located last
+    } st;
 };
 
 struct MaskArgs {
@@ -94,6 +104,9 @@ struct MaskArgs {
     unsigned long long *summary;  // per packed slot: sum_words words, zeroed by the pack kernel
     int sum_words;
     const int64_t *total_tiles;   // nullable: device-planned launch, tile ids >= *total_tiles do not exist
+    int ahead;                    // 1 .. 3: how many tiles ahead the scheduler thread runs (launch-uniform)
+    int group;                    // tiles per grid CTA (= per launch-control request): CTA c owns tiles c*group ...
+    int64_t tiles;                // host-side tile count (a bound when total_tiles is set)
 };
 
 // tile id -> (segment, I, J): tiles of a segment are numbered row block by row block,
@@ -121,7 +134,7 @@ __device__ TileInfo locate_tile(const NmsSegment *__restrict__ segs, int nseg, u
 // AREA: the packed set carries the area axis of the index (high thresholds, see
 // nms_area_axis_ratio): 3 ring stages of 7.7 KB instead of 4 of 5 KB, one more range lookup
 template <bool AREA>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, 4)   // 4 CTAs per SM: at most 64 registers
 nms_mask_kernel(const MaskArgs g) {
     __shared__ MaskSmem sm;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -154,16 +167,108 @@ nms_mask_kernel(const MaskArgs g) {
         tma_load_1d(sm.tab + s * tab_words, g.pt + (sg.pstart / kBlock + ti.J) * kTableWords,
                     tab_words * sizeof(uint32_t), &sm.full[s]);
     };
-    auto ask_next = [&](unsigned k) {
-        const int slot = (k - 1) % kInfoSlots;
+    // launch-control request number a = 1, 2, ... answers into resp[(a-1) % kInfoSlots]
+    auto ask_next = [&](unsigned a) {
+        const int slot = (a - 1) % kInfoSlots;
         mbar_expect_tx(&sm.sched[slot], 16);
         clc_try_cancel(&sm.resp[slot], &sm.sched[slot]);
+    };
+    // The scheduler runs D tiles ahead of the warps: while tile k is culled, the descriptor of
+    // tile k + D is published and its cull data are in flight, with D launch-control requests
+    // outstanding behind it.  A tile of a sparse scene is a few hundred instructions per warp,
+    // far less than one launch-control or TMA round trip: one tile of look-ahead left every CTA
+    // waiting for those two latencies in turn (ncu: 37 % of the instructions issued in the
+    // barrier spin loops), and a warp 0 that was busy clipping delayed everybody's next tile.
+    // Small grids keep D = 1: requests taken early are tiles the other CTAs cannot take.
+    int ahead = g.ahead & 15;
+    if (!(g.ahead & 16) && g.total_tiles && *g.total_tiles < kAheadMinTiles) ahead = 1;   // the real count, not the launch bound
+    const int D = min(max(ahead, 1), kStages - 1);
+    // One grid CTA (one launch-control request) stands for `group` consecutive tiles: the
+    // hardware answers requests at a few ns each for the whole GPU, which is as long as an
+    // empty tile takes.
+    const unsigned G = (unsigned)g.group;
+    const int64_t limit = g.total_tiles ? *g.total_tiles : g.tiles;
+    // Inside a group the next tile is one step along the triangle: a few integer instructions
+    // instead of a binary search over the segment table and a square root, which made thread 0
+    // the bottleneck of sparse scenes.
+    auto seg_blocks = [&](int sgi) {
+        return sgi < g.nseg ? (int)((g.segs[sgi].len + kTile - 1) / kTile) : 0x7fffffff;
+    };
+    auto take_tile = [&](unsigned j) {      // thread 0: find my j-th tile, start its cull data, publish it
+        MaskSmem::Sched st = sm.st;
+        TileInfo nx;
+        nx.valid = 0; nx.seg = 0; nx.I = 0; nx.J = 0;
+        for (;;) {
+            unsigned tn;
+            bool step = false;
+            if (st.grp_left > 0u) {
+                tn = st.grp_next++;
+                --st.grp_left;
+                step = true;
+            } else {
+                if (!st.alive) break;
+                const unsigned a = st.next_resp++;
+                mbar_wait(&sm.sched[(a - 1) % kInfoSlots], ((a - 1) / kInfoSlots) & 1);
+                unsigned cta;
+                if (!clc_decode(&sm.resp[(a - 1) % kInfoSlots], cta)) {
+                    // nothing left to cancel: later requests fail as well; wait for their answers so
+                    // that none is still on its way to this CTA's shared memory when it exits
+                    st.alive = 0;
+                    while (st.next_resp < st.next_ask) {
+                        const unsigned b = st.next_resp++;
+                        mbar_wait(&sm.sched[(b - 1) % kInfoSlots], ((b - 1) / kInfoSlots) & 1);
+                    }
+                    break;
+                }
+                fence_proxy_async_smem();   // my read of the slot precedes its reuse by a later request
+                ask_next(st.next_ask++);
+                tn = cta * G;
+                st.grp_next = tn + 1u;
+                st.grp_left = G - 1u;
+            }
+            if ((int64_t)tn < limit) {
+                if (step) {             // the tile with the next id
+                    if (++st.cur.J > st.cur.I) {
+                        st.cur.J = 0;
+                        ++st.cur.I;
+                        while (st.cur.I >= st.cur_nb) {   // next segment (empty ones have no tiles)
+                            ++st.cur.seg;
+                            st.cur.I = 0;
+                            st.cur_nb = seg_blocks(st.cur.seg);
+                        }
+                    }
+                } else {
+                    st.cur = locate_tile(g.segs, g.nseg, tn);
+                    st.cur_nb = seg_blocks(st.cur.seg);
+                }
+                nx = st.cur;
+                // ring stage of tile j was last read for tile j-kStages: wait until every warp
+                // left it; they then also left descriptor / response slots that old
+                if (j >= (unsigned)kStages) mbar_wait(&sm.empty[j % kStages], ((j / kStages) - 1) & 1);
+                issue_cull_data(j, nx);
+                break;
+            }
+            // past the (device-side) tile count: no work there, look further
+        }
+        sm.st = st;
+        sm.info[j % kInfoSlots] = nx;
+        mbar_arrive(&sm.ready[j % kInfoSlots]);
     };
     if (tid == 0) {
         TileInfo t0;
         t0.valid = 0; t0.seg = 0; t0.I = 0; t0.J = 0;
-        if (!g.total_tiles || (int64_t)blockIdx.x < *g.total_tiles)
-            t0 = locate_tile(g.segs, g.nseg, blockIdx.x);
+        MaskSmem::Sched st;
+        st.next_ask = st.next_resp = 1u;
+        st.grp_next = blockIdx.x * G + 1u;
+        st.grp_left = G - 1u;
+        st.alive = 1;
+        st.cur_nb = 0;
+        if ((int64_t)blockIdx.x * G < limit) {
+            t0 = locate_tile(g.segs, g.nseg, blockIdx.x * G);
+            st.cur_nb = seg_blocks(t0.seg);
+        }
+        st.cur = t0;
+        sm.st = st;
         sm.info[0] = t0;
         mbar_arrive(&sm.ready[0]);
     }
@@ -232,84 +337,69 @@ nms_mask_kernel(const MaskArgs g) {
             pdl_wait();
             if (tid == 0) {
                 issue_cull_data(0, ti);
-                ask_next(1);
+                for (int e = 0; e < D; ++e) ask_next(sm.st.next_ask++);
+                for (int j = 1; j < D; ++j) take_tile((unsigned)j);
             }
         }
 
-        // ---- scheduler: learn tile k+1, prefetch its cull data, ask for k+2, publish ---------
-        if (tid == 0) {
-            const unsigned kn = k + 1;
-            mbar_wait(&sm.sched[k % kInfoSlots], (k / kInfoSlots) & 1);
-            unsigned tn;
-            TileInfo nx;
-            nx.valid = 0; nx.seg = 0; nx.I = 0; nx.J = 0;
-            if (clc_decode(&sm.resp[k % kInfoSlots], tn) &&
-                (!g.total_tiles || (int64_t)tn < *g.total_tiles)) {
-                nx = locate_tile(g.segs, g.nseg, tn);
-                // ring stage of tile k+1 was last read for tile k+1-kStages: wait until every
-                // warp left it; they then also left descriptor / response slots that old
-                if (kn >= kStages) mbar_wait(&sm.empty[kn % kStages], ((kn / kStages) - 1) & 1);
-                issue_cull_data(kn, nx);
-                fence_proxy_async_smem();
-                ask_next(k + 2);
-            }
-            sm.info[kn % kInfoSlots] = nx;
-            mbar_arrive(&sm.ready[kn % kInfoSlots]);
-        }
+        // ---- scheduler: learn tile k+D, prefetch its cull data, keep D requests outstanding ---
+        if (tid == 0) take_tile(k + (unsigned)D);
 
-        // ---- cull level 1: per (row, 32-column word) two range-OR lookups per axis -----------
+        // ---- cull level 1: per (row, 64-column mask word) two range-OR lookups per axis ---------
+        // lane = (row of the warp's sixteen, half of the 128 columns): the whole tile in one pass,
+        // 8-byte table loads, and the range arithmetic of a row done by two lanes instead of four
         mbar_wait(&sm.full[s], (k / kStages) & 1);
-        uint32_t hits[2];
-        const int rl = lane >> 2, cw = lane & 3;
-#pragma unroll
-        for (int p = 0; p < 2; ++p) {
-            const int rloc = warp + kWarps * (rl + 8 * p);          // row inside the tile
+        const int rl = lane >> 1, ch = lane & 1;
+        const int rloc = warp + kWarps * rl;                        // row inside the tile
+        unsigned long long m = 0ull;
+        {
             const uint32_t rr = sm.rowr[s][rloc];
             const BinRanges br = unpack_ranges(rr);
             const int sx = br.sx, nx = br.nx, sy = br.sy, ny = br.ny;
-            uint32_t h = 0;
             if (nx != 0) {
                 const int jx = min(31 - __clz(nx), kTableLevels - 1), jy = min(31 - __clz(ny), kTableLevels - 1);
-                const uint32_t *const tab = sm.tab + s * tab_words;
-                const uint32_t *tx = tab + jx * 128 + cw;
-                const uint32_t *ty = tab + kTableAxisWords + jy * 128 + cw;
-                const uint32_t X = tx[sx * 4] | tx[((sx + nx - (1 << jx)) & 31) * 4];
-                const uint32_t Y = ty[sy * 4] | ty[((sy + ny - (1 << jy)) & 31) * 4];
-                h = X & Y;
+                const uint32_t *const tab = sm.tab + s * tab_words + 2 * ch;
+                const uint32_t *tx = tab + jx * 128;
+                const uint32_t *ty = tab + kTableAxisWords + jy * 128;
+                const uint2 x0 = *reinterpret_cast<const uint2 *>(tx + sx * 4);
+                const uint2 x1 = *reinterpret_cast<const uint2 *>(tx + ((sx + nx - (1 << jx)) & 31) * 4);
+                const uint2 y0 = *reinterpret_cast<const uint2 *>(ty + sy * 4);
+                const uint2 y1 = *reinterpret_cast<const uint2 *>(ty + ((sy + ny - (1 << jy)) & 31) * 4);
+                uint32_t lo = (x0.x | x1.x) & (y0.x | y1.x), hi = (x0.y | x1.y) & (y0.y | y1.y);
                 if (AREA && br.na != 0) {
                     // third axis: only columns whose area lies within the ratio that can still
                     // reach the threshold (IoU <= min(area) / max(area))
                     const int ja = min(31 - __clz(br.na), kTableLevels - 1);
-                    const uint32_t *ta = tab + 2 * kTableAxisWords + ja * 128 + cw;
-                    h &= ta[br.sa * 4] | ta[((br.sa + br.na - (1 << ja)) & 31) * 4];
+                    const uint32_t *ta = tab + 2 * kTableAxisWords + ja * 128;
+                    const uint2 a0 = *reinterpret_cast<const uint2 *>(ta + br.sa * 4);
+                    const uint2 a1 = *reinterpret_cast<const uint2 *>(ta + ((br.sa + br.na - (1 << ja)) & 31) * 4);
+                    lo &= a0.x | a1.x;
+                    hi &= a0.y | a1.y;
                 }
+                m = (unsigned long long)lo | ((unsigned long long)hi << 32);
                 if (ti.I == ti.J) {                                  // keep columns before the row only
-                    const int d = rloc - 32 * cw;                    // row's bit inside this word
-                    if (d <= 0) h = 0u;
-                    else if (d < 32) h &= (1u << d) - 1u;
+                    const int d = rloc - 64 * ch;                    // row's bit inside this mask word
+                    if (d <= 0) m = 0ull;
+                    else if (d < 64) m &= (1ull << d) - 1ull;
                 }
             }
-            hits[p] = h;
         }
         __syncwarp();
         if (lane == 0) mbar_arrive(&sm.empty[s]);   // this warp is done with the stage
 
         // ---- survivors -> queue 1, at most one per lane and round ---------------------------------
-#pragma unroll
-        for (int p = 0; p < 2; ++p) {
-            uint32_t m = hits[p];
-            const int rloc = warp + kWarps * (rl + 8 * p);
+        {
             QEntry e;
             e.prow = (int)sg.pstart + row_base + rloc;
-            e.word = (unsigned long long)(sg.mask_base + (int64_t)(row_base + rloc) * W + 2 * ti.J + (cw >> 1)) |
+            e.word = (unsigned long long)(sg.mask_base + (int64_t)(row_base + rloc) * W + 2 * ti.J + ch) |
                      ((unsigned long long)ti.J << 48);
-            const int pcol0 = (int)sg.pstart + col_base + 32 * cw;
+            const int pcol0 = (int)sg.pstart + col_base + 64 * ch;
             for (;;) {
-                const uint32_t act = __ballot_sync(0xffffffffu, m != 0u);
+                const uint32_t act = __ballot_sync(0xffffffffu, m != 0ull);
                 if (act == 0u) break;
                 if (m) {
-                    e.pcol = pcol0 + __ffs(m) - 1;
-                    m &= m - 1;
+                    e.pcol = pcol0 + __ffsll((long long)m) - 1;
+                    m &= m - 1ull;
                     q1[n1 + __popc(act & lt)] = e;
                 }
                 n1 += __popc(act);
@@ -753,12 +843,46 @@ static int resolve_grid_limit(bool mc) {
     return limit[mc];
 }
 
-static int launch_mask(const MaskArgs &g, int64_t tiles, cudaStream_t stream) {
+// look-ahead of the mask kernel's scheduler thread (MaskArgs::ahead).  Grids of fewer than
+// kAheadMinTiles tiles (8 per resident CTA) keep 1; ROTGEO_MASK_AHEAD=1..3 overrides (probe runs).
+constexpr int kAheadDefault = 3;
+static int mask_ahead_override() {
+    static int v = -1;
+    if (v < 0) {
+        const char *e = getenv("ROTGEO_MASK_AHEAD");
+        v = e ? atoi(e) : 0;
+        if (v < 0 || v > 3) v = 0;
+    }
+    return v;
+}
+
+// tiles per launch-control request (MaskArgs::group): 1 up to 16 tiles per resident CTA, then
+// doubled while every resident CTA still gets at least 16 requests; ROTGEO_MASK_GROUP overrides
+static int mask_group(int64_t tiles) {
+    static int forced = -1;
+    if (forced < 0) {
+        const char *e = getenv("ROTGEO_MASK_GROUP");
+        forced = e ? atoi(e) : 0;
+        if (forced < 0 || forced > 64) forced = 0;
+    }
+    if (forced) return forced;
+    int grp = 1;
+    while (grp < 16 && tiles / (2 * grp) >= 148 * 4 * 16) grp *= 2;
+    return grp;
+}
+
+static int launch_mask(const MaskArgs &g_in, int64_t tiles, cudaStream_t stream) {
     if (tiles > 0x7fffffffLL) return -1;
     if (tiles <= 0) return 0;
+    MaskArgs g = g_in;
+    const int forced = mask_ahead_override();
+    g.ahead = forced ? forced + 16 : (tiles >= kAheadMinTiles ? kAheadDefault : 1);   // + 16: also for small grids
+    g.tiles = tiles;
+    g.group = mask_group(tiles);
+    const int64_t ctas = (tiles + g.group - 1) / g.group;
     // one CTA per tile; running CTAs steal the not-yet-launched ones (launch control)
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3((unsigned)tiles);
+    cfg.gridDim = dim3((unsigned)ctas);
     cfg.blockDim = dim3(kThreads);
     cfg.stream = stream;
     cudaLaunchAttribute attr[1];
