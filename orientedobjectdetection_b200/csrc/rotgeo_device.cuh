@@ -10,6 +10,7 @@
 // rectangles (Sutherland-Hodgman's half-plane clipping applied per edge in
 // Liang-Barsky form): fixed work, registers only, no sort, no local memory.
 #pragma once
+#include <stdio.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -243,6 +244,30 @@ __device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
 __device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
+#ifdef ROTGEO_DEBUG_WAIT
+// probe builds: a wait that does not end reports where it hangs and stops the kernel
+__device__ __forceinline__ bool mbar_try(uint64_t *bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n" : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+    return ok != 0;
+}
+#define mbar_wait(bar, parity)                                                                      \
+    do {                                                                                            \
+        unsigned long long spins_ = 0;                                                              \
+        while (!mbar_try((bar), (parity))) {                                                        \
+            if (++spins_ > 2000000ull) {                                                            \
+                printf("stuck line %d block %d thread %d bar %u parity %u\n", __LINE__, blockIdx.x, \
+                       threadIdx.x, smem_u32(bar) & 0xffffu, (unsigned)(parity));                   \
+                __trap();                                                                           \
+            }                                                                                       \
+        }                                                                                           \
+    } while (0)
+#else
 __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
     asm volatile(
         "{\n"
@@ -256,6 +281,7 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
         "r"(parity)
         : "memory");
 }
+#endif
 // 1-D bulk copy global -> shared through the TMA unit (SASS: UBLKCP); bytes and
 // both addresses must be multiples of 16.
 __device__ __forceinline__ void tma_load_1d(void *dst_smem, const void *src_gmem, uint32_t bytes,

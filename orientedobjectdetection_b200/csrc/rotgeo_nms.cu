@@ -82,7 +82,7 @@ struct __align__(16) MaskSmem {
     uint64_t empty[kMaxStages];
     uint64_t sched[kInfoSlots];
     uint64_t ready[kInfoSlots];
-    // thread 0's scheduler state (kept here, not in registers that every thread would carry)
+    // the scheduler's state (the duty rotates over the warps; nobody carries it in registers)
     struct Sched {
         unsigned next_ask, next_resp;   // launch-control requests issued / answers consumed, from 1
         unsigned grp_next, grp_left;    // rest of the tile group in hand
@@ -338,12 +338,23 @@ nms_mask_kernel(const MaskArgs g) {
             if (tid == 0) {
                 issue_cull_data(0, ti);
                 for (int e = 0; e < D; ++e) ask_next(sm.st.next_ask++);
-                for (int j = 1; j < D; ++j) take_tile((unsigned)j);
+                for (int j = 1; j <= D; ++j) take_tile((unsigned)j);   // incl. this iteration's duty
             }
         }
 
         // ---- scheduler: learn tile k+D, prefetch its cull data, keep D requests outstanding ---
-        if (tid == 0) take_tile(k + (unsigned)D);
+        // The duty rotates over the warps (tile j: lane 0 of warp j % 8): one fixed scheduler
+        // thread made its warp ~1.5x slower than the others, which then waited for it at every
+        // tile (ncu: a third of all stall samples at the ready[] wait).  The state travels in
+        // shared memory; ready[j-1] (arrive = release, wait = acquire) orders the hand-over.
+        {
+            const unsigned j = k + (unsigned)D;
+            // (k == 0: thread 0 did it in the prologue; anybody else would race with its requests)
+            if (k > 0 && lane == 0 && warp == (int)(j % kWarps)) {
+                mbar_wait(&sm.ready[(j - 1) % kInfoSlots], ((j - 1) / kInfoSlots) & 1);
+                take_tile(j);
+            }
+        }
 
         // ---- cull level 1: per (row, 64-column mask word) two range-OR lookups per axis ---------
         // lane = (row of the warp's sixteen, half of the 128 columns): the whole tile in one pass,
@@ -856,8 +867,9 @@ static int mask_ahead_override() {
     return v;
 }
 
-// tiles per launch-control request (MaskArgs::group): 1 up to 16 tiles per resident CTA, then
-// doubled while every resident CTA still gets at least 16 requests; ROTGEO_MASK_GROUP overrides
+// tiles per launch-control request (MaskArgs::group): 4 for very large grids (measured on C5,
+// 175k mostly empty tiles: 0.88 -> 0.80 ms), else 1 (C4, 43k dense tiles: groups cost balance);
+// ROTGEO_MASK_GROUP overrides (probe runs)
 static int mask_group(int64_t tiles) {
     static int forced = -1;
     if (forced < 0) {
@@ -866,9 +878,7 @@ static int mask_group(int64_t tiles) {
         if (forced < 0 || forced > 64) forced = 0;
     }
     if (forced) return forced;
-    int grp = 1;
-    while (grp < 16 && tiles / (2 * grp) >= 148 * 4 * 16) grp *= 2;
-    return grp;
+    return tiles >= 148 * 4 * 128 ? 4 : 1;
 }
 
 static int launch_mask(const MaskArgs &g_in, int64_t tiles, cudaStream_t stream) {
