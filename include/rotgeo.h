@@ -226,6 +226,37 @@ int rotgeo_nms_prepared(const float *boxes, int64_t n, int stride, const float *
                         int64_t *keep_out, int64_t *num_keep_out, void *workspace,
                         size_t workspace_bytes, void *stream);
 
+/* ---- rotated NMS front-end for a batch of images ------------------------------------
+ * Replaces the reference's per-image python loop around batched_nms
+ * (mmrotate/models/dense_heads/rotated_rpn_head.py:414-426,515, oriented_rpn_head.py:275:
+ * for every image its own boxes.max(), id offsets, score sort, NMS, host syncs) by ONE
+ * pass over all images (BASELINE config C4).  The images
+ * lie back to back in (boxes, scores, ids); image g owns image_sizes_host[g] rows.
+ *
+ *   rotgeo_nms_batch_prepare  like rotgeo_nms_prepare with one segment per (image, id):
+ *                             score order, segment-major order, IMAGE-major emit order,
+ *                             segment sizes to the host (the one sync), and offsets_out
+ *                             (n,) = float(id) * (max(cx,cy) + max(w,h) + 1) with the
+ *                             maxima of the box's own image — mmcv.ops.batched_nms's
+ *                             arithmetic, per image.  ROTGEO_ERR_RANGE when
+ *                             num_images x (max id - min id + 1) exceeds 65536.
+ *   rotgeo_nms_prepared       as above, with offsets = offsets_out, seg_ids = ids,
+ *                             id_offsets = 0: keep_out comes out image-major, score
+ *                             order inside an image.
+ *   rotgeo_nms_batch_finish   keep[0 .. *num_keep) (device): global row -> row inside its
+ *                             image; counts_out (num_images,) int64 (device) = kept boxes
+ *                             per image.  No synchronisation.
+ *
+ * prep: rotgeo_nms_batch_prepare_bytes(n, num_images) bytes, 16-byte aligned, untouched
+ * between the three calls. */
+size_t rotgeo_nms_batch_prepare_bytes(int64_t n, int64_t num_images);
+int rotgeo_nms_batch_prepare(const float *boxes, int64_t n, int stride, const float *scores,
+                             const int64_t *ids, const int64_t *image_sizes_host, int64_t num_images,
+                             void *prep, size_t prep_bytes, float *offsets_out, int64_t *seg_counts_host,
+                             int64_t seg_cap, int64_t *num_segments_host, void *stream);
+int rotgeo_nms_batch_finish(int64_t *keep, const int64_t *num_keep, int64_t n, const void *prep,
+                            int64_t num_images, int64_t *counts_out, void *stream);
+
 /* ---- class-batched rotated NMS, fused ----------------------------------------
  * Replaces the whole body of the reference's multiclass_nms_rotated
  * (mmrotate/core/post_processing/bbox_nms_rotated.py:33-92, called from the eleven

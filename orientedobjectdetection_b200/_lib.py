@@ -18,6 +18,7 @@ SYMBOLS = (
     'rotgeo_eval_tpfp_workspace_bytes', 'rotgeo_eval_tpfp',
     'rotgeo_diff_iou_aligned',
     'rotgeo_nms_prepare_bytes', 'rotgeo_nms_prepare', 'rotgeo_nms_prepared',
+    'rotgeo_nms_batch_prepare_bytes', 'rotgeo_nms_batch_prepare', 'rotgeo_nms_batch_finish',
     'rotgeo_multiclass_nms_workspace_bytes', 'rotgeo_multiclass_nms',
 )
 ERR_RANGE = -4
@@ -78,6 +79,12 @@ def load():
     L.rotgeo_nms_prepare.restype = i32
     L.rotgeo_nms_prepared.argtypes = [vp, i64, i32, vp, vp, i32, vp, vp, i64, f32, vp, vp, vp, sz, vp]
     L.rotgeo_nms_prepared.restype = i32
+    L.rotgeo_nms_batch_prepare_bytes.argtypes = [i64, i64]
+    L.rotgeo_nms_batch_prepare_bytes.restype = sz
+    L.rotgeo_nms_batch_prepare.argtypes = [vp, i64, i32, vp, vp, vp, i64, vp, sz, vp, vp, i64, vp, vp]
+    L.rotgeo_nms_batch_prepare.restype = i32
+    L.rotgeo_nms_batch_finish.argtypes = [vp, vp, i64, vp, i64, vp, vp]
+    L.rotgeo_nms_batch_finish.restype = i32
     L.rotgeo_multiclass_nms_workspace_bytes.argtypes = [i64, i32]
     L.rotgeo_multiclass_nms_workspace_bytes.restype = sz
     L.rotgeo_multiclass_nms.argtypes = [vp, i32, vp, vp, i64, i32, f32, f32, i64, vp, vp, vp, vp, vp, sz, vp]

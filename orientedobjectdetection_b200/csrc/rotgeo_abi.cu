@@ -326,6 +326,44 @@ int rotgeo_nms_prepare(const float *boxes, int64_t n, int stride, const float *s
     return ROTGEO_OK;
 }
 
+size_t rotgeo_nms_batch_prepare_bytes(int64_t n, int64_t num_images) {
+    return rotgeo::nms_batch_prepare_bytes(n, num_images);
+}
+
+int rotgeo_nms_batch_prepare(const float *boxes, int64_t n, int stride, const float *scores,
+                             const int64_t *ids, const int64_t *image_sizes_host, int64_t num_images,
+                             void *prep, size_t prep_bytes, float *offsets_out, int64_t *seg_counts_host,
+                             int64_t seg_cap, int64_t *num_segments_host, void *stream) {
+    if (n <= 0 || n > 0x7fffffffLL || stride < 5 || num_images < 1 || num_images > 65536)
+        return fail(ROTGEO_ERR_ARG, "nms_batch_prepare: n=%lld stride=%d images=%lld", (long long)n, stride,
+                    (long long)num_images);
+    if (!boxes || !scores || !ids || !image_sizes_host || !prep || !offsets_out || !seg_counts_host ||
+        seg_cap < 1 || !num_segments_host)
+        return fail(ROTGEO_ERR_ARG, "nms_batch_prepare: null pointer");
+    for (int64_t g = 0; g < num_images; ++g)
+        if (image_sizes_host[g] < 0) return fail(ROTGEO_ERR_ARG, "nms_batch_prepare: negative image size");
+    if (!aligned16(prep) || prep_bytes < rotgeo::nms_batch_prepare_bytes(n, num_images))
+        return fail(ROTGEO_ERR_WORKSPACE, "nms_batch_prepare: buffer %zu < %zu bytes or misaligned", prep_bytes,
+                    rotgeo::nms_batch_prepare_bytes(n, num_images));
+    const int rc = rotgeo::nms_batch_prepare(boxes, n, stride, scores, ids, image_sizes_host, num_images, prep,
+                                             offsets_out, seg_counts_host, seg_cap, num_segments_host,
+                                             (cudaStream_t)stream);
+    if (rc == -1) return fail(ROTGEO_ERR_ARG, "nms_batch_prepare: image sizes do not add up to n");
+    if (rc == -4) return fail(ROTGEO_ERR_RANGE, "nms_batch_prepare: images x id range is 65536 or more");
+    if (rc == -5) return fail(ROTGEO_ERR_RANGE, "nms_batch_prepare: more than %lld segments", (long long)seg_cap);
+    if (rc) return cuda_fail("nms_batch_prepare");
+    return ROTGEO_OK;
+}
+
+int rotgeo_nms_batch_finish(int64_t *keep, const int64_t *num_keep, int64_t n, const void *prep,
+                            int64_t num_images, int64_t *counts_out, void *stream) {
+    if (n <= 0 || num_images < 1 || !keep || !num_keep || !prep || !counts_out)
+        return fail(ROTGEO_ERR_ARG, "nms_batch_finish: bad argument");
+    if (rotgeo::nms_batch_finish(keep, num_keep, n, prep, num_images, counts_out, (cudaStream_t)stream))
+        return cuda_fail("nms_batch_finish");
+    return ROTGEO_OK;
+}
+
 int rotgeo_nms_prepared(const float *boxes, int64_t n, int stride, const float *offsets,
                         const int64_t *seg_ids, int id_offsets, const void *prep,
                         const int64_t *seg_counts_host, int64_t num_segments, float iou_threshold,

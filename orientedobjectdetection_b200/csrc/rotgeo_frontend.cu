@@ -438,6 +438,228 @@ int nms_prepare(const float *boxes, int64_t n, int stride, const float *scores, 
     return 0;
 }
 
+
+// ============================================================================================
+// Batch of images front-end: what the reference does once per image around batched_nms
+// (mmrotate/models/dense_heads/oriented_rpn_head.py:275, rotated_rpn_head.py:414-426,515: a python
+// loop over the images of the batch, each with its own boxes.max(), offsets, sort and NMS) for
+// ALL images in one pass.  The images lie back to back in (boxes, scores, ids); a segment is one
+// (image, id); the centre offsets are mmcv.batched_nms's id * (max(cx,cy) + max(w,h) + 1) with the
+// maxima of the box's OWN image; the order the kept boxes are emitted in is image-major (score
+// order inside an image), so one more pass turns them into per-image lists:
+//
+//   batch_keys_kernel    32-bit score key + index, image of every box (16 bits), extremes of the
+//                        ids, per-image maxima (block-local reduction, then one atomic per block)
+//   cub radix sort       stable 32-bit pairs sort: global score order
+//   batch_segkey_kernel  16-bit segment key image * id_range + (id - min id) and the image key of
+//                        every entry of that order; per-box centre offsets
+//   cub radix sort x2    stable 16-bit sorts of the score order: segment-major and image-major
+//   cub run-length       sizes of the segments present
+//   batch_finish_kernel  (after the NMS) global kept index -> index inside its image + kept count
+//                        per image
+// ============================================================================================
+struct BatchExtra {
+    size_t off_starts, off_mxy, off_mwh, total;
+};
+static void batch_extra_layout(int64_t nimg, BatchExtra *e) {
+    size_t off = 0;
+    e->off_starts = off; off = align_up(off + (size_t)(nimg + 1) * 8, 256);
+    e->off_mxy = off;    off = align_up(off + (size_t)nimg * 4, 256);
+    e->off_mwh = off;    off = align_up(off + (size_t)nimg * 4, 256);
+    e->total = off;
+}
+
+size_t nms_batch_prepare_bytes(int64_t n, int64_t nimg) {
+    if (n <= 0 || nimg <= 0) return 0;
+    PrepLayout l;
+    prep_layout(n, &l);
+    BatchExtra e;
+    batch_extra_layout(nimg, &e);
+    return l.total_bytes + e.total;
+}
+
+// last image whose first row is <= i (images are contiguous row ranges, empty ones allowed)
+__device__ __forceinline__ int image_of_row(const int64_t *__restrict__ starts, int nimg, int64_t i) {
+    int lo = 0, hi = nimg - 1;
+    while (lo < hi) {
+        const int mid = (lo + hi + 1) >> 1;
+        if (starts[mid] <= i) lo = mid; else hi = mid - 1;
+    }
+    return lo;
+}
+
+__global__ void __launch_bounds__(256)
+batch_keys_kernel(const float *__restrict__ boxes, int stride, const float *__restrict__ scores,
+                  const int64_t *__restrict__ ids, int64_t n, const int64_t *__restrict__ starts, int nimg,
+                  uint32_t *__restrict__ keys, uint32_t *__restrict__ vals, uint16_t *__restrict__ imgkey,
+                  unsigned int *__restrict__ mxy, unsigned int *__restrict__ mwh, PrepHeader *__restrict__ hdr) {
+    __shared__ unsigned long long s_id[2];
+    __shared__ unsigned int s_max[2][2];   // [image - first image of the block][xy, wh]
+    __shared__ int s_img0;
+    const int tid = threadIdx.x;
+    if (tid < 2) { s_id[tid] = 0ull; s_max[tid][0] = 0u; s_max[tid][1] = 0u; }
+    if (tid == 0) s_img0 = image_of_row(starts, nimg, blockIdx.x * (int64_t)blockDim.x);
+    __syncthreads();
+    const int64_t i = blockIdx.x * (int64_t)blockDim.x + tid;
+    if (i < n) {
+        keys[i] = 0xffffffffu - ordered_bits(scores[i] + 0.0f);
+        vals[i] = (uint32_t)i;
+        int img = s_img0;
+        if (i >= starts[img + 1]) img = image_of_row(starts, nimg, i);
+        imgkey[i] = (uint16_t)img;
+        const unsigned long long u = id_image(ids[i]);
+        atomicMax(&s_id[0], u);
+        atomicMax(&s_id[1], ~u);
+        const float *b = boxes + i * stride;
+        const unsigned int xy = ordered_bits(fmaxf(b[0], b[1])), wh = ordered_bits(fmaxf(b[2], b[3]));
+        const int d = img - s_img0;
+        if (d < 2) {
+            atomicMax(&s_max[d][0], xy);
+            atomicMax(&s_max[d][1], wh);
+        } else {
+            atomicMax(mxy + img, xy);
+            atomicMax(mwh + img, wh);
+        }
+    }
+    __syncthreads();
+    if (tid == 0) {
+        atomicMax(&hdr->id_max_u, s_id[0]);
+        atomicMax(&hdr->id_min_inv_u, s_id[1]);
+    }
+    if (tid < 2 && s_max[tid][0] != 0u) {       // 0 = no box of that image in this block
+        atomicMax(mxy + s_img0 + tid, s_max[tid][0]);
+        atomicMax(mwh + s_img0 + tid, s_max[tid][1]);
+    }
+}
+
+__global__ void __launch_bounds__(256)
+batch_segkey_kernel(const int64_t *__restrict__ ids, const uint32_t *__restrict__ order,
+                    const uint16_t *__restrict__ imgkey, int64_t n, int nimg,
+                    const unsigned int *__restrict__ mxy, const unsigned int *__restrict__ mwh,
+                    uint16_t *__restrict__ segkey, uint16_t *__restrict__ imgkey_sorted,
+                    float *__restrict__ offsets_out, PrepHeader *hdr) {
+    const int64_t p = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    const unsigned long long lo = ~hdr->id_min_inv_u;
+    const unsigned long long range = hdr->id_max_u - lo + 1ull;
+    if (p == 0 && (range > 65536ull || range * (unsigned long long)nimg > 65536ull)) hdr->range_bad = 1;
+    if (p < n) {
+        // entry p of the score order
+        const uint32_t i = order[p];
+        const unsigned img = imgkey[i];
+        segkey[p] = (uint16_t)(img * range + (id_image(ids[i]) - lo));
+        imgkey_sorted[p] = (uint16_t)img;
+        // box p: id * (max(cx,cy) + max(w,h) + 1) with the maxima of its image, the float
+        // arithmetic of mmcv.ops.batched_nms (separate roundings, no fused multiply-add)
+        const unsigned im = imgkey[p];
+        const float m = __fadd_rn(ordered_float(mxy[im]), ordered_float(mwh[im]));
+        offsets_out[p] = __fmul_rn((float)ids[p], __fadd_rn(m, 1.0f));
+    }
+}
+
+// returns 0, -3 (CUDA), -4 (images x id range >= 2^16), -5 (more segments than seg_cap)
+int nms_batch_prepare(const float *boxes, int64_t n, int stride, const float *scores, const int64_t *ids,
+                      const int64_t *img_sizes_host, int64_t nimg, void *prep, float *offsets_out,
+                      int64_t *seg_counts_host, int64_t seg_cap, int64_t *num_segments_host,
+                      cudaStream_t stream) {
+    PrepLayout l;
+    prep_layout(n, &l);
+    BatchExtra x;
+    batch_extra_layout(nimg, &x);
+    char *ws = reinterpret_cast<char *>(prep);
+    char *xs = ws + l.total_bytes;
+    PrepHeader *hdr = reinterpret_cast<PrepHeader *>(ws + l.off_hdr);
+    uint32_t *keys = reinterpret_cast<uint32_t *>(ws + l.off_keys);
+    uint32_t *keys2 = reinterpret_cast<uint32_t *>(ws + l.off_keys2);
+    uint32_t *vals = reinterpret_cast<uint32_t *>(ws + l.off_vals);
+    uint32_t *order = reinterpret_cast<uint32_t *>(ws + l.off_order);           // image-major score order
+    uint32_t *score_order = reinterpret_cast<uint32_t *>(ws + l.off_runs_count);   // free until the run-length pass
+    uint16_t *imgkey = reinterpret_cast<uint16_t *>(ws + l.off_runs_unique);       // free until the run-length pass
+    uint16_t *imgkey_sorted = reinterpret_cast<uint16_t *>(ws + l.off_keys);       // keys are dead after the first sort
+    uint16_t *imgkey_sorted2 = reinterpret_cast<uint16_t *>(ws + l.off_keys2);     // so are the sorted keys
+    uint16_t *segkey = reinterpret_cast<uint16_t *>(ws + l.off_segkey);
+    uint16_t *segkey2 = reinterpret_cast<uint16_t *>(ws + l.off_segkey2);
+    uint32_t *seg_order = reinterpret_cast<uint32_t *>(ws + l.off_seg_order);
+    uint16_t *runs_unique = reinterpret_cast<uint16_t *>(ws + l.off_runs_unique);
+    int *runs_count = reinterpret_cast<int *>(ws + l.off_runs_count);
+    int64_t *starts = reinterpret_cast<int64_t *>(xs + x.off_starts);
+    unsigned int *mxy = reinterpret_cast<unsigned int *>(xs + x.off_mxy);
+    unsigned int *mwh = reinterpret_cast<unsigned int *>(xs + x.off_mwh);
+
+    std::vector<int64_t> st((size_t)nimg + 1, 0);
+    for (int64_t g = 0; g < nimg; ++g) st[(size_t)g + 1] = st[(size_t)g] + img_sizes_host[g];
+    if (st[(size_t)nimg] != n) return -1;
+    // pageable source: staged by the runtime before the call returns
+    if (cudaMemcpyAsync(starts, st.data(), st.size() * sizeof(int64_t), cudaMemcpyHostToDevice, stream) != cudaSuccess ||
+        cudaMemsetAsync(hdr, 0, sizeof(PrepHeader), stream) != cudaSuccess ||
+        cudaMemsetAsync(mxy, 0, x.total - x.off_mxy, stream) != cudaSuccess)
+        return -3;
+    const unsigned grid = (unsigned)((n + 255) / 256);
+    batch_keys_kernel<<<grid, 256, 0, stream>>>(boxes, stride, scores, ids, n, starts, (int)nimg, keys, vals,
+                                                imgkey, mxy, mwh, hdr);
+    if (cudaGetLastError() != cudaSuccess) return -3;
+    size_t cub_bytes = l.cub_bytes;
+    if (cub::DeviceRadixSort::SortPairs(ws + l.off_cub, cub_bytes, (const uint32_t *)keys, keys2,
+                                        (const uint32_t *)vals, score_order, (int)n, 0, 32, stream) != cudaSuccess)
+        return -3;
+    batch_segkey_kernel<<<grid, 256, 0, stream>>>(ids, score_order, imgkey, n, (int)nimg, mxy, mwh, segkey,
+                                                  imgkey_sorted, offsets_out, hdr);
+    if (cudaGetLastError() != cudaSuccess) return -3;
+    cub_bytes = l.cub_bytes;
+    if (cub::DeviceRadixSort::SortPairs(ws + l.off_cub, cub_bytes, (const uint16_t *)segkey, segkey2,
+                                        (const uint32_t *)score_order, seg_order, (int)n, 0, 16, stream) != cudaSuccess)
+        return -3;
+    int img_bits = 1;
+    while (img_bits < 16 && (1ll << img_bits) < nimg) ++img_bits;
+    cub_bytes = l.cub_bytes;
+    if (cub::DeviceRadixSort::SortPairs(ws + l.off_cub, cub_bytes, (const uint16_t *)imgkey_sorted, imgkey_sorted2,
+                                        (const uint32_t *)score_order, order, (int)n, 0, img_bits, stream) != cudaSuccess)
+        return -3;
+    cub_bytes = l.cub_bytes;
+    if (cub::DeviceRunLengthEncode::Encode(ws + l.off_cub, cub_bytes, (const uint16_t *)segkey2, runs_unique,
+                                           runs_count, &hdr->n_runs, (int)n, stream) != cudaSuccess)
+        return -3;
+    PrepHeader h;
+    const int64_t ncopy = n < seg_cap ? n : seg_cap;
+    std::vector<int> counts((size_t)ncopy);
+    if (cudaMemcpyAsync(&h, hdr, sizeof(PrepHeader), cudaMemcpyDeviceToHost, stream) != cudaSuccess ||
+        cudaMemcpyAsync(counts.data(), runs_count, (size_t)ncopy * sizeof(int), cudaMemcpyDeviceToHost,
+                        stream) != cudaSuccess ||
+        cudaStreamSynchronize(stream) != cudaSuccess)
+        return -3;
+    if (h.range_bad) return -4;
+    if (h.n_runs > seg_cap) return -5;
+    for (int r = 0; r < h.n_runs; ++r) seg_counts_host[r] = counts[(size_t)r];
+    *num_segments_host = h.n_runs;
+    return 0;
+}
+
+__global__ void __launch_bounds__(256)
+batch_finish_kernel(int64_t *__restrict__ keep, const int64_t *__restrict__ num_keep, const int64_t *__restrict__ starts,
+                    int nimg, unsigned long long *__restrict__ counts) {
+    const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= *num_keep) return;
+    const int64_t gidx = keep[i];
+    const int img = image_of_row(starts, nimg, gidx);
+    keep[i] = gidx - starts[img];
+    // kept boxes are image-major: most of a warp counts for the same image
+    const unsigned peers = __match_any_sync(__activemask(), img);
+    if ((int)(threadIdx.x & 31) == __ffs(peers) - 1) atomicAdd(counts + img, (unsigned long long)__popc(peers));
+}
+
+int nms_batch_finish(int64_t *keep, const int64_t *num_keep_dev, int64_t n, const void *prep, int64_t nimg,
+                     int64_t *counts_out_dev, cudaStream_t stream) {
+    PrepLayout l;
+    prep_layout(n, &l);
+    BatchExtra x;
+    batch_extra_layout(nimg, &x);
+    const char *xs = reinterpret_cast<const char *>(prep) + l.total_bytes;
+    const int64_t *starts = reinterpret_cast<const int64_t *>(xs + x.off_starts);
+    if (cudaMemsetAsync(counts_out_dev, 0, (size_t)nimg * sizeof(int64_t), stream) != cudaSuccess) return -3;
+    batch_finish_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(
+        keep, num_keep_dev, starts, (int)nimg, reinterpret_cast<unsigned long long *>(counts_out_dev));
+    return cudaGetLastError() == cudaSuccess ? 0 : -3;
+}
+
 int launch_nms_prepared(const float *boxes, int64_t n, int stride, const float *offsets,
                         const int64_t *offset_ids, bool segmented, const void *prep, const NmsPlan &plan,
                         const NmsSegment *segs_dev, float thr, void *packed, uint64_t *mask,

@@ -151,6 +151,13 @@ int launch_nms(const NmsPlan &plan, const void *packed, const NmsSegment *segmen
 
 // generic front-end (rotgeo_frontend.cu)
 size_t nms_prepare_bytes(int64_t n);
+size_t nms_batch_prepare_bytes(int64_t n, int64_t nimg);
+int nms_batch_prepare(const float *boxes, int64_t n, int stride, const float *scores, const int64_t *ids,
+                      const int64_t *img_sizes_host, int64_t nimg, void *prep, float *offsets_out,
+                      int64_t *seg_counts_host, int64_t seg_cap, int64_t *num_segments_host,
+                      cudaStream_t stream);
+int nms_batch_finish(int64_t *keep, const int64_t *num_keep_dev, int64_t n, const void *prep, int64_t nimg,
+                     int64_t *counts_out_dev, cudaStream_t stream);
 int nms_prepare(const float *boxes, int64_t n, int stride, const float *scores, const int64_t *ids,
                 void *prep, int64_t *seg_counts_host, int64_t seg_cap, int64_t *num_segments_host,
                 cudaStream_t stream);

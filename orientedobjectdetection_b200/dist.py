@@ -118,7 +118,6 @@ def nms_images(images, iou_threshold, max_per_img=-1, keep_fn=None):
     keep tensor per image (indices into that image's boxes, score-descending,
     cut to ``max_per_img``), identical to calling ``ops.batched_nms`` per image.
     """
-    keep_fn = keep_fn or ops._nms_keep
     if not images:
         return []
     sizes = [int(b.shape[0]) for b, _, _ in images]
@@ -128,6 +127,15 @@ def nms_images(images, iou_threshold, max_per_img=-1, keep_fn=None):
     boxes = torch.cat([b for b, _, _ in images], dim=0)
     scores = torch.cat([s for _, s, _ in images], dim=0)
     ids = torch.cat([i.to(torch.int64) for _, _, i in images], dim=0)
+    if keep_fn is None:
+        # the product path: offsets, orders, NMS and the split into images all on the device
+        # (csrc/rotgeo_frontend.cu "batch of images"); None = ids too spread out for it
+        got = ops._nms_keep_images(boxes, scores, ids, sizes, iou_threshold)
+        if got is not None:
+            keep, counts = got
+            out = list(torch.split(keep.to(dev), counts))
+            return [k[:max_per_img] for k in out] if max_per_img > 0 else out
+        keep_fn = ops._nms_keep
     nimg = len(images)
     total = sum(sizes)
     sizes_t = torch.tensor(sizes, dtype=torch.int64)

@@ -151,6 +151,58 @@ def _nms_keep(boxes, scores, iou_threshold, seg_ids=None, offsets=None, id_offse
     return keep[:k]
 
 
+def _nms_keep_images(boxes, scores, ids, sizes, iou_threshold):
+    """Greedy rotated NMS of several images stored back to back (image g owns
+    ``sizes[g]`` consecutive rows), one segment per (image, id), with
+    mmcv.ops.batched_nms's id offsets computed per image on the device.
+
+    Returns ``(keep, counts)``: ``keep`` (device int64) holds, image after image,
+    the kept rows as indices INSIDE their image in descending score order;
+    ``counts`` (python list) the number kept per image.  ``None`` when the
+    (image, id) pairs do not fit 16-bit segment keys (callers use the generic
+    path).  Three C-ABI calls (rotgeo_nms_batch_prepare: sorts + the segment
+    sizes, one sync; rotgeo_nms_prepared: pack + mask + resolve;
+    rotgeo_nms_batch_finish: per-image indices and counts) and one read of the
+    counts."""
+    dev = _cuda_device(boxes, scores)
+    n = boxes.size(0)
+    nimg = len(sizes)
+    b = _rows_f32(boxes, dev)
+    s = scores.detach().to(device=dev, dtype=torch.float32).reshape(-1).contiguous()
+    seg = ids.detach().to(device=dev, dtype=torch.int64).reshape(-1).contiguous()
+    L = _lib.load()
+    with torch.cuda.device(dev):
+        stream = _stream(dev)
+        sizes_h = np.ascontiguousarray(sizes, dtype=np.int64)
+        pbytes = L.rotgeo_nms_batch_prepare_bytes(n, nimg)
+        prep = torch.empty(pbytes, dtype=torch.uint8, device=dev)
+        offsets = torch.empty(n, dtype=torch.float32, device=dev)
+        cap = min(n, _SEG_CAP)
+        counts = np.empty(cap, dtype=np.int64)
+        nseg = ctypes.c_int64(0)
+        rc = L.rotgeo_nms_batch_prepare(b.data_ptr(), n, b.stride(0), s.data_ptr(), seg.data_ptr(),
+                                        sizes_h.ctypes.data, nimg, prep.data_ptr(), pbytes,
+                                        offsets.data_ptr(), counts.ctypes.data, cap, ctypes.byref(nseg), stream)
+        if rc == _lib.ERR_RANGE:
+            return None
+        _lib.check(rc, 'rotgeo_nms_batch_prepare')
+        nseg = nseg.value
+        seg_off = np.zeros(nseg + 1, dtype=np.int64)
+        np.cumsum(counts[:nseg], out=seg_off[1:])
+        nbytes = L.rotgeo_nms_workspace_bytes(n, seg_off.ctypes.data, nseg)
+        ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+        keep = torch.empty(n, dtype=torch.int64, device=dev)
+        tail = torch.empty(nimg + 1, dtype=torch.int64, device=dev)     # [kept per image ..., kept in all]
+        _lib.check(L.rotgeo_nms_prepared(b.data_ptr(), n, b.stride(0), offsets.data_ptr(), seg.data_ptr(), 0,
+                                         prep.data_ptr(), counts.ctypes.data, nseg, float(iou_threshold),
+                                         keep.data_ptr(), tail.data_ptr() + 8 * nimg, ws.data_ptr(), nbytes,
+                                         stream), 'rotgeo_nms_prepared')
+        _lib.check(L.rotgeo_nms_batch_finish(keep.data_ptr(), tail.data_ptr() + 8 * nimg, n, prep.data_ptr(),
+                                             nimg, tail.data_ptr(), stream), 'rotgeo_nms_batch_finish')
+        per_img = tail.tolist()        # the one sync after the launches: sizes the outputs
+    return keep[:per_img[-1]], per_img[:-1]
+
+
 def _nms_keep_split(b, s, iou_threshold, seg, offsets, id_offsets):
     """segment ids too spread out / too many segments for one call: renumber them
     densely (torch.unique) and run chunks of _SEG_CAP segments; the centre offsets

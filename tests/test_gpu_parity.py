@@ -363,6 +363,54 @@ def test_nms_images_c4_batch_vs_per_image_calls():
         assert g.cpu().tolist() == wk[:500].tolist()
 
 
+def test_nms_images_fused_batch_edge_cases():
+    """The device-side batch front-end (rotgeo_nms_batch_prepare / _finish) against the
+    per-image oracle: empty images first / in the middle / last, a one-box image, images whose
+    ids use different ranges, negative ids, no cut; and ids too spread out for 16-bit segment
+    keys, which must take the generic path and give the same lists."""
+    from orientedobjectdetection_b200 import dist as rdist, ops
+    empty = (np.zeros((0, 5), np.float32), np.zeros(0, np.float32), np.zeros(0, np.int64))
+    imgs = [empty]
+    for s in range(6):
+        b, sc, i = synth.c4_rpn_image(seed=10 + s, per_level=120 + 70 * s, levels=3 + s % 3)
+        i = i.astype(np.int64) + (0, 7, -3, 100, 0, 2)[s]      # per-image id ranges differ
+        imgs.append((b, sc, i))
+        if s == 2:
+            imgs.append(empty)
+    one = synth.c4_rpn_image(seed=99, per_level=1, levels=1)
+    imgs.append(one)
+    imgs.append(empty)
+    dev_imgs = [(_cuda(b), _cuda(s), torch.from_numpy(np.asarray(i, np.int64)).cuda()) for b, s, i in imgs]
+    for cut in (-1, 150):
+        got = rdist.nms_images(dev_imgs, 0.5, cut)
+        assert len(got) == len(imgs)
+        for (b, s, i), g in zip(imgs, got):
+            if b.shape[0] == 0:
+                assert g.numel() == 0
+                continue
+            _, wk = ref_api.batched_nms_rotated(torch.from_numpy(b), torch.from_numpy(s),
+                                                torch.from_numpy(np.asarray(i, np.int64)), 0.5)
+            want = wk.tolist() if cut < 0 else wk[:cut].tolist()
+            assert g.cpu().tolist() == want
+    # ids spanning more than 65536 / images values: rotgeo_nms_batch_prepare reports the range,
+    # the seam falls back to the generic front-end
+    wide = [(b, s, torch.where(i % 2 == 0, i, i + 40000)) for b, s, i in dev_imgs]
+    assert ops._nms_keep_images(torch.cat([b for b, _, _ in wide]), torch.cat([s for _, s, _ in wide]),
+                                torch.cat([i for _, _, i in wide]), [int(b.shape[0]) for b, _, _ in wide],
+                                0.5) is None
+    got_w = rdist.nms_images(wide, 0.5, -1)
+    gen_w = rdist.nms_images(wide, 0.5, -1, keep_fn=ops._nms_keep)
+    for a, b in zip(got_w, gen_w):
+        assert a.cpu().tolist() == b.cpu().tolist()
+    # and the fused path equals the generic one on the full C4 shape of two images
+    big = [tuple(_cuda(x) if x.dtype != np.int64 else torch.from_numpy(x).cuda() for x in synth.c4_rpn_image(seed=s))
+           for s in range(2)]
+    fused = rdist.nms_images(big, 0.8, 2000)
+    generic = rdist.nms_images(big, 0.8, 2000, keep_fn=ops._nms_keep)
+    for a, b in zip(fused, generic):
+        assert a.cpu().tolist() == b.cpu().tolist()
+
+
 # ---------------------------------------------------------------- fused assigner reductions
 def _assign_inputs(seed, num_gts, num_boxes, extent):
     gts = synth.le90_boxes(num_gts, 700 + seed, extent)
