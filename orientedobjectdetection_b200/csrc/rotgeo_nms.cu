@@ -660,12 +660,17 @@ nms_resolve_kernel(const ResolveArgs a) {
         if (sg.len <= 0 || nch > kLocalChunks) continue;
         for (int i = tid; i < 2 * nch; i += kResThreads) s_kr[i] = 0ull;
         __syncthreads();
+        // No barrier between the passes: both bitmaps only gain bits and any evaluation order
+        // reaches the greedy result, so every warp simply re-evaluates its own chunks until they
+        // are decided; a decision is visible to the warps behind it a shared-memory round trip
+        // later instead of one __syncthreads round later (a chain over c chunks needed c rounds).
         for (;;) {
             bool left = false;
             for (int c = warp; c < nch; c += kResWarps)
                 left |= resolve_chunk<true, true>(a, sg, c, s_kr, s_kr, lane);
-            if (!__syncthreads_or(left)) break;
+            if (!left) break;
         }
+        __syncthreads();
         for (int c = warp; c < nch; c += kResWarps) write_flags(a, sg, c, s_kr[2 * c], lane);
         __syncthreads();
     }
