@@ -307,6 +307,8 @@ def run_rotgeo(args, rank, world, local_rank):
     torch.cuda.set_device(local_rank)
     dev = torch.device('cuda', local_rank)
     if world > 1:
+        # stdout carries the one JSON line: NCCL's own messages (NCCL_DEBUG=VERSION on some boxes) go to stderr
+        os.environ.setdefault('NCCL_DEBUG_FILE', '/dev/stderr')
         dist.init_process_group('nccl', device_id=dev)
     L = _lib.load()
 
@@ -343,6 +345,16 @@ def run_rotgeo(args, rank, world, local_rank):
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
+    # The timed region is ~1 ms long and nvidia-smi samples every 100 ms: run the same step
+    # untimed for 0.5 s first (all ranks, so that they reach the timed region together), which
+    # puts samples taken under this very load on both sides of the timed region.
+    t_load = time.perf_counter()
+    while time.perf_counter() - t_load < 0.5:
+        for _ in range(50):
+            step()
+        torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
     torch.cuda.synchronize()
     ms = timed_steps(torch, step, args.steps, flush, None)
     torch.cuda.synchronize()
