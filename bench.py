@@ -134,7 +134,7 @@ def run_reference(args, rank):
     ms = 1e3 * float(np.mean(times))
     val = rows * N_COLS / (ms * 1e-3) / 1e9
     sample = '%d-row slice x %d columns of the 8192x8192 C3 matrix per step' % (rows, N_COLS)
-    print(json.dumps({
+    emit({
         'impl': 'reference', 'metric': 'rotated_iou_gpairs_per_s', 'value': val, 'unit': 'Gpairs/s',
         'n_gpus': args.gpus, 'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': ms,
         'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32',
@@ -144,7 +144,7 @@ def run_reference(args, rank):
         'cpu_baseline': {'value': val, 'unit': 'Gpairs/s', 'cores': threads, 'kind': 'port',
                          'sample': sample},
         'e2e': {'value': val, 'unit': 'Gpairs/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
-    }))
+    })
 
 
 def timed_steps(torch, fn, steps, flush, stream_sync):
@@ -447,13 +447,30 @@ def run_rotgeo(args, rank, world, local_rank):
             'single_thread': {'value': v1, 'cores': 1,
                               'sample': 'the whole 8192x8192 C3 block, %d repetition(s), %.1f s' % (r1, t1)}}
     if rank == 0:
-        print(json.dumps(line))
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 
 
+_JSON_OUT = None
+
+
+def emit(obj):
+    """the one JSON line, on the process's ORIGINAL stdout"""
+    out = _JSON_OUT or sys.stdout
+    out.write(json.dumps(obj) + '\n')
+    out.flush()
+
+
 def main():
+    global _JSON_OUT
     args = parse()
+    # stdout carries exactly one JSON line.  Libraries write there too (NCCL prints its version
+    # banner to stdout when the box exports NCCL_DEBUG=VERSION, and NCCL_DEBUG_FILE does not move
+    # it): keep the original stdout for the JSON line and point fd 1 at stderr for everything else.
+    sys.stdout.flush()
+    _JSON_OUT = os.fdopen(os.dup(1), 'w')
+    os.dup2(2, 1)
     rank = int(os.environ.get('RANK', 0))
     world = int(os.environ.get('WORLD_SIZE', 1))
     local_rank = int(os.environ.get('LOCAL_RANK', 0))
