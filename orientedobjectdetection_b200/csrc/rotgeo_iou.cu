@@ -30,7 +30,8 @@
 #include "rotgeo_internal.h"
 
 #ifndef ROTGEO_ABLATE
-#define ROTGEO_ABLATE 0   // probe builds (tools/ablate_iou.py): 1 no zero stores, 2 no cull, 4 no exact pass, 8 no final drain
+#define ROTGEO_ABLATE 0   // probe builds (tools/ablate_iou.py): 1 no zero stores, 2 no cull, 4 no exact pass, 8 no final drain,
+                          // 16 no value stores, 32 cull data staged by plain loads of warp 0 instead of TMA bulk copies, 64 streaming zero stores
 #endif
 
 namespace rotgeo {
@@ -131,6 +132,23 @@ iou_tile_kernel(const IouArgs g) {
         tma_load_1d(sm.rowr[s], g.ar + rb, kTileRows * sizeof(uint32_t), &sm.full[s]);
         tma_load_1d(sm.tab[s], g.bt + cblk * kTableWords, kTableXYWords * sizeof(uint32_t), &sm.full[s]);
     };
+#if ROTGEO_ABLATE & 32
+    // A/B probe: the same bytes through registers (ld.global + st.shared by the 32 lanes of
+    // warp 0), then one plain arrival on the full barrier
+    auto copy_masks_plain = [&](unsigned k, unsigned t) {   // warp 0, all lanes
+        const int s = k % kStages;
+        const int64_t rb = (int64_t)(t / g.tiles_x) * kTileRows;
+        const int64_t cblk = (int64_t)(t % g.tiles_x);
+        const uint4 *src_t = reinterpret_cast<const uint4 *>(g.bt + cblk * kTableWords);
+        uint4 *dst_t = reinterpret_cast<uint4 *>(sm.tab[s]);
+        for (int i = lane; i < kTableXYWords / 4; i += 32) dst_t[i] = __ldg(src_t + i);
+        const uint4 *src_r = reinterpret_cast<const uint4 *>(g.ar + rb);
+        uint4 *dst_r = reinterpret_cast<uint4 *>(sm.rowr[s]);
+        for (int i = lane; i < kTileRows / 4; i += 32) dst_r[i] = __ldg(src_r + i);
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&sm.full[s]);
+    };
+#endif
     // the answer for my k-th tile (k >= 1) lives in slot (k-1) % kRespSlots, use (k-1) / kRespSlots
     auto ask_next = [&](unsigned k) {                  // thread 0: who is my k-th tile?
         const int slot = (k - 1) % kRespSlots;
@@ -183,7 +201,13 @@ iou_tile_kernel(const IouArgs g) {
             if (rows_here == kTileRows && cols_here == 4) {   // interior tile: 8 plain stores
 #pragma unroll
                 for (int it = 0; it < kRowsPerWarp; ++it) {
+#if ROTGEO_ABLATE & 64   // probe: streaming (evict-first) stores.  Same time on sparse scenes, but a value
+                         // that lands after its zero line has left L2 costs a DRAM read-modify-write:
+                         // dense C3 (extent 1024) 60 -> 82 us (profiles/r01_iou_ablation_exact.txt)
                     __stcs(reinterpret_cast<float4 *>(dst), make_float4(0.f, 0.f, 0.f, 0.f));
+#else
+                    *reinterpret_cast<float4 *>(dst) = make_float4(0.f, 0.f, 0.f, 0.f);
+#endif
                     dst += step;
                 }
             } else if (cols_here > 0) {
@@ -217,10 +241,17 @@ iou_tile_kernel(const IouArgs g) {
         }
     }
     pdl_wait();
+#if ROTGEO_ABLATE & 32
+    if (warp == 0) {
+        copy_masks_plain(0, t);
+        if (lane == 0 && kPre == 0) ask_next(1);
+    }
+#else
     if (tid == 0) {
         issue_masks(0, t);
         if (kPre == 0) ask_next(1);
     }
+#endif
 
     for (unsigned k = 0;; ++k) {
         const int s = k % kStages;
@@ -229,6 +260,27 @@ iou_tile_kernel(const IouArgs g) {
 
         // ---- scheduler (thread 0): learn tile k+1, prefetch its masks, ask for k+2 ---
         // (the answer was requested a whole tile ago, so this wait is short)
+#if ROTGEO_ABLATE & 32
+        if (warp == 0) {
+            const unsigned kn = k + 1;
+            unsigned tn = 0;
+            int ok = 0;
+            if (lane == 0) {
+                mbar_wait(&sm.sched[k % kRespSlots], (k / kRespSlots) & 1);
+                ok = clc_decode(&sm.resp[k % kRespSlots], tn) ? 1 : 0;
+                if (ok && kn >= kStages) mbar_wait(&sm.empty[kn % kStages], ((kn / kStages) - 1) & 1);
+            }
+            ok = __shfl_sync(0xffffffffu, ok, 0);
+            tn = __shfl_sync(0xffffffffu, tn, 0);
+            if (ok) {
+                copy_masks_plain(kn, tn);
+                if (lane == 0) {
+                    fence_proxy_async_smem();
+                    if (k + 2 > (unsigned)kPre) ask_next(k + 2);
+                }
+            }
+        }
+#else
         if (tid == 0) {
             const unsigned kn = k + 1;
             mbar_wait(&sm.sched[k % kRespSlots], (k / kRespSlots) & 1);
@@ -243,6 +295,7 @@ iou_tile_kernel(const IouArgs g) {
                 if (k + 2 > (unsigned)kPre) ask_next(k + 2);   // the first kPre requests went out in the prologue
             }
         }
+#endif
 
         // ---- cull level 1: which of my 32 columns can my row touch? ------------------
         // (padding rows have empty ranges, padding columns are in no table entry)

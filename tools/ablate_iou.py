@@ -7,7 +7,9 @@ import ctypes, os, subprocess, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 OUT = os.path.join(ROOT, 'tools', '_ablate')
-VARIANTS = {'full': 0, 'no_exact': 4, 'no_value_store': 16, 'stores_only': 6}
+VARIANTS = {'full': 0, 'plain_loads_no_tma': 32, 'no_exact': 4, 'no_value_store': 16, 'zeros_streaming_stores': 64}
+if os.environ.get('ABLATE_ONLY'):
+    VARIANTS = {k: v for k, v in VARIANTS.items() if k in os.environ['ABLATE_ONLY'].split(',')}
 if os.environ.get('ABLATE_REGS'):
     VARIANTS = {'full_r%s' % r: (0, r) for r in os.environ['ABLATE_REGS'].split(',')}
 EXTRA = [a for a in sys.argv[2:]]
@@ -23,7 +25,7 @@ def build():
         so = os.path.join(OUT, 'librotgeo_%s.so' % name)
         cmd = ['/usr/local/cuda/bin/nvcc', '-gencode', 'arch=compute_100a,code=sm_100a', '-O3', '-lineinfo', '-std=c++17',
                '-DROTGEO_ABLATE=%d' % flag, '-Xcompiler', '-fPIC', '-shared', '-ccbin', '/usr/bin/g++', '-o', so] + EXTRA + extra + \
-              [os.path.join(csrc, f) for f in ('rotgeo_abi.cu', 'rotgeo_pack.cu', 'rotgeo_iou.cu', 'rotgeo_nms.cu')]
+              sorted(os.path.join(csrc, f) for f in os.listdir(csrc) if f.endswith('.cu'))
         subprocess.check_call(cmd)
     print('built', sorted(os.listdir(OUT)))
 
@@ -56,7 +58,10 @@ def run():
                 assert L.rotgeo_iou_pairwise_packed(pk1, N, pk2, N, 0, out.data_ptr(), N, st) == 0
                 e1.record(); e1.synchronize()
                 if i >= 3: ts.append(e0.elapsed_time(e1) * 1e3)
-            print('extent %5.0f  %-16s median %.1f us  best %.1f us' % (extent, name, float(np.median(ts)), min(ts)), flush=True)
+            if name == 'full':
+                want = out.clone()
+            same = bool(torch.equal(out, want)) if name.startswith('plain') else None
+            print('extent %5.0f  %-20s same_as_full=%s  median %.1f us  best %.1f us' % (extent, name, same, float(np.median(ts)), min(ts)), flush=True)
 
 if __name__ == '__main__':
     build() if sys.argv[1] == 'build' else run()
