@@ -208,6 +208,13 @@ def secondary_nms(torch, rg, synth, reps=5):
     t = best(lambda: rg.rbbox_overlaps_max(a3d, b3d))
     res['c3_rowcol_max_8192x8192_fused'] = {'pairs': a3.shape[0] * b3.shape[0], 'ms': 1e3 * t,
                                             'gpairs_per_s': a3.shape[0] * b3.shape[0] / t / 1e9}
+    # C3, dense variant (extent 1024: 2.6 % of the pairs overlap, the clipper matters), matrix out
+    a4, b4 = synth.c3_iou(0, extent=1024.0)
+    a4d, b4d = torch.from_numpy(a4).cuda(), torch.from_numpy(b4).cuda()
+    t = best(lambda: rg.rbbox_overlaps(a4d, b4d))
+    res['c3_dense_extent1024_8192x8192_python_call'] = {'pairs': a4.shape[0] * b4.shape[0], 'ms': 1e3 * t,
+                                                        'gpairs_per_s': a4.shape[0] * b4.shape[0] / t / 1e9}
+    del a4d, b4d
     anchors = torch.from_numpy(synth.le90_boxes(196416, 5, 1024.0)).cuda()
     gtb = torch.from_numpy(synth.le90_boxes(100, 6, 1024.0)).cuda()
     asg = rg.MaxIoUAssigner(0.5, 0.4, min_pos_iou=0.0)
