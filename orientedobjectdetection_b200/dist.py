@@ -174,26 +174,37 @@ def nms_images_sharded(images, iou_threshold, max_per_img=-1, group=None, keep_f
     mine = [i for i in range(len(images)) if owner[i] == rank]
     keeps = nms_images([images[i] for i in mine], iou_threshold, max_per_img, keep_fn)
     cdev = _comm_device(group)
-    # one flat int64 message per rank: [len_0, idx..., len_1, idx..., ...] in `mine` order
-    parts = []
-    for k in keeps:
-        parts.append(torch.tensor([k.numel()], dtype=torch.int64, device=cdev))
-        parts.append(k.to(cdev))
-    flat = torch.cat(parts) if parts else torch.zeros(0, dtype=torch.int64, device=cdev)
-    cap = 0
+    # ONE collective and ONE device->host read: every rank sends a fixed-size int64 message
+    # [kept count of each of its images (H slots) | kept indices, image after image]; the
+    # headers of all ranks come to the host in one copy, the index lists stay on the device
+    # and are handed out as views.
+    idx_of = [[i for i in range(len(images)) if owner[i] == r] for r in range(world)]
+    H = max(max(len(v) for v in idx_of), 1)
+    cap = 1
     for r in range(world):
-        idx = [i for i in range(len(images)) if owner[i] == r]
         per = [min(int(images[i][0].shape[0]), max_per_img) if max_per_img > 0
-               else int(images[i][0].shape[0]) for i in idx]
-        cap = max(cap, sum(per) + len(idx))
-    gathered = _all_gather_padded(flat, max(cap, 1), group)
+               else int(images[i][0].shape[0]) for i in idx_of[r]]
+        cap = max(cap, sum(per))
+    msg = torch.zeros(H + cap, dtype=torch.int64, device=cdev)
+    counts = [int(k.numel()) for k in keeps]
+    if counts:
+        msg[:len(counts)] = torch.tensor(counts, dtype=torch.int64)
+        total = sum(counts)
+        if total:
+            msg[H:H + total] = torch.cat([k.to(cdev) for k in keeps])
+    out_all = torch.empty(world * (H + cap), dtype=torch.int64, device=cdev)
+    dist.all_gather_into_tensor(out_all, msg, group=group)
+    out_all = out_all.view(world, H + cap)
+    heads = out_all[:, :H].cpu().tolist()
     out = [None] * len(images)
     for r in range(world):
-        buf, pos = gathered[r].cpu(), 0
-        for i in (j for j in range(len(images)) if owner[j] == r):
-            c = int(buf[pos])
-            out[i] = buf[pos + 1:pos + 1 + c].to(images[i][0].device)
-            pos += 1 + c
+        nr = len(idx_of[r])
+        if nr == 0:
+            continue
+        cr = heads[r][:nr]
+        parts = torch.split(out_all[r, H:H + sum(cr)], cr)
+        for i, part in zip(idx_of[r], parts):
+            out[i] = part.to(images[i][0].device)
     return out
 
 
