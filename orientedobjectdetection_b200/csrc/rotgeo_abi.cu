@@ -33,7 +33,7 @@ inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
 extern "C" {
 
-int rotgeo_version(void) { return 1000; }
+int rotgeo_version(void) { return 1001; }   // 1001: + rotgeo_nms_batch_prepare / _finish
 
 const char *rotgeo_last_error(void) { return g_err; }
 

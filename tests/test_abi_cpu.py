@@ -28,7 +28,7 @@ def test_exports_match_header(lib):
     raw = ctypes.CDLL(_lib.SO_PATH)
     for sym in declared:
         assert getattr(raw, sym) is not None
-    assert lib.rotgeo_version() == 1000
+    assert lib.rotgeo_version() == 1001
 
 
 def test_size_queries_without_gpu(lib):
