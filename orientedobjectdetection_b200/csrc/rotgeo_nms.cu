@@ -559,7 +559,9 @@ __device__ bool resolve_chunk(const ResolveArgs &a, const NmsSegment &sg, int c,
             const unsigned long long *srow = S + q * a.sc.sum_words;
             const int kmax = (int)(row >> 13);           // summary words that can hold a bit: column blocks 0 .. row / 128
             for (int k = 0; k <= kmax && !exK[p]; ++k) {
-                unsigned long long sb = __ldg(srow + k);
+                // (plain loads: this row's summary word is rewritten below)
+                const unsigned long long sb0 = __ldcg(srow + k);
+                unsigned long long sb = sb0, live = sb0;
                 while (sb != 0ull && !exK[p]) {
                     // four column blocks at a time: their mask loads are in flight together
                     int J[4];
@@ -575,6 +577,7 @@ __device__ bool resolve_chunk(const ResolveArgs &a, const NmsSegment &sg, int c,
                                          : make_ulonglong2(0ull, 0ull);
 #pragma unroll
                     for (int t = 0; t < 4; ++t) {
+                        bool dead = J[t] >= 0;       // every neighbour in this block is removed
 #pragma unroll
                         for (int h = 0; h < 2; ++h) {
                             const unsigned long long mv = h ? m[t].y : m[t].x;
@@ -584,12 +587,19 @@ __device__ bool resolve_chunk(const ResolveArgs &a, const NmsSegment &sg, int c,
                                 const ulonglong2 o = kr_load<RD_SMEM>(kr_others + 2 * w);
                                 if (mv & o.x) exK[p] = true;
                                 if (mv & ~(o.x | o.y)) exU[p] = true;
+                                if (mv & ~o.y) dead = false;
                             } else if (w == c) {
                                 D[p] = mv;                    // earlier boxes of this chunk
+                                dead = false;
                             }
                         }
+                        // removed boxes stay removed: this block can never again decide the row,
+                        // later rounds need not load it (dense scenes: a row has neighbours in a
+                        // hundred blocks and used to re-walk all of them every round)
+                        if (!WR_SMEM && dead) live &= ~(1ull << (J[t] & 63));
                     }
                 }
+                if (!WR_SMEM && live != sb0 && !exK[p]) __stcg(const_cast<unsigned long long *>(srow + k), live);
             }
         }
     }
@@ -679,33 +689,20 @@ nms_resolve_kernel(const ResolveArgs a) {
     if (a.has_large) {
         // consecutive chunks go to different CTAs: a mid-size segment is spread over every SM
         const int64_t gwarp = (int64_t)blockIdx.x + (int64_t)G * warp, nwarps = (int64_t)G * kResWarps;
-        volatile unsigned int *pend = a.sc.sync + 2;
-        for (unsigned int round = 0;; ++round) {
-            // slot (round + 1) % 3 was last read after the barrier of round - 2; every CTA has passed
-            // the barrier of round - 1 since, so it can be cleared for the next round now
-            if (blockIdx.x == 0 && tid == 0) pend[(round + 1) % 3] = 0u;
-            if (a.snapshot) {
-                // every row test below reads the state of earlier chunks: from shared memory
-                // instead of one L2 round trip each
-                for (int64_t i = tid; i < a.chunks; i += kResThreads) {
-                    const ulonglong2 v = ldcg_u64x2(a.sc.kr + 2 * i);
-                    s_kr[2 * i] = v.x;
-                    s_kr[2 * i + 1] = v.y;
-                }
-                __syncthreads();
-            }
+        // No rounds and no grid barrier here either: every warp re-evaluates its own chunks until
+        // they are decided, reading the state of earlier chunks through L2 (ld.cg / st.cg).  All
+        // CTAs are co-resident (cooperative launch), the bitmaps only gain bits, so this ends with
+        // the greedy result; a decision travels one L2 round trip instead of one grid-barrier
+        // round (~10 us with 148 CTAs) to the chunks that wait for it.
+        for (;;) {
             bool left = false;
             for (int64_t gw = gwarp; gw < a.chunks; gw += nwarps) {
                 const NmsSegment &sg = a.segs[segment_of_slot(a.segs, a.nseg, gw * 64)];
                 const int64_t c = gw - (sg.pstart >> 6), w0 = 2 * (sg.pstart >> 6);
                 if (sg.row_blocks <= kLocalChunks || c >= sg.row_blocks) continue;
-                left |= a.snapshot
-                    ? resolve_chunk<true, false>(a, sg, (int)c, s_kr + w0, a.sc.kr + w0, lane)
-                    : resolve_chunk<false, false>(a, sg, (int)c, a.sc.kr + w0, a.sc.kr + w0, lane);
+                left |= resolve_chunk<false, false>(a, sg, (int)c, a.sc.kr + w0, a.sc.kr + w0, lane);
             }
-            if (left && lane == 0) pend[round % 3] = 1u;
-            grid_barrier(a.sc.sync, G);
-            if (pend[round % 3] == 0u) break;
+            if (!left) break;
         }
         for (int64_t gw = gwarp; gw < a.chunks; gw += nwarps) {
             const NmsSegment &sg = a.segs[segment_of_slot(a.segs, a.nseg, gw * 64)];
