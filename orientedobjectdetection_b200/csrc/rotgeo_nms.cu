@@ -22,14 +22,14 @@
 //                       box is removed as soon as one earlier neighbour is kept, and kept
 //                       as soon as all earlier neighbours are removed — exactly the
 //                       greedy result, whatever the evaluation order.  One cooperative
-//                       persistent grid; a round gives every 64-box chunk that still has
-//                       undecided boxes to one warp, which walks the set summary bits of
-//                       each undecided row (16 B of mask per bit), tests them against
-//                       the bitmaps, and settles the chunk's internal chains by peeling
-//                       (ballots, usually 1-3 iterations).  Rounds are separated by a
-//                       grid barrier and stop when nothing is undecided: 1-2 rounds for
-//                       sparse scenes, ~10 for dense ones, at worst one per chunk of the
-//                       largest segment (the length of the old serial scan).  The same
+//                       persistent grid; every 64-box chunk belongs to one warp, which
+//                       walks the set summary bits of each undecided row (16 B of mask per
+//                       bit), tests them against the bitmaps, settles the chunk's internal
+//                       chains by peeling (ballots, usually 1-3 iterations), and repeats
+//                       until its chunks are decided.  No rounds and no barriers: segments
+//                       of <= 4096 boxes live in one CTA's shared memory, larger ones
+//                       exchange their bitmaps through L2 (ld.cg / st.cg); a row's
+//                       summary drops the blocks whose boxes are all removed.  The same
 //                       grid then writes the per-box flags and compacts them in GLOBAL
 //                       score order into keep_out (and, for the fused multiclass call,
 //                       the (box, score) rows and labels) — the order
@@ -446,7 +446,7 @@ struct ResolveArgs {
     const NmsSegment *segs;
     int nseg;
     int has_large;                // some segment may have more than kLocalChunks chunks
-    int snapshot;                 // grid path: the state of all chunks fits the dynamic shared memory
+    int snapshot;                 // unused (was: per-round shared-memory copy of all bitmaps)
     const unsigned long long *mask;
     NmsScratch sc;
     int64_t chunks;               // 64-slot words to visit (an upper bound when device-planned)
@@ -656,14 +656,14 @@ template <bool MC>
 __global__ void __launch_bounds__(kResThreads, 1)
 nms_resolve_kernel(const ResolveArgs a) {
     // dynamic shared memory: the (kept, removed) pairs of one small segment, or (grid path,
-    // a.snapshot) this round's copy of the pairs of ALL chunks
+    // formerly) a per-round copy of the pairs of all chunks
     extern __shared__ __align__(16) unsigned long long s_kr[];
     __shared__ int s_red[kResWarps];
     __shared__ int s_warp_cnt[kResWarps];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const unsigned int G = gridDim.x;
 
-    // ---- small segments: one CTA each, rounds separated by __syncthreads ------------------
+    // ---- small segments: one CTA each, state in shared memory ------------------------------
     for (int s = blockIdx.x; s < a.nseg; s += G) {
         const NmsSegment sg = a.segs[s];
         const int nch = sg.row_blocks;
@@ -685,7 +685,7 @@ nms_resolve_kernel(const ResolveArgs a) {
         __syncthreads();
     }
 
-    // ---- large segments: the whole grid, rounds separated by a grid barrier -------------------
+    // ---- large segments: their chunks spread over the whole grid -----------------------------
     if (a.has_large) {
         // consecutive chunks go to different CTAs: a mid-size segment is spread over every SM
         const int64_t gwarp = (int64_t)blockIdx.x + (int64_t)G * warp, nwarps = (int64_t)G * kResWarps;
@@ -915,14 +915,10 @@ static int launch_resolve(const ResolveArgs &a_in, cudaStream_t stream) {
     // tests are latency-bound: more SMs, more loads in flight)
     int64_t want = a_in.has_large ? a_in.chunks : a_in.nseg;
     if (want < 1) want = 1;
-    // dynamic shared memory: one small segment's state, or a snapshot of every chunk's
+    // dynamic shared memory: one small segment's state
     ResolveArgs a = a_in;
-    size_t dyn = 2 * kLocalChunks * sizeof(unsigned long long);
+    const size_t dyn = 2 * kLocalChunks * sizeof(unsigned long long);
     a.snapshot = 0;
-    if (a.has_large && (size_t)a.chunks * 16 <= kSnapshotBytes) {
-        a.snapshot = 1;
-        if ((size_t)a.chunks * 16 > dyn) dyn = (size_t)a.chunks * 16;
-    }
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)(want < limit ? want : limit));
     cfg.blockDim = dim3(kResThreads);
