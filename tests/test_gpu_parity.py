@@ -212,6 +212,31 @@ def test_nms_single_segment_12000_vs_oracle():
     _assert_keep(boxes, scores, 0.3, gk.cpu().numpy(), wk)
 
 
+def test_nms_mixed_large_and_small_segments_vs_oracle():
+    """Large segments (> 4096 boxes: chunks spread over the grid, bitmaps exchanged through L2,
+    no barriers), one-CTA segments, a 4097-box segment just over the limit, a single box and a
+    dense segment with long suppression chains, all in ONE launch; every segment's keep list
+    equals the oracle's, and the global order is descending in score."""
+    from orientedobjectdetection_b200 import ops
+    sizes = [6000, 40, 4500, 4097, 1, 700]
+    extents = [300.0, 64.0, 1500.0, 250.0, 10.0, 90.0]      # 300 / 250: dense, deep chains
+    boxes = np.concatenate([synth.le90_boxes(n, 70 + k, e, w_lo=8.0, w_hi=64.0)
+                            for k, (n, e) in enumerate(zip(sizes, extents))])
+    seg = np.repeat(np.arange(len(sizes), dtype=np.int64) * 3 - 4, sizes)    # ids -4, -1, 2, ...
+    n = boxes.shape[0]
+    scores = synth.unique_scores(n, 71)
+    perm = np.random.default_rng(5).permutation(n)          # segments interleaved in memory
+    boxes, seg, scores = boxes[perm], seg[perm], scores[perm]
+    thr = 0.2
+    keep = ops._nms_keep(_cuda(boxes), _cuda(scores), thr, seg_ids=torch.from_numpy(seg).cuda()).cpu().numpy()
+    assert np.all(scores[keep][:-1] > scores[keep][1:])
+    for sid in np.unique(seg):
+        idx = np.nonzero(seg == sid)[0]
+        _, wk = ref.nms_rotated(boxes[idx], scores[idx], thr)
+        got = keep[seg[keep] == sid]
+        _assert_keep(boxes, scores, thr, got, idx[wk])
+
+
 def test_nms_single_segment_30000_greedy_property():
     """BASELINE C2 worst case as ONE segment (30000 boxes).  The greedy result is the
     unique set S with: i in S  <=>  no higher-scored j in S has IoU(i, j) >= thr.
