@@ -652,14 +652,27 @@ __device__ __forceinline__ int block_sum(int v, int *s_red /* kResWarps */) {
     return t;
 }
 
+#ifdef ROTGEO_RESOLVE_TIMING   // probe builds: phase timestamps of CTA 0 (ns, %globaltimer), printed at the end
+#define RT_DECL unsigned long long rt_[8]; int rtn_ = 0;
+#define RT_MARK do { if (blockIdx.x == 0 && threadIdx.x == 0 && rtn_ < 8) { asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(rt_[rtn_])); ++rtn_; } } while (0)
+#define RT_PRINT do { if (blockIdx.x == 0 && threadIdx.x == 0) { printf("resolve phases (us):"); for (int i_ = 1; i_ < rtn_; ++i_) printf(" %.1f", (double)(rt_[i_] - rt_[i_ - 1]) * 1e-3); printf("\n"); } } while (0)
+#else
+#define RT_DECL
+#define RT_MARK do {} while (0)
+#define RT_PRINT do {} while (0)
+#endif
+
 template <bool MC>
 __global__ void __launch_bounds__(kResThreads, 1)
 nms_resolve_kernel(const ResolveArgs a) {
+    RT_DECL
+    RT_MARK;   // 0 start
     // dynamic shared memory: the (kept, removed) pairs of one small segment, or (grid path,
     // formerly) a per-round copy of the pairs of all chunks
     extern __shared__ __align__(16) unsigned long long s_kr[];
     __shared__ int s_red[kResWarps];
     __shared__ int s_warp_cnt[kResWarps];
+    __shared__ uint32_t s_list[kEmitTile];   // kept indices of one emit tile
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const unsigned int G = gridDim.x;
 
@@ -685,6 +698,7 @@ nms_resolve_kernel(const ResolveArgs a) {
         __syncthreads();
     }
 
+    RT_MARK;   // 1 small segments decided + flags
     // ---- large segments: their chunks spread over the whole grid -----------------------------
     if (a.has_large) {
         // consecutive chunks go to different CTAs: a mid-size segment is spread over every SM
@@ -711,7 +725,9 @@ nms_resolve_kernel(const ResolveArgs a) {
             write_flags(a, sg, (int)c, ldcg_u64x2(a.sc.kr + 2 * gw).x, lane);
         }
     }
+    RT_MARK;   // 2 large segments
     grid_barrier(a.sc.sync, G);
+    RT_MARK;   // 3 barrier
 
     // ---- ordered compaction in global score order: count, barrier, write ----------------------
     const int64_t n = a.n_dev ? *a.n_dev : a.n;
@@ -719,12 +735,23 @@ nms_resolve_kernel(const ResolveArgs a) {
     const int64_t per = ((n + G - 1) / G + kEmitTile - 1) / kEmitTile * kEmitTile;
     const int64_t lo = min(n, (int64_t)blockIdx.x * per), hi = min(n, lo + per);
     {
+        // (kEmitItems independent index loads, then as many independent flag loads per thread)
         int cnt = 0;
-        for (int64_t i = lo + tid; i < hi; i += kResThreads) cnt += __ldcg(a.flags + order_at(a, i)) != 0;
+        for (int64_t start = lo; start < hi; start += kEmitTile) {
+            const int64_t i0 = start + (int64_t)tid * kEmitItems;
+            int64_t idx[kEmitItems];
+#pragma unroll
+            for (int k = 0; k < kEmitItems; ++k) idx[k] = i0 + k < hi ? order_at(a, i0 + k) : -1;
+#pragma unroll
+            for (int k = 0; k < kEmitItems; ++k)
+                if (idx[k] >= 0) cnt += __ldcg(a.flags + idx[k]) != 0;
+        }
         cnt = block_sum(cnt, s_red);
         if (tid == 0) a.sc.block_counts[blockIdx.x] = cnt;
     }
+    RT_MARK;   // 4 count
     grid_barrier(a.sc.sync, G);
+    RT_MARK;   // 5 barrier
     int before = 0, total = 0;
     for (unsigned int b = tid; b < G; b += kResThreads) {
         const int cb = __ldcg(a.sc.block_counts + b);
@@ -735,6 +762,7 @@ nms_resolve_kernel(const ResolveArgs a) {
     total = block_sum(total, s_red);
     if (blockIdx.x == 0 && tid == 0) *a.num_keep_out = (int64_t)total < cap ? (int64_t)total : cap;
 
+    RT_MARK;   // 6 offsets
     int64_t base = before;
     for (int64_t start = lo; start < hi && base < cap; start += kEmitTile) {
         const int64_t i0 = start + (int64_t)tid * kEmitItems;
@@ -762,27 +790,36 @@ nms_resolve_kernel(const ResolveArgs a) {
             wbefore += (w < warp) ? cw : 0;
             wtotal += cw;
         }
-        int64_t pos = base + wbefore + incl - cnt;
+        // the tile's kept indices, compacted in shared memory; then ONE output row per thread and
+        // step: the gathers of a row (box, score) are independent loads of different threads
+        // instead of eight dependent chains inside one thread (C2: emit 16 -> 4 us), and the
+        // stores are coalesced
+        int local = wbefore + incl - cnt;
 #pragma unroll
-        for (int k = 0; k < kEmitItems; ++k) {
-            if ((f & (1u << k)) && pos < cap) {
-                a.keep_out[pos] = idx[k];
-                if (MC) {
-                    // the output row of a kept candidate: its box, its (factored) score, its class
-                    const int64_t row = idx[k] / a.mc.classes;
-                    const int cls = (int)(idx[k] - row * a.mc.classes);
-                    const float *bx = a.mc.boxes + (a.mc.shared ? row : idx[k]) * 5;
-                    float sc = a.mc.scores[row * a.mc.score_stride + cls];
-                    if (a.mc.factors) sc *= a.mc.factors[row];
-                    float *d = a.mc.dets_out + pos * 6;
-                    d[0] = bx[0]; d[1] = bx[1]; d[2] = bx[2]; d[3] = bx[3]; d[4] = bx[4]; d[5] = sc;
-                    a.mc.labels_out[pos] = cls;
-                }
+        for (int k = 0; k < kEmitItems; ++k)
+            if (f & (1u << k)) s_list[local++] = (uint32_t)idx[k];
+        __syncthreads();
+        for (int j = tid; j < wtotal; j += kResThreads) {
+            const int64_t pos = base + j;
+            if (pos >= cap) break;
+            const uint32_t id = s_list[j];
+            a.keep_out[pos] = (int64_t)id;
+            if (MC) {
+                // the output row of a kept candidate: its box, its (factored) score, its class
+                const uint32_t row = id / (uint32_t)a.mc.classes;
+                const int cls = (int)(id - row * (uint32_t)a.mc.classes);
+                const float *bx = a.mc.boxes + (a.mc.shared ? (int64_t)row : (int64_t)id) * 5;
+                float sc = a.mc.scores[(int64_t)row * a.mc.score_stride + cls];
+                if (a.mc.factors) sc *= a.mc.factors[row];
+                float *d = a.mc.dets_out + pos * 6;
+                d[0] = bx[0]; d[1] = bx[1]; d[2] = bx[2]; d[3] = bx[3]; d[4] = bx[4]; d[5] = sc;
+                a.mc.labels_out[pos] = cls;
             }
-            if (f & (1u << k)) ++pos;
         }
         base += wtotal;
     }
+    RT_MARK;   // 7 emit
+    RT_PRINT;
 }
 
 // ---- host-side plan + launch -------------------------------------------------------
