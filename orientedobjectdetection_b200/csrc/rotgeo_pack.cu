@@ -33,9 +33,11 @@ __device__ __forceinline__ float warp_max(float v) {
 // slot i = position i.  Segmented sets (NMS): every segment starts at a slot that is
 // a multiple of 128 (so each 128-slot table block lies inside one segment) and is
 // padded up to the next one; slots past the last segment are padding too.
-__device__ __forceinline__ int64_t slot_position(const PackSet &s, int64_t i, int64_t n) {
+// seg_hint >= 0: the segment is already known (cooperative lookup of the CTA, see pack_kernel)
+__device__ __forceinline__ int64_t slot_position(const PackSet &s, int64_t i, int64_t n, int seg_hint = -1) {
     if (s.segs) {
         int lo = 0, hi = s.nseg - 1;   // last segment with pstart <= i
+        if (seg_hint >= 0) lo = hi = seg_hint;
         while (lo < hi) {
             const int mid = (lo + hi + 1) >> 1;
             if (s.segs[mid].pstart <= i) lo = mid; else hi = mid - 1;
@@ -144,8 +146,28 @@ pack_kernel(PackSet s1, PackSet s2, float min_wh, float cell, float area_ratio) 
     const int64_t i = second ? g - s1.n_pad : g;
     const bool in_set = i < s.n_pad;
 
+    // Segmented sets: a 128-slot block lies inside one segment, so the 128 threads of a block find
+    // it together — every thread tests a few table entries, one count per block — instead of each
+    // thread walking a binary search of dependent loads (22 % of this kernel's stall samples on the
+    // 320-segment RPN batch).  Tables of more than 512 segments keep the per-thread search.
+    __shared__ int s_segcnt[2];
+    const int hb = tid >> 7;
+    const bool coop = in_set && s.segs != nullptr && s.nseg <= 512;
+    if (tid < 2) s_segcnt[tid] = 0;
+    __syncthreads();
+    if (coop) {
+        const int64_t b0 = i & ~(int64_t)127;
+        int c = 0;
+        for (int j = tid & 127; j < s.nseg; j += 128) c += s.segs[j].pstart <= b0 ? 1 : 0;
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) c += __shfl_xor_sync(0xffffffffu, c, d);
+        if (lane == 0 && c) atomicAdd(&s_segcnt[hb], c);
+    }
+    __syncthreads();
+    const int seg_hint = coop ? max(s_segcnt[hb] - 1, 0) : -1;
+
     // the box first: its loads are in flight while the bin width is being derived
-    const int64_t pos = in_set ? slot_position(s, i, s.n_dev ? *s.n_dev : s.n) : -1;
+    const int64_t pos = in_set ? slot_position(s, i, s.n_dev ? *s.n_dev : s.n, seg_hint) : -1;
     int64_t src = -1;
     float cx = 0.f, cy = 0.f, w = 0.f, h = 0.f, th = 0.f;
     if (pos >= 0) {
