@@ -42,13 +42,18 @@ int rotgeo_version(void);
 /* Thread-local text of the last error on this thread ("" if none). */
 const char *rotgeo_last_error(void);
 
-/* ---- packed SoA box layout ------------------------------------------------
- * The kernels read boxes from three planes, padded to a multiple of 128 boxes:
- * float4 (cx, cy, r, area), float4 (cos, sin, w/2, h/2) and uint2 (xbins,
- * ybins) — 32-bit occupancy masks of the box's circumscribed circle over a
- * modular grid of 32 bins per axis, the first (two-instruction) level of the
- * pair cull.  rotgeo_packed_bytes(n) is the size of one packed set (40 bytes
- * a padded box); the buffer must be 16-byte aligned. */
+/* ---- packed box layout -----------------------------------------------------
+ * The kernels read boxes from a packed set of n_pad slots (n rounded up to a
+ * multiple of 128), four planes back to back, 96 bytes per padded box:
+ *   plane0  float4 (cx, cy, r, area)      r = circumscribed radius, area = w*h
+ *   plane1  float4 (cos, sin, w/2, h/2)
+ *   planeR  uint32  the box's occupancy as cyclic bin ranges over a modular grid
+ *                   of 32 bins per axis (x, y; NMS packs: also log-area)
+ *   planeT  1920 uint32 per block of 128 boxes: the block's inverted bin index
+ *                   (which of its boxes occupy a run of bins), the column side of
+ *                   the pair cull
+ * (orientedobjectdetection_b200/csrc/rotgeo_device.cuh).  rotgeo_packed_bytes(n)
+ * is the size of one packed set; the buffer must be 16-byte aligned. */
 size_t rotgeo_packed_bytes(int64_t n);
 
 /* AoS rows -> packed SoA.  `gather` (nullable, int64[n]) selects rows:

@@ -33,7 +33,7 @@ def build(force=False, verbose=False):
     if not force and not stale():
         return SO
     cmd = [nvcc_path(), '-gencode', 'arch=compute_100a,code=sm_100a', '-O3', '-lineinfo',
-           '-std=c++17', '--use_fast_math=false' if False else '-fmad=true',
+           '-std=c++17', '-fmad=true',
            '-Xcompiler', '-fPIC,-O2,-Wall', '-shared', '-o', SO]
     if verbose:
         cmd += ['-Xptxas', '-v']

@@ -69,6 +69,8 @@ def _multiclass_nms_fused(multi_bboxes, multi_scores, score_thr, iou_thr, max_nu
     n, num_classes = multi_scores.size(0), multi_scores.size(1) - 1
     if n == 0 or num_classes < 1 or num_classes > 64 or n * num_classes >= (1 << 26):
         return None
+    if not float(iou_thr) > 0.0:
+        return None     # degenerate threshold: answered by the seam (ops._top1), not by the kernels
     if multi_bboxes.shape[1] not in (5, 5 * num_classes):
         return None
     if not multi_scores.is_cuda and not bool((multi_scores[:, :-1] > score_thr).any()):

@@ -55,7 +55,6 @@ constexpr int kMaxStages = 4;   // cull-data ring: 4 stages of the x/y index (5 
 constexpr int kTabWords = 3 * kTableWords;   // 5760 words >= 4 * kTableXYWords
 constexpr int kInfoSlots = 8;   // tile descriptors / launch-control responses (> kStages)
 constexpr int kQueueCap = 64;   // pairs per warp queue (never more than 31 + 32 queued)
-constexpr int64_t kAheadMinTiles = 148 * 4 * 8;   // smaller grids: scheduler look-ahead 1 (see MaskArgs::ahead)
 static_assert(kTile == kBlock, "a tile column is one inverted-index block");
 
 struct TileInfo {
@@ -107,6 +106,7 @@ struct MaskArgs {
     int ahead;                    // 1 .. 3: how many tiles ahead the scheduler thread runs (launch-uniform)
     int group;                    // tiles per grid CTA (= per launch-control request): CTA c owns tiles c*group ...
     int64_t tiles;                // host-side tile count (a bound when total_tiles is set)
+    int64_t ahead_min_tiles;      // 8 tiles per resident CTA of this device: smaller grids keep look-ahead 1
 };
 
 // tile id -> (segment, I, J): tiles of a segment are numbered row block by row block,
@@ -181,7 +181,7 @@ nms_mask_kernel(const MaskArgs g) {
     // barrier spin loops), and a warp 0 that was busy clipping delayed everybody's next tile.
     // Small grids keep D = 1: requests taken early are tiles the other CTAs cannot take.
     int ahead = g.ahead & 15;
-    if (!(g.ahead & 16) && g.total_tiles && *g.total_tiles < kAheadMinTiles) ahead = 1;   // the real count, not the launch bound
+    if (!(g.ahead & 16) && g.total_tiles && *g.total_tiles < g.ahead_min_tiles) ahead = 1;   // the real count, not the launch bound
     const int D = min(max(ahead, 1), kStages - 1);
     // One grid CTA (one launch-control request) stands for `group` consecutive tiles: the
     // hardware answers requests at a few ns each for the whole GPU, which is as long as an
@@ -446,7 +446,6 @@ struct ResolveArgs {
     const NmsSegment *segs;
     int nseg;
     int has_large;                // some segment may have more than kLocalChunks chunks
-    int snapshot;                 // unused (was: per-round shared-memory copy of all bitmaps)
     const unsigned long long *mask;
     NmsScratch sc;
     int64_t chunks;               // 64-slot words to visit (an upper bound when device-planned)
@@ -667,8 +666,7 @@ __global__ void __launch_bounds__(kResThreads, 1)
 nms_resolve_kernel(const ResolveArgs a) {
     RT_DECL
     RT_MARK;   // 0 start
-    // dynamic shared memory: the (kept, removed) pairs of one small segment, or (grid path,
-    // formerly) a per-round copy of the pairs of all chunks
+    // dynamic shared memory: the (kept, removed) pairs of one small segment
     extern __shared__ __align__(16) unsigned long long s_kr[];
     __shared__ int s_red[kResWarps];
     __shared__ int s_warp_cnt[kResWarps];
@@ -873,64 +871,60 @@ void nms_plan(int64_t n, const int64_t *seg_offsets_host, int64_t num_segments, 
     plan->total_bytes = off;
 }
 
-constexpr size_t kSnapshotBytes = 160 * 1024;   // chunks * 16 B: up to 655k boxes in one launch
-
-// CTAs of the resolve grid: all co-resident (cooperative launch), at most one per SM
-static int resolve_grid_limit(bool mc) {
-    static int limit[2] = {0, 0};
-    if (limit[mc] == 0) {
-        int dev = 0, sms = 0, per_sm = 0;
-        if (cudaGetDevice(&dev) != cudaSuccess ||
-            cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess)
-            return -1;
-        cudaError_t e = mc
-            ? cudaFuncSetAttribute(nms_resolve_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSnapshotBytes)
-            : cudaFuncSetAttribute(nms_resolve_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSnapshotBytes);
-        if (e != cudaSuccess) return -1;
-        e = mc
-            ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, nms_resolve_kernel<true>, kResThreads, kSnapshotBytes)
-            : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, nms_resolve_kernel<false>, kResThreads, kSnapshotBytes);
-        if (e != cudaSuccess || per_sm < 1) return -1;
-        limit[mc] = sms < kNmsMaxBlocks ? sms : kNmsMaxBlocks;   // one 1024-thread CTA per SM
+// Per-device launch limits, cached per device (not per process): SM count and the number of
+// resident CTAs the mask kernel's grid-size heuristics are expressed in.
+struct DeviceLimits {
+    int sms;          // multiprocessors
+    int mask_slots;   // resident mask-kernel CTAs: 4 per SM (__launch_bounds__(kThreads, 4))
+};
+static int device_limits(DeviceLimits *out) {
+    constexpr int kMaxDevices = 64;
+    static int cached_sms[kMaxDevices];   // 0 = not queried yet; benign race: every writer stores the same value
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return -1;
+    int sms = (dev >= 0 && dev < kMaxDevices) ? cached_sms[dev] : 0;
+    if (sms == 0) {
+        if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms < 1) return -1;
+        if (dev >= 0 && dev < kMaxDevices) cached_sms[dev] = sms;
     }
-    return limit[mc];
+    out->sms = sms;
+    out->mask_slots = sms * 4;
+    return 0;
 }
 
-// look-ahead of the mask kernel's scheduler thread (MaskArgs::ahead).  Grids of fewer than
-// kAheadMinTiles tiles (8 per resident CTA) keep 1; ROTGEO_MASK_AHEAD=1..3 overrides (probe runs).
+// look-ahead of the mask kernel's scheduler thread (MaskArgs::ahead): grids of fewer than 8 tiles
+// per resident CTA keep 1 (requests taken early are tiles the other CTAs cannot take).
 constexpr int kAheadDefault = 3;
-static int mask_ahead_override() {
-    static int v = -1;
-    if (v < 0) {
-        const char *e = getenv("ROTGEO_MASK_AHEAD");
-        v = e ? atoi(e) : 0;
-        if (v < 0 || v > 3) v = 0;
-    }
-    return v;
+#ifdef ROTGEO_PROBES   // probe builds only: ROTGEO_MASK_AHEAD=1..3 / ROTGEO_MASK_GROUP=1..64 override the heuristics
+static int probe_env(const char *name, int lo, int hi) {
+    const char *e = getenv(name);
+    const int v = e ? atoi(e) : 0;
+    return (v < lo || v > hi) ? 0 : v;
 }
+#endif
 
 // tiles per launch-control request (MaskArgs::group): 4 for very large grids (measured on C5,
-// 175k mostly empty tiles: 0.88 -> 0.80 ms), else 1 (C4, 43k dense tiles: groups cost balance);
-// ROTGEO_MASK_GROUP overrides (probe runs)
-static int mask_group(int64_t tiles) {
-    static int forced = -1;
-    if (forced < 0) {
-        const char *e = getenv("ROTGEO_MASK_GROUP");
-        forced = e ? atoi(e) : 0;
-        if (forced < 0 || forced > 64) forced = 0;
-    }
-    if (forced) return forced;
-    return tiles >= 148 * 4 * 128 ? 4 : 1;
+// 175k mostly empty tiles: 0.88 -> 0.80 ms), else 1 (C4, 43k dense tiles: groups cost balance)
+static int mask_group(int64_t tiles, const DeviceLimits &lim) {
+#ifdef ROTGEO_PROBES
+    if (const int forced = probe_env("ROTGEO_MASK_GROUP", 1, 64)) return forced;
+#endif
+    return tiles >= (int64_t)lim.mask_slots * 128 ? 4 : 1;
 }
 
 static int launch_mask(const MaskArgs &g_in, int64_t tiles, cudaStream_t stream) {
     if (tiles > 0x7fffffffLL) return -1;
     if (tiles <= 0) return 0;
     MaskArgs g = g_in;
-    const int forced = mask_ahead_override();
-    g.ahead = forced ? forced + 16 : (tiles >= kAheadMinTiles ? kAheadDefault : 1);   // + 16: also for small grids
+    DeviceLimits lim;
+    if (device_limits(&lim)) return -3;
+    g.ahead_min_tiles = (int64_t)lim.mask_slots * 8;
+    g.ahead = tiles >= g.ahead_min_tiles ? kAheadDefault : 1;
+#ifdef ROTGEO_PROBES
+    if (const int forced = probe_env("ROTGEO_MASK_AHEAD", 1, 3)) g.ahead = forced + 16;   // + 16: also for small grids
+#endif
     g.tiles = tiles;
-    g.group = mask_group(tiles);
+    g.group = mask_group(tiles, lim);
     const int64_t ctas = (tiles + g.group - 1) / g.group;
     // one CTA per tile; running CTAs steal the not-yet-launched ones (launch control)
     cudaLaunchConfig_t cfg = {};
@@ -949,8 +943,10 @@ static int launch_mask(const MaskArgs &g_in, int64_t tiles, cudaStream_t stream)
 
 static int launch_resolve(const ResolveArgs &a_in, cudaStream_t stream) {
     const bool mc = a_in.mc.dets_out != nullptr;
-    const int limit = resolve_grid_limit(mc);
-    if (limit < 1) return -3;
+    DeviceLimits lim;
+    if (device_limits(&lim)) return -3;
+    // all CTAs co-resident (cooperative launch): one 1024-thread CTA per SM
+    const int limit = lim.sms < kNmsMaxBlocks ? lim.sms : kNmsMaxBlocks;
     // one small segment per CTA; with large segments, their chunks spread over every SM (the row
     // tests are latency-bound: more SMs, more loads in flight)
     int64_t want = a_in.has_large ? a_in.chunks : a_in.nseg;
@@ -958,7 +954,6 @@ static int launch_resolve(const ResolveArgs &a_in, cudaStream_t stream) {
     // dynamic shared memory: one small segment's state
     ResolveArgs a = a_in;
     const size_t dyn = 2 * kLocalChunks * sizeof(unsigned long long);
-    a.snapshot = 0;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)(want < limit ? want : limit));
     cfg.blockDim = dim3(kResThreads);

@@ -29,24 +29,29 @@ def _extract_xy(img_id):
 
 
 def _nms_groups(label_dets_list, num_classes, iou_thr):
-    """label_dets_list[k]: (n_k, 7) rows (label, cx, cy, w, h, theta, score) of group k.
+    """label_dets_list[k]: (n_k, 1 + d) rows (label, dets) of group k, where the reference
+    takes the first five columns of ``dets`` as the box and the LAST one as the score
+    (dota.py:371-380: ``nms_rotated(cls_dets[:, :5], cls_dets[:, -1], iou_thr)``; d is 6 for
+    real detections and 5 in the reference's own smoke input, tests/test_data/test_datasets/
+    test_dota.py:13-21, whose last box column doubles as the score).
     Returns per group a list over classes of (m, 6) arrays (box + score), score-descending."""
     sizes = [d.shape[0] for d in label_dets_list]
     out = [[None] * num_classes for _ in label_dets_list]
     if sum(sizes) == 0:
         for k, d in enumerate(label_dets_list):
             for c in range(num_classes):
-                out[k][c] = d[:0, 1:]
+                out[k][c] = d[:0, 1:]      # the reference appends dets[labels == i] itself when empty
         return out
     allr = np.concatenate(label_dets_list, axis=0)
     group = np.repeat(np.arange(len(sizes), dtype=np.int64), sizes)
+    sizes_off = np.concatenate([[0], np.cumsum(sizes)])
     labels = allr[:, 0].astype(np.int64)
     inside = (labels >= 0) & (labels < num_classes)
     seg = group * num_classes + np.where(inside, labels, 0)
     idx = np.nonzero(inside)[0]
     dev = ops._cuda_device()
     d = torch.from_numpy(np.ascontiguousarray(allr[idx, 1:6], dtype=np.float32)).to(dev)
-    s = torch.from_numpy(np.ascontiguousarray(allr[idx, 6], dtype=np.float32)).to(dev)
+    s = torch.from_numpy(np.ascontiguousarray(allr[idx, -1], dtype=np.float32)).to(dev)
     sg = torch.from_numpy(seg[idx]).to(dev)
     keep = ops._nms_keep(d, s, iou_thr, seg_ids=sg)                  # global score order
     keep = keep[torch.sort(sg[keep], stable=True).indices].cpu().numpy()   # group/class-major, score order inside
@@ -56,7 +61,12 @@ def _nms_groups(label_dets_list, num_classes, iou_thr):
     for k in range(len(sizes)):
         for c in range(num_classes):
             lo, hi = bounds[k * num_classes + c], bounds[k * num_classes + c + 1]
-            out[k][c] = allr[kept_rows[lo:hi], 1:]
+            rows = allr[kept_rows[lo:hi]]
+            if (labels[sizes_off[k]:sizes_off[k + 1]] == c).sum() == 0:
+                out[k][c] = allr[:0, 1:]       # dota.py:372: an empty class keeps the input width
+            else:
+                # mmcv.nms_rotated returns cat(dets[keep, :5], scores[keep]): (m, 6) whatever d is
+                out[k][c] = np.concatenate([rows[:, 1:6], rows[:, -1:]], axis=1)
     return out
 
 

@@ -1,6 +1,17 @@
 """``patch()`` rebinds the reference's names to this package when mmcv /
 mmrotate are importable (they are not in this image).  The
 nine modules that bind the names at import time are listed in SURVEY.md §8(b).
+
+Two reference call sites run in WORKER PROCESSES and are deliberately left on
+the reference's own CPU op: ``RRandomCrop._crop_data`` (transforms.py:369-371,
+DataLoader workers) and ``_merge_func`` (dota.py:358-382, reached through
+``mmcv.track_parallel_progress(..., nproc=4)`` at dota.py:265-273).  A forked
+child of a parent that has initialised CUDA cannot use the GPU, and this
+package has no CPU fallback; the reference guards the second site with
+``try: .cuda() / except: CPU`` (dota.py:374-377).  Instead,
+``DOTADataset.merge_det`` itself is rebound to the single-process version that
+merges every (image, class) group in one segmented launch, so ``_merge_func``
+is no longer reached from it.
 """
 import importlib
 
@@ -12,7 +23,7 @@ _L1_MODULES = (
     'mmcv.ops',
     'mmrotate.core.bbox.iou_calculators.rotate_iou2d_calculator',
     'mmrotate.core.evaluation.eval_map',
-    'mmrotate.datasets.pipelines.transforms',
+    # not 'mmrotate.datasets.pipelines.transforms': RRandomCrop runs in DataLoader workers
     'mmrotate.core.post_processing.bbox_nms_rotated',
     'mmrotate.core.patch.merge_results',
     'mmrotate.datasets.dota',
@@ -35,7 +46,8 @@ _L2 = {
     'mmrotate.core.patch': {'merge_results': core.merge_results},
     'mmrotate.core.evaluation.eval_map': {'eval_rbbox_map': evaluation.eval_rbbox_map},
     'mmrotate.core.evaluation': {'eval_rbbox_map': evaluation.eval_rbbox_map},
-    'mmrotate.datasets.dota': {'_merge_func': datasets._merge_func, 'eval_rbbox_map': evaluation.eval_rbbox_map},
+    # not dota._merge_func (pool workers, see above); DOTADataset.merge_det is rebound in patch()
+    'mmrotate.datasets.dota': {'eval_rbbox_map': evaluation.eval_rbbox_map},
     'mmrotate.datasets.hrsc': {'eval_rbbox_map': evaluation.eval_rbbox_map},
     'mmrotate.core': {'rbbox_overlaps': core.rbbox_overlaps,
                       'multiclass_nms_rotated': core.multiclass_nms_rotated,
@@ -71,6 +83,17 @@ def patch(strict=False):
             if hasattr(mod, name):
                 setattr(mod, name, fn)
                 done.append((modname, name))
+    try:   # the submission path: one segmented launch in THIS process instead of a pool of forked workers
+        dota = importlib.import_module('mmrotate.datasets.dota')
+
+        def merge_det(self, results, nproc=4):
+            return datasets.merge_det(results, self.img_ids, self.CLASSES, nproc)   # (id_list, dets_list)
+
+        dota.DOTADataset.merge_det = merge_det
+        done.append(('mmrotate.datasets.dota', 'DOTADataset.merge_det'))
+    except Exception:
+        if strict:
+            raise
     try:   # configs say iou_calculator=dict(type='RBboxOverlaps2D')
         from mmdet.core.bbox.iou_calculators import IOU_CALCULATORS
         IOU_CALCULATORS.register_module(name='RBboxOverlaps2D', force=True,

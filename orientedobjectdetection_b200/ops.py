@@ -24,6 +24,12 @@ _MODE = {'iou': 0, 'iof': 1}
 
 
 def _cuda_device(*tensors):
+    if torch.cuda._is_in_bad_fork():
+        # e.g. a DataLoader / multiprocessing-pool worker forked after the parent touched CUDA
+        # (the reference reaches RRandomCrop and dota._merge_func that way)
+        raise RuntimeError('rotgeo: called in a forked child of a process that initialised CUDA; '
+                           'the GPU cannot be used here and there is no CPU fallback. Use the '
+                           "'spawn' start method, or leave this call site on the reference's CPU op")
     for t in tensors:
         if t is not None and t.is_cuda:
             return t.device
@@ -115,6 +121,8 @@ def _nms_keep(boxes, scores, iou_threshold, seg_ids=None, offsets=None, id_offse
     n = boxes.size(0)
     b = _rows_f32(boxes, dev)
     s = scores.detach().to(device=dev, dtype=torch.float32).reshape(-1).contiguous()
+    if not float(iou_threshold) > 0.0:
+        return _top1(s)
     L = _lib.load()
     with torch.cuda.device(dev):
         seg_ptr = None
@@ -151,6 +159,18 @@ def _nms_keep(boxes, scores, iou_threshold, seg_ids=None, offsets=None, id_offse
     return keep[:k]
 
 
+def _top1(s, lo=0, hi=None):
+    """iou_threshold <= 0: the reference's CPU kernel tests ``IoU >= thr``, which holds for
+    EVERY pair (IoU >= 0, boxes of other classes / levels included: their offset copies are
+    disjoint, IoU 0) — the best-scored box suppresses all others.  The pair culls of the CUDA
+    path never form disjoint pairs, so this case is answered here (ties: lower index)."""
+    hi = s.numel() if hi is None else hi
+    if hi <= lo:
+        return torch.zeros(0, dtype=torch.int64, device=s.device)
+    v = s[lo:hi]
+    return torch.nonzero(v == v.max()).reshape(-1)[:1] + lo
+
+
 def _nms_keep_images(boxes, scores, ids, sizes, iou_threshold):
     """Greedy rotated NMS of several images stored back to back (image g owns
     ``sizes[g]`` consecutive rows), one segment per (image, id), with
@@ -170,6 +190,10 @@ def _nms_keep_images(boxes, scores, ids, sizes, iou_threshold):
     b = _rows_f32(boxes, dev)
     s = scores.detach().to(device=dev, dtype=torch.float32).reshape(-1).contiguous()
     seg = ids.detach().to(device=dev, dtype=torch.int64).reshape(-1).contiguous()
+    if not float(iou_threshold) > 0.0:
+        st = np.concatenate([[0], np.cumsum(sizes)])
+        tops = [_top1(s, int(st[g]), int(st[g + 1])) - int(st[g]) for g in range(nimg)]
+        return torch.cat(tops), [int(t.numel()) for t in tops]
     L = _lib.load()
     with torch.cuda.device(dev):
         stream = _stream(dev)

@@ -42,7 +42,10 @@ def _assert_keep(boxes, scores, thr, got, want):
     if got != want:
         why = _explain_nms_divergence(boxes, scores, thr, got, want)
         assert why.startswith('band pair'), why
-        pytest.skip('keep lists differ only inside the 1e-5 threshold band: ' + why)
+        # north_star: "identical except at pairs whose IoU lies within 1e-5 of the threshold, which
+        # are listed" — recorded as an expected failure carrying the pair, never as a silent skip
+        print('NMS threshold-band divergence: ' + why)
+        pytest.xfail('keep lists differ only inside the 1e-5 threshold band: ' + why)
 
 
 # ------------------------------------------------------------------ IoU
@@ -709,3 +712,170 @@ def test_merge_results_c5_full_size_properties():
         if len(removed):
             rm, _, _, _ = rg.rbbox_overlaps_max(_cuda(removed[:, :5]), _cuda(kept[:, :5]), min_wh=0.0)
             assert float(rm.min()) >= 0.1 - 1e-5                                    # (2)
+
+
+# ---------------------------------------------------------------- round 2: parity holes closed
+def _aug_inputs(seed, n, classes, extent):
+    rng = np.random.default_rng(seed)
+    b = synth.le90_boxes(n, seed, extent)
+    sc = rng.uniform(0.0, 1.0, n).astype(np.float32) + np.arange(n, dtype=np.float32) * 1e-7
+    lab = rng.integers(0, classes, n).astype(np.int64)
+    return np.concatenate([b, sc[:, None]], axis=1).astype(np.float32), lab
+
+
+@pytest.mark.parametrize('max_num', [100000, 120, 1])
+def test_aug_multiclass_nms_vs_oracle(max_num):
+    """a6: reference bbox_nms_rotated.py:95-144 (TTA merge): per-class NMS of the boxes above
+    score_thr, concatenated class by class, cut to the max_num best.  Cases: a class nobody has,
+    a class whose scores are all below the threshold, labels outside [0, classes), the cut."""
+    classes = 9
+    dets, lab = _aug_inputs(5, 3000, classes, 500.0)
+    lab[lab == 4] = 3                                   # class 4 is empty
+    dets[lab == 6, 5] = 0.01                            # class 6: nothing above score_thr
+    lab[:40] = -1                                       # labels outside [0, classes) are never visited
+    lab[40:80] = classes + 3
+    wd, wl = ref_api.aug_multiclass_nms_rotated(torch.from_numpy(dets), torch.from_numpy(lab), 0.05, 0.1,
+                                                max_num, classes)
+    gd, gl = rg.aug_multiclass_nms_rotated(_cuda(dets), torch.from_numpy(lab).cuda(), 0.05, dict(iou_thr=0.1),
+                                           max_num, classes)
+    assert gd.is_cuda and gl.dtype == torch.int64
+    assert torch.equal(gd.cpu(), wd) and torch.equal(gl.cpu(), wl)
+    assert 4 not in set(gl.cpu().tolist()) and 6 not in set(gl.cpu().tolist())
+    assert gd.shape[0] == min(max_num, gd.shape[0]) and (max_num > 1000 or gd.shape[0] == max_num)
+    # CPU tensors in -> CPU tensors out (the TTA path hands over what it merged)
+    cd, cl = rg.aug_multiclass_nms_rotated(torch.from_numpy(dets), torch.from_numpy(lab), 0.05, dict(iou_thr=0.1),
+                                           max_num, classes)
+    assert not cd.is_cuda and torch.equal(cd, wd) and torch.equal(cl, wl)
+
+
+def test_aug_multiclass_nms_nothing_left():
+    dets, lab = _aug_inputs(6, 50, 3, 100.0)
+    dets[:, 5] = 0.01
+    gd, gl = rg.aug_multiclass_nms_rotated(_cuda(dets), torch.from_numpy(lab).cuda(), 0.05, dict(iou_thr=0.1), 10, 3)
+    wd, wl = ref_api.aug_multiclass_nms_rotated(torch.from_numpy(dets), torch.from_numpy(lab), 0.05, 0.1, 10, 3)
+    assert gd.shape == wd.shape == (0, 6) and gl.shape == wl.shape == (0,)
+
+
+def _oracle_nms_parallel(jobs, thr):
+    """jobs: list of (boxes, scores); the C oracle releases the GIL inside ctypes"""
+    from concurrent.futures import ThreadPoolExecutor
+    import os
+    with ThreadPoolExecutor(max_workers=max(1, min(16, len(os.sched_getaffinity(0))))) as ex:
+        return list(ex.map(lambda j: ref.nms_rotated(j[0], j[1], thr)[1], jobs))
+
+
+def test_nms_images_c4_eight_full_size_images_vs_oracle():
+    """BASELINE C4 at full size: 8 images x (5 levels x 2000 proposals), thr 0.8, top 2000 — the
+    batch call against per-image oracle calls of mmcv.batched_nms's arithmetic (level offsets
+    with the maxima of the image, one NMS per image)."""
+    from orientedobjectdetection_b200 import dist as rdist
+    imgs = [synth.c4_rpn_image(seed=100 + s) for s in range(8)]
+    dev_imgs = [(_cuda(b), _cuda(s), torch.from_numpy(i).cuda()) for b, s, i in imgs]
+    got = rdist.nms_images(dev_imgs, 0.8, 2000)
+    jobs = []
+    for b, s, i in imgs:
+        maxc = np.float32(b[:, :2].max()) + np.float32(b[:, 2:4].max())
+        shifted = b.copy()
+        shifted[:, :2] = b[:, :2] + (i.astype(np.float32) * (maxc + np.float32(1)))[:, None]
+        jobs.append((shifted, s))
+    want = _oracle_nms_parallel(jobs, 0.8)
+    for (b, s, i), g, w in zip(imgs, got, want):
+        _assert_keep(b, s, 0.8, g.cpu().numpy(), w[:2000])
+        assert g.numel() == min(2000, len(w))
+    # and the per-image drop-in gives the same lists
+    for (bd, sd, idd), g in zip(dev_imgs[:2], got[:2]):
+        _, k = rg.batched_nms(bd, sd, idd, dict(type='nms_rotated', iou_threshold=0.8))
+        assert k[:2000].cpu().tolist() == g.cpu().tolist()
+
+
+def test_merge_results_c5_full_size_vs_oracle_and_greedy_characterisation():
+    """BASELINE C5 at full size (~200k detections, 15 Zipf-skewed classes).  Every class of at
+    most 14 000 detections is compared with the oracle's keep list exactly (11 classes); for the
+    larger ones the greedy set is pinned by its characterisation — S is the greedy result iff
+    (a) no box of S has a HIGHER-SCORED box of S with IoU >= thr and (b) every box outside S has
+    a higher-scored box of S with IoU >= thr — evaluated on the parity-tested IoU kernel with
+    the 1e-5 band (r01's "overlaps some kept box" did not ask for the higher score)."""
+    import copy
+    thr = 0.1
+    res, offs, shape = synth.c5_patch_results(0)
+    src = copy.deepcopy(res)
+    merged = rg.merge_results(src, offs, shape, thr)
+    per_cls = [np.concatenate([src[p][c] for p in range(len(src))], axis=0) for c in range(15)]   # shifted in place
+    small = [c for c in range(15) if 0 < per_cls[c].shape[0] <= 14000]
+    large = [c for c in range(15) if per_cls[c].shape[0] > 14000]
+    assert len(small) >= 10 and len(large) >= 3
+    want = _oracle_nms_parallel([(per_cls[c][:, :5], per_cls[c][:, 5]) for c in small], thr)
+    for c, wk in zip(small, want):
+        wrows = per_cls[c][wk]
+        if not np.array_equal(merged[c], wrows):
+            # locate the rows of the product's result in the class to name the divergence
+            index = {r.tobytes(): i for i, r in enumerate(per_cls[c])}
+            got = [index[r.tobytes()] for r in merged[c]]
+            _assert_keep(per_cls[c][:, :5], per_cls[c][:, 5], thr, got, wk)
+    for c in large:
+        allc = torch.from_numpy(per_cls[c]).cuda()
+        kept = torch.from_numpy(np.ascontiguousarray(merged[c])).cuda()
+        assert bool(torch.all(kept[:-1, 5] >= kept[1:, 5]))
+        # membership of every input row in the kept set (rows are unique: scores carry a tie-breaker)
+        key_all = allc[:, 5].double() * 1e6 + allc[:, 0].double()
+        key_kept = kept[:, 5].double() * 1e6 + kept[:, 0].double()
+        in_s = torch.isin(key_all, key_kept)
+        assert int(in_s.sum()) == kept.shape[0]
+        viol_a = torch.zeros(allc.shape[0], dtype=torch.bool, device='cuda')
+        cover_b = torch.zeros(allc.shape[0], dtype=torch.bool, device='cuda')
+        for lo in range(0, allc.shape[0], 8192):
+            blk = allc[lo:lo + 8192]
+            iou = rg.box_iou_rotated(blk[:, :5].contiguous(), kept[:, :5].contiguous())
+            higher = kept[None, :, 5] > blk[:, None, 5]
+            viol_a[lo:lo + 8192] = ((iou >= thr + IOU_TOL) & higher).any(1)
+            cover_b[lo:lo + 8192] = ((iou >= thr - IOU_TOL) & higher).any(1)
+        assert not bool((in_s & viol_a).any()), 'class %d: a kept box is suppressed by a better kept box' % c
+        assert bool((in_s | cover_b).all()), 'class %d: a removed box has no better kept box above thr' % c
+
+
+def test_merge_det_replays_the_references_own_smoke_input():
+    """/root/reference/tests/test_data/test_datasets/test_dota.py:13-21,57-62: format_results ->
+    merge_det on ONE patch with three (3, 5) rows (the last box column doubles as the score)"""
+    from orientedobjectdetection_b200 import datasets
+    dets = np.array([[4.3150e+02, 7.0600e+02, 6.7686e+01, 2.1990e+01, 2.9842e-02],
+                     [5.6351e+02, 5.3575e+02, 1.0018e+02, 1.8971e+01, 5.5499e-02],
+                     [5.7450e+02, 5.8450e+02, 9.5567e+01, 2.1094e+01, 8.4012e-02]])
+    gi, gd = datasets.merge_det([[dets]], ['P0004__1__0___0'], CLASSES=('plane',))
+    wi, wd = ref_api.merge_det([[dets]], ['P0004__1__0___0'], 1)
+    assert gi == wi == ('P0004',)
+    assert gd[0][0].dtype == np.float64 and np.array_equal(gd[0][0], wd[0][0]) and gd[0][0].shape == (3, 6)
+    # a second, empty class keeps the reference's (0, 5) shape
+    gi, gd = datasets.merge_det([[dets, dets[:0]]], ['P0004__1__0___0'], CLASSES=('plane', 'ship'))
+    wi, wd = ref_api.merge_det([[dets, dets[:0]]], ['P0004__1__0___0'], 2)
+    assert gd[0][1].shape == wd[0][1].shape and np.array_equal(gd[0][0], wd[0][0])
+
+
+def test_nms_degenerate_threshold_keeps_one_box_like_the_cpu_reference():
+    """iou_threshold <= 0: mmcv's CPU kernel tests IoU >= thr, true for every pair (disjoint
+    boxes and other classes' offset copies included) — the best box suppresses everything."""
+    boxes = synth.le90_boxes(500, 3, 5000.0)
+    scores = synth.unique_scores(500, 3)
+    for thr in (0.0, -0.5):
+        _, wk = ref.nms_rotated(boxes, scores, thr)
+        _, gk = rg.nms_rotated(_cuda(boxes), _cuda(scores), thr)
+        assert gk.cpu().tolist() == wk.tolist() == [int(np.argmax(scores))]
+    ids = torch.arange(500) % 4
+    _, wk = ref_api.batched_nms_rotated(torch.from_numpy(boxes), torch.from_numpy(scores), ids, 0.0)
+    _, gk = rg.batched_nms(_cuda(boxes), _cuda(scores), ids.cuda(), dict(type='nms_rotated', iou_threshold=0.0))
+    assert gk.cpu().tolist() == wk.tolist()
+
+
+def test_sharded_entry_points_on_two_gpus_match_single_gpu():
+    """N = 2 over NCCL (skipped below 2 GPUs): tools/dist_check_nccl.py asserts that the sharded
+    IoU / many-image NMS / patch merge return bit-identical results to the single-GPU calls."""
+    import os
+    import subprocess
+    import sys
+    if torch.cuda.device_count() < 2:
+        pytest.skip('needs 2 GPUs')
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, '-m', 'torch.distributed.run', '--nnodes=1', '--nproc-per-node', '2',
+                        '--master-addr', '127.0.0.1', '--master-port', '29611',
+                        os.path.join(root, 'tools', 'dist_check_nccl.py'), '--check-only'],
+                       capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]

@@ -42,6 +42,12 @@ m0 = rg.merge_results(copy.deepcopy(res), offs, shape, 0.1)
 assert all(np.array_equal(x, y) for x, y in zip(m1, m0))
 out['merge_results_sharded_equal'] = True
 
+if '--check-only' in sys.argv:
+    if rank == 0:
+        print(json.dumps(out))
+    dist.destroy_process_group()
+    sys.exit(0)
+
 # ---- C3 timings: the global (8192 x 8192) matrix row-sharded (strong scaling of ONE matrix)
 a, b = synth.c3_iou(0)
 ad, bd = cu(a), cu(b)
