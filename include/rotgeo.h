@@ -31,7 +31,7 @@ extern "C" {
 #define ROTGEO_ERR_ARG (-1)        /* bad argument (null pointer, negative size, bad mode) */
 #define ROTGEO_ERR_WORKSPACE (-2)  /* workspace too small / misaligned */
 #define ROTGEO_ERR_CUDA (-3)       /* a CUDA runtime call or launch failed */
-#define ROTGEO_ERR_RANGE (-4)      /* rotgeo_nms_prepare: ids span >= 2^16 values / too many segments */
+#define ROTGEO_ERR_RANGE (-4)      /* NMS front-end: ids of a group span >= 2^16 values / too many segments */
 
 #define ROTGEO_MODE_IOU 0
 #define ROTGEO_MODE_IOF 1          /* intersection / area(first box) */
@@ -192,75 +192,63 @@ int rotgeo_eval_tpfp(const float *dets, int64_t num_dets, int det_stride, const 
 int rotgeo_diff_iou_aligned(const float *boxes1, const float *boxes2, int64_t n, int stride1, int stride2,
                             float *iou_out, float *grad1_out, float *grad2_out, void *stream);
 
-/* ---- rotated NMS front-end: orders and segment sizes ----------------------------
- * What the reference does in python/ATen around the native op
- * (mmcv/ops/nms.py nms_rotated: scores.sort(0, descending=True) + index_select;
- * mmcv/ops/nms.py batched_nms: boxes.max(), the id * (max + 1) offsets, the add),
- * in two calls:
+/* ---- rotated NMS front-end: one sort kernel, device-side plan -------------------
+ * What the reference does in python/ATen around the native op, for one call or a whole
+ * batch of calls at once:
+ *   - mmcv/ops/nms.py nms_rotated: scores.sort(0, descending=True) + index_select;
+ *   - mmcv/ops/nms.py batched_nms: boxes.max(), the id * (max + 1) offsets, the add;
+ *   - the per-image python loop of the RPN heads around batched_nms
+ *     (mmrotate/models/dense_heads/rotated_rpn_head.py:414-426,515, oriented_rpn_head.py:275);
+ *   - the per-class loop of the patch merge (mmrotate/core/patch/merge_results.py:90-119).
  *
- *   rotgeo_nms_prepare   stable descending score order of scores (n,); with seg_ids
- *                        (n,) int64 also the segment-major order (ascending id, score
- *                        order inside an id) and the size of every segment present.
- *                        The sizes are returned to the HOST (seg_counts_host[0 ..
- *                        *num_segments_host), ascending id) because the host lays out
- *                        the suppression mask from them: with seg_ids this call
- *                        synchronises `stream` (the one device->host read of the whole
- *                        NMS); without seg_ids it does not.  ROTGEO_ERR_RANGE when the
- *                        ids span 65536 values or more, or more than seg_cap segments
- *                        are present (callers then split the job).
- *   rotgeo_nms_prepared  pack + mask + resolve over the orders left in `prep`.  Centre
- *                        offsets: `offsets` (n,) float added to cx, cy, or, with
- *                        id_offsets != 0, mmcv.batched_nms's own
- *                        float(id) * (max(cx,cy) + max(w,h) + 1) computed in fp32 on the
- *                        device (the maxima were reduced by rotgeo_nms_prepare).
- *                        keep_out (n,) receives the kept indices in GLOBAL descending
- *                        score order; workspace: rotgeo_nms_workspace_bytes() of the
- *                        prefix sums of seg_counts_host.
+ * The n candidate rows are cut into GROUPS (contiguous row ranges, group_sizes_host[g] rows
+ * each; null = one group): a group's kept boxes are emitted together in descending score
+ * order (ties: lower row first), groups one after the other.  Inside a group, boxes of
+ * equal seg_ids form a SEGMENT; suppression never crosses segments (seg_ids null = one
+ * segment per group).  The ids of one group must span fewer than 65536 values and form at
+ * most seg_cap segments.
  *
- * prep: device buffer of rotgeo_nms_prepare_bytes(n) bytes, 16-byte aligned; it must stay
- * untouched between the two calls.  seg_ids must be the same pointer in both calls
- * (nullptr = one segment). */
-size_t rotgeo_nms_prepare_bytes(int64_t n);
-int rotgeo_nms_prepare(const float *boxes, int64_t n, int stride, const float *scores,
-                       const int64_t *seg_ids, void *prep, size_t prep_bytes,
-                       int64_t *seg_counts_host, int64_t seg_cap, int64_t *num_segments_host,
-                       void *stream);
-int rotgeo_nms_prepared(const float *boxes, int64_t n, int stride, const float *offsets,
-                        const int64_t *seg_ids, int id_offsets, const void *prep,
-                        const int64_t *seg_counts_host, int64_t num_segments, float iou_threshold,
-                        int64_t *keep_out, int64_t *num_keep_out, void *workspace,
-                        size_t workspace_bytes, void *stream);
-
-/* ---- rotated NMS front-end for a batch of images ------------------------------------
- * Replaces the reference's per-image python loop around batched_nms
- * (mmrotate/models/dense_heads/rotated_rpn_head.py:414-426,515, oriented_rpn_head.py:275:
- * for every image its own boxes.max(), id offsets, score sort, NMS, host syncs) by ONE
- * pass over all images (BASELINE config C4).  The images
- * lie back to back in (boxes, scores, ids); image g owns image_sizes_host[g] rows.
+ *   rotgeo_nms_sort       ONE kernel (one thread-block cluster per group): score order,
+ *                         segment-major order, with id_offsets != 0 the centre offsets
+ *                         float(id) * (max(cx,cy) + max(w,h) + 1) of mmcv.ops.batched_nms
+ *                         (maxima of the row's own group), and the segment table + slot /
+ *                         tile / mask-word counts in a device header.  No synchronisation.
+ *   rotgeo_nms_bounds     host-side UPPER BOUNDS of those counts from the group sizes and
+ *                         seg_cap: sizes_out[6] = {slots, tiles, mask words, blocks of the
+ *                         largest segment, segments, rows to emit}.  With them
+ *                         rotgeo_nms_run needs no device->host read at all.
+ *   rotgeo_nms_read_plan  the exact counts instead: copies the header back and
+ *                         SYNCHRONISES `stream` (for jobs whose worst-case workspace is not
+ *                         worth allocating).  ROTGEO_ERR_RANGE when the ids of a group
+ *                         span 65536 values or more, or a group has more than seg_cap
+ *                         segments (callers renumber / split).
+ *   rotgeo_nms_run        pack + mask + resolve over `sizes` (bounds or exact).  Centre
+ *                         offsets: `offsets` (n,) float added to cx, cy (nullable), or,
+ *                         with sort_offsets != 0, the ones rotgeo_nms_sort computed.
+ *                         keep_out (n,): kept rows, group after group, score-descending;
+ *                         num_keep_out int64[2] (device): [0] how many, [1] the front-end's
+ *                         error bits (non-zero = the result is void: same cases as
+ *                         rotgeo_nms_read_plan's ROTGEO_ERR_RANGE).  group_counts_out
+ *                         (nullable, (num_groups,) int64 device): when given, keep_out
+ *                         holds rows INSIDE their group and group_counts_out the kept
+ *                         boxes per group.  iou_threshold must be positive.
  *
- *   rotgeo_nms_batch_prepare  like rotgeo_nms_prepare with one segment per (image, id):
- *                             score order, segment-major order, IMAGE-major emit order,
- *                             segment sizes to the host (the one sync), and offsets_out
- *                             (n,) = float(id) * (max(cx,cy) + max(w,h) + 1) with the
- *                             maxima of the box's own image — mmcv.ops.batched_nms's
- *                             arithmetic, per image.  ROTGEO_ERR_RANGE when
- *                             num_images x (max id - min id + 1) exceeds 65536.
- *   rotgeo_nms_prepared       as above, with offsets = offsets_out, seg_ids = ids,
- *                             id_offsets = 0: keep_out comes out image-major, score
- *                             order inside an image.
- *   rotgeo_nms_batch_finish   keep[0 .. *num_keep) (device): global row -> row inside its
- *                             image; counts_out (num_images,) int64 (device) = kept boxes
- *                             per image.  No synchronisation.
- *
- * prep: rotgeo_nms_batch_prepare_bytes(n, num_images) bytes, 16-byte aligned, untouched
- * between the three calls. */
-size_t rotgeo_nms_batch_prepare_bytes(int64_t n, int64_t num_images);
-int rotgeo_nms_batch_prepare(const float *boxes, int64_t n, int stride, const float *scores,
-                             const int64_t *ids, const int64_t *image_sizes_host, int64_t num_images,
-                             void *prep, size_t prep_bytes, float *offsets_out, int64_t *seg_counts_host,
-                             int64_t seg_cap, int64_t *num_segments_host, void *stream);
-int rotgeo_nms_batch_finish(int64_t *keep, const int64_t *num_keep, int64_t n, const void *prep,
-                            int64_t num_images, int64_t *counts_out, void *stream);
+ * sortws: rotgeo_nms_sort_bytes(...) bytes, 16-byte aligned, untouched between the calls;
+ * workspace: rotgeo_nms_run_bytes(n, sizes).  group_sizes_host, num_groups and seg_cap must
+ * be the same in all calls of one job. */
+size_t rotgeo_nms_sort_bytes(int64_t n, const int64_t *group_sizes_host, int64_t num_groups, int64_t seg_cap);
+int rotgeo_nms_sort(const float *boxes, int64_t n, int stride, const float *scores, const int64_t *seg_ids,
+                    int id_offsets, const int64_t *group_sizes_host, int64_t num_groups, int64_t seg_cap,
+                    void *sortws, size_t sortws_bytes, void *stream);
+int rotgeo_nms_bounds(int64_t n, const int64_t *group_sizes_host, int64_t num_groups, int64_t seg_cap,
+                      int64_t *sizes_out);
+int rotgeo_nms_read_plan(const void *sortws, int64_t n, const int64_t *group_sizes_host, int64_t num_groups,
+                         int64_t seg_cap, int64_t *sizes_out, void *stream);
+size_t rotgeo_nms_run_bytes(int64_t n, const int64_t *sizes);
+int rotgeo_nms_run(const float *boxes, int64_t n, int stride, const float *offsets, int sort_offsets,
+                   const int64_t *group_sizes_host, int64_t num_groups, int64_t seg_cap, const void *sortws,
+                   const int64_t *sizes, float iou_threshold, int64_t *keep_out, int64_t *num_keep_out,
+                   int64_t *group_counts_out, void *workspace, size_t workspace_bytes, void *stream);
 
 /* ---- class-batched rotated NMS, fused ----------------------------------------
  * Replaces the whole body of the reference's multiclass_nms_rotated

@@ -17,8 +17,8 @@ SYMBOLS = (
     'rotgeo_iou_max_workspace_bytes', 'rotgeo_iou_rowcol_max', 'rotgeo_max_iou_assign',
     'rotgeo_eval_tpfp_workspace_bytes', 'rotgeo_eval_tpfp',
     'rotgeo_diff_iou_aligned',
-    'rotgeo_nms_prepare_bytes', 'rotgeo_nms_prepare', 'rotgeo_nms_prepared',
-    'rotgeo_nms_batch_prepare_bytes', 'rotgeo_nms_batch_prepare', 'rotgeo_nms_batch_finish',
+    'rotgeo_nms_sort_bytes', 'rotgeo_nms_sort', 'rotgeo_nms_bounds', 'rotgeo_nms_read_plan',
+    'rotgeo_nms_run_bytes', 'rotgeo_nms_run',
     'rotgeo_multiclass_nms_workspace_bytes', 'rotgeo_multiclass_nms',
 )
 ERR_RANGE = -4
@@ -73,18 +73,18 @@ def load():
     L.rotgeo_eval_tpfp.restype = i32
     L.rotgeo_diff_iou_aligned.argtypes = [vp, vp, i64, i32, i32, vp, vp, vp, vp]
     L.rotgeo_diff_iou_aligned.restype = i32
-    L.rotgeo_nms_prepare_bytes.argtypes = [i64]
-    L.rotgeo_nms_prepare_bytes.restype = sz
-    L.rotgeo_nms_prepare.argtypes = [vp, i64, i32, vp, vp, vp, sz, vp, i64, vp, vp]
-    L.rotgeo_nms_prepare.restype = i32
-    L.rotgeo_nms_prepared.argtypes = [vp, i64, i32, vp, vp, i32, vp, vp, i64, f32, vp, vp, vp, sz, vp]
-    L.rotgeo_nms_prepared.restype = i32
-    L.rotgeo_nms_batch_prepare_bytes.argtypes = [i64, i64]
-    L.rotgeo_nms_batch_prepare_bytes.restype = sz
-    L.rotgeo_nms_batch_prepare.argtypes = [vp, i64, i32, vp, vp, vp, i64, vp, sz, vp, vp, i64, vp, vp]
-    L.rotgeo_nms_batch_prepare.restype = i32
-    L.rotgeo_nms_batch_finish.argtypes = [vp, vp, i64, vp, i64, vp, vp]
-    L.rotgeo_nms_batch_finish.restype = i32
+    L.rotgeo_nms_sort_bytes.argtypes = [i64, vp, i64, i64]
+    L.rotgeo_nms_sort_bytes.restype = sz
+    L.rotgeo_nms_sort.argtypes = [vp, i64, i32, vp, vp, i32, vp, i64, i64, vp, sz, vp]
+    L.rotgeo_nms_sort.restype = i32
+    L.rotgeo_nms_bounds.argtypes = [i64, vp, i64, i64, vp]
+    L.rotgeo_nms_bounds.restype = i32
+    L.rotgeo_nms_read_plan.argtypes = [vp, i64, vp, i64, i64, vp, vp]
+    L.rotgeo_nms_read_plan.restype = i32
+    L.rotgeo_nms_run_bytes.argtypes = [i64, vp]
+    L.rotgeo_nms_run_bytes.restype = sz
+    L.rotgeo_nms_run.argtypes = [vp, i64, i32, vp, i32, vp, i64, i64, vp, vp, f32, vp, vp, vp, vp, sz, vp]
+    L.rotgeo_nms_run.restype = i32
     L.rotgeo_multiclass_nms_workspace_bytes.argtypes = [i64, i32]
     L.rotgeo_multiclass_nms_workspace_bytes.restype = sz
     L.rotgeo_multiclass_nms.argtypes = [vp, i32, vp, vp, i64, i32, f32, f32, i64, vp, vp, vp, vp, vp, sz, vp]

@@ -249,17 +249,18 @@ def merge_results(results, offsets, img_shape, iou_thr=0.1, device='cpu'):
             out, _ = ops._nms_horizontal(d[:, :-1], d[:, -1], iou_thr)
             merged[c] = out.cpu().numpy()
     if rot:
+        # every class is one GROUP of the segmented NMS: one upload, one launch sequence, one
+        # download; the kept rows come back class after class, score-descending inside a class
         counts = [per_cls[c].shape[0] for c in rot]
         allc = np.concatenate([per_cls[c] for c in rot], axis=0)
-        seg = np.repeat(np.arange(len(rot), dtype=np.int64), counts)
         dev = ops._cuda_device()
         d = torch.from_numpy(np.ascontiguousarray(allc)).to(dev)
-        s = torch.from_numpy(seg).to(dev)
-        keep = ops._nms_keep(d[:, :5], d[:, 5], iou_thr, seg_ids=s)
-        keep = keep[torch.sort(s[keep], stable=True).indices]       # class-major, score-desc inside
-        kept = d[keep].cpu().numpy()
-        kseg = s[keep].cpu().numpy()
-        bounds = np.searchsorted(kseg, np.arange(len(rot) + 1))
+        keep, kcounts = ops._nms_grouped(d[:, :5], d[:, 5], iou_thr, group_sizes=counts)
+        starts = np.concatenate([[0], np.cumsum(counts)])[:-1]
+        rows = keep + torch.repeat_interleave(torch.from_numpy(starts).to(dev),
+                                              torch.tensor(kcounts, device=dev), output_size=int(keep.numel()))
+        kept = d[rows].cpu().numpy()
+        bounds = np.concatenate([[0], np.cumsum(kcounts)])
         for j, c in enumerate(rot):
             merged[c] = kept[bounds[j]:bounds[j + 1]].astype(per_cls[c].dtype, copy=False)
     return merged

@@ -33,7 +33,7 @@ inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
 extern "C" {
 
-int rotgeo_version(void) { return 1001; }   // 1001: + rotgeo_nms_batch_prepare / _finish
+int rotgeo_version(void) { return 2000; }   // 2000: rotgeo_nms_sort / _bounds / _read_plan / _run replace the prepare family
 
 const char *rotgeo_last_error(void) { return g_err; }
 
@@ -245,6 +245,7 @@ int rotgeo_nms(const float *boxes, int64_t n, int stride, const float *offsets,
         return ROTGEO_OK;
     }
     if (!boxes || !keep_out || (!order && !seg_order)) return fail(ROTGEO_ERR_ARG, "nms: null pointer");
+    if (!(iou_threshold > 0.f)) return fail(ROTGEO_ERR_ARG, "nms: iou_threshold must be positive");
     const bool segmented = seg_order != nullptr;
     if (segmented) {
         if (!seg_offsets_host || num_segments < 1)
@@ -305,112 +306,112 @@ int rotgeo_nms(const float *boxes, int64_t n, int stride, const float *offsets,
     return ROTGEO_OK;
 }
 
-size_t rotgeo_nms_prepare_bytes(int64_t n) { return rotgeo::nms_prepare_bytes(n); }
-
-int rotgeo_nms_prepare(const float *boxes, int64_t n, int stride, const float *scores,
-                       const int64_t *seg_ids, void *prep, size_t prep_bytes,
-                       int64_t *seg_counts_host, int64_t seg_cap, int64_t *num_segments_host,
-                       void *stream) {
-    if (n <= 0 || n > 0x7fffffffLL || stride < 5)
-        return fail(ROTGEO_ERR_ARG, "nms_prepare: n=%lld stride=%d", (long long)n, stride);
-    if (!boxes || !scores || !prep || !seg_counts_host || seg_cap < 1 || !num_segments_host)
-        return fail(ROTGEO_ERR_ARG, "nms_prepare: null pointer");
-    if (!aligned16(prep) || prep_bytes < rotgeo::nms_prepare_bytes(n))
-        return fail(ROTGEO_ERR_WORKSPACE, "nms_prepare: buffer %zu < %zu bytes or misaligned", prep_bytes,
-                    rotgeo::nms_prepare_bytes(n));
-    const int rc = rotgeo::nms_prepare(boxes, n, stride, scores, seg_ids, prep, seg_counts_host, seg_cap,
-                                       num_segments_host, (cudaStream_t)stream);
-    if (rc == -4) return fail(ROTGEO_ERR_RANGE, "nms_prepare: segment ids span 65536 values or more");
-    if (rc == -5) return fail(ROTGEO_ERR_RANGE, "nms_prepare: more than %lld segments", (long long)seg_cap);
-    if (rc) return cuda_fail("nms_prepare");
-    return ROTGEO_OK;
-}
-
-size_t rotgeo_nms_batch_prepare_bytes(int64_t n, int64_t num_images) {
-    return rotgeo::nms_batch_prepare_bytes(n, num_images);
-}
-
-int rotgeo_nms_batch_prepare(const float *boxes, int64_t n, int stride, const float *scores,
-                             const int64_t *ids, const int64_t *image_sizes_host, int64_t num_images,
-                             void *prep, size_t prep_bytes, float *offsets_out, int64_t *seg_counts_host,
-                             int64_t seg_cap, int64_t *num_segments_host, void *stream) {
-    if (n <= 0 || n > 0x7fffffffLL || stride < 5 || num_images < 1 || num_images > 65536)
-        return fail(ROTGEO_ERR_ARG, "nms_batch_prepare: n=%lld stride=%d images=%lld", (long long)n, stride,
-                    (long long)num_images);
-    if (!boxes || !scores || !ids || !image_sizes_host || !prep || !offsets_out || !seg_counts_host ||
-        seg_cap < 1 || !num_segments_host)
-        return fail(ROTGEO_ERR_ARG, "nms_batch_prepare: null pointer");
-    for (int64_t g = 0; g < num_images; ++g)
-        if (image_sizes_host[g] < 0) return fail(ROTGEO_ERR_ARG, "nms_batch_prepare: negative image size");
-    if (!aligned16(prep) || prep_bytes < rotgeo::nms_batch_prepare_bytes(n, num_images))
-        return fail(ROTGEO_ERR_WORKSPACE, "nms_batch_prepare: buffer %zu < %zu bytes or misaligned", prep_bytes,
-                    rotgeo::nms_batch_prepare_bytes(n, num_images));
-    const int rc = rotgeo::nms_batch_prepare(boxes, n, stride, scores, ids, image_sizes_host, num_images, prep,
-                                             offsets_out, seg_counts_host, seg_cap, num_segments_host,
-                                             (cudaStream_t)stream);
-    if (rc == -1) return fail(ROTGEO_ERR_ARG, "nms_batch_prepare: image sizes do not add up to n");
-    if (rc == -4) return fail(ROTGEO_ERR_RANGE, "nms_batch_prepare: images x id range is 65536 or more");
-    if (rc == -5) return fail(ROTGEO_ERR_RANGE, "nms_batch_prepare: more than %lld segments", (long long)seg_cap);
-    if (rc) return cuda_fail("nms_batch_prepare");
-    return ROTGEO_OK;
-}
-
-int rotgeo_nms_batch_finish(int64_t *keep, const int64_t *num_keep, int64_t n, const void *prep,
-                            int64_t num_images, int64_t *counts_out, void *stream) {
-    if (n <= 0 || num_images < 1 || !keep || !num_keep || !prep || !counts_out)
-        return fail(ROTGEO_ERR_ARG, "nms_batch_finish: bad argument");
-    if (rotgeo::nms_batch_finish(keep, num_keep, n, prep, num_images, counts_out, (cudaStream_t)stream))
-        return cuda_fail("nms_batch_finish");
-    return ROTGEO_OK;
-}
-
-int rotgeo_nms_prepared(const float *boxes, int64_t n, int stride, const float *offsets,
-                        const int64_t *seg_ids, int id_offsets, const void *prep,
-                        const int64_t *seg_counts_host, int64_t num_segments, float iou_threshold,
-                        int64_t *keep_out, int64_t *num_keep_out, void *workspace,
-                        size_t workspace_bytes, void *stream) {
-    cudaStream_t st = (cudaStream_t)stream;
-    if (n <= 0 || stride < 5 || num_segments < 1)
-        return fail(ROTGEO_ERR_ARG, "nms_prepared: n=%lld stride=%d segments=%lld", (long long)n, stride,
-                    (long long)num_segments);
-    if (!boxes || !prep || !seg_counts_host || !keep_out || !num_keep_out)
-        return fail(ROTGEO_ERR_ARG, "nms_prepared: null pointer");
-    if (id_offsets && !seg_ids) return fail(ROTGEO_ERR_ARG, "nms_prepared: id_offsets without seg_ids");
-    if (!seg_ids && num_segments != 1)
-        return fail(ROTGEO_ERR_ARG, "nms_prepared: several segments need the seg_ids given to prepare");
-    std::vector<int64_t> seg_off((size_t)num_segments + 1, 0);
-    for (int64_t s = 0; s < num_segments; ++s) {
-        if (seg_counts_host[s] < 0) return fail(ROTGEO_ERR_ARG, "nms_prepared: negative segment size");
-        seg_off[(size_t)s + 1] = seg_off[(size_t)s] + seg_counts_host[s];
+static int64_t max_group_of(const int64_t *group_sizes_host, int64_t num_groups, int64_t n) {
+    int64_t m = 0;
+    for (int64_t g = 0; g < num_groups; ++g) {
+        const int64_t v = group_sizes_host ? group_sizes_host[g] : n;
+        m = v > m ? v : m;
     }
-    if (seg_off[(size_t)num_segments] != n)
-        return fail(ROTGEO_ERR_ARG, "nms_prepared: segment sizes do not add up to n");
-    rotgeo::NmsPlan plan;
-    std::vector<rotgeo::NmsSegment> segs((size_t)num_segments);
-    rotgeo::nms_plan(n, seg_off.data(), num_segments, &plan, segs.data());
-    if (!workspace || !aligned16(workspace) || workspace_bytes < plan.total_bytes)
-        return fail(ROTGEO_ERR_WORKSPACE, "nms_prepared: workspace %zu < %zu bytes or misaligned",
-                    workspace_bytes, plan.total_bytes);
-    for (const auto &g : segs)
-        if (g.words / 2 >= 65536)
-            return fail(ROTGEO_ERR_ARG, "nms: a segment of more than %d boxes is not supported", 65535 * 128);
-    char *ws = reinterpret_cast<char *>(workspace);
-    rotgeo::NmsSegment *segs_dev = reinterpret_cast<rotgeo::NmsSegment *>(ws + plan.off_segments);
-    rotgeo::NmsScratch scratch;
-    scratch.kr = reinterpret_cast<unsigned long long *>(ws + plan.off_kr);
-    scratch.summary = reinterpret_cast<unsigned long long *>(ws + plan.off_summary);
-    scratch.sum_words = plan.sum_words;
-    scratch.sync = reinterpret_cast<unsigned int *>(ws + plan.off_sync);
-    scratch.block_counts = reinterpret_cast<int *>(ws + plan.off_counts);
-    if (cudaMemcpyAsync(segs_dev, segs.data(), segs.size() * sizeof(rotgeo::NmsSegment),
-                        cudaMemcpyHostToDevice, st) != cudaSuccess)
-        return cuda_fail("nms segment upload");
-    const int rc = rotgeo::launch_nms_prepared(
-        boxes, n, stride, offsets, id_offsets ? seg_ids : nullptr, seg_ids != nullptr, prep, plan, segs_dev,
-        iou_threshold, ws + plan.off_packed, reinterpret_cast<uint64_t *>(ws + plan.off_mask),
-        reinterpret_cast<uint8_t *>(ws + plan.off_flags), scratch, keep_out, num_keep_out, st);
-    if (rc == -1) return fail(ROTGEO_ERR_ARG, "nms: too many tiles");
-    if (rc) return cuda_fail("nms launch");
+    return m;
+}
+static bool groups_ok(const int64_t *group_sizes_host, int64_t num_groups, int64_t n) {
+    if (num_groups < 1 || num_groups > (1 << 20) || (!group_sizes_host && num_groups != 1)) return false;
+    if (!group_sizes_host) return true;
+    int64_t s = 0;
+    for (int64_t g = 0; g < num_groups; ++g) {
+        if (group_sizes_host[g] < 0) return false;
+        s += group_sizes_host[g];
+    }
+    return s == n;
+}
+static rotgeo::NmsSizes sizes_from(const int64_t *v) {
+    rotgeo::NmsSizes z;
+    z.n_pad = v[0]; z.tiles = v[1]; z.mask_words = v[2]; z.max_blocks = v[3]; z.nseg = v[4]; z.n_emit = v[5];
+    return z;
+}
+static void sizes_to(const rotgeo::NmsSizes &z, int64_t *v) {
+    v[0] = z.n_pad; v[1] = z.tiles; v[2] = z.mask_words; v[3] = z.max_blocks; v[4] = z.nseg; v[5] = z.n_emit;
+}
+
+size_t rotgeo_nms_sort_bytes(int64_t n, const int64_t *group_sizes_host, int64_t num_groups, int64_t seg_cap) {
+    if (n <= 0 || seg_cap < 1 || !groups_ok(group_sizes_host, num_groups, n)) return 0;
+    return rotgeo::nms_sort_bytes(n, num_groups, seg_cap, max_group_of(group_sizes_host, num_groups, n));
+}
+
+int rotgeo_nms_sort(const float *boxes, int64_t n, int stride, const float *scores, const int64_t *seg_ids,
+                    int id_offsets, const int64_t *group_sizes_host, int64_t num_groups, int64_t seg_cap,
+                    void *sortws, size_t sortws_bytes, void *stream) {
+    if (n <= 0 || n > 0x7fffffffLL || stride < 5 || seg_cap < 1 || seg_cap > 65536)
+        return fail(ROTGEO_ERR_ARG, "nms_sort: n=%lld stride=%d seg_cap=%lld", (long long)n, stride, (long long)seg_cap);
+    if (!groups_ok(group_sizes_host, num_groups, n))
+        return fail(ROTGEO_ERR_ARG, "nms_sort: group sizes must be non-negative and add up to n");
+    if (!boxes || !scores || !sortws) return fail(ROTGEO_ERR_ARG, "nms_sort: null pointer");
+    const size_t need = rotgeo_nms_sort_bytes(n, group_sizes_host, num_groups, seg_cap);
+    if (!aligned16(sortws) || sortws_bytes < need)
+        return fail(ROTGEO_ERR_WORKSPACE, "nms_sort: buffer %zu < %zu bytes or misaligned", sortws_bytes, need);
+    const int rc = rotgeo::nms_sort(boxes, n, stride, scores, seg_ids, id_offsets, group_sizes_host, num_groups,
+                                    seg_cap, sortws, (cudaStream_t)stream);
+    if (rc == -6) return fail(ROTGEO_ERR_RANGE, "nms_sort: a group of more than sms * 12288 boxes");
+    if (rc == -1) return fail(ROTGEO_ERR_ARG, "nms_sort: bad group sizes");
+    if (rc) return cuda_fail("nms_sort");
+    return ROTGEO_OK;
+}
+
+int rotgeo_nms_bounds(int64_t n, const int64_t *group_sizes_host, int64_t num_groups, int64_t seg_cap,
+                      int64_t *sizes_out) {
+    if (n <= 0 || seg_cap < 1 || !sizes_out || !groups_ok(group_sizes_host, num_groups, n))
+        return fail(ROTGEO_ERR_ARG, "nms_bounds: bad argument");
+    rotgeo::NmsSizes z;
+    rotgeo::nms_bounds(group_sizes_host, num_groups, n, seg_cap, &z);
+    sizes_to(z, sizes_out);
+    return ROTGEO_OK;
+}
+
+int rotgeo_nms_read_plan(const void *sortws, int64_t n, const int64_t *group_sizes_host, int64_t num_groups,
+                         int64_t seg_cap, int64_t *sizes_out, void *stream) {
+    if (n <= 0 || seg_cap < 1 || !sortws || !sizes_out || !groups_ok(group_sizes_host, num_groups, n))
+        return fail(ROTGEO_ERR_ARG, "nms_read_plan: bad argument");
+    rotgeo::NmsSizes z;
+    unsigned int err = 0;
+    if (rotgeo::nms_read_plan(sortws, n, num_groups, seg_cap, max_group_of(group_sizes_host, num_groups, n), &z, &err,
+                              (cudaStream_t)stream))
+        return cuda_fail("nms_read_plan");
+    sizes_to(z, sizes_out);
+    if (err & rotgeo::kSortErrRange) return fail(ROTGEO_ERR_RANGE, "nms: segment ids of a group span 65536 values or more");
+    if (err & rotgeo::kSortErrSegments) return fail(ROTGEO_ERR_RANGE, "nms: more segments than seg_cap in a group");
+    return ROTGEO_OK;
+}
+
+size_t rotgeo_nms_run_bytes(int64_t n, const int64_t *sizes) {
+    if (n <= 0 || !sizes) return 0;
+    rotgeo::NmsRunLayout l;
+    rotgeo::nms_run_layout(n, sizes_from(sizes), &l);
+    return l.total_bytes;
+}
+
+int rotgeo_nms_run(const float *boxes, int64_t n, int stride, const float *offsets, int sort_offsets,
+                   const int64_t *group_sizes_host, int64_t num_groups, int64_t seg_cap, const void *sortws,
+                   const int64_t *sizes, float iou_threshold, int64_t *keep_out, int64_t *num_keep_out,
+                   int64_t *group_counts_out, void *workspace, size_t workspace_bytes, void *stream) {
+    if (n <= 0 || stride < 5 || seg_cap < 1 || !groups_ok(group_sizes_host, num_groups, n))
+        return fail(ROTGEO_ERR_ARG, "nms_run: n=%lld stride=%d", (long long)n, stride);
+    if (!(iou_threshold > 0.f))
+        return fail(ROTGEO_ERR_ARG, "nms_run: iou_threshold must be positive (<= 0 keeps only the best box: "
+                                    "the caller answers that case, the pair culls never form disjoint pairs)");
+    if (!boxes || !sortws || !sizes || !keep_out || !num_keep_out) return fail(ROTGEO_ERR_ARG, "nms_run: null pointer");
+    const rotgeo::NmsSizes z = sizes_from(sizes);
+    if (z.n_pad < 128 || z.n_pad % 128 || z.tiles < 0 || z.mask_words < 0 || z.max_blocks < 1 || z.nseg < 0)
+        return fail(ROTGEO_ERR_ARG, "nms_run: bad sizes");
+    if (z.max_blocks >= 65536)     // the mask kernel carries the column block in 16 bits
+        return fail(ROTGEO_ERR_ARG, "nms_run: a segment of more than %d boxes is not supported", 65535 * 128);
+    const size_t need = rotgeo_nms_run_bytes(n, sizes);
+    if (!workspace || !aligned16(workspace) || workspace_bytes < need)
+        return fail(ROTGEO_ERR_WORKSPACE, "nms_run: workspace %zu < %zu bytes or misaligned", workspace_bytes, need);
+    const int rc = rotgeo::nms_run(boxes, n, stride, offsets, sort_offsets, group_sizes_host, num_groups, seg_cap,
+                                   sortws, z, iou_threshold, keep_out, num_keep_out, group_counts_out, workspace,
+                                   (cudaStream_t)stream);
+    if (rc == -1) return fail(ROTGEO_ERR_ARG, "nms_run: too many tiles");
+    if (rc) return cuda_fail("nms_run");
     return ROTGEO_OK;
 }
 
@@ -439,6 +440,7 @@ int rotgeo_multiclass_nms(const float *multi_bboxes, int bbox_cols, const float 
     }
     if (!multi_bboxes || !multi_scores || !dets_out || !labels_out || !keep_flat_out)
         return fail(ROTGEO_ERR_ARG, "multiclass_nms: null pointer");
+    if (!(iou_threshold > 0.f)) return fail(ROTGEO_ERR_ARG, "multiclass_nms: iou_threshold must be positive");
     const size_t need = rotgeo::multiclass_nms_workspace_bytes(rows, num_classes);
     if (!workspace || !aligned16(workspace) || workspace_bytes < need)
         return fail(ROTGEO_ERR_WORKSPACE, "multiclass_nms: workspace %zu < %zu bytes or misaligned",

@@ -29,6 +29,8 @@ struct PackSet {
     const int64_t *offset_ids;  // nullable: centre offset = id * (mc_max[0] + mc_max[1] + 1) instead
     const NmsSegment *segs;  // nullable: segmented slot layout (see slot_source)
     int nseg;
+    const long long *nseg_dev;   // nullable: the segment count lives on the device (nseg is then a bound)
+    const long long *n_pad_dev;  // nullable: slots actually used (n_pad is then a bound)
     // device-planned sets (fused front-ends): the box count lives on the device, and gather32[]
     // holds FLAT candidate indices row * mc_classes + class of a (rows x classes) score matrix
     const int64_t *n_dev;    // nullable: overrides n
@@ -149,31 +151,39 @@ int launch_nms(const NmsPlan &plan, const void *packed, const NmsSegment *segmen
                const NmsScratch &scratch, int64_t *keep_out, int64_t *num_keep_out,
                cudaStream_t stream);
 
-// generic front-end (rotgeo_frontend.cu)
-size_t nms_prepare_bytes(int64_t n);
-size_t nms_batch_prepare_bytes(int64_t n, int64_t nimg);
-int nms_batch_prepare(const float *boxes, int64_t n, int stride, const float *scores, const int64_t *ids,
-                      const int64_t *img_sizes_host, int64_t nimg, void *prep, float *offsets_out,
-                      int64_t *seg_counts_host, int64_t seg_cap, int64_t *num_segments_host,
-                      cudaStream_t stream);
-int nms_batch_finish(int64_t *keep, const int64_t *num_keep_dev, int64_t n, const void *prep, int64_t nimg,
-                     int64_t *counts_out_dev, cudaStream_t stream);
-int nms_prepare(const float *boxes, int64_t n, int stride, const float *scores, const int64_t *ids,
-                void *prep, int64_t *seg_counts_host, int64_t seg_cap, int64_t *num_segments_host,
-                cudaStream_t stream);
-int launch_nms_prepared(const float *boxes, int64_t n, int stride, const float *offsets,
-                        const int64_t *offset_ids, bool segmented, const void *prep, const NmsPlan &plan,
-                        const NmsSegment *segs_dev, float thr, void *packed, uint64_t *mask,
-                        uint8_t *flags, const NmsScratch &scratch, int64_t *keep_out,
-                        int64_t *num_keep_out, cudaStream_t stream);
+// counts that size the workspace and the grids of pack / mask / resolve: exact (read back from
+// the device header) or upper bounds (made on the host from the group sizes)
+struct NmsSizes {
+    int64_t n_pad, tiles, mask_words, max_blocks, nseg, n_emit;
+};
+struct NmsRunLayout {
+    size_t off_packed, off_mask, off_flags, off_kr, off_summary, off_sync, off_counts, total_bytes;
+    int sum_words;
+};
+void nms_run_layout(int64_t n, const NmsSizes &z, NmsRunLayout *l);
+void nms_bounds(const int64_t *group_sizes_host, int64_t ngroups, int64_t n, int64_t seg_cap, NmsSizes *z);
+
+// generic front-end (rotgeo_frontend.cu): sort -> [read plan] -> run
+size_t nms_sort_bytes(int64_t n, int64_t ngroups, int64_t seg_cap, int64_t max_group);
+int nms_sort(const float *boxes, int64_t n, int stride, const float *scores, const int64_t *ids, int id_offsets,
+             const int64_t *group_sizes_host, int64_t ngroups, int64_t seg_cap, void *sortws, cudaStream_t stream);
+int nms_read_plan(const void *sortws, int64_t n, int64_t ngroups, int64_t seg_cap, int64_t max_group, NmsSizes *z,
+                  unsigned int *error, cudaStream_t stream);
+int nms_run(const float *boxes, int64_t n, int stride, const float *offsets, int sort_offsets,
+            const int64_t *group_sizes_host, int64_t ngroups, int64_t seg_cap, const void *sortws, const NmsSizes &z,
+            float thr, int64_t *keep_out, int64_t *num_keep_out, int64_t *group_counts_out, void *workspace,
+            cudaStream_t stream);
 
 // NMS over a plan made on the DEVICE (fused front-ends): grids and buffers are sized for
 // host-side upper bounds, the kernels read the actual counts from device memory.
 struct NmsDevLaunch {
     const void *packed;
     int64_t n_pad_bound;              // packed slots allocated
+    const long long *n_pad_dev;       // nullable: slots actually used
     const NmsSegment *segs_dev;
-    int nseg;
+    int nseg;                         // segments (a bound when nseg_dev is set)
+    const long long *nseg_dev;        // nullable: actual segment count
+    const unsigned int *error_dev;    // nullable: front-end error bits, copied to num_keep_out[1]
     int64_t tiles_bound;              // mask grid
     const int64_t *total_tiles_dev;   // actual tile count
     NmsScratch scratch;
@@ -189,6 +199,69 @@ struct NmsDevLaunch {
     McOut mc;
 };
 int launch_nms_device_planned(const NmsDevLaunch &a, cudaStream_t stream);
+
+// ---- sort front-end (rotgeo_sort.cu) ------------------------------------------------------------
+constexpr int kSortThreads = 1024;
+constexpr int kSortItems = 12;
+constexpr int kSortCap = kSortThreads * kSortItems;   // elements per CTA: 12 288
+constexpr int kSortMaxCluster = 8;                    // portable cluster size: 98 304 elements per group in shared memory
+constexpr int kSortGroupsInline = 64;                 // group tables up to this size travel as kernel parameters
+constexpr int64_t kSortSegsMax = 16384;               // segments one call handles
+constexpr unsigned int kSortErrRange = 1u;            // the ids of a group span 2^16 values or more
+constexpr unsigned int kSortErrSegments = 2u;         // more segments than seg_cap in a group / than kSortSegsMax in all
+
+struct SortHeader {            // device-side result of the front-end (zeroed before the launch)
+    unsigned int done;         // groups finished (ticket of the last-cluster plan)
+    unsigned int error;        // kSortErr* bits
+    long long n_valid;         // entries of `order` to emit (multiclass: the candidates)
+    long long nseg, n_pad, total_tiles, mask_words;
+    int max_blocks;            // 128-box blocks of the largest segment
+    int pad;
+    float mc_max[2];           // multiclass: max(cx, cy), max(w, h) of the candidates
+};
+
+struct SortArgs {
+    int mode;                  // 0: scores (n,) [+ ids (n,)];  1: multiclass score matrix (rows, classes + 1)
+    const float *boxes;
+    int stride;
+    const float *scores;
+    const int64_t *ids;        // nullable (mode 0)
+    const float *factors;      // nullable (mode 1)
+    int classes, shared;       // mode 1
+    float score_thr;           // mode 1
+    int id_offsets;            // mode 0 with ids: offsets_out[row] = float(id) * (max(cx,cy) + max(w,h) + 1) of the row's group
+    int ngroups;
+    int seg_cap;               // segments per group
+    const int64_t *gstart;     // device (ngroups + 1) row offsets, or null: gstart_inline
+    int64_t gstart_inline[kSortGroupsInline + 1];
+    // outputs (carved from the sort workspace by launch_sort)
+    SortHeader *hdr;
+    uint32_t *order;           // emission order: group-major, score-descending; global rows (mode 1: flat indices)
+    uint32_t *seg_order;       // pack order: group-major, id-ascending, score-descending
+    uint32_t *seg_rank;        // position inside the group's score order of every seg_order entry
+    float *offsets_out;
+    int *gseg_count, *gseg_off;
+    uint32_t *gseg_start;      // (ngroups, seg_cap + 1)
+    NmsSegment *segs;
+    int segs_cap;
+    // oversize groups
+    uint32_t *big_buf;
+    uint32_t big_cap;
+    unsigned int *big_hist;
+    void *big_red;
+    unsigned int *big_count;
+};
+
+struct SortLayout {
+    size_t off_hdr, off_order, off_seg_order, off_seg_rank, off_offsets, off_gseg_count, off_gseg_off,
+        off_gseg_start, off_segs, off_gstart, off_big_buf, off_big_hist, off_big_red, off_big_count, total_bytes;
+    int64_t segs_cap, big_cap;
+};
+void sort_layout(int64_t n, int64_t ngroups, int64_t seg_cap, int64_t max_group, SortLayout *l);
+// fills the output pointers of `a` from the workspace and launches; group_sizes_host null = one group of n.
+// returns 0, -1 (sizes), -3 (CUDA), -6 (a group beyond what one cooperative grid sorts)
+int launch_sort(SortArgs &a, const int64_t *group_sizes_host, int64_t n, void *sortws, const SortLayout &l,
+                cudaStream_t stream);
 
 int launch_multiclass_nms(const float *multi_bboxes, int shared, const float *multi_scores,
                           const float *score_factors, int64_t rows, int classes, float score_thr,

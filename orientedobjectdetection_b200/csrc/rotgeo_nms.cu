@@ -96,6 +96,7 @@ struct MaskArgs {
     const uint32_t *pr, *pt;
     const NmsSegment *segs;
     int nseg;
+    const long long *nseg_dev;    // nullable: actual segment count (device-planned launch)
     float thr;
     float area_ratio;             // pairs with min(area) < area_ratio * max(area) cannot reach thr
     int area_axis;                // the packed set carries the area axis of the index (launch-uniform)
@@ -140,6 +141,7 @@ nms_mask_kernel(const MaskArgs g) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     constexpr int kStages = AREA ? 3 : 4;
     constexpr uint32_t tab_words = AREA ? kTableWords : kTableXYWords;
+    const int nseg = g.nseg_dev ? (int)*g.nseg_dev : g.nseg;
 
     if (tid == 0) {
 #pragma unroll
@@ -192,7 +194,7 @@ nms_mask_kernel(const MaskArgs g) {
     // instead of a binary search over the segment table and a square root, which made thread 0
     // the bottleneck of sparse scenes.
     auto seg_blocks = [&](int sgi) {
-        return sgi < g.nseg ? (int)((g.segs[sgi].len + kTile - 1) / kTile) : 0x7fffffff;
+        return sgi < nseg ? (int)((g.segs[sgi].len + kTile - 1) / kTile) : 0x7fffffff;
     };
     auto take_tile = [&](unsigned j) {      // thread 0: find my j-th tile, start its cull data, publish it
         MaskSmem::Sched st = sm.st;
@@ -238,7 +240,7 @@ nms_mask_kernel(const MaskArgs g) {
                         }
                     }
                 } else {
-                    st.cur = locate_tile(g.segs, g.nseg, tn);
+                    st.cur = locate_tile(g.segs, nseg, tn);
                     st.cur_nb = seg_blocks(st.cur.seg);
                 }
                 nx = st.cur;
@@ -264,7 +266,7 @@ nms_mask_kernel(const MaskArgs g) {
         st.alive = 1;
         st.cur_nb = 0;
         if ((int64_t)blockIdx.x * G < limit) {
-            t0 = locate_tile(g.segs, g.nseg, blockIdx.x * G);
+            t0 = locate_tile(g.segs, nseg, blockIdx.x * G);
             st.cur_nb = seg_blocks(t0.seg);
         }
         st.cur = t0;
@@ -445,6 +447,9 @@ constexpr int kEmitTile = kResThreads * kEmitItems;
 struct ResolveArgs {
     const NmsSegment *segs;
     int nseg;
+    const long long *nseg_dev;    // nullable: actual segment count
+    const long long *n_pad_dev;   // nullable: slots actually used
+    const unsigned int *error_dev;  // nullable: front-end error bits -> num_keep_out[1]
     int has_large;                // some segment may have more than kLocalChunks chunks
     const unsigned long long *mask;
     NmsScratch sc;
@@ -663,7 +668,10 @@ __device__ __forceinline__ int block_sum(int v, int *s_red /* kResWarps */) {
 
 template <bool MC>
 __global__ void __launch_bounds__(kResThreads, 1)
-nms_resolve_kernel(const ResolveArgs a) {
+nms_resolve_kernel(const ResolveArgs a_in) {
+    ResolveArgs a = a_in;
+    if (a.nseg_dev) a.nseg = (int)*a.nseg_dev;
+    if (a.n_pad_dev) a.chunks = min(a.chunks, (int64_t)(*a.n_pad_dev >> 6));
     RT_DECL
     RT_MARK;   // 0 start
     // dynamic shared memory: the (kept, removed) pairs of one small segment
@@ -761,7 +769,10 @@ nms_resolve_kernel(const ResolveArgs a) {
     }
     before = block_sum(before, s_red);
     total = block_sum(total, s_red);
-    if (blockIdx.x == 0 && tid == 0) *a.num_keep_out = (int64_t)total < cap ? (int64_t)total : cap;
+    if (blockIdx.x == 0 && tid == 0) {
+        a.num_keep_out[0] = (int64_t)total < cap ? (int64_t)total : cap;
+        if (a.error_dev) a.num_keep_out[1] = (int64_t)*a.error_dev;
+    }
 
     RT_MARK;   // 6 offsets
     int64_t base = before;
@@ -986,6 +997,7 @@ int launch_nms(const NmsPlan &plan, const void *packed, const NmsSegment *segmen
     g.summary = scratch.summary;
     g.sum_words = scratch.sum_words;
     g.total_tiles = nullptr;
+    g.nseg_dev = nullptr;
     int rc = launch_mask(g, plan.total_tiles, stream);
     if (rc) return rc;
     ResolveArgs a = {};
@@ -1020,11 +1032,15 @@ int launch_nms_device_planned(const NmsDevLaunch &d, cudaStream_t stream) {
     g.summary = d.scratch.summary;
     g.sum_words = d.scratch.sum_words;
     g.total_tiles = d.total_tiles_dev;
+    g.nseg_dev = d.nseg_dev;
     int rc = launch_mask(g, d.tiles_bound, stream);
     if (rc) return rc;
     ResolveArgs a = {};
     a.segs = d.segs_dev;
     a.nseg = d.nseg;
+    a.nseg_dev = d.nseg_dev;
+    a.n_pad_dev = d.n_pad_dev;
+    a.error_dev = d.error_dev;
     a.mask = g.mask;
     a.sc = d.scratch;
     a.has_large = d.max_chunks_bound > kLocalChunks;

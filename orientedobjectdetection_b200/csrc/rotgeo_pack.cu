@@ -141,8 +141,11 @@ pack_kernel(PackSet s1, PackSet s2, float min_wh, float cell, float area_ratio) 
     // the consumer kernel may start now: it streams zeros until it needs the packed set
     pdl_launch_dependents();
     const int64_t g = blockIdx.x * (int64_t)kPackThreads + tid;
+    // device-planned sets: blocks past the slots actually in use have nothing to do (block-uniform)
+    if (s1.n_pad_dev && blockIdx.x * (int64_t)kPackThreads >= *s1.n_pad_dev) return;
     const bool second = g >= s1.n_pad;
-    const PackSet s = second ? s2 : s1;
+    PackSet s = second ? s2 : s1;
+    if (s.nseg_dev) s.nseg = (int)*s.nseg_dev;
     const int64_t i = second ? g - s1.n_pad : g;
     const bool in_set = i < s.n_pad;
 
@@ -297,6 +300,8 @@ PackSet make_pack_set(const float *boxes, int64_t n, int stride, const int64_t *
     PackSet s;
     s.segs = nullptr;
     s.nseg = 0;
+    s.nseg_dev = nullptr;
+    s.n_pad_dev = nullptr;
     s.n_dev = nullptr;
     s.gather32 = nullptr;
     s.offset_ids = nullptr;

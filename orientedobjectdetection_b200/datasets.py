@@ -44,25 +44,25 @@ def _nms_groups(label_dets_list, num_classes, iou_thr):
         return out
     allr = np.concatenate(label_dets_list, axis=0)
     group = np.repeat(np.arange(len(sizes), dtype=np.int64), sizes)
-    sizes_off = np.concatenate([[0], np.cumsum(sizes)])
     labels = allr[:, 0].astype(np.int64)
     inside = (labels >= 0) & (labels < num_classes)
     seg = group * num_classes + np.where(inside, labels, 0)
     idx = np.nonzero(inside)[0]
+    # one GROUP of the segmented NMS per (image, class): rows made contiguous per group on the host
+    perm = idx[np.argsort(seg[idx], kind='stable')]
+    gsizes = np.bincount(seg[perm], minlength=len(sizes) * num_classes)
     dev = ops._cuda_device()
-    d = torch.from_numpy(np.ascontiguousarray(allr[idx, 1:6], dtype=np.float32)).to(dev)
-    s = torch.from_numpy(np.ascontiguousarray(allr[idx, -1], dtype=np.float32)).to(dev)
-    sg = torch.from_numpy(seg[idx]).to(dev)
-    keep = ops._nms_keep(d, s, iou_thr, seg_ids=sg)                  # global score order
-    keep = keep[torch.sort(sg[keep], stable=True).indices].cpu().numpy()   # group/class-major, score order inside
-    kept_rows = idx[keep]
-    kseg = seg[kept_rows]
-    bounds = np.searchsorted(kseg, np.arange(len(sizes) * num_classes + 1))
+    d = torch.from_numpy(np.ascontiguousarray(allr[perm, 1:6], dtype=np.float32)).to(dev)
+    s = torch.from_numpy(np.ascontiguousarray(allr[perm, -1], dtype=np.float32)).to(dev)
+    keep, kcounts = ops._nms_grouped(d, s, iou_thr, group_sizes=gsizes)
+    gstart = np.concatenate([[0], np.cumsum(gsizes)])[:-1]
+    kept_rows = perm[keep.cpu().numpy() + np.repeat(gstart, kcounts)]       # group-major, score order inside
+    bounds = np.concatenate([[0], np.cumsum(kcounts)])
     for k in range(len(sizes)):
         for c in range(num_classes):
             lo, hi = bounds[k * num_classes + c], bounds[k * num_classes + c + 1]
             rows = allr[kept_rows[lo:hi]]
-            if (labels[sizes_off[k]:sizes_off[k + 1]] == c).sum() == 0:
+            if gsizes[k * num_classes + c] == 0:
                 out[k][c] = allr[:0, 1:]       # dota.py:372: an empty class keeps the input width
             else:
                 # mmcv.nms_rotated returns cat(dets[keep, :5], scores[keep]): (m, 6) whatever d is

@@ -103,60 +103,27 @@ def box_iou_rotated(bboxes1, bboxes2, mode='iou', aligned=False, clockwise=True)
     return _overlaps(bboxes1, bboxes2, mode, aligned, 0.0)
 
 
-_SEG_CAP = 16384     # segments one call handles (ids must also span fewer than 2**16 values)
+_SEG_CAP = 16384          # segments one call handles (the ids of a group must also span fewer than 2**16 values)
+_PLAN_LIMIT = 256 << 20   # worst-case workspace above this: read the device plan back once instead
+_ERR_RANGE_BIT, _ERR_SEGMENTS_BIT = 1, 2
+
+_WS = {}
 
 
-def _nms_keep(boxes, scores, iou_threshold, seg_ids=None, offsets=None, id_offsets=False):
-    """kept indices (int64, score-descending, on the CUDA device) of a greedy
-    rotated NMS.
+def _workspace(dev, stream, name, nbytes):
+    """Reusable device scratch per (device, stream, purpose): grows, never shrinks.  The C-ABI
+    takes caller-owned workspace; allocating it per call cost more than small NMS calls take."""
+    key = (dev.index, stream, name)
+    t = _WS.get(key)
+    if t is None or t.numel() < nbytes:
+        t = torch.empty(max(int(nbytes * 1.25), 1 << 16), dtype=torch.uint8, device=dev)
+        _WS[key] = t
+    return t
 
-    ``seg_ids`` (ints per box) restricts suppression to boxes of equal id.  Centre
-    offsets (added to cx, cy before the geometry, as the reference's class
-    separation does): ``offsets`` (float per box), or ``id_offsets=True`` for
-    mmcv.batched_nms's own ``id * (max(cx,cy) + max(w,h) + 1)``, computed on the
-    device.  Two C-ABI calls: rotgeo_nms_prepare (key transform, radix sorts,
-    segment sizes -> host: the one sync before the launch) and rotgeo_nms_prepared
-    (pack + mask + resolve kernels), then one read of the kept count."""
-    dev = _cuda_device(boxes, scores)
-    n = boxes.size(0)
-    b = _rows_f32(boxes, dev)
-    s = scores.detach().to(device=dev, dtype=torch.float32).reshape(-1).contiguous()
-    if not float(iou_threshold) > 0.0:
-        return _top1(s)
-    L = _lib.load()
-    with torch.cuda.device(dev):
-        seg_ptr = None
-        if seg_ids is not None:
-            seg = seg_ids.detach().to(device=dev, dtype=torch.int64).reshape(-1).contiguous()
-            seg_ptr = seg.data_ptr()
-        off_ptr = None
-        if offsets is not None:
-            offsets = offsets.detach().to(device=dev, dtype=torch.float32).contiguous()
-            off_ptr = offsets.data_ptr()
-        stream = _stream(dev)
-        pbytes = L.rotgeo_nms_prepare_bytes(n)
-        prep = torch.empty(pbytes, dtype=torch.uint8, device=dev)
-        cap = min(n, _SEG_CAP)
-        counts = np.empty(cap, dtype=np.int64)
-        nseg = ctypes.c_int64(0)
-        rc = L.rotgeo_nms_prepare(b.data_ptr(), n, b.stride(0), s.data_ptr(), seg_ptr, prep.data_ptr(),
-                                  pbytes, counts.ctypes.data, cap, ctypes.byref(nseg), stream)
-        if rc == _lib.ERR_RANGE:
-            return _nms_keep_split(b, s, iou_threshold, seg, offsets, id_offsets)
-        _lib.check(rc, 'rotgeo_nms_prepare')
-        nseg = nseg.value
-        seg_off = np.zeros(nseg + 1, dtype=np.int64)
-        np.cumsum(counts[:nseg], out=seg_off[1:])
-        nbytes = L.rotgeo_nms_workspace_bytes(n, seg_off.ctypes.data, nseg)
-        ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
-        keep = torch.empty(n, dtype=torch.int64, device=dev)
-        nkeep = torch.empty(1, dtype=torch.int64, device=dev)
-        _lib.check(L.rotgeo_nms_prepared(b.data_ptr(), n, b.stride(0), off_ptr, seg_ptr,
-                                         1 if id_offsets else 0, prep.data_ptr(), counts.ctypes.data,
-                                         nseg, float(iou_threshold), keep.data_ptr(), nkeep.data_ptr(),
-                                         ws.data_ptr(), nbytes, stream), 'rotgeo_nms_prepared')
-        k = int(nkeep.item())          # the one sync after the launch: sizes the output
-    return keep[:k]
+
+def release_workspaces():
+    """drop the cached scratch buffers (they are plain torch tensors)"""
+    _WS.clear()
 
 
 def _top1(s, lo=0, hi=None):
@@ -171,6 +138,116 @@ def _top1(s, lo=0, hi=None):
     return torch.nonzero(v == v.max()).reshape(-1)[:1] + lo
 
 
+def _nms_grouped(boxes, scores, iou_threshold, seg_ids=None, offsets=None, id_offsets=False,
+                 group_sizes=None, seg_cap=None):
+    """Greedy rotated NMS of one or several GROUPS of boxes stored back to back (group g owns
+    ``group_sizes[g]`` consecutive rows; None = one group).  Suppression only among boxes of
+    equal ``seg_ids`` inside a group.  Centre offsets (added to cx, cy before the geometry, as
+    the reference's class separation does): ``offsets`` (float per box), or ``id_offsets=True``
+    for mmcv.batched_nms's own ``id * (max(cx,cy) + max(w,h) + 1)`` with the maxima of the
+    box's own group, computed on the device.
+
+    Returns ``(keep, counts)``: ``keep`` (device int64) holds, group after group, the kept rows
+    in descending score order — global row indices when ``group_sizes`` is None, else indices
+    INSIDE the group; ``counts`` the kept boxes per group (python list, None for one group).
+    ``None`` when the ids do not fit the device front-end (callers renumber and split).
+
+    Launch sequence (C-ABI): rotgeo_nms_sort (ONE kernel: orders, offsets, segment table and
+    launch totals in a device header) and rotgeo_nms_run (pack + mask + resolve over worst-case
+    bounds): no device->host read until the kept count is fetched at the end.  Jobs whose
+    worst-case workspace exceeds _PLAN_LIMIT read the 64-byte plan back once instead."""
+    dev = _cuda_device(boxes, scores)
+    n = boxes.size(0)
+    b = _rows_f32(boxes, dev)
+    s = scores.detach().to(device=dev, dtype=torch.float32).reshape(-1).contiguous()
+    grouped = group_sizes is not None
+    sizes_h = np.ascontiguousarray(group_sizes, dtype=np.int64) if grouped else None
+    ngroups = int(sizes_h.shape[0]) if grouped else 1
+    if n == 0:
+        return torch.zeros(0, dtype=torch.int64, device=dev), ([0] * ngroups if grouped else None)
+    if not float(iou_threshold) > 0.0:
+        if not grouped:
+            return _top1(s), None
+        st = np.concatenate([[0], np.cumsum(sizes_h)])
+        tops = [_top1(s, int(st[g]), int(st[g + 1])) - int(st[g]) for g in range(ngroups)]
+        return torch.cat(tops), [int(t.numel()) for t in tops]
+    L = _lib.load()
+    with torch.cuda.device(dev):
+        seg_ptr = None
+        if seg_ids is not None:
+            seg = seg_ids.detach().to(device=dev, dtype=torch.int64).reshape(-1).contiguous()
+            seg_ptr = seg.data_ptr()
+        off_ptr = None
+        if offsets is not None:
+            offsets = offsets.detach().to(device=dev, dtype=torch.float32).contiguous()
+            off_ptr = offsets.data_ptr()
+        stream = _stream(dev)
+        sizes_ptr = sizes_h.ctypes.data if grouped else None
+        max_group = int(sizes_h.max()) if grouped else n
+        if seg_ptr is None:
+            cap = 1
+        elif seg_cap is not None:
+            cap = int(seg_cap)
+        else:
+            cap = min(max(max_group, 1), 256 if ngroups == 1 else 16, _SEG_CAP)
+        sizes = np.zeros(6, dtype=np.int64)
+        for attempt in range(2):
+            sbytes = L.rotgeo_nms_sort_bytes(n, sizes_ptr, ngroups, cap)
+            sortws = _workspace(dev, stream, 'nms_sort', sbytes)
+            _lib.check(L.rotgeo_nms_sort(b.data_ptr(), n, b.stride(0), s.data_ptr(), seg_ptr,
+                                         1 if (id_offsets and seg_ptr) else 0, sizes_ptr, ngroups, cap,
+                                         sortws.data_ptr(), sortws.numel(), stream), 'rotgeo_nms_sort')
+            _lib.check(L.rotgeo_nms_bounds(n, sizes_ptr, ngroups, cap, sizes.ctypes.data), 'rotgeo_nms_bounds')
+            nbytes = L.rotgeo_nms_run_bytes(n, sizes.ctypes.data)
+            err = 0
+            if nbytes > _PLAN_LIMIT:
+                rc = L.rotgeo_nms_read_plan(sortws.data_ptr(), n, sizes_ptr, ngroups, cap, sizes.ctypes.data, stream)
+                if rc == _lib.ERR_RANGE:
+                    err = _plan_error_bits()
+                else:
+                    _lib.check(rc, 'rotgeo_nms_read_plan')
+                    nbytes = L.rotgeo_nms_run_bytes(n, sizes.ctypes.data)
+            if not err:
+                ws = _workspace(dev, stream, 'nms_run', nbytes)
+                keep = torch.empty(n, dtype=torch.int64, device=dev)
+                tail = torch.empty(2 + ngroups, dtype=torch.int64, device=dev)   # kept, error bits, kept per group
+                _lib.check(L.rotgeo_nms_run(b.data_ptr(), n, b.stride(0), off_ptr,
+                                            1 if (id_offsets and seg_ptr) else 0, sizes_ptr, ngroups, cap,
+                                            sortws.data_ptr(), sizes.ctypes.data, float(iou_threshold),
+                                            keep.data_ptr(), tail.data_ptr(),
+                                            tail.data_ptr() + 16 if grouped else None,
+                                            ws.data_ptr(), ws.numel(), stream), 'rotgeo_nms_run')
+                host = tail.tolist()          # the one device->host read of the call: sizes the outputs
+                err = int(host[1])
+                if not err:
+                    return keep[:host[0]], (host[2:] if grouped else None)
+            if (err & _ERR_RANGE_BIT) or attempt == 1 or cap >= min(max_group, _SEG_CAP):
+                return None
+            cap = min(max_group, _SEG_CAP)     # more segments in a group than assumed: once more with room
+    return None
+
+
+def _plan_error_bits():
+    msg = _lib.load().rotgeo_last_error().decode('utf-8', 'replace')
+    return _ERR_RANGE_BIT if 'span' in msg else _ERR_SEGMENTS_BIT
+
+
+def _nms_keep(boxes, scores, iou_threshold, seg_ids=None, offsets=None, id_offsets=False):
+    """kept indices (int64, score-descending, on the CUDA device) of a greedy rotated NMS of
+    ONE group (see _nms_grouped); ids that the device front-end does not take (spread over
+    65536 values or more, more than 16384 segments) are renumbered and split."""
+    got = _nms_grouped(boxes, scores, iou_threshold, seg_ids, offsets, id_offsets)
+    if got is not None:
+        return got[0]
+    dev = _cuda_device(boxes, scores)
+    b = _rows_f32(boxes, dev)
+    s = scores.detach().to(device=dev, dtype=torch.float32).reshape(-1).contiguous()
+    seg = seg_ids.detach().to(device=dev, dtype=torch.int64).reshape(-1)
+    if offsets is not None:
+        offsets = offsets.detach().to(device=dev, dtype=torch.float32)
+    return _nms_keep_split(b, s, iou_threshold, seg, offsets, id_offsets)
+
+
 def _nms_keep_images(boxes, scores, ids, sizes, iou_threshold):
     """Greedy rotated NMS of several images stored back to back (image g owns
     ``sizes[g]`` consecutive rows), one segment per (image, id), with
@@ -178,53 +255,9 @@ def _nms_keep_images(boxes, scores, ids, sizes, iou_threshold):
 
     Returns ``(keep, counts)``: ``keep`` (device int64) holds, image after image,
     the kept rows as indices INSIDE their image in descending score order;
-    ``counts`` (python list) the number kept per image.  ``None`` when the
-    (image, id) pairs do not fit 16-bit segment keys (callers use the generic
-    path).  Three C-ABI calls (rotgeo_nms_batch_prepare: sorts + the segment
-    sizes, one sync; rotgeo_nms_prepared: pack + mask + resolve;
-    rotgeo_nms_batch_finish: per-image indices and counts) and one read of the
-    counts."""
-    dev = _cuda_device(boxes, scores)
-    n = boxes.size(0)
-    nimg = len(sizes)
-    b = _rows_f32(boxes, dev)
-    s = scores.detach().to(device=dev, dtype=torch.float32).reshape(-1).contiguous()
-    seg = ids.detach().to(device=dev, dtype=torch.int64).reshape(-1).contiguous()
-    if not float(iou_threshold) > 0.0:
-        st = np.concatenate([[0], np.cumsum(sizes)])
-        tops = [_top1(s, int(st[g]), int(st[g + 1])) - int(st[g]) for g in range(nimg)]
-        return torch.cat(tops), [int(t.numel()) for t in tops]
-    L = _lib.load()
-    with torch.cuda.device(dev):
-        stream = _stream(dev)
-        sizes_h = np.ascontiguousarray(sizes, dtype=np.int64)
-        pbytes = L.rotgeo_nms_batch_prepare_bytes(n, nimg)
-        prep = torch.empty(pbytes, dtype=torch.uint8, device=dev)
-        offsets = torch.empty(n, dtype=torch.float32, device=dev)
-        cap = min(n, _SEG_CAP)
-        counts = np.empty(cap, dtype=np.int64)
-        nseg = ctypes.c_int64(0)
-        rc = L.rotgeo_nms_batch_prepare(b.data_ptr(), n, b.stride(0), s.data_ptr(), seg.data_ptr(),
-                                        sizes_h.ctypes.data, nimg, prep.data_ptr(), pbytes,
-                                        offsets.data_ptr(), counts.ctypes.data, cap, ctypes.byref(nseg), stream)
-        if rc == _lib.ERR_RANGE:
-            return None
-        _lib.check(rc, 'rotgeo_nms_batch_prepare')
-        nseg = nseg.value
-        seg_off = np.zeros(nseg + 1, dtype=np.int64)
-        np.cumsum(counts[:nseg], out=seg_off[1:])
-        nbytes = L.rotgeo_nms_workspace_bytes(n, seg_off.ctypes.data, nseg)
-        ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
-        keep = torch.empty(n, dtype=torch.int64, device=dev)
-        tail = torch.empty(nimg + 1, dtype=torch.int64, device=dev)     # [kept per image ..., kept in all]
-        _lib.check(L.rotgeo_nms_prepared(b.data_ptr(), n, b.stride(0), offsets.data_ptr(), seg.data_ptr(), 0,
-                                         prep.data_ptr(), counts.ctypes.data, nseg, float(iou_threshold),
-                                         keep.data_ptr(), tail.data_ptr() + 8 * nimg, ws.data_ptr(), nbytes,
-                                         stream), 'rotgeo_nms_prepared')
-        _lib.check(L.rotgeo_nms_batch_finish(keep.data_ptr(), tail.data_ptr() + 8 * nimg, n, prep.data_ptr(),
-                                             nimg, tail.data_ptr(), stream), 'rotgeo_nms_batch_finish')
-        per_img = tail.tolist()        # the one sync after the launches: sizes the outputs
-    return keep[:per_img[-1]], per_img[:-1]
+    ``counts`` (python list) the number kept per image.  ``None`` when the ids of
+    an image do not fit the device front-end (callers use the generic path)."""
+    return _nms_grouped(boxes, scores, iou_threshold, seg_ids=ids, id_offsets=True, group_sizes=sizes)
 
 
 def _nms_keep_split(b, s, iou_threshold, seg, offsets, id_offsets):
@@ -239,9 +272,11 @@ def _nms_keep_split(b, s, iou_threshold, seg, offsets, id_offsets):
     keeps = []
     for lo in range(0, nseg, _SEG_CAP):
         sel = torch.nonzero((dense >= lo) & (dense < lo + _SEG_CAP)).squeeze(1)
-        k = _nms_keep(b[sel], s[sel], iou_threshold, seg_ids=dense[sel] - lo,
-                      offsets=None if offsets is None else offsets[sel])
-        keeps.append(sel[k])
+        got = _nms_grouped(b[sel], s[sel], iou_threshold, seg_ids=dense[sel] - lo,
+                           offsets=None if offsets is None else offsets[sel], seg_cap=_SEG_CAP)
+        if got is None:
+            raise RuntimeError('rotgeo: the NMS front-end rejected a renumbered job')
+        keeps.append(sel[got[0]])
     keep = torch.cat(keeps)
     # chunks -> global score order (ties: lower index first)
     order = torch.sort(keep).values

@@ -28,7 +28,7 @@ def test_exports_match_header(lib):
     raw = ctypes.CDLL(_lib.SO_PATH)
     for sym in declared:
         assert getattr(raw, sym) is not None
-    assert lib.rotgeo_version() == 1001
+    assert lib.rotgeo_version() == 2000
 
 
 def test_size_queries_without_gpu(lib):
@@ -41,6 +41,30 @@ def test_size_queries_without_gpu(lib):
     offs = np.array([0, 500, 500, 2000], dtype=np.int64)
     seg = lib.rotgeo_nms_workspace_bytes(2000, offs.ctypes.data, 3)
     assert 0 < seg < one            # block-diagonal mask is smaller than the full one
+
+
+def test_nms_front_end_size_queries_and_bounds(lib):
+    """the device-planned NMS is sized on the host: worst-case bounds from the group sizes"""
+    sizes = np.zeros(6, dtype=np.int64)
+    assert lib.rotgeo_nms_bounds(10000, None, 1, 5, sizes.ctypes.data) == 0
+    n_pad, tiles, words, maxb, nseg, n_emit = sizes.tolist()
+    C = (10000 + 127) // 128
+    assert n_pad == (C + 4) * 128 and maxb == C and nseg == 5 and n_emit == 10000
+    assert tiles >= 5 * (16 * 17 // 2) and words >= 5 * 2000 * 2 * 16      # covers 5 levels x 2000
+    one = lib.rotgeo_nms_run_bytes(10000, sizes.ctypes.data)
+    g = np.array([2000] * 5, dtype=np.int64)
+    assert lib.rotgeo_nms_bounds(10000, g.ctypes.data, 5, 1, sizes.ctypes.data) == 0
+    assert sizes[0] == 5 * 16 * 128 and sizes[1] == 5 * (16 * 17 // 2) and sizes[4] == 5
+    assert 0 < lib.rotgeo_nms_run_bytes(10000, sizes.ctypes.data) < one
+    assert lib.rotgeo_nms_sort_bytes(10000, g.ctypes.data, 5, 1) > 3 * 4 * 10000
+    assert lib.rotgeo_nms_sort_bytes(10000, g.ctypes.data, 4, 1) == 0        # sizes do not add up
+    assert lib.rotgeo_nms_bounds(10000, g.ctypes.data, 4, 1, sizes.ctypes.data) == -1
+    # argument errors before any launch
+    assert lib.rotgeo_nms_sort(None, 10, 5, None, None, 0, None, 1, 1, None, 0, None) == -1
+    ok = np.array([128, 1, 2, 1, 1, 10], dtype=np.int64)
+    assert lib.rotgeo_nms_run(None, 10, 5, None, 0, None, 1, 1, None, ok.ctypes.data, 0.0, None, None, None,
+                              None, 0, None) == -1
+    assert b'positive' in lib.rotgeo_last_error()
 
 
 def test_argument_errors_do_not_need_a_gpu(lib):

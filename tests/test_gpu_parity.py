@@ -334,7 +334,7 @@ def test_nms_chain_needs_many_rounds(n):
 
 def test_batched_nms_id_ranges_and_split_path(monkeypatch):
     """ids of batched_nms are arbitrary integers: negative, sparse, spread over more than
-    2**16 values (rotgeo_nms_prepare reports ROTGEO_ERR_RANGE and the caller splits), and
+    2**16 values (the front-end flags the range and the caller renumbers and splits), and
     more segments than one call takes."""
     from orientedobjectdetection_b200 import ops
     n = 3000
@@ -392,7 +392,7 @@ def test_nms_images_c4_batch_vs_per_image_calls():
 
 
 def test_nms_images_fused_batch_edge_cases():
-    """The device-side batch front-end (rotgeo_nms_batch_prepare / _finish) against the
+    """The device-side batch front-end (one group per image, rotgeo_nms_sort / _run) against the
     per-image oracle: empty images first / in the middle / last, a one-box image, images whose
     ids use different ranges, negative ids, no cut; and ids too spread out for 16-bit segment
     keys, which must take the generic path and give the same lists."""
@@ -420,9 +420,9 @@ def test_nms_images_fused_batch_edge_cases():
                                                 torch.from_numpy(np.asarray(i, np.int64)), 0.5)
             want = wk.tolist() if cut < 0 else wk[:cut].tolist()
             assert g.cpu().tolist() == want
-    # ids spanning more than 65536 / images values: rotgeo_nms_batch_prepare reports the range,
-    # the seam falls back to the generic front-end
-    wide = [(b, s, torch.where(i % 2 == 0, i, i + 40000)) for b, s, i in dev_imgs]
+    # ids of ONE image spanning 65536 values or more: the device front-end flags the range, the
+    # seam falls back to the generic path (renumbered ids)
+    wide = [(b, s, torch.where(i % 2 == 0, i, i + 400000)) for b, s, i in dev_imgs]
     assert ops._nms_keep_images(torch.cat([b for b, _, _ in wide]), torch.cat([s for _, s, _ in wide]),
                                 torch.cat([i for _, _, i in wide]), [int(b.shape[0]) for b, _, _ in wide],
                                 0.5) is None
