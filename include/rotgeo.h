@@ -91,6 +91,25 @@ int rotgeo_iou_pairwise(const float *boxes1, int64_t n1, int stride1, const floa
 int rotgeo_iou_pairwise_packed(const void *packed1, int64_t n1, const void *packed2, int64_t n2,
                                int mode, float *out, int64_t ld_out, void *stream);
 
+/* ---- rotated IoU without any allocation by anybody -----------------------------
+ * NO COUNTERPART IN THE REFERENCE: added for callers
+ * that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  Same result as rotgeo_iou_pairwise (the same two kernels); the packed box
+ * sets live in a file-scope __device__ array of ROTGEO_STATIC_SCRATCH_BYTES inside the
+ * library instead of a caller-owned workspace, so the call takes inputs and the output only
+ * and calls no cudaMalloc / cudaFree / allocating routine.  Every GPU that loads the library
+ * holds the array until exit.
+ *   limit   padded_count(n1) + padded_count(n2) <= 16384 boxes (each count rounded up to a
+ *           multiple of 128; 8192 x 8192 fits); beyond it ROTGEO_ERR_WORKSPACE with text.
+ *   state   all calls share the array and it keeps the last call's contents; nothing in it
+ *           has to start from zero (every slot read is rewritten first).  Calls that OVERLAP
+ *           on the GPU (different streams, unordered graph branches) race; calls on one
+ *           stream are ordered and safe. */
+#define ROTGEO_STATIC_SCRATCH_BYTES (2 * 8192 * 96)
+int rotgeo_iou_pairwise_static(const float *boxes1, int64_t n1, int stride1, const float *boxes2,
+                               int64_t n2, int stride2, int mode, float min_wh, float *out,
+                               int64_t ld_out, void *stream);
+
 /* aligned=True variant: out[i] = IoU(boxes1[i], boxes2[i]). */
 int rotgeo_iou_aligned(const float *boxes1, const float *boxes2, int64_t n, int stride1,
                        int stride2, int mode, float min_wh, float *out, void *stream);

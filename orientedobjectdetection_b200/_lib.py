@@ -13,7 +13,7 @@ SO_PATH = os.path.join(_PKG, 'librotgeo.so')
 SYMBOLS = (
     'rotgeo_version', 'rotgeo_last_error', 'rotgeo_packed_bytes', 'rotgeo_pack_boxes',
     'rotgeo_iou_workspace_bytes', 'rotgeo_iou_pairwise', 'rotgeo_iou_pairwise_packed',
-    'rotgeo_iou_aligned', 'rotgeo_nms_workspace_bytes', 'rotgeo_nms',
+    'rotgeo_iou_aligned', 'rotgeo_iou_pairwise_static', 'rotgeo_nms_workspace_bytes', 'rotgeo_nms',
     'rotgeo_iou_max_workspace_bytes', 'rotgeo_iou_rowcol_max', 'rotgeo_max_iou_assign',
     'rotgeo_eval_tpfp_workspace_bytes', 'rotgeo_eval_tpfp',
     'rotgeo_diff_iou_aligned',
@@ -54,6 +54,8 @@ def load():
     L.rotgeo_iou_pairwise.restype = i32
     L.rotgeo_iou_pairwise_packed.argtypes = [vp, i64, vp, i64, i32, vp, i64, vp]
     L.rotgeo_iou_pairwise_packed.restype = i32
+    L.rotgeo_iou_pairwise_static.argtypes = [vp, i64, i32, vp, i64, i32, i32, f32, vp, i64, vp]
+    L.rotgeo_iou_pairwise_static.restype = i32
     L.rotgeo_iou_aligned.argtypes = [vp, vp, i64, i32, i32, i32, f32, vp, vp]
     L.rotgeo_iou_aligned.restype = i32
     L.rotgeo_nms_workspace_bytes.argtypes = [i64, vp, i64]

@@ -31,6 +31,17 @@ inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
 }  // namespace
 
+namespace rotgeo {
+// the same thread-local error text for entry points that live in other translation units
+int abi_fail(int code, const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+}  // namespace rotgeo
+
 extern "C" {
 
 int rotgeo_version(void) { return 2000; }   // 2000: rotgeo_nms_sort / _bounds / _read_plan / _run replace the prepare family
