@@ -362,7 +362,7 @@ int rotgeo_nms_sort(const float *boxes, int64_t n, int stride, const float *scor
         return fail(ROTGEO_ERR_WORKSPACE, "nms_sort: buffer %zu < %zu bytes or misaligned", sortws_bytes, need);
     const int rc = rotgeo::nms_sort(boxes, n, stride, scores, seg_ids, id_offsets, group_sizes_host, num_groups,
                                     seg_cap, sortws, (cudaStream_t)stream);
-    if (rc == -6) return fail(ROTGEO_ERR_RANGE, "nms_sort: a group of more than sms * 12288 boxes");
+    if (rc == -6) return fail(ROTGEO_ERR_RANGE, "nms_sort: a group of more than sms * 8192 boxes");
     if (rc == -1) return fail(ROTGEO_ERR_ARG, "nms_sort: bad group sizes");
     if (rc) return cuda_fail("nms_sort");
     return ROTGEO_OK;

@@ -202,9 +202,9 @@ int launch_nms_device_planned(const NmsDevLaunch &a, cudaStream_t stream);
 
 // ---- sort front-end (rotgeo_sort.cu) ------------------------------------------------------------
 constexpr int kSortThreads = 1024;
-constexpr int kSortItems = 12;
-constexpr int kSortCap = kSortThreads * kSortItems;   // elements per CTA: 12 288
-constexpr int kSortMaxCluster = 8;                    // portable cluster size: 98 304 elements per group in shared memory
+constexpr int kSortItems = 8;
+constexpr int kSortCap = kSortThreads * kSortItems;   // elements per CTA: 8192
+constexpr int kSortMaxCluster = 8;                    // portable cluster size: 65 536 elements per group in shared memory
 constexpr int kSortGroupsInline = 64;                 // group tables up to this size travel as kernel parameters
 constexpr int64_t kSortSegsMax = 16384;               // segments one call handles
 constexpr unsigned int kSortErrRange = 1u;            // the ids of a group span 2^16 values or more
@@ -232,6 +232,7 @@ struct SortArgs {
     int id_offsets;            // mode 0 with ids: offsets_out[row] = float(id) * (max(cx,cy) + max(w,h) + 1) of the row's group
     int ngroups;
     int seg_cap;               // segments per group
+    int cta_cap;               // elements per CTA buffer of the cluster kernel (set by launch_sort)
     const int64_t *gstart;     // device (ngroups + 1) row offsets, or null: gstart_inline
     int64_t gstart_inline[kSortGroupsInline + 1];
     // outputs (carved from the sort workspace by launch_sort)

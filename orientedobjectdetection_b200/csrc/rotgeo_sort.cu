@@ -12,24 +12,28 @@
 // together in descending score order (a whole nms_rotated / batched_nms / multiclass call, one image
 // of an RPN batch, one class of a patch merge).  Inside a group, boxes of equal id form a SEGMENT
 // (class, FPN level): suppression never crosses segments.  One thread-block CLUSTER (1, 2, 4 or 8
-// CTAs, 12 288 elements each) owns a group and keeps it in (distributed) shared memory from the
-// first load to the last store:
+// CTAs, up to 8192 elements each) owns a group and keeps it in (distributed) shared memory from
+// the first load to the last store; an element is one 8-byte (key, source index) pair:
 //
 //   load     32-bit key = descending image of the score (multiclass: candidate filter on the raw
 //            score, stable compaction of the candidates across the cluster), extremes of the ids,
 //            max(cx, cy) / max(w, h) of the offset formula, all reduced across the cluster
-//   sort 1   4 LSD radix passes (8 bits) over the keys, payload = index: stable, so equal scores
-//            keep their index order.  Per pass: warp-level ranking with match.any (no atomics),
-//            per-CTA digit histogram, histograms exchanged through DISTRIBUTED SHARED MEMORY,
-//            scatter straight into the owning CTA's shared memory (st.shared::cluster), two
-//            cluster barriers.  -> `order` (emission order)
-//   sort 2   1-2 more stable passes on (id - min id) with payload = score position: segment-major
-//            order, score order inside a segment.  -> `seg_order`, `seg_rank`, segment starts
-//   plan     the cluster that finishes last (atomic ticket) turns the segment sizes of ALL groups
-//            into the segment table, tile / mask / slot totals the host used to compute after a
-//            device->host read (nms_plan() in rotgeo_nms.cu), and leaves them in a device header.
+//   sort 1   4 stable LSD radix passes (8 bits) over the keys -> `order` (emission order).  Per
+//            pass: every element is ranked inside its warp with 8 ballots (no atomics; match.any
+//            is serialised by the hardware over the ~30 distinct digits of a warp), per-warp
+//            counters in a padded digit-major table are prefix-summed by (digit, quarter) threads,
+//            the CTA histograms are exchanged through DISTRIBUTED SHARED MEMORY, the elements are
+//            first reordered by digit inside the CTA and only then copied to their owners, so
+//            that a warp's remote stores are a few contiguous runs instead of 32 scattered words
+//            (measured: 7500 scattered 4-byte st.shared::cluster per CTA and pass took 5.4 us)
+//   sort 2   1-2 more passes on key' = (id - min id) << 16 | score position: segment-major order,
+//            score order inside a segment -> `seg_order`, `seg_rank`, segment starts
+//   plan     the segment table and the slot / tile / mask-word totals the host used to compute
+//            after a device->host read (nms_plan() in rotgeo_nms.cu), left in a device header:
+//            from shared memory when the call is one group, else by the cluster that finishes
+//            last (atomic ticket) from the per-group results.
 //
-// Groups beyond one cluster's capacity (98 304 elements) take the same code with the element
+// Groups beyond one cluster's capacity (65 536 elements) take the same code with the element
 // buffers and the histogram exchange in global memory and a cooperative grid barrier in place of
 // the cluster barrier (template parameter GLOBAL).
 #include <cooperative_groups.h>
@@ -47,9 +51,11 @@ namespace {
 
 constexpr int kThreads = kSortThreads;          // 1024
 constexpr int kWarps = kThreads / 32;
-constexpr int kItems = kSortItems;              // 12
+constexpr int kItems = kSortItems;              // 8
 constexpr int kCap = kSortCap;                  // elements per CTA
 constexpr int kTile = 128;
+constexpr int kCntRow = kWarps + 2;             // u16 per digit row: 17 words, so digits fall into different banks
+constexpr int kPlanLocal = 320;                 // segments of a single-group call planned from shared memory
 
 // float -> unsigned whose integer order is the float order
 __device__ __forceinline__ unsigned int ordered_bits(float f) {
@@ -72,16 +78,16 @@ struct Red {
 };
 
 struct __align__(16) SortSmem {
-    unsigned short cnt[kWarps][256];    // per-warp digit counters, then exclusive prefixes over the warps
+    unsigned short cnt[256][kCntRow];   // [digit][warp]: per-warp counters, then exclusive prefixes over the warps
     unsigned int hist[256];             // this CTA's digit histogram (read by the whole cluster)
-    unsigned int tot[256];              // digit totals of the group
-    unsigned int dbase[256];            // first destination of (digit, this CTA)
-    unsigned int wsum[kWarps];
+    unsigned int lstart[256];           // first staging slot of a digit inside this CTA
+    unsigned int dbase[256];            // first destination of (digit, this CTA) in the group
+    unsigned int wsum[2][kWarps + 1];
+    unsigned int gs_local[kPlanLocal + 1];   // rank 0 of a single-group call: the segment starts
     Red red;
     unsigned int bcount;                // segment boundaries in this CTA
     int skip;                           // every key of the group has the same digit: nothing moves
     int last;                           // this cluster took the last ticket: it makes the plan
-    long long carry[4];
 };
 
 // ---- team = the CTAs that own one group: a cluster (shared memory) or the cooperative grid (global) ----
@@ -89,13 +95,16 @@ template <bool GLOBAL>
 struct Team {
     int rank, size;
     SortSmem *sm;
-    // element buffers: CLUSTER -> this CTA's shared arrays of kCap entries; GLOBAL -> global arrays
-    // of the whole group (index = position)
-    uint32_t *key[2], *val[2];
+    // two element buffers: CLUSTER -> this CTA's shared arrays of `stride` entries; GLOBAL -> global
+    // arrays of the whole group (index = position).  stage: always this CTA's shared memory.
+    uint2 *base;
+    uint32_t stride;
+    uint2 *stage;
     unsigned int *ghist;     // GLOBAL: [size][256]
     Red *gred;               // GLOBAL: [size]
     unsigned int *gcount;    // GLOBAL: [size] boundary counts
 
+    __device__ __forceinline__ uint2 *buf(int c) const { return base + (size_t)c * stride; }
     __device__ __forceinline__ void sync() const {
         if (GLOBAL) {
             __threadfence();
@@ -105,27 +114,27 @@ struct Team {
         }
     }
     // element at local position lp of this CTA (share = positions per CTA)
-    __device__ __forceinline__ uint32_t ld(const uint32_t *buf, uint32_t share, uint32_t lp) const {
-        return GLOBAL ? __ldcg(buf + (size_t)rank * share + lp) : buf[lp];
+    __device__ __forceinline__ uint2 ld(int c, uint32_t share, uint32_t lp) const {
+        return GLOBAL ? __ldcg(buf(c) + (size_t)rank * share + lp) : buf(c)[lp];
     }
-    __device__ __forceinline__ void st_local(uint32_t *buf, uint32_t share, uint32_t lp, uint32_t v) const {
-        if (GLOBAL) __stcg(buf + (size_t)rank * share + lp, v); else buf[lp] = v;
+    __device__ __forceinline__ void st_local(int c, uint32_t share, uint32_t lp, uint2 v) const {
+        if (GLOBAL) __stcg(buf(c) + (size_t)rank * share + lp, v); else buf(c)[lp] = v;
     }
     // element at group position p (lands in the shared memory of CTA p / share)
-    __device__ __forceinline__ void st_pos(uint32_t *buf, uint32_t share, uint32_t p, uint32_t v) const {
+    __device__ __forceinline__ void st_pos(int c, uint32_t share, uint32_t p, uint2 v) const {
         if (GLOBAL) {
-            __stcg(buf + p, v);
+            __stcg(buf(c) + p, v);
         } else {
-            const uint32_t c = p / share;
-            uint32_t *dst = cg::this_cluster().map_shared_rank(buf, c);
-            dst[p - c * share] = v;
+            const uint32_t r = p / share;
+            uint2 *dst = (int)r == rank ? buf(c) : cg::this_cluster().map_shared_rank(buf(c), r);
+            dst[p - r * share] = v;
         }
     }
-    __device__ __forceinline__ uint32_t ld_pos(const uint32_t *buf, uint32_t share, uint32_t p) const {
-        if (GLOBAL) return __ldcg(buf + p);
-        const uint32_t c = p / share;
-        const uint32_t *src = cg::this_cluster().map_shared_rank(const_cast<uint32_t *>(buf), c);
-        return src[p - c * share];
+    __device__ __forceinline__ uint32_t ld_pos_key(int c, uint32_t share, uint32_t p) const {
+        if (GLOBAL) return __ldcg(&buf(c)[p].x);
+        const uint32_t r = p / share;
+        const uint2 *src = cg::this_cluster().map_shared_rank(buf(c), r);
+        return src[p - r * share].x;
     }
     __device__ __forceinline__ void publish_hist(int d, unsigned int v) const {
         sm->hist[d] = v;
@@ -151,6 +160,10 @@ struct Team {
         }
         return *cg::this_cluster().map_shared_rank(&sm->red, c);
     }
+    __device__ __forceinline__ unsigned int peer_count(int c) const {
+        if (GLOBAL) return *reinterpret_cast<const volatile unsigned int *>(&gred[c].count);
+        return cg::this_cluster().map_shared_rank(&sm->red, c)->count;
+    }
     __device__ __forceinline__ void publish_bcount(unsigned int v) const {
         sm->bcount = v;
         if (GLOBAL) __stcg(gcount + rank, v);
@@ -158,6 +171,12 @@ struct Team {
     __device__ __forceinline__ unsigned int peer_bcount(int c) const {
         if (GLOBAL) return __ldcg(gcount + c);
         return *cg::this_cluster().map_shared_rank(&sm->bcount, c);
+    }
+    // rank 0's copy of the segment starts (single-group calls, cluster path only)
+    __device__ __forceinline__ void st_gs_rank0(uint32_t idx, unsigned int v) const {
+        if (GLOBAL) return;
+        unsigned int *dst = rank == 0 ? sm->gs_local : cg::this_cluster().map_shared_rank(sm->gs_local, 0);
+        dst[idx] = v;
     }
 };
 
@@ -171,28 +190,75 @@ __device__ __forceinline__ uint32_t count_of(uint32_t n, uint32_t share, int ran
     return lo >= n ? 0u : (n - lo < share ? (uint32_t)(n - lo) : share);
 }
 
-// exclusive scan of one value per thread over the block; returns the exclusive prefix, total in `total`
-__device__ __forceinline__ long long block_exclusive_scan(long long v, long long *s_warp /* kWarps */, long long &total) {
+// exclusive scan of one value per thread over the block; returns the exclusive prefix, total in `total`.
+// Two levels: warp scans, then warp 0 scans the 32 warp sums (every thread reading all 32 sums cost
+// ~1 us of shared-memory bandwidth per scan with 1024 threads).  s_warp: kWarps + 1 entries.
+template <typename V>
+__device__ __forceinline__ V block_exclusive_scan(V v, V *s_warp, V &total) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    long long incl = v;
+    V incl = v;
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
-        const long long t = __shfl_up_sync(0xffffffffu, incl, d);
+        const V t = __shfl_up_sync(0xffffffffu, incl, d);
         if (lane >= d) incl += t;
     }
-    __syncthreads();
+    __syncthreads();                       // s_warp may still be read from the previous scan
     if (lane == 31) s_warp[warp] = incl;
     __syncthreads();
-    long long before = 0, tot = 0;
+    if (warp == 0) {
+        const V w = s_warp[lane];          // kWarps == 32
+        V wi = w;
 #pragma unroll
-    for (int w = 0; w < kWarps; ++w) {
-        const long long c = s_warp[w];
-        before += w < warp ? c : 0;
-        tot += c;
+        for (int d = 1; d < 32; d <<= 1) {
+            const V t = __shfl_up_sync(0xffffffffu, wi, d);
+            if (lane >= d) wi += t;
+        }
+        s_warp[lane] = wi - w;
+        if (lane == 31) s_warp[kWarps] = wi;
     }
-    total = tot;
-    return before + incl - v;
+    __syncthreads();
+    total = s_warp[kWarps];
+    return s_warp[warp] + incl - v;
 }
+
+// `run` is a warp-uniform count; returns the sum over the warps before mine, `total` = all warps.
+// s: kWarps + 1 entries.
+__device__ __forceinline__ unsigned int warp_totals_exclusive(unsigned int run, unsigned int *s, unsigned int &total) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    __syncthreads();
+    if (lane == 0) s[warp] = run;
+    __syncthreads();
+    if (warp == 0) {
+        const unsigned int w = s[lane];
+        unsigned int wi = w;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const unsigned int t = __shfl_up_sync(0xffffffffu, wi, d);
+            if (lane >= d) wi += t;
+        }
+        s[lane] = wi - w;
+        if (lane == 31) s[kWarps] = wi;
+    }
+    __syncthreads();
+    total = s[kWarps];
+    return s[warp];
+}
+
+#ifdef ROTGEO_SORT_TIMING   // probe builds (tools/sort_phases.py): clocks of one pass and of the phases of group 0
+#define PT_DECL unsigned long long pt_[12]; int ptn_ = 0;
+#define PT_MARK do { if (blockIdx.x == 0 && threadIdx.x == 0 && shift == 8 && ptn_ < 12) { asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(pt_[ptn_])); ++ptn_; } } while (0)
+#define PT_PRINT do { if (blockIdx.x == 0 && threadIdx.x == 0 && shift == 8) { printf("  pass steps (us):"); for (int i_ = 1; i_ < ptn_; ++i_) printf(" %.2f", (double)(pt_[i_] - pt_[i_ - 1]) * 1e-3); printf("\n"); } } while (0)
+#define ST_DECL unsigned long long st_[24]; int stn_ = 0;
+#define ST_MARK do { if (g == 0 && T.rank == 0 && threadIdx.x == 0 && stn_ < 24) { asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(st_[stn_])); ++stn_; } } while (0)
+#define ST_PRINT do { if (g == 0 && T.rank == 0 && threadIdx.x == 0) { printf("sort phases (us), n=%u size=%d:", n, T.size); for (int i_ = 1; i_ < stn_; ++i_) printf(" %.1f", (double)(st_[i_] - st_[i_ - 1]) * 1e-3); printf("\n"); } } while (0)
+#else
+#define PT_DECL
+#define PT_MARK do {} while (0)
+#define PT_PRINT do {} while (0)
+#define ST_DECL
+#define ST_MARK do {} while (0)
+#define ST_PRINT do {} while (0)
+#endif
 
 // One stable LSD pass over the 8 key bits at `shift`: the n elements of the group move from buffer
 // `cur` to buffer `cur ^ 1`.  Position order inside a CTA = (warp, item, lane), iu items per thread.
@@ -200,90 +266,158 @@ __device__ __forceinline__ long long block_exclusive_scan(long long v, long long
 template <bool GLOBAL>
 __device__ bool radix_pass(const Team<GLOBAL> &T, int cur, int shift, uint32_t n, uint32_t share) {
     SortSmem &sm = *T.sm;
+    PT_DECL
+    PT_MARK;   // 0
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t count = count_of(n, share, T.rank);
     const int iu = (int)((share + kThreads - 1) / kThreads);
     const uint32_t lt = (1u << lane) - 1u;
-    // 1. zero the counters
+    // 1. zero the counters and the match masks (they alias the staging array, dirty from the last pass)
+    unsigned int *const mm = reinterpret_cast<unsigned int *>(T.stage) + warp * 256;   // [warp][digit] lane masks
     {
         uint4 *z = reinterpret_cast<uint4 *>(&sm.cnt[0][0]);
-        z[tid] = make_uint4(0u, 0u, 0u, 0u);      // 32 * 256 * 2 B = 1024 * 16 B
+        constexpr int kZ = 256 * kCntRow * 2 / 16;
+        for (int i = tid; i < kZ; i += kThreads) z[i] = make_uint4(0u, 0u, 0u, 0u);
+        uint4 *zm = reinterpret_cast<uint4 *>(T.stage);
+        for (int i = tid; i < kWarps * 256 * 4 / 16; i += kThreads) zm[i] = make_uint4(0u, 0u, 0u, 0u);
         if (tid == 0) sm.skip = 0;
     }
     __syncthreads();
-    // 2. rank every element among the elements of its warp with the same digit
-    uint32_t dr[kItems];       // digit << 16 | rank inside (warp, digit); 0xffffffff = no element
+    PT_MARK;   // 1 zeroed
+    // 2. rank every element among the elements of its warp with the same digit: the lanes that share
+    //    a digit meet in one shared-memory word (atomicOr of the lane bit, read back) — 3 shared-memory
+    //    operations per element where 8 ballots cost 0.75 us per item (the VOTE pipe) and match.any is
+    //    serialised over the ~30 distinct digits of a warp; then the warp's running count of the digit
+    uint32_t dg[kItems], pm[kItems];       // digit (0xffffffff = no element), rank inside (warp, digit)
 #pragma unroll
     for (int i = 0; i < kItems; ++i) {
-        dr[i] = 0xffffffffu;
+        dg[i] = 0xffffffffu;
+        pm[i] = 0u;
         if (i < iu) {                                  // warp-uniform
             const uint32_t lp = (uint32_t)warp * 32u * iu + (uint32_t)i * 32u + lane;
             const bool active = lp < count;
-            const uint32_t d = active ? ((T.ld(T.key[cur], share, lp) >> shift) & 0xffu) : (0x10000u + lane);
-            const uint32_t peers = __match_any_sync(0xffffffffu, d);
-            unsigned int base = 0;
-            if (active) base = sm.cnt[warp][d];
+            const uint32_t d = active ? ((T.ld(cur, share, lp).x >> shift) & 0xffu) : 0u;
+            if (active) atomicOr(mm + d, 1u << lane);
             __syncwarp();
-            if (active && (peers & lt) == 0u) sm.cnt[warp][d] = (unsigned short)(base + __popc(peers));
+            uint32_t peers = 0u;
+            unsigned int base = 0u;
+            if (active) {
+                peers = mm[d];
+                base = sm.cnt[d][warp];
+            }
             __syncwarp();
-            if (active) dr[i] = (d << 16) | (base + __popc(peers & lt));
+            if (active) {
+                if ((peers & lt) == 0u) {              // lowest lane of the digit
+                    mm[d] = 0u;
+                    sm.cnt[d][warp] = (unsigned short)(base + __popc(peers));
+                }
+                dg[i] = d;
+                pm[i] = base + __popc(peers & lt);
+            }
+            __syncwarp();
         }
     }
     __syncthreads();
-    // 3. exclusive prefix over the warps, CTA histogram
-    if (tid < 256) {
-        unsigned int run = 0;
-#pragma unroll 8
-        for (int w = 0; w < kWarps; ++w) {
-            const unsigned int c = sm.cnt[w][tid];
-            sm.cnt[w][tid] = (unsigned short)run;
-            run += c;
-        }
-        T.publish_hist(tid, run);
-    }
-    T.sync();
-    // 4. totals of the group and what lies before this CTA
-    unsigned int tot = 0, before = 0;
-    if (tid < 256) {
-        for (int c = 0; c < T.size; ++c) {
-            const unsigned int h = T.peer_hist(c, tid);
-            tot += h;
-            before += c < T.rank ? h : 0u;
-        }
-        if (tot == n) sm.skip = 1;
-    }
+    PT_MARK;   // 2 ranked
+    // 3. exclusive prefix over the warps + the CTA histogram: thread = (digit, quarter of the warps),
+    //    its 8 counters are 4 consecutive words of the digit's row, the quarters joined by shuffles
     {
-        // exclusive scan of the 256 digit totals (warps 0..7)
-        unsigned int incl = tot;
+        const int d = tid >> 2, q = tid & 3;
+        uint32_t *row = reinterpret_cast<uint32_t *>(&sm.cnt[d][0]) + 4 * q;
+        uint32_t w[4];
+        unsigned int c[8], sum = 0;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            w[k] = row[k];
+            c[2 * k] = w[k] & 0xffffu;
+            c[2 * k + 1] = w[k] >> 16;
+            sum += c[2 * k] + c[2 * k + 1];
+        }
+        unsigned int incl = sum;
+#pragma unroll
+        for (int o = 1; o < 4; o <<= 1) {
+            const unsigned int t = __shfl_up_sync(0xffffffffu, incl, o, 4);
+            if (q >= o) incl += t;
+        }
+        unsigned int run = incl - sum;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const unsigned int lo = run;
+            run += c[2 * k];
+            const unsigned int hi = run;
+            run += c[2 * k + 1];
+            row[k] = lo | (hi << 16);
+        }
+        if (q == 3) T.publish_hist(d, incl);
+    }
+    PT_MARK;   // 3 warp prefix
+    T.sync();
+    PT_MARK;   // 4 cluster sync
+    // 4. totals of the group, what lies before this CTA, and two exclusive scans over the digits:
+    //    of the totals (destinations in the group) and of my own histogram (staging slots)
+    {
+        unsigned int tot = 0, before = 0, mine = 0;
+        if (tid < 256) {
+            mine = sm.hist[tid];
+            if (!GLOBAL) {
+                unsigned int h[kSortMaxCluster];
+#pragma unroll
+                for (int c = 0; c < kSortMaxCluster; ++c) h[c] = c < T.size ? T.peer_hist(c, tid) : 0u;
+#pragma unroll
+                for (int c = 0; c < kSortMaxCluster; ++c) {
+                    tot += h[c];
+                    before += c < T.rank ? h[c] : 0u;
+                }
+            } else {
+                for (int c = 0; c < T.size; ++c) {
+                    const unsigned int h = T.peer_hist(c, tid);
+                    tot += h;
+                    before += c < T.rank ? h : 0u;
+                }
+            }
+            if (tot == n) sm.skip = 1;
+        }
+        unsigned int i1 = tot, i2 = mine;
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) {
-            const unsigned int t = __shfl_up_sync(0xffffffffu, incl, d);
-            if (lane >= d) incl += t;
+            const unsigned int t1 = __shfl_up_sync(0xffffffffu, i1, d);
+            const unsigned int t2 = __shfl_up_sync(0xffffffffu, i2, d);
+            if (lane >= d) { i1 += t1; i2 += t2; }
         }
-        if (tid < 256 && lane == 31) sm.wsum[warp] = incl;
+        if (tid < 256 && lane == 31) { sm.wsum[0][warp] = i1; sm.wsum[1][warp] = i2; }
         __syncthreads();
         if (tid < 256) {
-            unsigned int pre = 0;
-            for (int w = 0; w < warp; ++w) pre += sm.wsum[w];
-            sm.dbase[tid] = pre + incl - tot + before;
+            unsigned int p1 = 0, p2 = 0;
+            for (int w = 0; w < warp; ++w) { p1 += sm.wsum[0][w]; p2 += sm.wsum[1][w]; }
+            sm.dbase[tid] = p1 + i1 - tot + before;
+            sm.lstart[tid] = p2 + i2 - mine;
         }
     }
     __syncthreads();
+    PT_MARK;   // 5 totals + digit scans
     const bool moved = sm.skip == 0;
-    // 5. scatter
     if (moved) {
+        // 5. reorder by digit inside the CTA (stable: warp-major, then item, then lane) ...
 #pragma unroll
         for (int i = 0; i < kItems; ++i) {
-            if (i < iu && dr[i] != 0xffffffffu) {
+            if (i < iu && dg[i] != 0xffffffffu) {
                 const uint32_t lp = (uint32_t)warp * 32u * iu + (uint32_t)i * 32u + lane;
-                const uint32_t d = dr[i] >> 16, r = dr[i] & 0xffffu;
-                const uint32_t p = sm.dbase[d] + sm.cnt[warp][d] + r;
-                T.st_pos(T.key[cur ^ 1], share, p, T.ld(T.key[cur], share, lp));
-                T.st_pos(T.val[cur ^ 1], share, p, T.ld(T.val[cur], share, lp));
+                const uint32_t d = dg[i];
+                T.stage[sm.lstart[d] + sm.cnt[d][warp] + pm[i]] = T.ld(cur, share, lp);
             }
         }
+        __syncthreads();
+        // 6. ... and copy the runs to their owners: consecutive threads, consecutive destinations
+        for (uint32_t j = tid; j < count; j += kThreads) {
+            const uint2 e = T.stage[j];
+            const uint32_t d = (e.x >> shift) & 0xffu;
+            T.st_pos(cur ^ 1, share, sm.dbase[d] + (j - sm.lstart[d]), e);
+        }
     }
+    PT_MARK;   // 6 scatter issued
     T.sync();     // also: nobody overwrites its histogram while a peer still reads it
+    PT_MARK;   // 7 cluster sync
+    PT_PRINT;
     return moved;
 }
 
@@ -291,45 +425,21 @@ __device__ __forceinline__ int64_t group_start(const SortArgs &a, int g) {
     return a.gstart ? a.gstart[g] : a.gstart_inline[g];
 }
 
-// the plan nms_plan() makes on the host, made by the last CTA to finish (1024 threads)
-__device__ void make_plan(const SortArgs &a, SortSmem &sm) {
+// The plan nms_plan() makes on the host: segment table + totals, by one CTA (1024 threads).
+// fetch(j, start, len): first position (in seg_order) and length of segment j of all Tc segments.
+template <typename Fetch>
+__device__ void emit_plan(const SortArgs &a, long long Tc, unsigned int err, Fetch fetch) {
     const int tid = threadIdx.x;
-    __shared__ long long s_warp[kWarps];
+    __shared__ long long s_warp[kWarps + 1];
     __shared__ int s_maxc[kWarps];
-    // segments before each group
-    long long carry = 0;
-    for (int base = 0; base < a.ngroups; base += kThreads) {
-        const int g = base + tid;
-        long long v = 0;
-        if (g < a.ngroups) v = __ldcg(a.gseg_count + g);
-        long long tot;
-        const long long ex = block_exclusive_scan(v, s_warp, tot);
-        if (g < a.ngroups) a.gseg_off[g] = (int)(carry + ex);
-        carry += tot;
-    }
-    const long long T = carry;
-    __threadfence_block();
-    __syncthreads();
-    unsigned int err = 0;
-    if (T > a.segs_cap) err |= kSortErrSegments;
     long long slots = 0, words = 0, tiles = 0;
     int maxc = 0;
-    const long long Tc = T > a.segs_cap ? a.segs_cap : T;
     for (long long base = 0; base < Tc; base += kThreads) {
         const long long j = base + tid;
         long long len = 0, C = 0, start = 0;
         if (j < Tc) {
-            int lo = 0, hi = a.ngroups - 1;     // last group with gseg_off <= j (groups without segments share offsets)
-            while (lo < hi) {
-                const int mid = (lo + hi + 1) >> 1;
-                if (a.gseg_off[mid] <= j) lo = mid; else hi = mid - 1;
-            }
-            const int k = (int)(j - a.gseg_off[lo]);
-            const uint32_t *gs = a.gseg_start + (size_t)lo * (a.seg_cap + 1);
-            const long long s0 = __ldcg(gs + k), s1 = __ldcg(gs + k + 1);
-            len = s1 - s0;
+            fetch(j, start, len);
             C = (len + kTile - 1) / kTile;
-            start = (a.mode == 1 ? 0 : group_start(a, lo)) + s0;
         }
         long long t1, t2, t3;
         const long long e1 = block_exclusive_scan(C * kTile, s_warp, t1);
@@ -366,6 +476,46 @@ __device__ void make_plan(const SortArgs &a, SortSmem &sm) {
     }
 }
 
+// several groups: from the per-group results in global memory, by the cluster that finished last
+__device__ void make_plan(const SortArgs &a) {
+    const int tid = threadIdx.x;
+    __shared__ long long s_warp2[kWarps + 1];
+    long long carry = 0;                  // segments before each group
+    for (int base = 0; base < a.ngroups; base += kThreads) {
+        const int g = base + tid;
+        long long v = 0;
+        if (g < a.ngroups) v = __ldcg(a.gseg_count + g);
+        long long tot;
+        const long long ex = block_exclusive_scan(v, s_warp2, tot);
+        if (g < a.ngroups) a.gseg_off[g] = (int)(carry + ex);
+        carry += tot;
+    }
+    const long long Tall = carry;
+    __threadfence_block();
+    __syncthreads();
+    const long long Tc = Tall > a.segs_cap ? a.segs_cap : Tall;
+    emit_plan(a, Tc, Tall > a.segs_cap ? kSortErrSegments : 0u, [&](long long j, long long &start, long long &len) {
+        int lo = 0, hi = a.ngroups - 1;     // last group with gseg_off <= j (groups without segments share offsets)
+        while (lo < hi) {
+            const int mid = (lo + hi + 1) >> 1;
+            if (a.gseg_off[mid] <= j) lo = mid; else hi = mid - 1;
+        }
+        const int k = (int)(j - a.gseg_off[lo]);
+        const uint32_t *gs = a.gseg_start + (size_t)lo * (a.seg_cap + 1);
+        const long long s0 = __ldcg(gs + k), s1 = __ldcg(gs + k + 1);
+        len = s1 - s0;
+        start = (a.mode == 1 ? 0 : group_start(a, lo)) + s0;
+    });
+}
+
+// one group: the segment starts are in rank 0's shared memory (gs_local[0 .. nseg], the last = n)
+__device__ void make_plan_local(const SortArgs &a, const SortSmem &sm, int nseg) {
+    emit_plan(a, nseg, 0u, [&](long long j, long long &start, long long &len) {
+        start = sm.gs_local[j];
+        len = (long long)sm.gs_local[j + 1] - start;
+    });
+}
+
 // everything one team does for one group
 template <bool GLOBAL>
 __device__ void sort_group(const SortArgs &a, int g, Team<GLOBAL> &T) {
@@ -375,12 +525,16 @@ __device__ void sort_group(const SortArgs &a, int g, Team<GLOBAL> &T) {
     const int64_t g0 = group_start(a, g);
     const uint32_t n_in = (uint32_t)(group_start(a, g + 1) - g0);    // rows (mode 1: flat candidates)
     const bool mc = a.mode == 1;
+    const bool fast_plan = !GLOBAL && a.ngroups == 1;
+    ST_DECL
+    ST_MARK;   // 0 start
 
     if (tid == 0) {
         sm.red.id_max = 0ull; sm.red.id_min_inv = 0ull; sm.red.max_xy = 0u; sm.red.max_wh = 0u;
         sm.red.count = 0u; sm.red.pad = 0u;
         sm.bcount = 0u;
         sm.last = 0;
+        sm.gs_local[0] = 0u;
     }
     __syncthreads();
 
@@ -394,7 +548,6 @@ __device__ void sort_group(const SortArgs &a, int g, Team<GLOBAL> &T) {
         unsigned long long idmx = 0ull, idmn = 0ull;
         unsigned int mxy = 0u, mwh = 0u;
         uint32_t kv[kItems];          // keys of my elements (multiclass: 0xffffffff = not a candidate)
-        unsigned int nvalid = 0;
 #pragma unroll
         for (int i = 0; i < kItems; ++i) {
             kv[i] = 0xffffffffu;
@@ -422,7 +575,6 @@ __device__ void sort_group(const SortArgs &a, int g, Team<GLOBAL> &T) {
                         uint32_t key = 0xffffffffu - ordered_bits(sc + 0.0f);
                         if (mc && key == 0xffffffffu) key = 0xfffffffeu;     // -NaN payloads only
                         kv[i] = key;
-                        ++nvalid;
                         if (mc || a.ids) {
                             mxy = max(mxy, ordered_bits(fmaxf(b[0], b[1])));
                             mwh = max(mwh, ordered_bits(fmaxf(b[2], b[3])));
@@ -433,10 +585,7 @@ __device__ void sort_group(const SortArgs &a, int g, Team<GLOBAL> &T) {
                             idmn = max(idmn, ~u);
                         }
                     }
-                    if (!mc) {
-                        T.st_local(T.key[0], share, lp, kv[i]);
-                        T.st_local(T.val[0], share, lp, q);
-                    }
+                    if (!mc) T.st_local(0, share, lp, make_uint2(kv[i], q));
                 }
             }
         }
@@ -469,24 +618,30 @@ __device__ void sort_group(const SortArgs &a, int g, Team<GLOBAL> &T) {
                     run += __popc(bal);
                 }
             }
-            if (lane == 0) sm.wsum[warp] = run;
-            __syncthreads();
-            unsigned int wbefore = 0, ctot = 0;
-#pragma unroll
-            for (int w = 0; w < kWarps; ++w) {
-                const unsigned int c = sm.wsum[w];
-                wbefore += w < warp ? c : 0u;
-                ctot += c;
-            }
+            unsigned int ctot;
+            const unsigned int wbefore = warp_totals_exclusive(run, sm.wsum[0], ctot);
             if (tid == 0) sm.red.count = ctot;
             __syncthreads();
             T.publish_red();
             T.sync();
             unsigned int before = 0, total = 0;
-            for (int c = 0; c < T.size; ++c) {
-                const unsigned int h = T.peer_red(c).count;
-                total += h;
-                before += c < T.rank ? h : 0u;
+            {
+                unsigned int h[kSortMaxCluster];
+                if (!GLOBAL) {
+#pragma unroll
+                    for (int c = 0; c < kSortMaxCluster; ++c) h[c] = c < T.size ? T.peer_count(c) : 0u;
+#pragma unroll
+                    for (int c = 0; c < kSortMaxCluster; ++c) {
+                        total += h[c];
+                        before += c < T.rank ? h[c] : 0u;
+                    }
+                } else {
+                    for (int c = 0; c < T.size; ++c) {
+                        const unsigned int v = T.peer_count(c);
+                        total += v;
+                        before += c < T.rank ? v : 0u;
+                    }
+                }
             }
             n = total;
             const uint32_t share2 = share_of(n, T.size);
@@ -495,9 +650,7 @@ __device__ void sort_group(const SortArgs &a, int g, Team<GLOBAL> &T) {
                 if (i < iu && kv[i] != 0xffffffffu) {
                     const uint32_t lp = (uint32_t)warp * 32u * iu + (uint32_t)i * 32u + lane;
                     const uint32_t q = (uint32_t)T.rank * share + lp;
-                    const uint32_t p = before + wbefore + rk[i];
-                    T.st_pos(T.key[0], share2, p, kv[i]);
-                    T.st_pos(T.val[0], share2, p, q);
+                    T.st_pos(0, share2, before + wbefore + rk[i], make_uint2(kv[i], q));
                 }
             }
             share = share2;
@@ -507,11 +660,22 @@ __device__ void sort_group(const SortArgs &a, int g, Team<GLOBAL> &T) {
             T.publish_red();
             T.sync();
         }
-        (void)nvalid;
     }
     // group-wide reductions
     Red R;
-    {
+    if (!GLOBAL) {
+        Red o[kSortMaxCluster];       // all remote reads in flight together
+#pragma unroll
+        for (int c = 0; c < kSortMaxCluster; ++c) o[c] = T.peer_red(c < T.size ? c : 0);
+        R = o[0];
+#pragma unroll
+        for (int c = 1; c < kSortMaxCluster; ++c) {
+            R.id_max = max(R.id_max, o[c].id_max);
+            R.id_min_inv = max(R.id_min_inv, o[c].id_min_inv);
+            R.max_xy = max(R.max_xy, o[c].max_xy);
+            R.max_wh = max(R.max_wh, o[c].max_wh);
+        }
+    } else {
         R = T.peer_red(0);
         for (int c = 1; c < T.size; ++c) {
             const Red o = T.peer_red(c);
@@ -530,15 +694,21 @@ __device__ void sort_group(const SortArgs &a, int g, Team<GLOBAL> &T) {
         id_range = 1ull;
     }
     const float off_unit = __fadd_rn(__fadd_rn(ordered_float(R.max_xy), ordered_float(R.max_wh)), 1.0f);
+    ST_MARK;   // 1 load + reductions
 
     // ---------------------------------------------------------------- sort 1: score order
-    for (int shift = 0; shift < 32; shift += 8)
+    for (int shift = 0; shift < 32; shift += 8) {
         if (radix_pass(T, cur, shift, n, share)) cur ^= 1;
+        ST_MARK;   // 2..5 passes
+    }
 
     const uint32_t count = count_of(n, share, T.rank);
     const int iu = (int)((share + kThreads - 1) / kThreads);
     const int64_t obase = mc ? 0 : g0;       // `order` holds global rows (multiclass: flat candidate indices)
-    // -> order; sort-2 keys in place: key = id - min id, val = position in the score order
+    // -> order; the elements become those of sort 2, in place.  Cluster path: key' = (id - min id) << 16 |
+    // score position (a group in shared memory has at most 65 536 elements), the source index stays
+    // the payload, so nothing has to be gathered afterwards.  Global path: key' = id - min id, payload =
+    // score position, and the source index is gathered from `order` after the passes.
     const bool two = has_ids && !range_bad && id_range > 1ull;
 #pragma unroll
     for (int i = 0; i < kItems; ++i) {
@@ -546,7 +716,7 @@ __device__ void sort_group(const SortArgs &a, int g, Team<GLOBAL> &T) {
             const uint32_t lp = (uint32_t)warp * 32u * iu + (uint32_t)i * 32u + lane;
             if (lp < count) {
                 const uint32_t p = (uint32_t)T.rank * share + lp;
-                const uint32_t idx = T.ld(T.val[cur], share, lp);
+                const uint32_t idx = T.ld(cur, share, lp).y;
                 const uint32_t src = (uint32_t)(obase + idx);
                 a.order[obase + p] = src;
                 uint32_t idk = 0u;
@@ -559,8 +729,7 @@ __device__ void sort_group(const SortArgs &a, int g, Team<GLOBAL> &T) {
                     if (a.id_offsets) a.offsets_out[g0 + idx] = __fmul_rn((float)id, off_unit);
                 }
                 if (two) {
-                    T.st_local(T.key[cur], share, lp, idk);
-                    T.st_local(T.val[cur], share, lp, p);
+                    T.st_local(cur, share, lp, GLOBAL ? make_uint2(idk, p) : make_uint2((idk << 16) | p, idx));
                 } else {
                     a.seg_order[obase + p] = src;
                     a.seg_rank[obase + p] = p;
@@ -568,15 +737,20 @@ __device__ void sort_group(const SortArgs &a, int g, Team<GLOBAL> &T) {
             }
         }
     }
-    __threadfence();
-    T.sync();
+    if (GLOBAL) {          // `order` is read back through global memory below
+        __threadfence();
+        T.sync();
+    }
+    ST_MARK;   // 6 order written
 
     // ---------------------------------------------------------------- sort 2: segment-major order
     unsigned int nseg_here = n > 0 ? 1u : 0u;
+    uint32_t *gs = a.gseg_start + (size_t)g * (a.seg_cap + 1);
     if (two) {
-        if (radix_pass(T, cur, 0, n, share)) cur ^= 1;
+        const int s0 = GLOBAL ? 0 : 16;
+        if (radix_pass(T, cur, s0, n, share)) cur ^= 1;
         if (id_range > 256ull)
-            if (radix_pass(T, cur, 8, n, share)) cur ^= 1;
+            if (radix_pass(T, cur, s0 + 8, n, share)) cur ^= 1;
         // seg_order / seg_rank, segment boundaries (count, then write)
         uint32_t bmask = 0u;      // bit i: my item i starts a segment
         unsigned int run = 0;
@@ -589,11 +763,17 @@ __device__ void sort_group(const SortArgs &a, int g, Team<GLOBAL> &T) {
                 bool isb = false;
                 if (lp < count) {
                     const uint32_t q = (uint32_t)T.rank * share + lp;
-                    const uint32_t p = T.ld(T.val[cur], share, lp);
-                    const uint32_t k = T.ld(T.key[cur], share, lp);
+                    const uint2 e = T.ld(cur, share, lp);
+                    const uint32_t k = GLOBAL ? e.x : (e.x >> 16);
+                    const uint32_t p = GLOBAL ? e.y : (e.x & 0xffffu);
                     a.seg_rank[obase + q] = p;
-                    a.seg_order[obase + q] = __ldcg(a.order + obase + p);
-                    isb = q == 0u || T.ld_pos(T.key[cur], share, q - 1u) != k;
+                    a.seg_order[obase + q] = GLOBAL ? __ldcg(a.order + obase + p) : (uint32_t)(obase + e.y);
+                    if (q == 0u) {
+                        isb = true;
+                    } else {
+                        const uint32_t pk = lp > 0u ? T.ld(cur, share, lp - 1u).x : T.ld_pos_key(cur, share, q - 1u);
+                        isb = (GLOBAL ? pk : (pk >> 16)) != k;
+                    }
                 }
                 const uint32_t bal = __ballot_sync(0xffffffffu, isb);
                 if (isb) bmask |= 1u << i;
@@ -601,48 +781,52 @@ __device__ void sort_group(const SortArgs &a, int g, Team<GLOBAL> &T) {
                 run += __popc(bal);
             }
         }
-        if (lane == 0) sm.wsum[warp] = run;
-        __syncthreads();
-        unsigned int wbefore = 0, ctot = 0;
-#pragma unroll
-        for (int w = 0; w < kWarps; ++w) {
-            const unsigned int c = sm.wsum[w];
-            wbefore += w < warp ? c : 0u;
-            ctot += c;
-        }
-        __syncthreads();
+        unsigned int ctot;
+        const unsigned int wbefore = warp_totals_exclusive(run, sm.wsum[0], ctot);
         if (tid == 0) T.publish_bcount(ctot);
         T.sync();
         unsigned int before = 0, total = 0;
-        for (int c = 0; c < T.size; ++c) {
-            const unsigned int h = T.peer_bcount(c);
-            total += h;
-            before += c < T.rank ? h : 0u;
+        if (!GLOBAL) {
+            unsigned int h[kSortMaxCluster];
+#pragma unroll
+            for (int c = 0; c < kSortMaxCluster; ++c) h[c] = c < T.size ? T.peer_bcount(c) : 0u;
+#pragma unroll
+            for (int c = 0; c < kSortMaxCluster; ++c) {
+                total += h[c];
+                before += c < T.rank ? h[c] : 0u;
+            }
+        } else {
+            for (int c = 0; c < T.size; ++c) {
+                const unsigned int h = T.peer_bcount(c);
+                total += h;
+                before += c < T.rank ? h : 0u;
+            }
         }
         nseg_here = total;
-        uint32_t *gs = a.gseg_start + (size_t)g * (a.seg_cap + 1);
         if (total <= (unsigned int)a.seg_cap) {
+            const bool to_rank0 = fast_plan && total <= (unsigned int)kPlanLocal;
 #pragma unroll
             for (int i = 0; i < kItems; ++i) {
                 if (i < iu && (bmask >> i) & 1u) {
                     const uint32_t lp = (uint32_t)warp * 32u * iu + (uint32_t)i * 32u + lane;
-                    gs[before + wbefore + ordl[i]] = (uint32_t)T.rank * share + lp;
+                    const uint32_t at = before + wbefore + ordl[i];
+                    gs[at] = (uint32_t)T.rank * share + lp;
+                    if (to_rank0) T.st_gs_rank0(at, (uint32_t)T.rank * share + lp);
                 }
             }
         }
     } else if (T.rank == 0 && tid == 0 && n > 0) {
-        a.gseg_start[(size_t)g * (a.seg_cap + 1)] = 0u;
+        gs[0] = 0u;
     }
-    // ---------------------------------------------------------------- group summary, ticket, plan
+    ST_MARK;   // 7 sort 2 + segment starts
+    // ---------------------------------------------------------------- group summary, plan
+    unsigned int nseg_ok = nseg_here > (unsigned int)a.seg_cap ? 0u : nseg_here;
     if (T.rank == 0 && tid == 0) {
         unsigned int err = range_bad ? kSortErrRange : 0u;
-        unsigned int s = nseg_here;
-        if (s > (unsigned int)a.seg_cap) {
-            err |= kSortErrSegments;
-            s = 0u;
-        }
-        a.gseg_start[(size_t)g * (a.seg_cap + 1) + s] = n;      // end of the last segment
-        a.gseg_count[g] = (int)s;
+        if (nseg_here > (unsigned int)a.seg_cap) err |= kSortErrSegments;
+        gs[nseg_ok] = n;      // end of the last segment
+        if (nseg_ok <= (unsigned int)kPlanLocal) sm.gs_local[nseg_ok] = n;
+        a.gseg_count[g] = (int)nseg_ok;
         if (err) atomicOr(&a.hdr->error, err);
         atomicAdd(reinterpret_cast<unsigned long long *>(&a.hdr->n_valid), (unsigned long long)n);
         if (mc) {
@@ -652,17 +836,24 @@ __device__ void sort_group(const SortArgs &a, int g, Team<GLOBAL> &T) {
     }
     __threadfence();
     T.sync();       // every CTA of the team has written its share
+    ST_MARK;   // 8 summary
     if (T.rank == 0) {
-        if (tid == 0) {
-            __threadfence();
-            sm.last = atomicAdd(&a.hdr->done, 1u) == (unsigned int)a.ngroups - 1u ? 1 : 0;
-        }
-        __syncthreads();
-        if (sm.last) {
-            __threadfence();
-            make_plan(a, sm);
+        if (fast_plan && nseg_ok <= (unsigned int)kPlanLocal) {
+            make_plan_local(a, sm, (int)nseg_ok);       // no ticket, no global round trips
+        } else {
+            if (tid == 0) {
+                __threadfence();
+                sm.last = atomicAdd(&a.hdr->done, 1u) == (unsigned int)a.ngroups - 1u ? 1 : 0;
+            }
+            __syncthreads();
+            if (sm.last) {
+                __threadfence();
+                make_plan(a);
+            }
         }
     }
+    ST_MARK;   // 9 plan
+    ST_PRINT;
 }
 
 }  // namespace
@@ -682,11 +873,9 @@ sort_cluster_kernel(const SortArgs a) {
     T.rank = (int)cluster.block_rank();
     T.size = K;
     T.sm = &sm;
-    uint32_t *buf = reinterpret_cast<uint32_t *>(dyn);
-    T.key[0] = buf;
-    T.val[0] = buf + kCap;
-    T.key[1] = buf + 2 * kCap;
-    T.val[1] = buf + 3 * kCap;
+    T.base = reinterpret_cast<uint2 *>(dyn);
+    T.stride = (uint32_t)a.cta_cap;
+    T.stage = T.base + 2 * (size_t)a.cta_cap;
     T.ghist = nullptr; T.gred = nullptr; T.gcount = nullptr;
     cluster.sync();        // every CTA of the cluster has started: its shared memory may be written
     sort_group<false>(a, g, T);
@@ -696,6 +885,7 @@ sort_cluster_kernel(const SortArgs a) {
 // cooperative grid: the groups the clusters skipped, one after the other
 __global__ void __launch_bounds__(kSortThreads, 1)
 sort_global_kernel(const SortArgs a, int K_cluster) {
+    extern __shared__ __align__(16) unsigned char dyn[];
     __shared__ SortSmem sm;
     for (int g = 0; g < a.ngroups; ++g) {
         const int64_t n_in = group_start(a, g + 1) - group_start(a, g);
@@ -704,10 +894,9 @@ sort_global_kernel(const SortArgs a, int K_cluster) {
         T.rank = (int)blockIdx.x;
         T.size = (int)gridDim.x;
         T.sm = &sm;
-        T.key[0] = a.big_buf;
-        T.val[0] = a.big_buf + a.big_cap;
-        T.key[1] = a.big_buf + 2 * a.big_cap;
-        T.val[1] = a.big_buf + 3 * a.big_cap;
+        T.base = reinterpret_cast<uint2 *>(a.big_buf);
+        T.stride = a.big_cap;
+        T.stage = reinterpret_cast<uint2 *>(dyn);       // kSortCap entries: the grid has >= n / kSortCap CTAs
         T.ghist = a.big_hist;
         T.gred = reinterpret_cast<Red *>(a.big_red);
         T.gcount = a.big_count;
@@ -733,16 +922,21 @@ void sort_layout(int64_t n, int64_t ngroups, int64_t seg_cap, int64_t max_group,
     l->off_segs = off;       off = align_up(off + (size_t)l->segs_cap * sizeof(NmsSegment), 256);
     l->off_gstart = off;     off = align_up(off + (size_t)(ngroups + 1) * 8, 256);
     l->big_cap = max_group > (int64_t)kSortMaxCluster * kSortCap ? max_group : 0;
-    l->off_big_buf = off;    off = align_up(off + (size_t)l->big_cap * 16, 256);
+    l->off_big_buf = off;    off = align_up(off + (size_t)l->big_cap * 16, 256);     // two buffers of uint2
     l->off_big_hist = off;   off = align_up(off + (size_t)(l->big_cap ? kNmsMaxBlocks * 256 * 4 : 0), 256);
     l->off_big_red = off;    off = align_up(off + (size_t)(l->big_cap ? kNmsMaxBlocks * sizeof(Red) : 0), 256);
     l->off_big_count = off;  off = align_up(off + (size_t)(l->big_cap ? kNmsMaxBlocks * 4 : 0), 256);
     l->total_bytes = off;
 }
 
-static int sort_cluster_size(int64_t max_group) {
+// CTAs per group: what the capacity needs, and beyond that as many as keep all clusters of the
+// launch resident at once (one 1024-thread CTA per SM): a pass is mostly fixed cost, so a single
+// image of 10 000 boxes sorts faster on 8 SMs than on one, while a batch of 64 images is spread
+// 2 CTAs per image
+static int sort_cluster_size(int64_t max_group, int64_t ngroups, int sms) {
     int K = 1;
     while (K < kSortMaxCluster && (int64_t)K * kSortCap < max_group) K *= 2;
+    while (K < kSortMaxCluster && (int64_t)2 * K * ngroups <= sms && (int64_t)K * 1024 < max_group) K *= 2;
     return K;
 }
 
@@ -795,8 +989,20 @@ int launch_sort(SortArgs &a, const int64_t *group_sizes_host, int64_t n, void *s
     a.big_count = reinterpret_cast<unsigned int *>(ws + l.off_big_count);
     if (cudaMemsetAsync(a.hdr, 0, sizeof(SortHeader), stream) != cudaSuccess) return -3;
 
-    const int K = sort_cluster_size(max_group);
-    const size_t dyn = (size_t)4 * kSortCap * sizeof(uint32_t);
+    int dev = 0, sms = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess ||
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess)
+        return -3;
+    const int K = sort_cluster_size(max_group, a.ngroups, sms);
+    // elements per CTA buffer: the share of the largest group that fits the cluster
+    int64_t cap_elems = max_group < (int64_t)K * kSortCap ? (max_group + K - 1) / K : kSortCap;
+    cap_elems = (cap_elems + 31) / 32 * 32;
+    if (cap_elems < 32) cap_elems = 32;
+    a.cta_cap = (int)cap_elems;
+    // two buffers + the staging array, which also holds the 32 KB of per-warp match masks while ranking
+    size_t stage_bytes = (size_t)cap_elems * sizeof(uint2);
+    if (stage_bytes < (size_t)kSortThreads / 32 * 256 * 4) stage_bytes = (size_t)kSortThreads / 32 * 256 * 4;
+    const size_t dyn = (size_t)2 * cap_elems * sizeof(uint2) + stage_bytes;
     // (set on every call: the attribute belongs to the current device's copy of the function)
     if (cudaFuncSetAttribute(sort_cluster_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn) != cudaSuccess)
         return -3;
@@ -816,18 +1022,18 @@ int launch_sort(SortArgs &a, const int64_t *group_sizes_host, int64_t n, void *s
         if (cudaLaunchKernelEx(&cfg, sort_cluster_kernel, a) != cudaSuccess) return -3;
     }
     if (max_group > (int64_t)K * kSortCap) {
-        // the oversize groups: cooperative grid, buffers in global memory
-        int dev = 0, sms = 0;
-        if (cudaGetDevice(&dev) != cudaSuccess ||
-            cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess)
-            return -3;
+        // the oversize groups: cooperative grid, buffers in global memory, staging in shared memory
         int64_t want = (max_group + kSortCap - 1) / kSortCap;
         const int64_t limit = sms < kNmsMaxBlocks ? sms : kNmsMaxBlocks;
-        if (want > limit) return -6;              // beyond sms * 12 288 elements in one group
+        if (want > limit) return -6;              // beyond sms * 8192 elements in one group
         if (want < 8) want = 8;
+        const size_t gdyn = (size_t)kSortCap * sizeof(uint2);
+        if (cudaFuncSetAttribute(sort_global_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gdyn) != cudaSuccess)
+            return -3;
         cudaLaunchConfig_t cfg = {};
         cfg.gridDim = dim3((unsigned)want);
         cfg.blockDim = dim3(kSortThreads);
+        cfg.dynamicSmemBytes = gdyn;
         cfg.stream = stream;
         cudaLaunchAttribute attr[1];
         attr[0].id = cudaLaunchAttributeCooperative;

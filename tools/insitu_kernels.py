@@ -37,3 +37,38 @@ imgs = [tuple(cu(x) for x in synth.c4_rpn_image(s)) for s in range(64)]
 run('C4 64 images nms_images', lambda: rdist.nms_images(imgs, 0.8, 2000), 5)
 bs, sc = cu(synth.le90_boxes(30000, 9, 1024.0)), cu(synth.unique_scores(30000, 9))
 run('single segment 30000', lambda: ops._nms_keep(bs, sc, 0.1), 5)
+# C5: ~200k detections, one GROUP per class (class-contiguous rows, as merge_results uploads them)
+import numpy as np, time
+res, offs, shape = synth.c5_patch_results(0)
+for p, o in zip(res, offs):
+    for a in p:
+        a[:, :2] += o
+per_cls = [np.concatenate([p[c] for p in res], axis=0) for c in range(15)]
+counts = [a.shape[0] for a in per_cls]
+dd = cu(np.concatenate(per_cls, axis=0))
+run('C5 200k, classes as groups', lambda: ops._nms_grouped(dd[:, :5], dd[:, 5], 0.1, group_sizes=counts), 5)
+
+
+def wall(name, fn, reps=20):
+    fn()
+    ts = []
+    for _ in range(reps):
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        fn()
+        torch.cuda.synchronize()
+        ts.append(time.perf_counter() - t0)
+    print('wall %-40s best %.3f ms  median %.3f ms' % (name, 1e3 * min(ts), 1e3 * sorted(ts)[len(ts) // 2]))
+
+
+for dense in (False, True):
+    mb, ms = synth.c2_multiclass(0, dense=dense)
+    mbd, msd = cu(mb), cu(ms)
+    wall('C2 %s' % ('dense' if dense else 'sparse'), lambda: rg.multiclass_nms_rotated(mbd, msd, 0.05, dict(iou_thr=0.1), 2000))
+cfg = dict(type='nms_rotated', iou_threshold=0.8)
+wall('C4 one image', lambda: rg.batched_nms(b1, s1, i1, cfg))
+wall('C4 64 images one call', lambda: rdist.nms_images(imgs, 0.8, 2000), 5)
+wall('C4 64 per-image calls', lambda: [rg.batched_nms(b, s, i, cfg) for b, s, i in imgs], 3)
+wall('C4 8 images one call', lambda: rdist.nms_images(imgs[:8], 0.8, 2000), 10)
+wall('single segment 30000', lambda: ops._nms_keep(bs, sc, 0.1), 5)
+wall('C5 groups device-resident', lambda: ops._nms_grouped(dd[:, :5], dd[:, 5], 0.1, group_sizes=counts), 5)
