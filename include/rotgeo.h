@@ -269,6 +269,63 @@ int rotgeo_nms_run(const float *boxes, int64_t n, int stride, const float *offse
                    const int64_t *sizes, float iou_threshold, int64_t *keep_out, int64_t *num_keep_out,
                    int64_t *group_counts_out, void *workspace, size_t workspace_bytes, void *stream);
 
+/* ---- multi-GPU: results exchanged over peer memory (NVLink / NVSwitch) ---------------
+ * The reference has no multi-GPU form of this path: it loops over the images of a batch and
+ * over the classes of a patch merge in python inside one rank
+ * (mmrotate/models/dense_heads/rotated_rpn_head.py:414-426,515,
+ * mmrotate/core/patch/merge_results.py:90-119).  These entry points are what one rank of a
+ * one-process-per-GPU job calls: it computes ITS shard and stores the result straight into
+ * every peer's memory; no library collective sits in the data path.
+ *
+ * Window: one symmetric device buffer per rank, every rank's buffer mapped into every
+ * process (the host layer allocates and exchanges them, e.g. torch symmetric memory);
+ * peer_bases_host[r] = address of rank r's window IN THIS PROCESS (HOST array of `world`
+ * pointers, world <= 16).  The first rotgeo_peer_pad_bytes() of a window are its signal pad
+ * and must be zero before the first call; offsets passed below start behind it.
+ * epoch: a counter the caller advances monotonically, identically on all ranks; every call
+ * states how many values it consumes.  All ranks must issue the same calls in the same order.
+ *
+ *   rotgeo_peer_barrier           all ranks' earlier writes (remote ones included) are
+ *                                 visible to all ranks behind it on `stream`.  1 epoch.
+ *   rotgeo_dist_iou_allgather     the (n1_total, n2) matrix of rotgeo_iou_pairwise, rows
+ *                                 [row_lo, row_lo + n1_local) computed here, complete in EVERY
+ *                                 window at matrix_offset afterwards.  Zeros never travel:
+ *                                 each rank zero-fills the foreign rows locally and pushes
+ *                                 only the non-zero 16-byte groups of its block.  2 epochs.
+ *                                 workspace: rotgeo_iou_workspace_bytes(n1_local, n2).
+ *   rotgeo_dist_iou_rowcol_max    rotgeo_iou_rowcol_max of the row-sharded matrix: all four
+ *                                 outputs complete on every rank (row_* (n1_total,), col_*
+ *                                 (n2,), local buffers, any may be null).  Stage in the
+ *                                 window: rotgeo_dist_rowcol_stage_bytes(...) at stage_offset.
+ *                                 2 epochs.  workspace: rotgeo_iou_max_workspace_bytes(n1_local, n2).
+ *   rotgeo_dist_push_keeps        the kept rows of this rank's NMS groups (keep / tail as
+ *                                 rotgeo_nms_run leaves them: tail = num_keep_out[0..1] followed
+ *                                 by group_counts_out) into every window at out_offset:
+ *                                   int64 counts[num_groups_total] | int64 errors[world] |
+ *                                   int64 keep[num_groups_total][cap] |
+ *                                   float rows[num_groups_total][cap][row_floats]   (optional)
+ *                                 group_ids_host[g] = global id of local group g (at most 64
+ *                                 local groups); lists are cut to cap; rows (nullable) are
+ *                                 gathered from rows_src at group_base_host[g] + kept index.
+ *                                 Region size: rotgeo_dist_keeps_bytes(...).  1 epoch. */
+size_t rotgeo_peer_pad_bytes(void);
+int rotgeo_peer_barrier(void *const *peer_bases_host, int world, int rank, uint64_t epoch, void *stream);
+int rotgeo_dist_iou_allgather(void *const *peer_bases_host, int world, int rank, uint64_t epoch, size_t matrix_offset,
+                              const float *boxes1_local, int64_t row_lo, int64_t n1_local, int64_t n1_total,
+                              int stride1, const float *boxes2, int64_t n2, int stride2, int mode, float min_wh,
+                              void *workspace, size_t workspace_bytes, void *stream);
+size_t rotgeo_dist_rowcol_stage_bytes(int64_t n1_total, int64_t n2, int world);
+int rotgeo_dist_iou_rowcol_max(void *const *peer_bases_host, int world, int rank, uint64_t epoch, size_t stage_offset,
+                               const float *boxes1_local, int64_t row_lo, int64_t n1_local, int64_t n1_total,
+                               int stride1, const float *boxes2, int64_t n2, int stride2, int mode, float min_wh,
+                               float *row_max, int64_t *row_argmax, float *col_max, int64_t *col_argmax,
+                               void *workspace, size_t workspace_bytes, void *stream);
+size_t rotgeo_dist_keeps_bytes(int64_t num_groups_total, int64_t cap, int world, int row_floats);
+int rotgeo_dist_push_keeps(void *const *peer_bases_host, int world, int rank, uint64_t epoch, size_t out_offset,
+                           const int64_t *keep, const int64_t *tail, int num_local, const int64_t *group_ids_host,
+                           int64_t cap, int64_t num_groups_total, const float *rows_src, int row_floats,
+                           int row_stride, const int64_t *group_base_host, void *stream);
+
 /* ---- class-batched rotated NMS, fused ----------------------------------------
  * Replaces the whole body of the reference's multiclass_nms_rotated
  * (mmrotate/core/post_processing/bbox_nms_rotated.py:33-92, called from the eleven

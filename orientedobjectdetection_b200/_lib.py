@@ -20,6 +20,8 @@ SYMBOLS = (
     'rotgeo_nms_sort_bytes', 'rotgeo_nms_sort', 'rotgeo_nms_bounds', 'rotgeo_nms_read_plan',
     'rotgeo_nms_run_bytes', 'rotgeo_nms_run',
     'rotgeo_multiclass_nms_workspace_bytes', 'rotgeo_multiclass_nms',
+    'rotgeo_peer_pad_bytes', 'rotgeo_peer_barrier', 'rotgeo_dist_iou_allgather', 'rotgeo_dist_rowcol_stage_bytes',
+    'rotgeo_dist_iou_rowcol_max', 'rotgeo_dist_keeps_bytes', 'rotgeo_dist_push_keeps',
 )
 ERR_RANGE = -4
 
@@ -91,6 +93,22 @@ def load():
     L.rotgeo_multiclass_nms_workspace_bytes.restype = sz
     L.rotgeo_multiclass_nms.argtypes = [vp, i32, vp, vp, i64, i32, f32, f32, i64, vp, vp, vp, vp, vp, sz, vp]
     L.rotgeo_multiclass_nms.restype = i32
+    u64 = ctypes.c_uint64
+    L.rotgeo_peer_pad_bytes.restype = sz
+    L.rotgeo_peer_barrier.argtypes = [vp, i32, i32, u64, vp]
+    L.rotgeo_peer_barrier.restype = i32
+    L.rotgeo_dist_iou_allgather.argtypes = [vp, i32, i32, u64, sz, vp, i64, i64, i64, i32, vp, i64, i32, i32, f32,
+                                            vp, sz, vp]
+    L.rotgeo_dist_iou_allgather.restype = i32
+    L.rotgeo_dist_rowcol_stage_bytes.argtypes = [i64, i64, i32]
+    L.rotgeo_dist_rowcol_stage_bytes.restype = sz
+    L.rotgeo_dist_iou_rowcol_max.argtypes = [vp, i32, i32, u64, sz, vp, i64, i64, i64, i32, vp, i64, i32, i32, f32,
+                                             vp, vp, vp, vp, vp, sz, vp]
+    L.rotgeo_dist_iou_rowcol_max.restype = i32
+    L.rotgeo_dist_keeps_bytes.argtypes = [i64, i64, i32, i32]
+    L.rotgeo_dist_keeps_bytes.restype = sz
+    L.rotgeo_dist_push_keeps.argtypes = [vp, i32, i32, u64, sz, vp, vp, i32, vp, i64, i64, vp, i32, i32, vp, vp]
+    L.rotgeo_dist_push_keeps.restype = i32
     _lib = L
     return L
 

@@ -10,7 +10,7 @@ PKG = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(PKG, 'csrc')
 SO = os.path.join(PKG, 'librotgeo.so')
 SOURCES = ['rotgeo_abi.cu', 'rotgeo_pack.cu', 'rotgeo_iou.cu', 'rotgeo_nms.cu', 'rotgeo_sort.cu', 'rotgeo_frontend.cu',
-           'rotgeo_static.cu', 'rotgeo_assign.cu', 'rotgeo_eval.cu', 'rotgeo_diff.cu']
+           'rotgeo_static.cu', 'rotgeo_dist.cu', 'rotgeo_assign.cu', 'rotgeo_eval.cu', 'rotgeo_diff.cu']
 HEADERS = ['rotgeo_device.cuh', 'rotgeo_internal.h', os.path.join('..', '..', 'include', 'rotgeo.h')]
 
 

@@ -467,4 +467,108 @@ int rotgeo_multiclass_nms(const float *multi_bboxes, int bbox_cols, const float 
     return ROTGEO_OK;
 }
 
+// ---- multi-GPU exchange over peer memory -----------------------------------------------------------
+static int make_peer_table(void *const *peer_bases_host, int world, int rank, rotgeo::PeerTable *t, const char *who) {
+    if (!peer_bases_host || world < 1 || world > rotgeo::kPeerMax || rank < 0 || rank >= world)
+        return fail(ROTGEO_ERR_ARG, "%s: world=%d rank=%d (at most %d ranks)", who, world, rank, rotgeo::kPeerMax);
+    for (int r = 0; r < rotgeo::kPeerMax; ++r) t->base[r] = nullptr;
+    for (int r = 0; r < world; ++r) {
+        if (!peer_bases_host[r] || !aligned16(peer_bases_host[r]))
+            return fail(ROTGEO_ERR_ARG, "%s: window of rank %d is null or misaligned", who, r);
+        t->base[r] = peer_bases_host[r];
+    }
+    t->world = world;
+    t->rank = rank;
+    return ROTGEO_OK;
+}
+
+size_t rotgeo_peer_pad_bytes(void) { return rotgeo::kPeerPadBytes; }
+
+int rotgeo_peer_barrier(void *const *peer_bases_host, int world, int rank, uint64_t epoch, void *stream) {
+    rotgeo::PeerTable t;
+    if (int rc = make_peer_table(peer_bases_host, world, rank, &t, "peer_barrier")) return rc;
+    if (rotgeo::launch_peer_barrier(t, epoch, (cudaStream_t)stream)) return cuda_fail("peer_barrier launch");
+    return ROTGEO_OK;
+}
+
+int rotgeo_dist_iou_allgather(void *const *peer_bases_host, int world, int rank, uint64_t epoch, size_t matrix_offset,
+                              const float *boxes1_local, int64_t row_lo, int64_t n1_local, int64_t n1_total,
+                              int stride1, const float *boxes2, int64_t n2, int stride2, int mode, float min_wh,
+                              void *workspace, size_t workspace_bytes, void *stream) {
+    rotgeo::PeerTable t;
+    if (int rc = make_peer_table(peer_bases_host, world, rank, &t, "dist_iou_allgather")) return rc;
+    if (n1_local < 0 || row_lo < 0 || row_lo + n1_local > n1_total || n2 <= 0 || stride1 < 5 || stride2 < 5 ||
+        (mode != 0 && mode != 1) || matrix_offset < rotgeo::kPeerPadBytes || matrix_offset % 16)
+        return fail(ROTGEO_ERR_ARG, "dist_iou_allgather: rows [%lld, +%lld) of %lld, n2=%lld, mode=%d, offset=%zu",
+                    (long long)row_lo, (long long)n1_local, (long long)n1_total, (long long)n2, mode, matrix_offset);
+    if (n1_local > 0 && (!boxes1_local || !boxes2)) return fail(ROTGEO_ERR_ARG, "dist_iou_allgather: null pointer");
+    const size_t need = n1_local > 0 ? rotgeo_iou_workspace_bytes(n1_local, n2) : 0;
+    if (need && (!workspace || !aligned16(workspace) || workspace_bytes < need))
+        return fail(ROTGEO_ERR_WORKSPACE, "dist_iou_allgather: workspace %zu < %zu bytes or misaligned", workspace_bytes, need);
+    const int rc = rotgeo::launch_dist_iou_allgather(t, epoch, matrix_offset, boxes1_local, row_lo, n1_local, n1_total,
+                                                     stride1, boxes2, n2, stride2, mode, min_wh, workspace,
+                                                     (cudaStream_t)stream);
+    if (rc == -1) return fail(ROTGEO_ERR_ARG, "dist_iou_allgather: too many tiles");
+    if (rc) return cuda_fail("dist_iou_allgather launch");
+    return ROTGEO_OK;
+}
+
+size_t rotgeo_dist_rowcol_stage_bytes(int64_t n1_total, int64_t n2, int world) {
+    if (n1_total < 0 || n2 < 0 || world < 1) return 0;
+    return align_up((size_t)n1_total * 8, 256) + align_up((size_t)world * n2 * 8, 256);
+}
+
+int rotgeo_dist_iou_rowcol_max(void *const *peer_bases_host, int world, int rank, uint64_t epoch, size_t stage_offset,
+                               const float *boxes1_local, int64_t row_lo, int64_t n1_local, int64_t n1_total,
+                               int stride1, const float *boxes2, int64_t n2, int stride2, int mode, float min_wh,
+                               float *row_max, int64_t *row_argmax, float *col_max, int64_t *col_argmax,
+                               void *workspace, size_t workspace_bytes, void *stream) {
+    rotgeo::PeerTable t;
+    if (int rc = make_peer_table(peer_bases_host, world, rank, &t, "dist_iou_rowcol_max")) return rc;
+    if (n1_local < 0 || row_lo < 0 || row_lo + n1_local > n1_total || n2 <= 0 || stride1 < 5 || stride2 < 5 ||
+        (mode != 0 && mode != 1) || stage_offset < rotgeo::kPeerPadBytes || stage_offset % 16 ||
+        n1_total >= 0x7fffffffLL)
+        return fail(ROTGEO_ERR_ARG, "dist_iou_rowcol_max: rows [%lld, +%lld) of %lld, n2=%lld, mode=%d",
+                    (long long)row_lo, (long long)n1_local, (long long)n1_total, (long long)n2, mode);
+    if (n1_local > 0 && (!boxes1_local || !boxes2)) return fail(ROTGEO_ERR_ARG, "dist_iou_rowcol_max: null pointer");
+    const size_t need = n1_local > 0 ? rotgeo::iou_max_workspace_bytes(n1_local, n2) : 0;
+    if (need && (!workspace || !aligned16(workspace) || workspace_bytes < need))
+        return fail(ROTGEO_ERR_WORKSPACE, "dist_iou_rowcol_max: workspace %zu < %zu bytes or misaligned", workspace_bytes, need);
+    const int rc = rotgeo::launch_dist_iou_rowcol_max(t, epoch, stage_offset, boxes1_local, row_lo, n1_local, n1_total,
+                                                      stride1, boxes2, n2, stride2, mode, min_wh, row_max, row_argmax,
+                                                      col_max, col_argmax, workspace, (cudaStream_t)stream);
+    if (rc == -1) return fail(ROTGEO_ERR_ARG, "dist_iou_rowcol_max: too many tiles");
+    if (rc) return cuda_fail("dist_iou_rowcol_max launch");
+    return ROTGEO_OK;
+}
+
+size_t rotgeo_dist_keeps_bytes(int64_t num_groups_total, int64_t cap, int world, int row_floats) {
+    if (num_groups_total < 0 || cap < 0 || world < 1 || row_floats < 0) return 0;
+    return align_up((size_t)num_groups_total * 8 + (size_t)world * 8 + (size_t)num_groups_total * cap * 8 +
+                        (size_t)num_groups_total * cap * row_floats * 4, 256);
+}
+
+int rotgeo_dist_push_keeps(void *const *peer_bases_host, int world, int rank, uint64_t epoch, size_t out_offset,
+                           const int64_t *keep, const int64_t *tail, int num_local, const int64_t *group_ids_host,
+                           int64_t cap, int64_t num_groups_total, const float *rows_src, int row_floats,
+                           int row_stride, const int64_t *group_base_host, void *stream) {
+    rotgeo::PeerTable t;
+    if (int rc = make_peer_table(peer_bases_host, world, rank, &t, "dist_push_keeps")) return rc;
+    if (num_local < 0 || num_local > rotgeo::kSortGroupsInline || cap < 1 || num_groups_total < 1 || row_floats < 0 ||
+        row_floats > 8 || out_offset < rotgeo::kPeerPadBytes || out_offset % 16)
+        return fail(ROTGEO_ERR_ARG, "dist_push_keeps: local groups=%d (at most %d), cap=%lld, row_floats=%d", num_local,
+                    rotgeo::kSortGroupsInline, (long long)cap, row_floats);
+    if (num_local > 0 && (!keep || !tail || !group_ids_host)) return fail(ROTGEO_ERR_ARG, "dist_push_keeps: null pointer");
+    if (rows_src && (!group_base_host || row_stride < row_floats))
+        return fail(ROTGEO_ERR_ARG, "dist_push_keeps: payload rows need group_base_host and row_stride >= row_floats");
+    for (int g = 0; g < num_local; ++g)
+        if (group_ids_host[g] < 0 || group_ids_host[g] >= num_groups_total)
+            return fail(ROTGEO_ERR_ARG, "dist_push_keeps: group id out of range");
+    const int rc = rotgeo::launch_dist_push_keeps(t, epoch, out_offset, keep, tail, num_local, group_ids_host, cap,
+                                                  num_groups_total, rows_src, row_floats, row_stride, group_base_host,
+                                                  (cudaStream_t)stream);
+    if (rc) return cuda_fail("dist_push_keeps launch");
+    return ROTGEO_OK;
+}
+
 }  // extern "C"

@@ -113,6 +113,17 @@ static int pack_and_reduce(const float *boxes1, int64_t n1, int stride1, const f
                           reinterpret_cast<unsigned long long *>(ws + l.off_col_key), true, stream);
 }
 
+int launch_iou_max_keys(const float *boxes1, int64_t n1, int stride1, const float *boxes2, int64_t n2, int stride2,
+                        int mode, float min_wh, void *workspace, unsigned long long **row_key,
+                        unsigned long long **col_key, cudaStream_t stream) {
+    AssignLayout l;
+    assign_layout(n1, n2, &l);
+    char *ws = reinterpret_cast<char *>(workspace);
+    *row_key = reinterpret_cast<unsigned long long *>(ws + l.off_row_key);
+    *col_key = reinterpret_cast<unsigned long long *>(ws + l.off_col_key);
+    return pack_and_reduce(boxes1, n1, stride1, boxes2, n2, stride2, mode, min_wh, ws, l, stream);
+}
+
 int launch_iou_rowcol_max(const float *boxes1, int64_t n1, int stride1, const float *boxes2, int64_t n2,
                           int stride2, int mode, float min_wh, float *row_max, int64_t *row_argmax,
                           float *col_max, int64_t *col_argmax, void *workspace, cudaStream_t stream) {

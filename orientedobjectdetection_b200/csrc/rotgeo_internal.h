@@ -264,6 +264,34 @@ void sort_layout(int64_t n, int64_t ngroups, int64_t seg_cap, int64_t max_group,
 int launch_sort(SortArgs &a, const int64_t *group_sizes_host, int64_t n, void *sortws, const SortLayout &l,
                 cudaStream_t stream);
 
+// ---- multi-GPU exchange over peer memory (rotgeo_dist.cu) -----------------------------------------
+constexpr int kPeerMax = 16;                          // ranks of one window
+constexpr size_t kPeerPadBytes = 4096;                // signal pad at the start of every window
+constexpr int kPeerErrorSlot = 64;                    // u64 slot of the pad raised when a barrier times out
+constexpr unsigned long long kPeerTimeoutNs = 2000000000ull;   // 2 s
+struct PeerTable {
+    void *base[kPeerMax];      // window of every rank, mapped into this process
+    int world, rank;
+};
+int launch_peer_barrier(const PeerTable &t, unsigned long long epoch, cudaStream_t stream);
+int launch_dist_iou_allgather(const PeerTable &t, unsigned long long epoch, size_t matrix_off,
+                              const float *boxes1_local, int64_t row_lo, int64_t n1_local, int64_t n1_total,
+                              int stride1, const float *boxes2, int64_t n2, int stride2, int mode, float min_wh,
+                              void *workspace, cudaStream_t stream);
+int launch_dist_iou_rowcol_max(const PeerTable &t, unsigned long long epoch, size_t stage_off,
+                               const float *boxes1_local, int64_t row_lo, int64_t n1_local, int64_t n1_total,
+                               int stride1, const float *boxes2, int64_t n2, int stride2, int mode, float min_wh,
+                               float *row_max, int64_t *row_argmax, float *col_max, int64_t *col_argmax,
+                               void *workspace, cudaStream_t stream);
+int launch_dist_push_keeps(const PeerTable &t, unsigned long long epoch, size_t out_off, const int64_t *keep,
+                           const int64_t *tail, int nlocal, const int64_t *gid_host, int64_t cap,
+                           int64_t ngroups_total, const float *rows_src, int row_floats, int row_stride,
+                           const int64_t *group_base_host, cudaStream_t stream);
+// rotgeo_assign.cu: pack + reduction sink only; the packed (value, ~index) keys stay in the workspace
+int launch_iou_max_keys(const float *boxes1, int64_t n1, int stride1, const float *boxes2, int64_t n2, int stride2,
+                        int mode, float min_wh, void *workspace, unsigned long long **row_key,
+                        unsigned long long **col_key, cudaStream_t stream);
+
 int launch_multiclass_nms(const float *multi_bboxes, int shared, const float *multi_scores,
                           const float *score_factors, int64_t rows, int classes, float score_thr,
                           float iou_threshold, int64_t cap, float *dets_out, int64_t *labels_out,

@@ -24,7 +24,7 @@ import numpy as np
 import torch
 import torch.distributed as dist
 
-from . import core, ops
+from . import _lib, core, ops, peer
 
 
 # ------------------------------------------------------------------ partitioning
@@ -88,10 +88,12 @@ def rbbox_overlaps_sharded(bboxes1, bboxes2, mode='iou', gather=True, group=None
                     N/G x M blocks: 268 MB total at 8192^2);
     gather=False -> ``(block, (lo, hi))``, nothing is communicated.
     """
-    compute = compute or core.rbbox_overlaps
     world, rank = _world(group)
     n, m = bboxes1.size(0), bboxes2.size(0)
     lo, hi = row_shard(n, world, rank)
+    if (gather and compute is None and world > 1 and n * m > 0 and bboxes1.is_cuda and peer.available(group)):
+        return _overlaps_allgather_peer(bboxes1, bboxes2, mode, lo, hi, group)
+    compute = compute or core.rbbox_overlaps
     block = compute(bboxes1[lo:hi], bboxes2, mode, False)
     if not gather:
         return block, (lo, hi)
@@ -106,6 +108,142 @@ def rbbox_overlaps_sharded(bboxes1, bboxes2, mode='iou', gather=True, group=None
     else:
         out = torch.cat(_all_gather_padded(block, rows_max, group), dim=0)
     return out.to(bboxes1.device) if out.device != bboxes1.device and not bboxes1.is_cuda else out
+
+
+def _overlaps_allgather_peer(bboxes1, bboxes2, mode, lo, hi, group):
+    """the full (N, M) matrix on every rank through peer memory: rank r computes rows [lo, hi)
+    straight into its window, zero-fills the foreign rows locally and pushes only the non-zero
+    16-byte groups of its block into the peers' windows (rotgeo_dist_iou_allgather) — no library
+    collective, and the zeros (99.9 % of BASELINE C3) never cross NVLink.  The returned tensor is
+    a view of the window: valid until the next sharded IoU call of this process."""
+    assert mode in ops._MODE
+    n, m = bboxes1.size(0), bboxes2.size(0)
+    dev = bboxes1.device
+    b1 = ops._rows_f32(bboxes1[lo:hi], dev)
+    b2 = ops._rows_f32(bboxes2, dev)
+    L = _lib.load()
+    with torch.cuda.device(dev):
+        stream = ops._stream(dev)
+        off = 4096
+        w = peer.window(off + n * m * 4, group)
+        nbytes = L.rotgeo_iou_workspace_bytes(hi - lo, m) if hi > lo else 0
+        ws = ops._workspace(dev, stream, 'dist_iou', max(nbytes, 16))
+        _lib.check(L.rotgeo_dist_iou_allgather(w.ptrs, w.world, w.rank, w.take(2), off, b1.data_ptr(), lo, hi - lo, n,
+                                               b1.stride(0) if hi > lo else 5, b2.data_ptr(), m, b2.stride(0),
+                                               ops._MODE[mode], 1e-3, ws.data_ptr(), ws.numel(), stream),
+                   'rotgeo_dist_iou_allgather')
+        return w.view(off, (n, m), torch.float32)
+
+
+def rbbox_overlaps_max_sharded(bboxes1, bboxes2, mode='iou', group=None):
+    """``assign.rbbox_overlaps_max`` of the row-sharded matrix (BASELINE C3 variant (iii)): rank r
+    reduces rows ``row_shard(N, G, r)``; all four results are complete on every rank.  The packed
+    (value, index) keys are exchanged through peer memory and reduced locally — an all-reduce of
+    64 KB instead of an all-gather of the 268 MB matrix."""
+    from . import assign
+    world, rank = _world(group)
+    n, m = bboxes1.size(0), bboxes2.size(0)
+    if world == 1 or n * m == 0 or not (bboxes1.is_cuda and peer.available(group)):
+        lo, hi = row_shard(n, world, rank)
+        if world == 1:
+            return assign.rbbox_overlaps_max(bboxes1, bboxes2, mode)
+        # collective fallback (gloo tests / no peer memory): gather the partial results
+        rm, ra, cm, ca = assign.rbbox_overlaps_max(bboxes1[lo:hi], bboxes2, mode)
+        cdev = _comm_device(group)
+        rows = _all_gather_padded(torch.stack([rm.double(), ra.double()], 1).to(cdev), row_shard(n, world, 0)[1], group)
+        rows = torch.cat(rows)
+        cols = [torch.zeros((m, 2), dtype=torch.float64, device=cdev) for _ in range(world)]
+        dist.all_gather(cols, torch.stack([cm.double(), (ca + lo).double()], 1).to(cdev), group=group)
+        cv = torch.stack([c[:, 0] for c in cols])                    # (G, m)
+        best = cv.max(0).values
+        first = (cv == best[None]).float().argmax(0)                 # lowest rank = lowest rows among equals
+        carg = torch.stack([c[:, 1] for c in cols])[first, torch.arange(m, device=cdev)]
+        carg = torch.where(best > 0, carg, torch.zeros_like(carg))
+        d = bboxes1.device
+        return (rows[:, 0].float().to(d), rows[:, 1].long().to(d), best.float().to(d), carg.long().to(d))
+    assert mode in ops._MODE
+    lo, hi = row_shard(n, world, rank)
+    dev = bboxes1.device
+    b1 = ops._rows_f32(bboxes1[lo:hi], dev)
+    b2 = ops._rows_f32(bboxes2, dev)
+    L = _lib.load()
+    with torch.cuda.device(dev):
+        stream = ops._stream(dev)
+        off = 4096
+        w = peer.window(off + L.rotgeo_dist_rowcol_stage_bytes(n, m, world), group)
+        nbytes = L.rotgeo_iou_max_workspace_bytes(hi - lo, m) if hi > lo else 0
+        ws = ops._workspace(dev, stream, 'dist_max', max(nbytes, 16))
+        row_max = torch.empty(n, dtype=torch.float32, device=dev)
+        row_arg = torch.empty(n, dtype=torch.int64, device=dev)
+        col_max = torch.empty(m, dtype=torch.float32, device=dev)
+        col_arg = torch.empty(m, dtype=torch.int64, device=dev)
+        _lib.check(L.rotgeo_dist_iou_rowcol_max(w.ptrs, w.world, w.rank, w.take(2), off, b1.data_ptr(), lo, hi - lo, n,
+                                                b1.stride(0) if hi > lo else 5, b2.data_ptr(), m, b2.stride(0),
+                                                ops._MODE[mode], 1e-3, row_max.data_ptr(), row_arg.data_ptr(),
+                                                col_max.data_ptr(), col_arg.data_ptr(), ws.data_ptr(), ws.numel(),
+                                                stream), 'rotgeo_dist_iou_rowcol_max')
+    return row_max, row_arg, col_max, col_arg
+
+
+# ------------------------------------------------------------------ NMS results through peer memory
+def _nms_exchange_peer(boxes, scores, ids, id_offsets, local_sizes, local_gids, ngroups, cap, iou_threshold,
+                       group, rows_src=None):
+    """Grouped NMS of THIS rank's groups (no host read) + push of the keep lists (and, with
+    ``rows_src`` (n, 6), of the kept rows) into every rank's window + ONE read of the counts.
+    Returns ``(counts[ngroups], keep (ngroups, cap) int64, rows (ngroups, cap, 6) | None)`` —
+    private copies — or None when some rank's ids do not fit the device front-end (every rank
+    sees the same error words, so all of them fall back together).  The two halves of the
+    region alternate between calls: a peer can only write the half of call k + 2 after this rank
+    has copied the half of call k out (its barrier of call k + 1 is stream-ordered behind the copy)."""
+    L = _lib.load()
+    world, rank = _world(group)
+    dev = torch.device('cuda', torch.cuda.current_device())
+    nlocal = len(local_gids)
+    if nlocal > 64:
+        return None
+    row_floats = 6 if rows_src is not None else 0
+    with torch.cuda.device(dev):
+        stream = ops._stream(dev)
+        region = L.rotgeo_dist_keeps_bytes(ngroups, cap, world, row_floats)
+        w = peer.window(4096 + 2 * region, group)
+        w.keep_calls = getattr(w, 'keep_calls', 0) + 1
+        off = 4096 + (w.keep_calls & 1) * region
+        n = int(sum(local_sizes))
+        keep = tail = None
+        failed = False
+        if n > 0:
+            got = ops._nms_grouped(boxes, scores, iou_threshold, seg_ids=ids, id_offsets=id_offsets,
+                                   group_sizes=local_sizes, no_read=True)
+            if got is None:
+                failed = True
+                tail = torch.tensor([0, 1] + [0] * nlocal, dtype=torch.int64, device=dev)
+                keep = torch.zeros(1, dtype=torch.int64, device=dev)
+            else:
+                keep, tail = got
+        elif nlocal > 0:
+            tail = torch.zeros(2 + nlocal, dtype=torch.int64, device=dev)
+            keep = torch.zeros(1, dtype=torch.int64, device=dev)
+        gid = np.ascontiguousarray(local_gids, dtype=np.int64)
+        gbase = np.concatenate([[0], np.cumsum(local_sizes)])[:-1].astype(np.int64) if nlocal else np.zeros(0, np.int64)
+        rs = None
+        if rows_src is not None and n > 0 and not failed:
+            rs = rows_src
+            assert rs.dtype == torch.float32 and rs.is_contiguous() and rs.shape[1] == 6
+        _lib.check(L.rotgeo_dist_push_keeps(w.ptrs, w.world, w.rank, w.take(1), off,
+                                            keep.data_ptr() if keep is not None else None,
+                                            tail.data_ptr() if tail is not None else None, nlocal,
+                                            gid.ctypes.data if nlocal else None, cap, ngroups,
+                                            rs.data_ptr() if rs is not None else None, row_floats, 6,
+                                            gbase.ctypes.data if nlocal else None, stream), 'rotgeo_dist_push_keeps')
+        head_t = w.view(off, (ngroups + world,), torch.int64)
+        keep_all = w.view(off + (ngroups + world) * 8, (ngroups, cap), torch.int64).clone()
+        rows_all = None
+        if rows_src is not None:
+            rows_all = w.view(off + (ngroups + world) * 8 + ngroups * cap * 8, (ngroups, cap, 6), torch.float32).clone()
+        head = head_t.tolist()            # the one device->host read: kept per group of ALL ranks + error words
+    if any(head[ngroups:]):
+        return None
+    return head[:ngroups], keep_all, rows_all
 
 
 # ------------------------------------------------------------------ many-image NMS
@@ -163,15 +301,36 @@ def nms_images(images, iou_threshold, max_per_img=-1, keep_fn=None):
     return [k[:max_per_img] for k in out] if max_per_img > 0 else out
 
 
-def nms_images_sharded(images, iou_threshold, max_per_img=-1, group=None, keep_fn=None):
-    """``nms_images`` with the images spread over the ranks (BASELINE C4).
-    Every rank passes the SAME list; image i is processed by
-    ``lpt_assign([n_i^2], G)[i]`` and every rank returns all keep lists."""
+def nms_images_sharded(images, iou_threshold, max_per_img=-1, group=None, keep_fn=None, sizes=None):
+    """``nms_images`` with the images spread over the ranks (BASELINE C4).  Image i is processed
+    by rank ``lpt_assign([n_i^2], G)[i]`` and every rank returns all keep lists.  Every rank
+    passes a list of the same length; with ``sizes`` (the box count of every image) the entries
+    of images a rank does not own may be ``None`` — a rank then only holds (uploads) its own
+    images.  On NCCL the keep lists travel through peer memory (``_nms_exchange_peer``: no
+    library collective, one device->host read per call); otherwise one padded all-gather."""
     world, rank = _world(group)
     if world == 1:
         return nms_images(images, iou_threshold, max_per_img, keep_fn)
-    owner = lpt_assign([float(b.shape[0]) ** 2 for b, _, _ in images], world)
+    if sizes is None:
+        sizes = [int(im[0].shape[0]) for im in images]
+    owner = lpt_assign([float(v) ** 2 for v in sizes], world)
     mine = [i for i in range(len(images)) if owner[i] == rank]
+    if keep_fn is None and peer.available(group) and float(iou_threshold) > 0.0 and sum(sizes) > 0:
+        dev = torch.device('cuda', torch.cuda.current_device())
+        loc = [images[i] for i in mine]
+        lsz = [sizes[i] for i in mine]
+        if sum(lsz) > 0:
+            boxes = torch.cat([b for b, _, _ in loc], dim=0).to(dev)
+            scores = torch.cat([sc for _, sc, _ in loc], dim=0).to(dev)
+            ids = torch.cat([i.to(torch.int64) for _, _, i in loc], dim=0).to(dev)
+        else:
+            boxes = scores = ids = None
+        cap = max(1, max((min(v, max_per_img) if max_per_img > 0 else v) for v in sizes))
+        got = _nms_exchange_peer(boxes, scores, ids, True, lsz, mine, len(images), cap, iou_threshold, group)
+        if got is not None:
+            counts, keep_all, _ = got
+            return [keep_all[i, :counts[i]] for i in range(len(images))]
+        assert all(im is not None for im in images), 'ids outside the device front-end need every image on every rank'
     keeps = nms_images([images[i] for i in mine], iou_threshold, max_per_img, keep_fn)
     cdev = _comm_device(group)
     # ONE collective and ONE device->host read: every rank sends a fixed-size int64 message
@@ -209,6 +368,46 @@ def nms_images_sharded(images, iou_threshold, max_per_img=-1, group=None, keep_f
 
 
 # ------------------------------------------------------------------ huge-image merge
+def merge_dets_sharded(dets, sizes, iou_thr=0.1, group=None):
+    """Class-sharded patch-merge NMS on DEVICE-RESIDENT detections (BASELINE C5).  ``sizes[c]`` is
+    the detection count of class c (known to every rank); class c is merged by rank
+    ``lpt_assign([n_c^2], G)[c]``, which passes its ``dets[c]`` as a float32 CUDA tensor (n_c, 6)
+    (box + score, image coordinates); entries of classes a rank does not own may be None.
+    Returns, on EVERY rank, the list over classes of (k_c, 6) kept rows in descending score
+    order.  One grouped NMS per rank (a class = a group) and one push of the kept rows through
+    peer memory; the reference loops over the classes in one process (merge_results.py:90-119)."""
+    world, rank = _world(group)
+    ncls = len(sizes)
+    owner = lpt_assign([float(v) ** 2 for v in sizes], world)
+    mine = [c for c in range(ncls) if owner[c] == rank and sizes[c] > 0]
+    dev = torch.device('cuda', torch.cuda.current_device())
+    if world == 1 or not peer.available(group):
+        assert world == 1, 'merge_dets_sharded needs peer memory (NCCL on CUDA devices)'
+    lsz = [int(sizes[c]) for c in mine]
+    if mine:
+        d = dets[mine[0]] if len(mine) == 1 else torch.cat([dets[c] for c in mine], dim=0)
+        d = d.to(device=dev, dtype=torch.float32).contiguous()
+    else:
+        d = None
+    if world == 1:
+        out = [torch.zeros((0, 6), dtype=torch.float32, device=dev) for _ in range(ncls)]
+        if mine:
+            keep, kcounts = ops._nms_grouped(d[:, :5], d[:, 5], iou_thr, group_sizes=lsz)
+            starts = np.concatenate([[0], np.cumsum(lsz)])[:-1]
+            pos = 0
+            for j, c in enumerate(mine):
+                out[c] = d[keep[pos:pos + kcounts[j]] + int(starts[j])]
+                pos += kcounts[j]
+        return out
+    cap = max(1, max(int(v) for v in sizes))
+    got = _nms_exchange_peer(d[:, :5] if d is not None else None, d[:, 5] if d is not None else None, None, False,
+                             lsz, mine, ncls, cap, iou_thr, group, rows_src=d if d is not None else torch.zeros((0, 6), device=dev))
+    if got is None:
+        raise RuntimeError('rotgeo: class-sharded merge failed in the NMS front-end')
+    counts, _, rows_all = got
+    return [rows_all[c, :counts[c]] for c in range(ncls)]
+
+
 def merge_results_sharded(results, offsets, img_shape, iou_thr=0.1, device='cpu', group=None,
                           merge_fn=None):
     """``core.merge_results`` with the classes spread over the ranks (BASELINE
@@ -224,6 +423,21 @@ def merge_results_sharded(results, offsets, img_shape, iou_thr=0.1, device='cpu'
     n_c = [sum(results[p][c].shape[0] for p in range(num_patches)) for c in range(num_classes)]
     owner = lpt_assign([float(v) ** 2 for v in n_c], world)
     mine = [c for c in range(num_classes) if owner[c] == rank]
+    rotated = all(results[0][c].shape[1] == 6 for c in range(num_classes))
+    if merge_fn is core.merge_results and rotated and peer.available(group) and not isinstance(results[0], tuple):
+        # every class is shifted in place (the reference's observable side effect), but only this
+        # rank's classes are concatenated, uploaded and merged; the kept rows come back through
+        # peer memory and leave the device once
+        dets = [None] * num_classes
+        dev = torch.device('cuda', torch.cuda.current_device())
+        for c in range(num_classes):
+            parts = [core.translate_bboxes(results[p][c], offsets[p]) for p in range(num_patches)]
+            if owner[c] == rank and n_c[c] > 0:
+                dets[c] = torch.from_numpy(np.ascontiguousarray(np.concatenate(parts, axis=0), dtype=np.float32)).to(dev)
+        merged = merge_dets_sharded(dets, n_c, iou_thr, group)
+        flat = torch.cat(merged, dim=0).cpu().numpy()
+        bounds = np.concatenate([[0], np.cumsum([m.shape[0] for m in merged])])
+        return [flat[bounds[c]:bounds[c + 1]].astype(results[0][c].dtype, copy=False) for c in range(num_classes)]
     # this rank's classes only; translation (in place) happens for ALL classes so the
     # observable side effect on the caller's arrays matches the single-process call
     sub = [[results[p][c] for c in mine] for p in range(num_patches)]

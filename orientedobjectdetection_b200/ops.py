@@ -139,7 +139,7 @@ def _top1(s, lo=0, hi=None):
 
 
 def _nms_grouped(boxes, scores, iou_threshold, seg_ids=None, offsets=None, id_offsets=False,
-                 group_sizes=None, seg_cap=None):
+                 group_sizes=None, seg_cap=None, no_read=False):
     """Greedy rotated NMS of one or several GROUPS of boxes stored back to back (group g owns
     ``group_sizes[g]`` consecutive rows; None = one group).  Suppression only among boxes of
     equal ``seg_ids`` inside a group.  Centre offsets (added to cx, cy before the geometry, as
@@ -155,7 +155,12 @@ def _nms_grouped(boxes, scores, iou_threshold, seg_ids=None, offsets=None, id_of
     Launch sequence (C-ABI): rotgeo_nms_sort (ONE kernel: orders, offsets, segment table and
     launch totals in a device header) and rotgeo_nms_run (pack + mask + resolve over worst-case
     bounds): no device->host read until the kept count is fetched at the end.  Jobs whose
-    worst-case workspace exceeds _PLAN_LIMIT read the 64-byte plan back once instead."""
+    worst-case workspace exceeds _PLAN_LIMIT read the 64-byte plan back once instead.
+
+    ``no_read=True`` (the multi-GPU callers, which push the result to their peers first and read
+    once at the very end): nothing is read back; returns ``(keep (n,), tail)`` with ``tail`` the
+    device int64 vector ``[kept in all, front-end error bits, kept per group ...]``; a non-zero
+    error word means the result is void (ids the front-end does not take)."""
     dev = _cuda_device(boxes, scores)
     n = boxes.size(0)
     b = _rows_f32(boxes, dev)
@@ -163,6 +168,8 @@ def _nms_grouped(boxes, scores, iou_threshold, seg_ids=None, offsets=None, id_of
     grouped = group_sizes is not None
     sizes_h = np.ascontiguousarray(group_sizes, dtype=np.int64) if grouped else None
     ngroups = int(sizes_h.shape[0]) if grouped else 1
+    if no_read:
+        assert grouped and n > 0 and float(iou_threshold) > 0.0
     if n == 0:
         return torch.zeros(0, dtype=torch.int64, device=dev), ([0] * ngroups if grouped else None)
     if not float(iou_threshold) > 0.0:
@@ -217,6 +224,8 @@ def _nms_grouped(boxes, scores, iou_threshold, seg_ids=None, offsets=None, id_of
                                             keep.data_ptr(), tail.data_ptr(),
                                             tail.data_ptr() + 16 if grouped else None,
                                             ws.data_ptr(), ws.numel(), stream), 'rotgeo_nms_run')
+                if no_read:
+                    return keep, tail
                 host = tail.tolist()          # the one device->host read of the call: sizes the outputs
                 err = int(host[1])
                 if not err:
