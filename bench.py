@@ -23,6 +23,8 @@ sys.path.insert(0, ROOT)
 N_ROWS = 8192          # rows per GPU (weak scaling: the global matrix is (N_ROWS*G) x N_COLS)
 N_COLS = 8192
 EXTENT = 4096.0
+WORKLOAD = ('C3 rbbox_overlaps 8192x8192 le90 boxes, extent 4096, synth.c3_iou(seed 0), w,h clamp 1e-3: one such '
+            'block per GPU (weak scaling: rank r > 0 draws its rows with seed 1000 + r)')
 FLOP_PER_PAIR = 450.0  # mandatory part of the reference algorithm
 FP32_PEAK_TFLOPS = 148 * 128 * 2 * 1.965e9 / 1e12   # 74.5, theoretical at max boost
 
@@ -137,10 +139,9 @@ def run_reference(args, rank):
     emit({
         'impl': 'reference', 'metric': 'rotated_iou_gpairs_per_s', 'value': val, 'unit': 'Gpairs/s',
         'n_gpus': args.gpus, 'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': ms,
-        'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32',
+        'higher_is_better': True, 'scaling': 'weak', 'collective': 'none', 'vs_baseline': None, 'dtype': 'f32',
         'data': 'synthetic',
-        'config': {'workload': 'C3 rbbox_overlaps 8192x8192 le90 boxes, extent 4096, seed 0',
-                   'sample': sample},
+        'config': {'workload': WORKLOAD, 'sample': sample},
         'cpu_baseline': {'value': val, 'unit': 'Gpairs/s', 'cores': threads, 'kind': 'port',
                          'sample': sample},
         'e2e': {'value': val, 'unit': 'Gpairs/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
@@ -196,6 +197,11 @@ def secondary_nms(torch, rg, synth, reps=5):
     res['c4_64img_per_image_calls'] = {'boxes': nb, 'ms': 1e3 * t, 'boxes_per_s': nb / t}
     t = best(lambda: rdist.nms_images(imgs, 0.8, 2000), 3)
     res['c4_64img_one_segmented_launch'] = {'boxes': nb, 'ms': 1e3 * t, 'boxes_per_s': nb / t}
+    bat = rdist.Batched(torch.cat([b for b, _, _ in imgs]), torch.cat([s for _, s, _ in imgs]),
+                        torch.cat([i for _, _, i in imgs]), [int(b.shape[0]) for b, _, _ in imgs])
+    t = best(lambda: rdist.nms_images(bat, 0.8, 2000), 3)
+    res['c4_64img_one_segmented_launch_batched_input'] = {'boxes': nb, 'ms': 1e3 * t, 'boxes_per_s': nb / t}
+    del bat
     del imgs
     n = 30000
     b1 = torch.from_numpy(synth.le90_boxes(n, 9, 1024.0)).cuda()
@@ -232,45 +238,73 @@ def secondary_nms(torch, rg, synth, reps=5):
         rg.merge_results(cp, offs, shape, 0.1)
         ts.append(time.perf_counter() - t0)
     res['c5_merge_results_200k_host_lists'] = {'boxes': nd, 'ms': 1e3 * min(ts), 'boxes_per_s': nd / min(ts)}
-    # `cp` was shifted to image coordinates in place by the last merge_results call
-    allc = np.concatenate([a for p in cp for a in p], axis=0)
-    seg = np.concatenate([np.full(a.shape[0], c, np.int64) for p in cp for c, a in enumerate(p)])
-    dd, sg = torch.from_numpy(allc).cuda(), torch.from_numpy(seg).cuda()
+    # `cp` was shifted to image coordinates in place by the last merge_results call; one GROUP per class
+    per_cls = [np.concatenate([p[c] for p in cp], axis=0) for c in range(len(cp[0]))]
+    counts = [a.shape[0] for a in per_cls]
+    dd = torch.from_numpy(np.concatenate(per_cls, axis=0)).cuda()
     from orientedobjectdetection_b200 import ops
-    t = best(lambda: ops._nms_keep(dd[:, :5], dd[:, 5], 0.1, seg_ids=sg), 3)
+    t = best(lambda: ops._nms_grouped(dd[:, :5], dd[:, 5], 0.1, group_sizes=counts), 3)
     res['c5_class_batched_nms_200k_device_resident'] = {'boxes': nd, 'ms': 1e3 * t, 'boxes_per_s': nd / t}
     return res
 
 
 def secondary_sharded(torch, dist, rg, synth, dev):
-    """N > 1: the NMS workloads that shard (BASELINE C4: images over ranks, C5: classes over
-    ranks) and C3 as ONE global matrix row-sharded (strong scaling), wall clock, max over ranks.
-    Every rank builds the same synthetic inputs; results are all-gathered (dist.py)."""
+    """N > 1: the workloads that SHARD (BASELINE C3 as ONE matrix row-sharded, C4 images over ranks, C5
+    classes over ranks).  Every rank holds only its own shard on the device; results reach all ranks
+    through peer memory (orientedobjectdetection_b200/dist.py).  Per entry: device_ms = CUDA events
+    around the call on the launching stream, ms = wall clock of the call incl. its one host read; both
+    the max over ranks, best of a few repetitions."""
     from orientedobjectdetection_b200 import dist as rdist
     import copy
-    res = {}
+    rank, world = dist.get_rank(), dist.get_world_size()
+    res = {'peer_memory': bool(rdist.peer.available())}
 
-    def timed(fn, reps=3):
+    def timed(fn, reps=5):
         fn()
-        ts = []
+        ev, wl = [], []
         for _ in range(reps):
             torch.cuda.synchronize()
             dist.barrier()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             t0 = time.perf_counter()
+            e0.record()
             fn()
+            e1.record()
             torch.cuda.synchronize()
-            t = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+            t = torch.tensor([e0.elapsed_time(e1), 1e3 * (time.perf_counter() - t0)], dtype=torch.float64, device=dev)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            ts.append(float(t))
-        return min(ts)
+            ev.append(float(t[0]))
+            wl.append(float(t[1]))
+        return min(ev), min(wl)
 
-    imgs = [tuple(torch.from_numpy(x).to(dev) for x in synth.c4_rpn_image(s)) for s in range(64)]
-    nb = sum(int(b.shape[0]) for b, _, _ in imgs)
-    t = timed(lambda: rdist.nms_images_sharded(imgs, 0.8, 2000))
-    res['c4_64img_sharded_over_ranks'] = {'boxes': nb, 'ms': 1e3 * t, 'boxes_per_s': nb / t}
-    del imgs
+    def entry(units, key, ev, wl):
+        return {key: units, 'device_ms': ev, 'ms': wl, key + '_per_s': units / (wl * 1e-3)}
+
+    # C4: 64 images, each rank uploads only the images it owns
+    c4 = [synth.c4_rpn_image(s) for s in range(64)]
+    sizes = [int(b.shape[0]) for b, _, _ in c4]
+    owner = rdist.lpt_assign([float(v) ** 2 for v in sizes], world)
+    mine = [i for i in range(64) if owner[i] == rank]
+    bat = rdist.Batched(*[torch.from_numpy(np.concatenate([c4[i][k] for i in mine])).to(dev) for k in range(3)], sizes)
+    ev, wl = timed(lambda: rdist.nms_images_sharded(bat, 0.8, 2000))
+    res['c4_64img_sharded_over_ranks'] = entry(sum(sizes), 'boxes', ev, wl)
+    res['c4_64img_sharded_over_ranks']['input'] = 'each rank holds the proposals of ITS images back to back on the device'
+    del bat
+    # C5: ~200k detections, classes over ranks; device-resident (each rank holds its classes) ...
     patches, offs, shape = synth.c5_patch_results(0)
     nd = sum(a.shape[0] for p in patches for a in p)
+    shifted = copy.deepcopy(patches)
+    for p, o in zip(shifted, offs):
+        for a in p:
+            a[:, :2] += o
+    per_cls = [np.concatenate([p[c] for p in shifted], axis=0) for c in range(len(shifted[0]))]
+    n_c = [a.shape[0] for a in per_cls]
+    own = rdist.lpt_assign([float(v) ** 2 for v in n_c], world)
+    dets = [torch.from_numpy(per_cls[c]).to(dev) if own[c] == rank else None for c in range(len(n_c))]
+    ev, wl = timed(lambda: rdist.merge_dets_sharded(dets, n_c, 0.1))
+    res['c5_200k_class_sharded_device_resident'] = entry(nd, 'boxes', ev, wl)
+    del dets
+    # ... and through the reference's host-list API (merge_results: numpy lists in, numpy lists out)
     ts = []
     for _ in range(2):
         cp = copy.deepcopy(patches)
@@ -282,14 +316,116 @@ def secondary_sharded(torch, dist, rg, synth, dev):
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         ts.append(float(tt))
     res['c5_merge_results_classes_sharded_over_ranks'] = {'boxes': nd, 'ms': 1e3 * min(ts), 'boxes_per_s': nd / min(ts)}
+    # C3 as ONE 8192 x 8192 matrix, rows over ranks: (i) compute only, (ii) + the full matrix on every rank,
+    # (iii) fused row / column maxima on every rank instead of the matrix
     a3, b3 = synth.c3_iou(0)
     ad, bd = torch.from_numpy(a3).to(dev), torch.from_numpy(b3).to(dev)
     pairs = a3.shape[0] * b3.shape[0]
-    t = timed(lambda: rdist.rbbox_overlaps_sharded(ad, bd, gather=False), 5)
-    res['c3_one_8192x8192_matrix_row_sharded_compute_only'] = {'pairs': pairs, 'ms': 1e3 * t, 'gpairs_per_s': pairs / t / 1e9}
-    t = timed(lambda: rdist.rbbox_overlaps_sharded(ad, bd), 5)
-    res['c3_one_8192x8192_matrix_row_sharded_plus_allgather'] = {'pairs': pairs, 'ms': 1e3 * t, 'gpairs_per_s': pairs / t / 1e9}
+    ev, wl = timed(lambda: rdist.rbbox_overlaps_sharded(ad, bd, gather=False))
+    res['c3_one_8192x8192_matrix_row_sharded_compute_only'] = entry(pairs, 'pairs', ev, wl)
+    ev, wl = timed(lambda: rdist.rbbox_overlaps_sharded(ad, bd))
+    res['c3_one_8192x8192_matrix_row_sharded_plus_allgather'] = entry(pairs, 'pairs', ev, wl)
+    ev, wl = timed(lambda: rdist.rbbox_overlaps_max_sharded(ad, bd))
+    res['c3_one_8192x8192_matrix_row_sharded_fused_maxima'] = entry(pairs, 'pairs', ev, wl)
     return res
+
+
+def fp32_peak():
+    """measured FFMA peak of this part (tools/fp32_peak.cu, committed result), else the theoretical one"""
+    p = os.path.join(ROOT, 'profiles', 'r02_fp32_ffma_peak.json')
+    try:
+        d = json.load(open(p))
+        return max(r['tflops'] for r in d['runs']), 'measured (profiles/r02_fp32_ffma_peak.json, 16 FFMA chains per thread)'
+    except Exception:
+        return FP32_PEAK_TFLOPS, 'theoretical at max boost'
+
+
+def dense_roofline(torch, L, _lib, synth, flush, steps):
+    """SURVEY C3's second variant: extent 1024, 2.6 % of the pairs overlap, so the clipper's FP32 work
+    is no longer hidden behind the write stream.  The tile kernel alone, CUDA events, L2 flushed."""
+    a, b = synth.c3_iou(0, N_ROWS, N_COLS, 1024.0)
+    ad, bd = torch.from_numpy(a).cuda(), torch.from_numpy(b).cuda()
+    out = torch.empty((N_ROWS, N_COLS), dtype=torch.float32, device='cuda')
+    nbytes = L.rotgeo_iou_workspace_bytes(N_ROWS, N_COLS)
+    ws = torch.empty(nbytes, dtype=torch.uint8, device='cuda')
+    stream = torch.cuda.current_stream().cuda_stream
+    _lib.check(L.rotgeo_iou_pairwise(ad.data_ptr(), N_ROWS, 5, bd.data_ptr(), N_COLS, 5, 0, 1e-3, out.data_ptr(),
+                                     N_COLS, ws.data_ptr(), nbytes, stream), 'rotgeo_iou_pairwise')
+    pk1 = ws.data_ptr()
+    pk2 = pk1 + (L.rotgeo_packed_bytes(N_ROWS) + 255) // 256 * 256
+    kms = timed_steps(torch, lambda: _lib.check(L.rotgeo_iou_pairwise_packed(pk1, N_ROWS, pk2, N_COLS, 0, out.data_ptr(),
+                                                                           N_COLS, stream), 'packed'), steps, flush, None)
+    k_ms = float(np.mean(kms))
+    nz = int((out > 0).sum().item())
+    alg_bytes = 4.0 * N_ROWS * N_COLS + 20.0 * (N_ROWS + N_COLS)
+    peak, src = peaks()
+    fpk, fsrc = fp32_peak()
+    pairs_s = N_ROWS * N_COLS / (k_ms * 1e-3)
+    return {'workload': 'C3 dense variant: extent 1024, %d of %d pairs overlap' % (nz, N_ROWS * N_COLS),
+            'bound': 'hbm', 'kernel': 'iou_tile_kernel<0,true>', 'kernel_ms': k_ms,
+            'achieved': alg_bytes / (k_ms * 1e-3) / 1e9, 'peak': peak, 'unit': 'GB/s',
+            'frac': alg_bytes / (k_ms * 1e-3) / 1e9 / peak, 'peak_source': src, 'traffic': None,
+            'alternative_bound_fp32': {'flop_per_pair': FLOP_PER_PAIR, 'achieved_tflops': pairs_s * FLOP_PER_PAIR / 1e12,
+                                       'peak_tflops': fpk, 'peak_source': fsrc,
+                                       'frac': pairs_s * FLOP_PER_PAIR / 1e12 / fpk,
+                                       'note': 'the 450 flop/pair model is the reference algorithm\'s mandatory work; '
+                                               'the cull skips it for disjoint pairs, so this is not a utilisation'}}
+
+
+def nms_block(torch, rg, synth):
+    """the rotated-NMS half of the metric in the driver-run line: BASELINE C2 (2000 proposals x 15 classes)
+    through the public call, device time by CUDA events, per-kernel times by CUPTI, the roofline of the
+    suppression-mask pass (B_nms = 24 N + 8 N ceil(N / 64) / 2 + 8 K bytes per
+    segment) and the oracle on the same input on one host core (what upstream mmcv's CPU op is)."""
+    from torch.profiler import profile, ProfilerActivity
+    from oracle import ref_api
+    peak, src = peaks()
+    out = {}
+    for name, dense in (('c2_sparse', False), ('c2_dense', True)):
+        mb, ms = synth.c2_multiclass(0, dense=dense)
+        mbd, msd = torch.from_numpy(mb).cuda(), torch.from_numpy(ms).cuda()
+        per_cls = (ms[:, :-1] > 0.05).sum(0).astype(np.int64)
+        ncand = int(per_cls.sum())
+
+        def call():
+            return rg.multiclass_nms_rotated(mbd, msd, 0.05, dict(iou_thr=0.1), 2000)
+        for _ in range(5):
+            kept = call()[0].shape[0]
+        torch.cuda.synchronize()
+        reps = 20
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            call()
+        e1.record()
+        e1.synchronize()
+        dev_ms = e0.elapsed_time(e1) / reps       # includes the call's own host work between launches
+        with profile(activities=[ProfilerActivity.CUDA]) as prof:
+            for _ in range(10):
+                call()
+            torch.cuda.synchronize()
+        kt = {}
+        for e in prof.key_averages():
+            if 'rotgeo::' in e.key:
+                short = e.key.split('rotgeo::')[1].split('(')[0].split('<')[0]
+                kt[short] = kt.get(short, 0.0) + e.device_time_total / 10.0
+        alg = float(sum(24 * n + 8 * n * ((n + 63) // 64) / 2 for n in per_cls) + 8 * kept)
+        pairs = float(sum(n * (n - 1) / 2 for n in per_cls))
+        mask_us = kt.get('nms_mask_kernel', float('nan'))
+        t0 = time.perf_counter()
+        ref_api.multiclass_nms_rotated(torch.from_numpy(mb), torch.from_numpy(ms), 0.05, 0.1, 2000)
+        cpu_s = time.perf_counter() - t0
+        out[name] = {
+            'boxes': ncand, 'kept': int(kept), 'ms_per_call': dev_ms, 'boxes_per_s': ncand / (dev_ms * 1e-3),
+            'kernels_us': {k: round(v, 2) for k, v in sorted(kt.items())},
+            'roofline': {'bound': 'hbm', 'kernel': 'nms_mask_kernel', 'kernel_us': mask_us,
+                         'algorithmic_bytes_per_launch': alg, 'achieved': alg / (mask_us * 1e-6) / 1e9, 'peak': peak,
+                         'unit': 'GB/s', 'frac': alg / (mask_us * 1e-6) / 1e9 / peak, 'peak_source': src,
+                         'pairs_per_launch': pairs, 'gpairs_per_s': pairs / (mask_us * 1e-6) / 1e9, 'traffic': None,
+                         'note': 'latency/issue-bound at this size: 15 segments of <= 2000 boxes are 120 tiles'},
+            'cpu_baseline': {'value': ncand / cpu_s, 'unit': 'boxes/s', 'cores': 1, 'kind': 'port', 'seconds': cpu_s,
+                             'sample': 'the whole call on the same input, 1 repetition'}}
+    return out
 
 
 def measured_traffic():
@@ -320,8 +456,9 @@ def run_rotgeo(args, rank, world, local_rank):
     L = _lib.load()
 
     # rank r owns rows [r*N_ROWS, (r+1)*N_ROWS) of the global matrix; columns replicated
-    a = synth.le90_boxes(N_ROWS, 1000 + rank, EXTENT)
-    b = synth.le90_boxes(N_COLS, 1, EXTENT)
+    a, b = synth.c3_iou(0, N_ROWS, N_COLS, EXTENT)      # the reference arm's block (rank 0 times exactly this one)
+    if rank > 0:
+        a = synth.le90_boxes(N_ROWS, 1000 + rank, EXTENT)
     a_host, b_host = torch.from_numpy(a).pin_memory(), torch.from_numpy(b).pin_memory()
     a_dev, b_dev = a_host.to(dev), b_host.to(dev)
     out = torch.empty((N_ROWS, N_COLS), dtype=torch.float32, device=dev)
@@ -405,11 +542,11 @@ def run_rotgeo(args, rank, world, local_rank):
     line = {
         'metric': 'rotated_iou_gpairs_per_s', 'value': value, 'unit': 'Gpairs/s', 'n_gpus': world,
         'steps': args.steps, 'warmup': max(args.warmup, 3), 'ms_per_step': ms_per_step,
-        'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32',
+        'higher_is_better': True, 'scaling': 'weak',
+        'collective': 'none',    # every rank times its own block: NOT a sharding result (see secondary for those)
+        'vs_baseline': None, 'dtype': 'f32',
         'data': 'synthetic',
-        'config': {'workload': 'C3 rbbox_overlaps: one 8192x8192 block of le90 boxes per GPU '
-                               '(global matrix (8192*G) x 8192 row-sharded, columns replicated), '
-                               'extent 4096, w,h clamp 1e-3 fused',
+        'config': {'workload': WORKLOAD,
                    'rows_per_gpu': N_ROWS, 'cols': N_COLS,
                    'l2': 'output 268 MB/step exceeds the 126 MB L2; a 512 MB memset flushes L2 '
                          'between steps, outside the CUDA events',
@@ -420,7 +557,9 @@ def run_rotgeo(args, rank, world, local_rank):
                 'd2h_bytes_per_step': int(N_ROWS * N_COLS * 4), 'steps': e2e_steps,
                 'api': 'orientedobjectdetection_b200.rbbox_overlaps(pinned CPU tensors) -> pinned CPU tensor'},
         'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
-                     'frac': achieved / peak, 'traffic': measured_traffic(), 'kernel': 'iou_tile_kernel<0,true>',
+                     'frac': achieved / peak, 'traffic': measured_traffic(),
+                     'traffic_source': 'committed ncu --set full capture of this kernel (profiles/r01_iou_tile_kernel_traffic.json), not re-measured in this run',
+                     'kernel': 'iou_tile_kernel<0,true>',
                      'kernel_ms': k_ms, 'peak_source': peak_src,
                      'algorithmic_bytes_per_launch': alg_bytes,
                      'fp32_view': {'flop_per_pair': FLOP_PER_PAIR,
@@ -430,6 +569,8 @@ def run_rotgeo(args, rank, world, local_rank):
         'clocks': clocks,
     }
     if rank == 0 and world == 1 and not args.no_secondary:
+        line['roofline_dense'] = dense_roofline(torch, L, _lib, synth, flush, args.steps)
+        line['nms'] = nms_block(torch, rg, synth)
         line['secondary'] = secondary_nms(torch, rg, synth)
     if world > 1 and not args.no_secondary:
         try:

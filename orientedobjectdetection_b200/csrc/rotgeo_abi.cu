@@ -396,7 +396,7 @@ int rotgeo_nms_read_plan(const void *sortws, int64_t n, const int64_t *group_siz
 size_t rotgeo_nms_run_bytes(int64_t n, const int64_t *sizes) {
     if (n <= 0 || !sizes) return 0;
     rotgeo::NmsRunLayout l;
-    rotgeo::nms_run_layout(n, sizes_from(sizes), &l);
+    rotgeo::nms_run_layout(n, sizes_from(sizes), true, &l);     // with the regions of a spatially packed launch
     return l.total_bytes;
 }
 

@@ -116,6 +116,20 @@ __device__ __forceinline__ bool circles_disjoint(float ax, float ay, float ar, f
     return fmaf(dx, dx, dy * dy) > rs * rs;
 }
 
+// Upper bound of the intersection area of A and B: in A's frame A is the slab |x| <= aA, |y| <= bA,
+// and the intersection lies inside A clipped by the axis-aligned bounding box of B in that frame
+// (half extents aB|c| + bB|s| and aB|s| + bB|c| around B's centre).  <= 0: the boxes are separated
+// along one of A's axes.  ~25 FP32 instructions against the clipper's ~170.
+__device__ __forceinline__ float intersection_upper_bound(float4 A0, float4 A1, float4 B0, float4 B1) {
+    const float dx = B0.x - A0.x, dy = B0.y - A0.y;
+    const float X = fmaf(dx, A1.x, dy * A1.y), Y = fmaf(dy, A1.x, -dx * A1.y);
+    const float c = fabsf(fmaf(A1.x, B1.x, A1.y * B1.y)), s = fabsf(fmaf(B1.y, A1.x, -B1.x * A1.y));
+    const float px = fmaf(B1.z, c, B1.w * s), py = fmaf(B1.z, s, B1.w * c);
+    const float ox = fminf(A1.z, X + px) - fmaxf(-A1.z, X - px);
+    const float oy = fminf(A1.w, Y + py) - fmaxf(-A1.w, Y - py);
+    return fmaxf(ox, 0.f) * fmaxf(oy, 0.f);
+}
+
 __device__ __forceinline__ float fmax3(float a, float b, float c) { return fmaxf(fmaxf(a, b), c); }
 __device__ __forceinline__ float fmin3(float a, float b, float c) { return fminf(fminf(a, b), c); }
 

@@ -36,7 +36,7 @@ constexpr int kTile = 128;
 static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
 // ---- workspace of pack / mask / resolve for given (bounds of the) counts ---------------------------
-void nms_run_layout(int64_t n, const NmsSizes &z, NmsRunLayout *l) {
+void nms_run_layout(int64_t n, const NmsSizes &z, bool spatial, NmsRunLayout *l) {
     size_t off = 0;
     l->sum_words = nms_sum_words(z.max_blocks);
     l->off_packed = off;   off = align_up(off + (size_t)z.n_pad * kPackedBytesPerBox, 256);
@@ -46,6 +46,9 @@ void nms_run_layout(int64_t n, const NmsSizes &z, NmsRunLayout *l) {
     l->off_summary = off;  off = align_up(off + (size_t)z.n_pad * l->sum_words * 8, 256);
     l->off_sync = off;     off = align_up(off + kNmsSyncWords * sizeof(unsigned int), 256);
     l->off_counts = off;   off = align_up(off + kNmsMaxBlocks * sizeof(int), 256);
+    l->off_rank = off;     off = align_up(off + (spatial ? (size_t)z.n_pad * 4 : 0), 256);
+    l->off_aabb = off;     off = align_up(off + (spatial ? (size_t)(z.n_pad / kTile) * 16 : 0), 256);
+    l->off_tiles = off;    off = align_up(off + (spatial ? (size_t)z.tiles * 8 : 0), 256);
     l->total_bytes = off;
 }
 
@@ -119,6 +122,7 @@ int nms_sort(const float *boxes, int64_t n, int stride, const float *scores, con
     a.id_offsets = ids ? id_offsets : 0;
     a.ngroups = (int)ngroups;
     a.seg_cap = (int)seg_cap;
+    a.spatial = nms_spatial(max_group) ? 1 : 0;
     return launch_sort(a, group_sizes_host, n, sortws, l, stream);
 }
 
@@ -164,8 +168,9 @@ int nms_run(const float *boxes, int64_t n, int stride, const float *offsets, int
     const NmsSegment *segs = reinterpret_cast<const NmsSegment *>(sw + sl.off_segs);
     const uint32_t *order = reinterpret_cast<const uint32_t *>(sw + sl.off_order);
     const uint32_t *seg_order = reinterpret_cast<const uint32_t *>(sw + sl.off_seg_order);
+    const bool spatial = nms_spatial(max_group);
     NmsRunLayout l;
-    nms_run_layout(n, z, &l);
+    nms_run_layout(n, z, spatial, &l);
     char *ws = reinterpret_cast<char *>(workspace);
 
     PackSet s1 = make_pack_set(boxes, n, stride, nullptr,
@@ -186,6 +191,11 @@ int nms_run(const float *boxes, int64_t n, int stride, const float *offsets, int
     s1.z_summary = scratch.summary;
     s1.z_sum_words = scratch.sum_words;
     s1.z_sync = scratch.sync;
+    if (spatial) {
+        s1.rank_src = reinterpret_cast<const uint32_t *>(sw + sl.off_seg_rank);
+        s1.rank_out = reinterpret_cast<uint32_t *>(ws + l.off_rank);
+        s1.aabb_out = reinterpret_cast<float4 *>(ws + l.off_aabb);
+    }
     const PackSet none = make_pack_set(nullptr, 0, 5, nullptr, nullptr, nullptr, 0);
     if (launch_pack(s1, none, 0.f, 0.f, nms_area_axis_ratio(thr), stream)) return -3;
 
@@ -197,6 +207,11 @@ int nms_run(const float *boxes, int64_t n, int stride, const float *offsets, int
     a.nseg = (int)z.nseg;
     a.nseg_dev = &hdr->nseg;
     a.error_dev = &hdr->error;
+    if (spatial) {
+        a.rank = s1.rank_out;
+        a.aabb = s1.aabb_out;
+        a.tile_list = reinterpret_cast<unsigned long long *>(ws + l.off_tiles);
+    }
     a.tiles_bound = z.tiles;
     a.total_tiles_dev = reinterpret_cast<const int64_t *>(&hdr->total_tiles);
     a.scratch = scratch;
@@ -253,7 +268,7 @@ static void mc_layout(int64_t rows, int classes, McLayout *l) {
     l->z.nseg = classes;
     l->z.n_emit = l->total;
     sort_layout(l->total, 1, classes, l->total, &l->sort);
-    nms_run_layout(l->total, l->z, &l->run);
+    nms_run_layout(l->total, l->z, false, &l->run);
     l->off_run = align_up(l->sort.total_bytes, 256);
     l->total_bytes = l->off_run + l->run.total_bytes;
 }

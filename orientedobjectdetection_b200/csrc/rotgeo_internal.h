@@ -44,11 +44,15 @@ struct PackSet {
     unsigned long long *z_summary;  // n_pad * z_sum_words row summaries
     int z_sum_words;
     unsigned int *z_sync;           // kNmsSyncWords words of barrier / round state
+    // spatially packed NMS sets: the score rank of every slot and one bounding box per 128-slot block
+    const uint32_t *rank_src;       // nullable: rank of every position of the gather list
+    uint32_t *rank_out;             // per slot (0xffffffff: padding)
+    float4 *aabb_out;               // per block: (x lo, y lo, x hi, y hi) of the circumscribed circles; empty: lo > hi
     float4 *p0, *p1;
     uint32_t *pr, *pt;
     int64_t n_pad;
 };
-constexpr int kNmsSyncWords = 16;
+constexpr int kNmsSyncWords = 16;     // [0..1] grid barrier of the resolve kernel, [8..9] 64-bit length of the tile list
 
 // The area axis of the inverted index pays off when the threshold is high enough for the
 // admissible area range to be narrow (RPN: 0.8 -> a few of the 32 bins); at the usual 0.1 of
@@ -158,9 +162,10 @@ struct NmsSizes {
 };
 struct NmsRunLayout {
     size_t off_packed, off_mask, off_flags, off_kr, off_summary, off_sync, off_counts, total_bytes;
+    size_t off_rank, off_aabb, off_tiles;     // spatially packed launches only
     int sum_words;
 };
-void nms_run_layout(int64_t n, const NmsSizes &z, NmsRunLayout *l);
+void nms_run_layout(int64_t n, const NmsSizes &z, bool spatial, NmsRunLayout *l);
 void nms_bounds(const int64_t *group_sizes_host, int64_t ngroups, int64_t n, int64_t seg_cap, NmsSizes *z);
 
 // generic front-end (rotgeo_frontend.cu): sort -> [read plan] -> run
@@ -184,6 +189,10 @@ struct NmsDevLaunch {
     int nseg;                         // segments (a bound when nseg_dev is set)
     const long long *nseg_dev;        // nullable: actual segment count
     const unsigned int *error_dev;    // nullable: front-end error bits, copied to num_keep_out[1]
+    // spatially packed set (null otherwise): score rank per slot, bounding box per block, room for the tile list
+    const uint32_t *rank;
+    const float4 *aabb;
+    unsigned long long *tile_list;
     int64_t tiles_bound;              // mask grid
     const int64_t *total_tiles_dev;   // actual tile count
     NmsScratch scratch;
@@ -208,6 +217,8 @@ constexpr int kSortMaxCluster = 8;                    // portable cluster size: 
 constexpr int kSortGroupsInline = 64;                 // group tables up to this size travel as kernel parameters
 constexpr int64_t kSortSegsMax = 16384;               // segments one call handles
 constexpr unsigned int kSortErrRange = 1u;            // the ids of a group span 2^16 values or more
+constexpr int64_t kSpatialMinGroup = 16384;          // launches whose largest group has at least this many boxes pack spatially
+static inline bool nms_spatial(int64_t max_group) { return max_group >= kSpatialMinGroup; }
 constexpr unsigned int kSortErrSegments = 2u;         // more segments than seg_cap in a group / than kSortSegsMax in all
 
 struct SortHeader {            // device-side result of the front-end (zeroed before the launch)
@@ -233,6 +244,8 @@ struct SortArgs {
     int ngroups;
     int seg_cap;               // segments per group
     int cta_cap;               // elements per CTA buffer of the cluster kernel (set by launch_sort)
+    int spatial;               // pack order inside a segment: Morton order of the centres instead of score order
+                               // (large sparse segments: only neighbouring 128-box blocks form mask tiles); mode 0 only
     const int64_t *gstart;     // device (ngroups + 1) row offsets, or null: gstart_inline
     int64_t gstart_inline[kSortGroupsInline + 1];
     // outputs (carved from the sort workspace by launch_sort)

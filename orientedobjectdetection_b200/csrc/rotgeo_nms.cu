@@ -99,6 +99,7 @@ struct MaskArgs {
     const long long *nseg_dev;    // nullable: actual segment count (device-planned launch)
     float thr;
     float area_ratio;             // pairs with min(area) < area_ratio * max(area) cannot reach thr
+    float inter_need;             // 0.999 thr / (1 + thr): intersection / (areaA + areaB) a pair needs to reach thr
     int area_axis;                // the packed set carries the area axis of the index (launch-uniform)
     unsigned long long *mask;
     unsigned long long *summary;  // per packed slot: sum_words words, zeroed by the pack kernel
@@ -107,8 +108,14 @@ struct MaskArgs {
     int ahead;                    // 1 .. 3: how many tiles ahead the scheduler thread runs (launch-uniform)
     int group;                    // tiles per grid CTA (= per launch-control request): CTA c owns tiles c*group ...
     int64_t tiles;                // host-side tile count (a bound when total_tiles is set)
+    // spatially packed sets: the tiles to visit (seg << 32 | I << 16 | J, any order; *total_tiles of them) and the
+    // score rank of every slot; the bit of a pair goes into the row of the LOWER-ranked box
+    const unsigned long long *tile_list;
+    const uint32_t *rank;
     int64_t ahead_min_tiles;      // 8 tiles per resident CTA of this device: smaller grids keep look-ahead 1
 };
+
+__device__ __forceinline__ int segment_of_slot(const NmsSegment *__restrict__ segs, int nseg, int64_t slot);
 
 // tile id -> (segment, I, J): tiles of a segment are numbered row block by row block,
 // row block I holding the I + 1 tiles J = 0 .. I
@@ -132,6 +139,36 @@ __device__ TileInfo locate_tile(const NmsSegment *__restrict__ segs, int nseg, u
     return ti;
 }
 
+// Spatially packed sets: of the C (C + 1) / 2 block pairs of a segment only those whose blocks' bounding
+// boxes touch can hold an overlapping pair.  One thread per candidate pair; the survivors are appended to
+// `list` (warp-aggregated atomic; the order is irrelevant).  C5: 175 k candidate tiles -> a few thousand.
+__global__ void __launch_bounds__(256)
+nms_tile_list_kernel(const NmsSegment *__restrict__ segs, int nseg_in, const long long *__restrict__ nseg_dev,
+                     const int64_t *__restrict__ total_dev, int64_t tiles_bound, const float4 *__restrict__ aabb,
+                     unsigned long long *__restrict__ list, unsigned long long *__restrict__ count) {
+    const int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    const int64_t limit = total_dev ? min(*total_dev, tiles_bound) : tiles_bound;
+    const int nseg = nseg_dev ? (int)*nseg_dev : nseg_in;
+    bool keep = false;
+    TileInfo ti;
+    ti.valid = 0; ti.seg = 0; ti.I = 0; ti.J = 0;
+    if (t < limit) {
+        ti = locate_tile(segs, nseg, (unsigned)t);
+        const int64_t b0 = segs[ti.seg].pstart / kTile;
+        const float4 A = aabb[b0 + ti.I], B = aabb[b0 + ti.J];
+        keep = ti.I == ti.J || (A.x <= B.z && B.x <= A.z && A.y <= B.w && B.y <= A.w);
+    }
+    const unsigned bal = __ballot_sync(0xffffffffu, keep);
+    if (bal == 0u) return;
+    const int lane = threadIdx.x & 31, lead = __ffs(bal) - 1;
+    unsigned long long base = 0ull;
+    if (lane == lead) base = atomicAdd(count, (unsigned long long)__popc(bal));
+    base = __shfl_sync(0xffffffffu, base, lead);
+    if (keep)
+        list[base + __popc(bal & ((1u << lane) - 1u))] =
+            ((unsigned long long)ti.seg << 32) | ((unsigned long long)ti.I << 16) | (unsigned long long)ti.J;
+}
+
 // AREA: the packed set carries the area axis of the index (high thresholds, see
 // nms_area_axis_ratio): 3 ring stages of 7.7 KB instead of 4 of 5 KB, one more range lookup
 template <bool AREA>
@@ -142,6 +179,8 @@ nms_mask_kernel(const MaskArgs g) {
     constexpr int kStages = AREA ? 3 : 4;
     constexpr uint32_t tab_words = AREA ? kTableWords : kTableXYWords;
     const int nseg = g.nseg_dev ? (int)*g.nseg_dev : g.nseg;
+    const bool LIST = g.tile_list != nullptr;       // launch-uniform
+    if (LIST) pdl_wait();                           // the list and its length come from the kernel before this one
 
     if (tid == 0) {
 #pragma unroll
@@ -239,6 +278,12 @@ nms_mask_kernel(const MaskArgs g) {
                             st.cur_nb = seg_blocks(st.cur.seg);
                         }
                     }
+                } else if (LIST) {
+                    const unsigned long long v = g.tile_list[tn];
+                    st.cur.valid = 1;
+                    st.cur.seg = (int)(v >> 32);
+                    st.cur.I = (int)((v >> 16) & 0xffffull);
+                    st.cur.J = (int)(v & 0xffffull);
                 } else {
                     st.cur = locate_tile(g.segs, nseg, tn);
                     st.cur_nb = seg_blocks(st.cur.seg);
@@ -266,8 +311,16 @@ nms_mask_kernel(const MaskArgs g) {
         st.alive = 1;
         st.cur_nb = 0;
         if ((int64_t)blockIdx.x * G < limit) {
-            t0 = locate_tile(g.segs, nseg, blockIdx.x * G);
-            st.cur_nb = seg_blocks(t0.seg);
+            if (LIST) {
+                const unsigned long long v = g.tile_list[blockIdx.x];      // G == 1 in list mode
+                t0.valid = 1;
+                t0.seg = (int)(v >> 32);
+                t0.I = (int)((v >> 16) & 0xffffull);
+                t0.J = (int)(v & 0xffffull);
+            } else {
+                t0 = locate_tile(g.segs, nseg, blockIdx.x * G);
+                st.cur_nb = seg_blocks(t0.seg);
+            }
         }
         st.cur = t0;
         sm.st = st;
@@ -290,8 +343,18 @@ nms_mask_kernel(const MaskArgs g) {
                                             __ldg(g.p0 + e.pcol), __ldg(g.p1 + e.pcol));
             if (v >= g.thr) {
                 const int J = (int)(e.word >> 48);
-                atomicOr(g.mask + (e.word & kWordMask), 1ull << (e.pcol & 63));
-                atomicOr(g.summary + (int64_t)e.prow * g.sum_words + (J >> 6), 1ull << (J & 63));
+                if (LIST && g.rank[e.prow] < g.rank[e.pcol]) {
+                    // the row box is the better one: it suppresses the column box, the bit belongs to the
+                    // column box's row (rare path: one segment lookup per suppressing pair)
+                    const NmsSegment &sh = g.segs[segment_of_slot(g.segs, nseg, e.prow)];
+                    const int64_t rpos = e.pcol - sh.pstart, cpos = e.prow - sh.pstart;
+                    const int I = (int)(cpos >> 7);
+                    atomicOr(g.mask + sh.mask_base + rpos * sh.words + (cpos >> 6), 1ull << (cpos & 63));
+                    atomicOr(g.summary + (int64_t)e.pcol * g.sum_words + (I >> 6), 1ull << (I & 63));
+                } else {
+                    atomicOr(g.mask + (e.word & kWordMask), 1ull << (e.pcol & 63));
+                    atomicOr(g.summary + (int64_t)e.prow * g.sum_words + (J >> 6), 1ull << (J & 63));
+                }
             }
         }
         n2 -= take;
@@ -307,6 +370,16 @@ nms_mask_kernel(const MaskArgs g) {
             // different sizes end here, 1e-4 below the threshold to stay clear of rounding
             pass = !circles_disjoint(A0.x, A0.y, A0.z, B0.x, B0.y, B0.z) &&
                    fminf(A0.w, B0.w) >= g.area_ratio * fmaxf(A0.w, B0.w);
+            if (AREA && pass) {
+                // high thresholds (RPN: 0.8): IoU >= thr needs inter >= thr (areaA + areaB) / (1 + thr);
+                // a cheap upper bound of the intersection (the smaller box clipped by the other's
+                // bounding box in its frame) sends most circle survivors home before the ~170-instruction
+                // clipper.  0.1 % below the requirement: clear of the rounding of either computation.
+                const bool a_small = A0.w <= B0.w;
+                const float4 S0 = a_small ? A0 : B0, L0 = a_small ? B0 : A0;
+                const float4 S1 = __ldg(g.p1 + (a_small ? e.prow : e.pcol)), L1 = __ldg(g.p1 + (a_small ? e.pcol : e.prow));
+                pass = intersection_upper_bound(S0, S1, L0, L1) >= g.inter_need * (A0.w + B0.w);
+            }
         }
         n1 -= take;
         const uint32_t b = __ballot_sync(0xffffffffu, pass);
@@ -331,6 +404,13 @@ nms_mask_kernel(const MaskArgs g) {
             const int r = row_base + warp + kWarps * lane;
             if (r < L)
                 *reinterpret_cast<uint4 *>(g.mask + sg.mask_base + (int64_t)r * W + 2 * ti.J) =
+                    make_uint4(0u, 0u, 0u, 0u);
+        } else if (LIST && ti.I != ti.J) {
+            // spatial packing: a pair's bit may land in the row of the COLUMN box (the lower-ranked one),
+            // i.e. in rows of block J at the words of block I
+            const int r = col_base + warp + kWarps * (lane - 16);
+            if (r < L)
+                *reinterpret_cast<uint4 *>(g.mask + sg.mask_base + (int64_t)r * W + 2 * ti.I) =
                     make_uint4(0u, 0u, 0u, 0u);
         }
         if (k == 0) {
@@ -450,6 +530,7 @@ struct ResolveArgs {
     const long long *nseg_dev;    // nullable: actual segment count
     const long long *n_pad_dev;   // nullable: slots actually used
     const unsigned int *error_dev;  // nullable: front-end error bits -> num_keep_out[1]
+    int spatial;                  // rows may depend on boxes at LATER positions (spatially packed sets)
     int has_large;                // some segment may have more than kLocalChunks chunks
     const unsigned long long *mask;
     NmsScratch sc;
@@ -561,7 +642,8 @@ __device__ bool resolve_chunk(const ResolveArgs &a, const NmsSegment &sg, int c,
             const int64_t row = pos0 + q;
             const unsigned long long *mrow = M + row * W;
             const unsigned long long *srow = S + q * a.sc.sum_words;
-            const int kmax = (int)(row >> 13);           // summary words that can hold a bit: column blocks 0 .. row / 128
+            // summary words that can hold a bit: column blocks 0 .. row / 128 when packed in score order
+            const int kmax = a.spatial ? (sg.words / 2 - 1) >> 6 : (int)(row >> 13);
             for (int k = 0; k <= kmax && !exK[p]; ++k) {
                 // (plain loads: this row's summary word is rewritten below)
                 const unsigned long long sb0 = __ldcg(srow + k);
@@ -587,7 +669,7 @@ __device__ bool resolve_chunk(const ResolveArgs &a, const NmsSegment &sg, int c,
                             const unsigned long long mv = h ? m[t].y : m[t].x;
                             const int w = 2 * J[t] + h;
                             if (mv == 0ull) continue;
-                            if (w < c) {                      // earlier chunk: its state
+                            if (w != c) {                     // another chunk (an earlier one when packed in score order): its state
                                 const ulonglong2 o = kr_load<RD_SMEM>(kr_others + 2 * w);
                                 if (mv & o.x) exK[p] = true;
                                 if (mv & ~(o.x | o.y)) exU[p] = true;
@@ -935,7 +1017,7 @@ static int launch_mask(const MaskArgs &g_in, int64_t tiles, cudaStream_t stream)
     if (const int forced = probe_env("ROTGEO_MASK_AHEAD", 1, 3)) g.ahead = forced + 16;   // + 16: also for small grids
 #endif
     g.tiles = tiles;
-    g.group = mask_group(tiles, lim);
+    g.group = g.tile_list ? 1 : mask_group(tiles, lim);
     const int64_t ctas = (tiles + g.group - 1) / g.group;
     // one CTA per tile; running CTAs steal the not-yet-launched ones (launch control)
     cudaLaunchConfig_t cfg = {};
@@ -992,12 +1074,15 @@ int launch_nms(const NmsPlan &plan, const void *packed, const NmsSegment *segmen
     g.nseg = (int)plan.num_segments;
     g.thr = thr;
     g.area_ratio = thr - 1e-4f;
+    g.inter_need = 0.999f * thr / (1.f + thr);
     g.area_axis = nms_area_axis_ratio(thr) > 0.f;
     g.mask = reinterpret_cast<unsigned long long *>(mask);
     g.summary = scratch.summary;
     g.sum_words = scratch.sum_words;
     g.total_tiles = nullptr;
     g.nseg_dev = nullptr;
+    g.tile_list = nullptr;
+    g.rank = nullptr;
     int rc = launch_mask(g, plan.total_tiles, stream);
     if (rc) return rc;
     ResolveArgs a = {};
@@ -1027,12 +1112,28 @@ int launch_nms_device_planned(const NmsDevLaunch &d, cudaStream_t stream) {
     g.nseg = d.nseg;
     g.thr = d.thr;
     g.area_ratio = d.thr - 1e-4f;
+    g.inter_need = 0.999f * d.thr / (1.f + d.thr);
     g.area_axis = nms_area_axis_ratio(d.thr) > 0.f;
     g.mask = reinterpret_cast<unsigned long long *>(d.mask);
     g.summary = d.scratch.summary;
     g.sum_words = d.scratch.sum_words;
     g.total_tiles = d.total_tiles_dev;
     g.nseg_dev = d.nseg_dev;
+    g.tile_list = nullptr;
+    g.rank = nullptr;
+    if (d.tile_list) {
+        // spatially packed: list the block pairs whose bounding boxes touch, then visit only those
+        if (d.tiles_bound > 0x7fffffffLL) return -1;
+        unsigned long long *count = reinterpret_cast<unsigned long long *>(d.scratch.sync + 8);   // zeroed by the pack kernel
+        if (d.tiles_bound > 0) {
+            nms_tile_list_kernel<<<(unsigned)((d.tiles_bound + 255) / 256), 256, 0, stream>>>(
+                d.segs_dev, d.nseg, d.nseg_dev, d.total_tiles_dev, d.tiles_bound, d.aabb, d.tile_list, count);
+            if (cudaGetLastError() != cudaSuccess) return -3;
+        }
+        g.tile_list = d.tile_list;
+        g.rank = d.rank;
+        g.total_tiles = reinterpret_cast<const int64_t *>(count);
+    }
     int rc = launch_mask(g, d.tiles_bound, stream);
     if (rc) return rc;
     ResolveArgs a = {};
@@ -1041,6 +1142,7 @@ int launch_nms_device_planned(const NmsDevLaunch &d, cudaStream_t stream) {
     a.nseg_dev = d.nseg_dev;
     a.n_pad_dev = d.n_pad_dev;
     a.error_dev = d.error_dev;
+    a.spatial = d.tile_list != nullptr;
     a.mask = g.mask;
     a.sc = d.scratch;
     a.has_large = d.max_chunks_bound > kLocalChunks;

@@ -201,6 +201,8 @@ pack_kernel(PackSet s1, PackSet s2, float min_wh, float cell, float area_ratio) 
     }
 
     uint32_t xm = 0u, ym = 0u, am = 0u;
+    float bx0 = INFINITY, by0 = INFINITY, bx1 = -INFINITY, by1 = -INFINITY;   // this slot's part of the block's box
+    if (in_set && s.rank_out) s.rank_out[i] = pos >= 0 ? s.rank_src[pos] : 0xffffffffu;
     if (in_set) {
         if (src < 0) {
             // padding: occupies no bin, so no pair with it survives the cull
@@ -237,6 +239,26 @@ pack_kernel(PackSet s1, PackSet s2, float min_wh, float cell, float area_ratio) 
             s.p0[i] = make_float4(cx, cy, r, w * h);
             s.p1[i] = make_float4((float)cd, (float)sd, a, hb);
             s.pr[i] = pack_ranges(sx, nx, sy, ny, sa, na);
+            bx0 = cx - rx; bx1 = cx + rx; by0 = cy - ry; by1 = cy + ry;     // the radius the bins use (rounding included)
+        }
+    }
+
+    // ---- bounding box of every 128-slot block (spatially packed NMS sets only; launch-uniform) ----
+    if (s1.aabb_out) {
+        __shared__ float s_box[kPackThreads / 32][4];
+        bx0 = warp_min(bx0); by0 = warp_min(by0); bx1 = warp_max(bx1); by1 = warp_max(by1);
+        if (lane == 0) { s_box[warp][0] = bx0; s_box[warp][1] = by0; s_box[warp][2] = bx1; s_box[warp][3] = by1; }
+        __syncthreads();
+        if (tid < 2) {
+            const int64_t blk = blockIdx.x * 2 + tid;                       // block of set 1 (NMS packs have no set 2)
+            if (blk * kBlock < s1.n_pad) {
+                float4 bb = make_float4(INFINITY, INFINITY, -INFINITY, -INFINITY);
+                for (int w4 = 0; w4 < 4; ++w4) {
+                    bb.x = fminf(bb.x, s_box[4 * tid + w4][0]); bb.y = fminf(bb.y, s_box[4 * tid + w4][1]);
+                    bb.z = fmaxf(bb.z, s_box[4 * tid + w4][2]); bb.w = fmaxf(bb.w, s_box[4 * tid + w4][3]);
+                }
+                s1.aabb_out[blk] = bb;
+            }
         }
     }
 
@@ -308,6 +330,9 @@ PackSet make_pack_set(const float *boxes, int64_t n, int stride, const int64_t *
     s.mc_classes = 0;
     s.mc_shared = 0;
     s.mc_max = nullptr;
+    s.rank_src = nullptr;
+    s.rank_out = nullptr;
+    s.aabb_out = nullptr;
     s.z_kr = nullptr;
     s.z_summary = nullptr;
     s.z_sum_words = 0;

@@ -74,6 +74,7 @@ struct Red {
     unsigned long long id_max, id_min_inv;
     unsigned int max_xy, max_wh;
     unsigned int count;      // elements (multiclass: candidates) of this CTA
+    unsigned int max_x, min_x_inv, max_y, min_y_inv;   // spatial mode: extremes of the centres (ordered images)
     unsigned int pad;
 };
 
@@ -156,6 +157,7 @@ struct Team {
             const volatile Red *p = gred + c;
             r.id_max = p->id_max; r.id_min_inv = p->id_min_inv; r.max_xy = p->max_xy; r.max_wh = p->max_wh;
             r.count = p->count; r.pad = 0;
+            r.max_x = p->max_x; r.min_x_inv = p->min_x_inv; r.max_y = p->max_y; r.min_y_inv = p->min_y_inv;
             return r;
         }
         return *cg::this_cluster().map_shared_rank(&sm->red, c);
@@ -532,6 +534,7 @@ __device__ void sort_group(const SortArgs &a, int g, Team<GLOBAL> &T) {
     if (tid == 0) {
         sm.red.id_max = 0ull; sm.red.id_min_inv = 0ull; sm.red.max_xy = 0u; sm.red.max_wh = 0u;
         sm.red.count = 0u; sm.red.pad = 0u;
+        sm.red.max_x = sm.red.min_x_inv = sm.red.max_y = sm.red.min_y_inv = 0u;
         sm.bcount = 0u;
         sm.last = 0;
         sm.gs_local[0] = 0u;
@@ -547,6 +550,7 @@ __device__ void sort_group(const SortArgs &a, int g, Team<GLOBAL> &T) {
         const int iu = (int)((share + kThreads - 1) / kThreads);
         unsigned long long idmx = 0ull, idmn = 0ull;
         unsigned int mxy = 0u, mwh = 0u;
+        unsigned int cxmx = 0u, cxmn = 0u, cymx = 0u, cymn = 0u;
         uint32_t kv[kItems];          // keys of my elements (multiclass: 0xffffffff = not a candidate)
 #pragma unroll
         for (int i = 0; i < kItems; ++i) {
@@ -584,6 +588,11 @@ __device__ void sort_group(const SortArgs &a, int g, Team<GLOBAL> &T) {
                             idmx = max(idmx, u);
                             idmn = max(idmn, ~u);
                         }
+                        if (a.spatial) {
+                            const unsigned int ux = ordered_bits(b[0]), uy = ordered_bits(b[1]);
+                            cxmx = max(cxmx, ux); cxmn = max(cxmn, ~ux);
+                            cymx = max(cymx, uy); cymn = max(cymn, ~uy);
+                        }
                     }
                     if (!mc) T.st_local(0, share, lp, make_uint2(kv[i], q));
                 }
@@ -602,6 +611,21 @@ __device__ void sort_group(const SortArgs &a, int g, Team<GLOBAL> &T) {
             atomicMax(&sm.red.id_min_inv, idmn);
             atomicMax(&sm.red.max_xy, mxy);
             atomicMax(&sm.red.max_wh, mwh);
+        }
+        if (a.spatial) {
+#pragma unroll
+            for (int d = 16; d > 0; d >>= 1) {
+                cxmx = max(cxmx, __shfl_xor_sync(0xffffffffu, cxmx, d));
+                cxmn = max(cxmn, __shfl_xor_sync(0xffffffffu, cxmn, d));
+                cymx = max(cymx, __shfl_xor_sync(0xffffffffu, cymx, d));
+                cymn = max(cymn, __shfl_xor_sync(0xffffffffu, cymn, d));
+            }
+            if (lane == 0) {
+                atomicMax(&sm.red.max_x, cxmx);
+                atomicMax(&sm.red.min_x_inv, cxmn);
+                atomicMax(&sm.red.max_y, cymx);
+                atomicMax(&sm.red.min_y_inv, cymn);
+            }
         }
         if (mc) {
             // stable compaction of the candidates: rank inside the CTA in position order
@@ -674,6 +698,8 @@ __device__ void sort_group(const SortArgs &a, int g, Team<GLOBAL> &T) {
             R.id_min_inv = max(R.id_min_inv, o[c].id_min_inv);
             R.max_xy = max(R.max_xy, o[c].max_xy);
             R.max_wh = max(R.max_wh, o[c].max_wh);
+            R.max_x = max(R.max_x, o[c].max_x); R.min_x_inv = max(R.min_x_inv, o[c].min_x_inv);
+            R.max_y = max(R.max_y, o[c].max_y); R.min_y_inv = max(R.min_y_inv, o[c].min_y_inv);
         }
     } else {
         R = T.peer_red(0);
@@ -683,6 +709,8 @@ __device__ void sort_group(const SortArgs &a, int g, Team<GLOBAL> &T) {
             R.id_min_inv = max(R.id_min_inv, o.id_min_inv);
             R.max_xy = max(R.max_xy, o.max_xy);
             R.max_wh = max(R.max_wh, o.max_wh);
+            R.max_x = max(R.max_x, o.max_x); R.min_x_inv = max(R.min_x_inv, o.min_x_inv);
+            R.max_y = max(R.max_y, o.max_y); R.min_y_inv = max(R.min_y_inv, o.min_y_inv);
         }
     }
     const bool has_ids = mc || a.ids != nullptr;
@@ -710,6 +738,16 @@ __device__ void sort_group(const SortArgs &a, int g, Team<GLOBAL> &T) {
     // the payload, so nothing has to be gathered afterwards.  Global path: key' = id - min id, payload =
     // score position, and the source index is gathered from `order` after the passes.
     const bool two = has_ids && !range_bad && id_range > 1ull;
+    // Spatial mode (large sparse segments): inside a segment the boxes are packed in Morton order of
+    // their centres instead of score order, so that a 128-box block covers a small area and only
+    // neighbouring blocks form mask tiles; key' = (id - min id) << 16 | Morton16, payload = score position
+    // (the rank the mask kernel compares), source index gathered from `order` like on the global path.
+    const bool spatial = a.spatial != 0 && !mc;
+    const bool resort = two || spatial;
+    const bool gather = GLOBAL || spatial;
+    const float sp_x0 = ordered_float(~R.min_x_inv), sp_y0 = ordered_float(~R.min_y_inv);
+    const float sp_ext = fmaxf(fmaxf(ordered_float(R.max_x) - sp_x0, ordered_float(R.max_y) - sp_y0), 1e-20f);
+    const float sp_scale = 255.999f / sp_ext;
 #pragma unroll
     for (int i = 0; i < kItems; ++i) {
         if (i < iu) {
@@ -728,7 +766,15 @@ __device__ void sort_group(const SortArgs &a, int g, Team<GLOBAL> &T) {
                     // mmcv.ops.batched_nms: float(id) * (max(cx,cy) + max(w,h) + 1), separate roundings
                     if (a.id_offsets) a.offsets_out[g0 + idx] = __fmul_rn((float)id, off_unit);
                 }
-                if (two) {
+                if (spatial) {
+                    const float *b = a.boxes + (size_t)(g0 + idx) * a.stride;
+                    // 8 bits per axis, interleaved (NaN / inf centres land in cell 0 or 255: order only)
+                    uint32_t ix = (uint32_t)fminf(fmaxf((b[0] - sp_x0) * sp_scale, 0.f), 255.f);
+                    uint32_t iy = (uint32_t)fminf(fmaxf((b[1] - sp_y0) * sp_scale, 0.f), 255.f);
+                    ix = (ix | (ix << 4)) & 0x0f0fu; ix = (ix | (ix << 2)) & 0x3333u; ix = (ix | (ix << 1)) & 0x5555u;
+                    iy = (iy | (iy << 4)) & 0x0f0fu; iy = (iy | (iy << 2)) & 0x3333u; iy = (iy | (iy << 1)) & 0x5555u;
+                    T.st_local(cur, share, lp, make_uint2(((two ? idk : 0u) << 16) | ix | (iy << 1), p));
+                } else if (two) {
                     T.st_local(cur, share, lp, GLOBAL ? make_uint2(idk, p) : make_uint2((idk << 16) | p, idx));
                 } else {
                     a.seg_order[obase + p] = src;
@@ -737,7 +783,7 @@ __device__ void sort_group(const SortArgs &a, int g, Team<GLOBAL> &T) {
             }
         }
     }
-    if (GLOBAL) {          // `order` is read back through global memory below
+    if (gather) {          // `order` is read back through global memory below
         __threadfence();
         T.sync();
     }
@@ -746,11 +792,18 @@ __device__ void sort_group(const SortArgs &a, int g, Team<GLOBAL> &T) {
     // ---------------------------------------------------------------- sort 2: segment-major order
     unsigned int nseg_here = n > 0 ? 1u : 0u;
     uint32_t *gs = a.gseg_start + (size_t)g * (a.seg_cap + 1);
-    if (two) {
-        const int s0 = GLOBAL ? 0 : 16;
-        if (radix_pass(T, cur, s0, n, share)) cur ^= 1;
-        if (id_range > 256ull)
-            if (radix_pass(T, cur, s0 + 8, n, share)) cur ^= 1;
+    if (resort) {
+        if (spatial) {
+            if (radix_pass(T, cur, 0, n, share)) cur ^= 1;
+            if (radix_pass(T, cur, 8, n, share)) cur ^= 1;
+        }
+        if (two) {
+            const int s0 = (GLOBAL && !spatial) ? 0 : 16;
+            if (radix_pass(T, cur, s0, n, share)) cur ^= 1;
+            if (id_range > 256ull)
+                if (radix_pass(T, cur, s0 + 8, n, share)) cur ^= 1;
+        }
+        const bool key_hi = !(GLOBAL && !spatial);       // the segment key sits in the upper half of the key
         // seg_order / seg_rank, segment boundaries (count, then write)
         uint32_t bmask = 0u;      // bit i: my item i starts a segment
         unsigned int run = 0;
@@ -764,15 +817,15 @@ __device__ void sort_group(const SortArgs &a, int g, Team<GLOBAL> &T) {
                 if (lp < count) {
                     const uint32_t q = (uint32_t)T.rank * share + lp;
                     const uint2 e = T.ld(cur, share, lp);
-                    const uint32_t k = GLOBAL ? e.x : (e.x >> 16);
-                    const uint32_t p = GLOBAL ? e.y : (e.x & 0xffffu);
+                    const uint32_t k = key_hi ? (e.x >> 16) : e.x;
+                    const uint32_t p = gather ? e.y : (e.x & 0xffffu);
                     a.seg_rank[obase + q] = p;
-                    a.seg_order[obase + q] = GLOBAL ? __ldcg(a.order + obase + p) : (uint32_t)(obase + e.y);
+                    a.seg_order[obase + q] = gather ? __ldcg(a.order + obase + p) : (uint32_t)(obase + e.y);
                     if (q == 0u) {
                         isb = true;
                     } else {
                         const uint32_t pk = lp > 0u ? T.ld(cur, share, lp - 1u).x : T.ld_pos_key(cur, share, q - 1u);
-                        isb = (GLOBAL ? pk : (pk >> 16)) != k;
+                        isb = (key_hi ? (pk >> 16) : pk) != k;
                     }
                 }
                 const uint32_t bal = __ballot_sync(0xffffffffu, isb);

@@ -104,7 +104,8 @@ def box_iou_rotated(bboxes1, bboxes2, mode='iou', aligned=False, clockwise=True)
 
 
 _SEG_CAP = 16384          # segments one call handles (the ids of a group must also span fewer than 2**16 values)
-_PLAN_LIMIT = 256 << 20   # worst-case workspace above this: read the device plan back once instead
+_PLAN_LIMIT = 4 << 30     # worst-case workspace above this: read the device plan back once instead (the
+                          # workspace is cached per stream, so its size costs memory, not time)
 _ERR_RANGE_BIT, _ERR_SEGMENTS_BIT = 1, 2
 
 _WS = {}

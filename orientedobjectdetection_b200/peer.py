@@ -10,6 +10,7 @@ The reference has no multi-GPU form of this path (python loops inside one rank, 
 mmrotate/models/dense_heads/rotated_rpn_head.py:414-426,515, mmrotate/core/patch/merge_results.py:90-119).
 """
 import ctypes
+import importlib
 
 import torch
 import torch.distributed as dist
@@ -26,7 +27,7 @@ def available(group=None):
     if dist.get_backend(group) != 'nccl' or not torch.cuda.is_available():
         return False
     try:
-        import torch.distributed._symmetric_memory  # noqa: F401
+        importlib.import_module('torch.distributed._symmetric_memory')
     except Exception:
         return False
     return dist.get_world_size(group) <= 16

@@ -879,3 +879,56 @@ def test_sharded_entry_points_on_two_gpus_match_single_gpu():
                         os.path.join(root, 'tools', 'dist_check_nccl.py'), '--check-only'],
                        capture_output=True, text=True, timeout=900)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+
+
+# ---------------------------------------------------------------- spatially packed launches (groups >= 16384 boxes)
+def test_nms_spatial_packing_segments_vs_oracle():
+    """A group of >= 16384 boxes is packed in Morton order of the centres (only block pairs whose
+    bounding boxes touch become mask tiles; the bit of a pair goes to the lower-ranked box's row; the
+    resolve stage has no positional assumption).  Four segments of very different density in ONE group,
+    rows shuffled; every segment's keep list equals the oracle's."""
+    from orientedobjectdetection_b200 import ops
+    sizes = [9000, 5000, 4000, 2500]
+    extents = [4000.0, 350.0, 1500.0, 120.0]           # sparse ... very dense (long chains)
+    boxes = np.concatenate([synth.le90_boxes(n, 170 + k, e, w_lo=8.0, w_hi=64.0)
+                            for k, (n, e) in enumerate(zip(sizes, extents))])
+    seg = np.repeat(np.array([7, -2, 3, 11], dtype=np.int64), sizes)
+    n = boxes.shape[0]
+    assert n >= 16384
+    scores = synth.unique_scores(n, 171)
+    perm = np.random.default_rng(6).permutation(n)
+    boxes, seg, scores = boxes[perm], seg[perm], scores[perm]
+    thr = 0.2
+    keep = ops._nms_keep(_cuda(boxes), _cuda(scores), thr, seg_ids=torch.from_numpy(seg).cuda()).cpu().numpy()
+    assert np.all(scores[keep][:-1] > scores[keep][1:])
+    jobs = [np.nonzero(seg == sid)[0] for sid in np.unique(seg)]
+    wants = _oracle_nms_parallel([(boxes[idx], scores[idx]) for idx in jobs], thr)
+    for idx, wk in zip(jobs, wants):
+        got = keep[np.isin(keep, idx)]
+        _assert_keep(boxes, scores, thr, got, idx[wk])
+
+
+def test_nms_spatial_packing_chain_and_groups():
+    """spatial mode: (a) a chain of 17000 boxes, each suppressing the next (the decision of box i depends
+    on all before it, while the packed order follows the geometry, not the score); (b) two groups in one
+    launch, one large one small, with per-group emission."""
+    from orientedobjectdetection_b200 import ops
+    n = 17000
+    b = np.zeros((n, 5), np.float32)
+    b[:, 0] = (np.arange(n) % 1000) * 6.0
+    b[:, 1] = (np.arange(n) // 1000) * 40.0
+    b[:, 2:4] = 10.0
+    s = np.linspace(1.0, 0.1, n).astype(np.float32)
+    _, want = ref.nms_rotated(b, s, 0.1)
+    _, keep = rg.nms_rotated(_cuda(b), _cuda(s), 0.1)
+    assert keep.cpu().tolist() == want.tolist()
+    g1 = synth.le90_boxes(16500, 301, 3000.0, w_lo=8.0, w_hi=96.0)
+    g2 = synth.le90_boxes(700, 302, 200.0)
+    s1, s2 = synth.unique_scores(16500, 301), synth.unique_scores(700, 302)
+    allb, alls = np.concatenate([g1, g2]), np.concatenate([s1, s2])
+    keep, counts = ops._nms_grouped(_cuda(allb), _cuda(alls), 0.1, group_sizes=[16500, 700])
+    w1, w2 = _oracle_nms_parallel([(g1, s1), (g2, s2)], 0.1)
+    keep = keep.cpu().numpy()
+    assert counts == [len(w1), len(w2)]
+    _assert_keep(g1, s1, 0.1, keep[:counts[0]], w1)
+    _assert_keep(g2, s2, 0.1, keep[counts[0]:], w2)

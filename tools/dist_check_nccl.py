@@ -55,6 +55,13 @@ for _ in range(3):
     got = rdist.nms_images_sharded(local, 0.8, 500, sizes=sizes)
     assert all(torch.equal(g.to(dev), w.to(dev)) for g, w in zip(got, want))
 out['nms_images_rank_local_equal'] = True
+mine_ = [i for i in range(len(imgs)) if owner[i] == rank]
+bat = rdist.Batched(torch.cat([imgs[i][0] for i in mine_]), torch.cat([imgs[i][1] for i in mine_]),
+                    torch.cat([imgs[i][2] for i in mine_]), sizes)
+for _ in range(2):
+    got = rdist.nms_images_sharded(bat, 0.8, 500)
+    assert all(torch.equal(g.to(dev), w.to(dev)) for g, w in zip(got, want))
+out['nms_images_batched_equal'] = True
 
 # ---- patch merge, classes sharded
 res, offs, shape = synth.c5_patch_results(seed=2, width=4000, height=4000, dets_per_patch=200, num_classes=15)
@@ -132,6 +139,10 @@ sizes = [int(b_.shape[0]) for b_, _, _ in c4]
 owner = rdist.lpt_assign([float(v) ** 2 for v in sizes], world)
 local = [tuple(cu(x) for x in im) if owner[i] == rank else None for i, im in enumerate(c4)]
 out['c4_64img_sharded_rank_local'] = both(lambda: rdist.nms_images_sharded(local, 0.8, 2000, sizes=sizes))
+mine_ = [i for i in range(64) if owner[i] == rank]
+bat = rdist.Batched(torch.cat([local[i][0] for i in mine_]), torch.cat([local[i][1] for i in mine_]),
+                    torch.cat([local[i][2] for i in mine_]), sizes)
+out['c4_64img_sharded_rank_local_batched'] = both(lambda: rdist.nms_images_sharded(bat, 0.8, 2000))
 res, offs, shape = synth.c5_patch_results(0)
 for p_, o_ in zip(res, offs):
     for a_ in p_:
@@ -141,6 +152,44 @@ n_c = [a_.shape[0] for a_ in per_cls]
 own = rdist.lpt_assign([float(v) ** 2 for v in n_c], world)
 dets = [cu(per_cls[c]) if own[c] == rank else None for c in range(15)]
 out['c5_200k_class_sharded_device_resident'] = both(lambda: rdist.merge_dets_sharded(dets, n_c, 0.1))
+if '--profile' in sys.argv and rank == 0:
+    from torch.profiler import profile, ProfilerActivity
+    for name, fn in (('c4 sharded', lambda: rdist.nms_images_sharded(local, 0.8, 2000, sizes=sizes)),
+                     ('c5 sharded', lambda: rdist.merge_dets_sharded(dets, n_c, 0.1))):
+        pass
+if '--profile' in sys.argv:
+    from torch.profiler import profile, ProfilerActivity
+    for name, fn in (('c4 sharded', lambda: rdist.nms_images_sharded(bat, 0.8, 2000)),
+                     ('c5 sharded', lambda: rdist.merge_dets_sharded(dets, n_c, 0.1))):
+        for _ in range(2):
+            fn()
+        torch.cuda.synchronize(); dist.barrier()
+        with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
+            for _ in range(5):
+                fn()
+            torch.cuda.synchronize()
+        if rank == 0:
+            rows = [(e.key, e.device_time_total / 5, e.cpu_time_total / 5, e.count / 5) for e in prof.key_averages()]
+            print('== %s (rank 0): GPU %.1f us per call' % (name, sum(r[1] for r in rows)), file=sys.stderr)
+            for k, d, c, n_ in sorted(rows, key=lambda r: -r[1])[:10]:
+                print('   gpu %7.1f us  x%.0f  %s' % (d, n_, k[:80]), file=sys.stderr)
+            for k, d, c, n_ in sorted(rows, key=lambda r: -r[2])[:12]:
+                print('   cpu %7.1f us  x%.0f  %s' % (c, n_, k[:80]), file=sys.stderr)
+if '--cprofile' in sys.argv:
+    import cProfile, pstats, io
+    fn = lambda: rdist.nms_images_sharded(bat, 0.8, 2000)
+    for _ in range(3):
+        fn()
+    torch.cuda.synchronize(); dist.barrier()
+    pr = cProfile.Profile()
+    pr.enable()
+    for _ in range(50):
+        fn()
+    pr.disable()
+    if rank == 0:
+        st = io.StringIO()
+        pstats.Stats(pr, stream=st).sort_stats('tottime').print_stats(22)
+        print(st.getvalue(), file=sys.stderr)
 out['c5_class_sizes'] = n_c
 out['c5_class_owner'] = [int(v) for v in own]
 if rank == 0:
