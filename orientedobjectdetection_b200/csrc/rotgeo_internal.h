@@ -52,7 +52,7 @@ struct PackSet {
     uint32_t *pr, *pt;
     int64_t n_pad;
 };
-constexpr int kNmsSyncWords = 16;     // [0..1] grid barrier of the resolve kernel, [8..9] 64-bit length of the tile list
+constexpr int kNmsSyncWords = 16;     // [0..1] grid barrier of the resolve kernel, [8..9] 64-bit length of the tile list, [10..11] tiles handed out
 
 // The area axis of the inverted index pays off when the threshold is high enough for the
 // admissible area range to be narrow (RPN: 0.8 -> a few of the 32 bins); at the usual 0.1 of

@@ -112,6 +112,7 @@ struct MaskArgs {
     // score rank of every slot; the bit of a pair goes into the row of the LOWER-ranked box
     const unsigned long long *tile_list;
     const uint32_t *rank;
+    unsigned long long *tile_next;   // list mode: tiles handed out beyond the first one of every CTA (zeroed by the pack kernel)
     int64_t ahead_min_tiles;      // 8 tiles per resident CTA of this device: smaller grids keep look-ahead 1
 };
 
@@ -149,6 +150,7 @@ nms_tile_list_kernel(const NmsSegment *__restrict__ segs, int nseg_in, const lon
     const int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     const int64_t limit = total_dev ? min(*total_dev, tiles_bound) : tiles_bound;
     const int nseg = nseg_dev ? (int)*nseg_dev : nseg_in;
+    const int lane = threadIdx.x & 31;
     bool keep = false;
     TileInfo ti;
     ti.valid = 0; ti.seg = 0; ti.I = 0; ti.J = 0;
@@ -158,15 +160,51 @@ nms_tile_list_kernel(const NmsSegment *__restrict__ segs, int nseg_in, const lon
         const float4 A = aabb[b0 + ti.I], B = aabb[b0 + ti.J];
         keep = ti.I == ti.J || (A.x <= B.z && B.x <= A.z && A.y <= B.w && B.y <= A.w);
     }
-    const unsigned bal = __ballot_sync(0xffffffffu, keep);
+    unsigned bal = __ballot_sync(0xffffffffu, keep);
+    // one atomic per CTA on the list length
+    __shared__ unsigned int s_cnt[8];
+    __shared__ unsigned long long s_base;
+    const int warp = threadIdx.x >> 5;
+    if (lane == 0) s_cnt[warp] = __popc(bal);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned int tot = 0;
+        for (int w = 0; w < 8; ++w) tot += s_cnt[w];
+        s_base = tot ? atomicAdd(count, (unsigned long long)tot) : 0ull;
+    }
+    __syncthreads();
     if (bal == 0u) return;
-    const int lane = threadIdx.x & 31, lead = __ffs(bal) - 1;
-    unsigned long long base = 0ull;
-    if (lane == lead) base = atomicAdd(count, (unsigned long long)__popc(bal));
-    base = __shfl_sync(0xffffffffu, base, lead);
+    unsigned long long base = s_base;
+    for (int w = 0; w < warp; ++w) base += s_cnt[w];
     if (keep)
         list[base + __popc(bal & ((1u << lane) - 1u))] =
             ((unsigned long long)ti.seg << 32) | ((unsigned long long)ti.I << 16) | (unsigned long long)ti.J;
+}
+
+// The mask words of the listed tiles start from zero — BOTH word blocks of a pair of blocks, because a
+// pair's bit lands in the row of its lower-ranked box, which may be the column box.  Zeroed here and not
+// in the mask kernel: there any warp of a CTA may hit any row of the mirrored block while another warp's
+// zero store is still on its way.  One warp per listed tile over a persistent grid (doing it inside the
+// listing kernel left the stores to the few warps that held kept tiles: 57 us, 5 % of the issue slots).
+__global__ void __launch_bounds__(256)
+nms_tile_zero_kernel(const NmsSegment *__restrict__ segs, const unsigned long long *__restrict__ list,
+                     const unsigned long long *__restrict__ count, unsigned long long *__restrict__ mask) {
+    const int lane = threadIdx.x & 31;
+    const int64_t nwarps = (int64_t)gridDim.x * (blockDim.x >> 5);
+    const int64_t total = (int64_t)*count;
+    for (int64_t t = blockIdx.x * (int64_t)(blockDim.x >> 5) + (threadIdx.x >> 5); t < total; t += nwarps) {
+        const unsigned long long v = list[t];
+        const int I = (int)((v >> 16) & 0xffffull), J = (int)(v & 0xffffull);
+        const NmsSegment &sg = segs[(int)(v >> 32)];
+        const int64_t L = sg.len, W = sg.words;
+        unsigned long long *const M = mask + sg.mask_base;
+#pragma unroll
+        for (int r = lane; r < kTile; r += 32) {
+            const int64_t ri = (int64_t)I * kTile + r, rj = (int64_t)J * kTile + r;
+            if (ri < L) *reinterpret_cast<uint4 *>(M + ri * W + 2 * J) = make_uint4(0u, 0u, 0u, 0u);
+            if (I != J && rj < L) *reinterpret_cast<uint4 *>(M + rj * W + 2 * I) = make_uint4(0u, 0u, 0u, 0u);
+        }
+    }
 }
 
 // AREA: the packed set carries the area axis of the index (high thresholds, see
@@ -236,9 +274,30 @@ nms_mask_kernel(const MaskArgs g) {
         return sgi < nseg ? (int)((g.segs[sgi].len + kTile - 1) / kTile) : 0x7fffffff;
     };
     auto take_tile = [&](unsigned j) {      // thread 0: find my j-th tile, start its cull data, publish it
-        MaskSmem::Sched st = sm.st;
         TileInfo nx;
         nx.valid = 0; nx.seg = 0; nx.I = 0; nx.J = 0;
+        if (LIST) {
+            // spatially packed launches: a persistent grid strides over the tile list.  The grid bound of a
+            // device-planned launch can exceed the real tile count 20-fold, and every empty CTA id would cost
+            // one launch-control round trip to cancel (C5: 146 us for 9 k tiles); the list is in arbitrary
+            // order.  Tiles after a CTA's first come from a global counter (taken D tiles ahead of use, so its
+            // latency is hidden): dense scenes have tiles of very different cost, a static stride left SMs idle.
+            const int64_t tn = (int64_t)gridDim.x + (int64_t)atomicAdd(g.tile_next, 1ull);
+            (void)j;
+            if (tn < limit) {
+                const unsigned long long v = g.tile_list[tn];
+                nx.valid = 1;
+                nx.seg = (int)(v >> 32);
+                nx.I = (int)((v >> 16) & 0xffffull);
+                nx.J = (int)(v & 0xffffull);
+                if (j >= (unsigned)kStages) mbar_wait(&sm.empty[j % kStages], ((j / kStages) - 1) & 1);
+                issue_cull_data(j, nx);
+            }
+            sm.info[j % kInfoSlots] = nx;
+            mbar_arrive(&sm.ready[j % kInfoSlots]);
+            return;
+        }
+        MaskSmem::Sched st = sm.st;
         for (;;) {
             unsigned tn;
             bool step = false;
@@ -278,12 +337,6 @@ nms_mask_kernel(const MaskArgs g) {
                             st.cur_nb = seg_blocks(st.cur.seg);
                         }
                     }
-                } else if (LIST) {
-                    const unsigned long long v = g.tile_list[tn];
-                    st.cur.valid = 1;
-                    st.cur.seg = (int)(v >> 32);
-                    st.cur.I = (int)((v >> 16) & 0xffffull);
-                    st.cur.J = (int)(v & 0xffffull);
                 } else {
                     st.cur = locate_tile(g.segs, nseg, tn);
                     st.cur_nb = seg_blocks(st.cur.seg);
@@ -400,17 +453,10 @@ nms_mask_kernel(const MaskArgs g) {
         const int row_base = ti.I * kTile, col_base = ti.J * kTile;   // positions inside the segment
 
         // ---- zeros of this warp's 16 rows of the tile (two mask words a row) ---------------
-        if (lane < 16) {
+        if (!LIST && lane < 16) {      // (list mode: the tile-list kernel zeroed both word blocks of the tile)
             const int r = row_base + warp + kWarps * lane;
             if (r < L)
                 *reinterpret_cast<uint4 *>(g.mask + sg.mask_base + (int64_t)r * W + 2 * ti.J) =
-                    make_uint4(0u, 0u, 0u, 0u);
-        } else if (LIST && ti.I != ti.J) {
-            // spatial packing: a pair's bit may land in the row of the COLUMN box (the lower-ranked one),
-            // i.e. in rows of block J at the words of block I
-            const int r = col_base + warp + kWarps * (lane - 16);
-            if (r < L)
-                *reinterpret_cast<uint4 *>(g.mask + sg.mask_base + (int64_t)r * W + 2 * ti.I) =
                     make_uint4(0u, 0u, 0u, 0u);
         }
         if (k == 0) {
@@ -419,7 +465,8 @@ nms_mask_kernel(const MaskArgs g) {
             pdl_wait();
             if (tid == 0) {
                 issue_cull_data(0, ti);
-                for (int e = 0; e < D; ++e) ask_next(sm.st.next_ask++);
+                if (!LIST)
+                    for (int e = 0; e < D; ++e) ask_next(sm.st.next_ask++);
                 for (int j = 1; j <= D; ++j) take_tile((unsigned)j);   // incl. this iteration's duty
             }
         }
@@ -1018,7 +1065,8 @@ static int launch_mask(const MaskArgs &g_in, int64_t tiles, cudaStream_t stream)
 #endif
     g.tiles = tiles;
     g.group = g.tile_list ? 1 : mask_group(tiles, lim);
-    const int64_t ctas = (tiles + g.group - 1) / g.group;
+    int64_t ctas = (tiles + g.group - 1) / g.group;
+    if (g.tile_list && ctas > lim.mask_slots) ctas = lim.mask_slots;      // persistent: one CTA per resident slot
     // one CTA per tile; running CTAs steal the not-yet-launched ones (launch control)
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)ctas);
@@ -1083,6 +1131,7 @@ int launch_nms(const NmsPlan &plan, const void *packed, const NmsSegment *segmen
     g.nseg_dev = nullptr;
     g.tile_list = nullptr;
     g.rank = nullptr;
+    g.tile_next = nullptr;
     int rc = launch_mask(g, plan.total_tiles, stream);
     if (rc) return rc;
     ResolveArgs a = {};
@@ -1121,6 +1170,7 @@ int launch_nms_device_planned(const NmsDevLaunch &d, cudaStream_t stream) {
     g.nseg_dev = d.nseg_dev;
     g.tile_list = nullptr;
     g.rank = nullptr;
+    g.tile_next = nullptr;
     if (d.tile_list) {
         // spatially packed: list the block pairs whose bounding boxes touch, then visit only those
         if (d.tiles_bound > 0x7fffffffLL) return -1;
@@ -1128,10 +1178,15 @@ int launch_nms_device_planned(const NmsDevLaunch &d, cudaStream_t stream) {
         if (d.tiles_bound > 0) {
             nms_tile_list_kernel<<<(unsigned)((d.tiles_bound + 255) / 256), 256, 0, stream>>>(
                 d.segs_dev, d.nseg, d.nseg_dev, d.total_tiles_dev, d.tiles_bound, d.aabb, d.tile_list, count);
+            DeviceLimits zl;
+            if (device_limits(&zl)) return -3;
+            nms_tile_zero_kernel<<<(unsigned)(zl.sms * 8), 256, 0, stream>>>(
+                d.segs_dev, d.tile_list, count, reinterpret_cast<unsigned long long *>(d.mask));
             if (cudaGetLastError() != cudaSuccess) return -3;
         }
         g.tile_list = d.tile_list;
         g.rank = d.rank;
+        g.tile_next = reinterpret_cast<unsigned long long *>(d.scratch.sync + 10);
         g.total_tiles = reinterpret_cast<const int64_t *>(count);
     }
     int rc = launch_mask(g, d.tiles_bound, stream);

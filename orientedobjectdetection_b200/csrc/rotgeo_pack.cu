@@ -75,7 +75,7 @@ struct BinScale {
 // identical in every CTA of the launch: every CTA reduces the same strided sample of <= 256
 // raw boxes (centres and log2 areas)
 __device__ BinScale sample_bin_scale(const PackSet &s1, const PackSet &s2) {
-    __shared__ float red[6][kPackThreads / 32];
+    __shared__ float red[8][kPackThreads / 32];
     const int tid = threadIdx.x;
     const bool two = s2.n > 0;
     const int64_t n1 = s1.n_dev ? *s1.n_dev : s1.n;
@@ -85,6 +85,7 @@ __device__ BinScale sample_bin_scale(const PackSet &s1, const PackSet &s2) {
     const int t = two ? (tid & (kPackThreads / 2 - 1)) : tid;
     float lo_x = INFINITY, hi_x = -INFINITY, lo_y = INFINITY, hi_y = -INFINITY;
     float lo_a = INFINITY, hi_a = -INFINITY;
+    float sum_d = 0.f, cnt_d = 0.f;                  // sampled box diagonals (spatially packed sets)
     const int64_t sn = (two && tid >= kPackThreads / 2) ? s2.n : n1;   // only set 1 is ever device-counted
     if (sn > 0) {
         const int64_t i = (sn >= slots) ? (int64_t)t * (sn / slots) : (t % sn);
@@ -97,18 +98,28 @@ __device__ BinScale sample_bin_scale(const PackSet &s1, const PackSet &s2) {
         }
         const float la = __log2f(b[2] * b[3]);
         if (fabsf(la) < 1e30f) lo_a = hi_a = la;     // also rejects NaN / -inf (zero area)
+        const float dm = sqrtf(fmaf(b[2], b[2], b[3] * b[3]));
+        if (dm < 1e30f) { sum_d = dm; cnt_d = 1.f; }
     }
     lo_x = warp_min(lo_x); hi_x = warp_max(hi_x);
     lo_y = warp_min(lo_y); hi_y = warp_max(hi_y);
     lo_a = warp_min(lo_a); hi_a = warp_max(hi_a);
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) {
+        sum_d += __shfl_xor_sync(0xffffffffu, sum_d, d);
+        cnt_d += __shfl_xor_sync(0xffffffffu, cnt_d, d);
+    }
     if ((tid & 31) == 0) {
+        red[6][tid >> 5] = sum_d; red[7][tid >> 5] = cnt_d;
         red[0][tid >> 5] = lo_x; red[1][tid >> 5] = hi_x;
         red[2][tid >> 5] = lo_y; red[3][tid >> 5] = hi_y;
         red[4][tid >> 5] = lo_a; red[5][tid >> 5] = hi_a;
     }
     __syncthreads();
+    sum_d = 0.f; cnt_d = 0.f;
 #pragma unroll
     for (int w = 0; w < kPackThreads / 32; ++w) {
+        sum_d += red[6][w]; cnt_d += red[7][w];
         lo_x = fminf(lo_x, red[0][w]); hi_x = fmaxf(hi_x, red[1][w]);
         lo_y = fminf(lo_y, red[2][w]); hi_y = fmaxf(hi_y, red[3][w]);
         lo_a = fminf(lo_a, red[4][w]); hi_a = fmaxf(hi_a, red[5][w]);
@@ -117,6 +128,11 @@ __device__ BinScale sample_bin_scale(const PackSet &s1, const PackSet &s2) {
     const float extent = fmaxf(hi_x - lo_x, hi_y - lo_y);
     // 30 bins across the sampled extent (the sample misses a little at the edges)
     float cell = extent * (1.f / 30.f);
+    // Spatially packed sets: a tile pairs two NEIGHBOURING blocks, whose boxes all sit in the same two or
+    // three bins of an extent-wide grid (C5: a quarter of a tile's pairs passed the bins).  The bins are
+    // modular, so any width is correct; one mean box diagonal keeps a box in two or three of the 32 bins
+    // wherever it lies: (3 / 32)^2 of the pairs of a local tile survive.
+    if (s1.aabb_out && cnt_d > 0.f) cell = fminf(cell, fmaxf(sum_d / cnt_d, extent * (1.f / 30.f / 64.f)));
     if (!(cell > 1e-30f) || !(cell < 1e30f)) cell = 1.f;
     sc.inv_cell = 1.f / cell;
     const float span = hi_a - lo_a;
