@@ -255,6 +255,21 @@ int rotgeo_diff_iou_aligned(const float *boxes1, const float *boxes2, int64_t n,
  * sortws: rotgeo_nms_sort_bytes(...) bytes, 16-byte aligned, untouched between the calls;
  * workspace: rotgeo_nms_run_bytes(n, sizes).  group_sizes_host, num_groups and seg_cap must
  * be the same in all calls of one job. */
+/*   rotgeo_nms_grouped    rotgeo_nms_sort + rotgeo_nms_bounds + rotgeo_nms_run in ONE call over worst-case
+ *                         bounds (no device->host read), for hosts where every boundary crossing counts
+ *                         (a python caller pays ~10 us per ctypes call).  tail_out int64[2 + num_groups]
+ *                         (device): kept in all, front-end error bits, and with want_group_counts != 0
+ *                         the kept boxes per group (keep_out then holds rows inside their group).
+ *                         dets_out (nullable, float (n, 6)): the rows cat(boxes[keep], scores[keep]) that
+ *                         mmcv's nms_rotated / batched_nms return, written by the same kernels.
+ *                         need_out[2] (HOST) always receives the sizes of sortws and workspace this job
+ *                         needs; ROTGEO_ERR_WORKSPACE (nothing launched) when the given ones are smaller,
+ *                         so a caller keeps two growing buffers and retries once. */
+int rotgeo_nms_grouped(const float *boxes, int64_t n, int stride, const float *scores, const int64_t *seg_ids,
+                       int id_offsets, const float *offsets, const int64_t *group_sizes_host, int64_t num_groups,
+                       int64_t seg_cap, float iou_threshold, int64_t *keep_out, int64_t *tail_out,
+                       int want_group_counts, float *dets_out, void *sortws, size_t sortws_bytes, void *workspace,
+                       size_t workspace_bytes, size_t *need_out, void *stream);
 size_t rotgeo_nms_sort_bytes(int64_t n, const int64_t *group_sizes_host, int64_t num_groups, int64_t seg_cap);
 int rotgeo_nms_sort(const float *boxes, int64_t n, int stride, const float *scores, const int64_t *seg_ids,
                     int id_offsets, const int64_t *group_sizes_host, int64_t num_groups, int64_t seg_cap,

@@ -18,12 +18,13 @@ SYMBOLS = (
     'rotgeo_eval_tpfp_workspace_bytes', 'rotgeo_eval_tpfp',
     'rotgeo_diff_iou_aligned',
     'rotgeo_nms_sort_bytes', 'rotgeo_nms_sort', 'rotgeo_nms_bounds', 'rotgeo_nms_read_plan',
-    'rotgeo_nms_run_bytes', 'rotgeo_nms_run',
+    'rotgeo_nms_run_bytes', 'rotgeo_nms_run', 'rotgeo_nms_grouped',
     'rotgeo_multiclass_nms_workspace_bytes', 'rotgeo_multiclass_nms',
     'rotgeo_peer_pad_bytes', 'rotgeo_peer_barrier', 'rotgeo_dist_iou_allgather', 'rotgeo_dist_rowcol_stage_bytes',
     'rotgeo_dist_iou_rowcol_max', 'rotgeo_dist_keeps_bytes', 'rotgeo_dist_push_keeps',
 )
 ERR_RANGE = -4
+ERR_WORKSPACE = -2
 
 _lib = None
 
@@ -89,6 +90,8 @@ def load():
     L.rotgeo_nms_run_bytes.restype = sz
     L.rotgeo_nms_run.argtypes = [vp, i64, i32, vp, i32, vp, i64, i64, vp, vp, f32, vp, vp, vp, vp, sz, vp]
     L.rotgeo_nms_run.restype = i32
+    L.rotgeo_nms_grouped.argtypes = [vp, i64, i32, vp, vp, i32, vp, vp, i64, i64, f32, vp, vp, i32, vp, vp, sz, vp, sz, vp, vp]
+    L.rotgeo_nms_grouped.restype = i32
     L.rotgeo_multiclass_nms_workspace_bytes.argtypes = [i64, i32]
     L.rotgeo_multiclass_nms_workspace_bytes.restype = sz
     L.rotgeo_multiclass_nms.argtypes = [vp, i32, vp, vp, i64, i32, f32, f32, i64, vp, vp, vp, vp, vp, sz, vp]

@@ -400,10 +400,11 @@ size_t rotgeo_nms_run_bytes(int64_t n, const int64_t *sizes) {
     return l.total_bytes;
 }
 
-int rotgeo_nms_run(const float *boxes, int64_t n, int stride, const float *offsets, int sort_offsets,
-                   const int64_t *group_sizes_host, int64_t num_groups, int64_t seg_cap, const void *sortws,
-                   const int64_t *sizes, float iou_threshold, int64_t *keep_out, int64_t *num_keep_out,
-                   int64_t *group_counts_out, void *workspace, size_t workspace_bytes, void *stream) {
+static int nms_run_checked(const float *boxes, int64_t n, int stride, const float *offsets, int sort_offsets,
+                           const int64_t *group_sizes_host, int64_t num_groups, int64_t seg_cap, const void *sortws,
+                           const int64_t *sizes, float iou_threshold, int64_t *keep_out, int64_t *num_keep_out,
+                           int64_t *group_counts_out, void *workspace, size_t workspace_bytes, void *stream,
+                           const float *det_scores, float *dets_out) {
     if (n <= 0 || stride < 5 || seg_cap < 1 || !groups_ok(group_sizes_host, num_groups, n))
         return fail(ROTGEO_ERR_ARG, "nms_run: n=%lld stride=%d", (long long)n, stride);
     if (!(iou_threshold > 0.f))
@@ -420,10 +421,46 @@ int rotgeo_nms_run(const float *boxes, int64_t n, int stride, const float *offse
         return fail(ROTGEO_ERR_WORKSPACE, "nms_run: workspace %zu < %zu bytes or misaligned", workspace_bytes, need);
     const int rc = rotgeo::nms_run(boxes, n, stride, offsets, sort_offsets, group_sizes_host, num_groups, seg_cap,
                                    sortws, z, iou_threshold, keep_out, num_keep_out, group_counts_out, workspace,
-                                   (cudaStream_t)stream);
+                                   (cudaStream_t)stream, det_scores, dets_out);
     if (rc == -1) return fail(ROTGEO_ERR_ARG, "nms_run: too many tiles");
     if (rc) return cuda_fail("nms_run");
     return ROTGEO_OK;
+}
+
+int rotgeo_nms_run(const float *boxes, int64_t n, int stride, const float *offsets, int sort_offsets,
+                   const int64_t *group_sizes_host, int64_t num_groups, int64_t seg_cap, const void *sortws,
+                   const int64_t *sizes, float iou_threshold, int64_t *keep_out, int64_t *num_keep_out,
+                   int64_t *group_counts_out, void *workspace, size_t workspace_bytes, void *stream) {
+    return nms_run_checked(boxes, n, stride, offsets, sort_offsets, group_sizes_host, num_groups, seg_cap, sortws, sizes,
+                           iou_threshold, keep_out, num_keep_out, group_counts_out, workspace, workspace_bytes, stream,
+                           nullptr, nullptr);
+}
+
+int rotgeo_nms_grouped(const float *boxes, int64_t n, int stride, const float *scores, const int64_t *seg_ids,
+                       int id_offsets, const float *offsets, const int64_t *group_sizes_host, int64_t num_groups,
+                       int64_t seg_cap, float iou_threshold, int64_t *keep_out, int64_t *tail_out,
+                       int want_group_counts, float *dets_out, void *sortws, size_t sortws_bytes, void *workspace,
+                       size_t workspace_bytes, size_t *need_out, void *stream) {
+    if (n <= 0 || n > 0x7fffffffLL || stride < 5 || seg_cap < 1 || seg_cap > 65536 || !need_out)
+        return fail(ROTGEO_ERR_ARG, "nms_grouped: n=%lld stride=%d seg_cap=%lld", (long long)n, stride, (long long)seg_cap);
+    if (!groups_ok(group_sizes_host, num_groups, n))
+        return fail(ROTGEO_ERR_ARG, "nms_grouped: group sizes must be non-negative and add up to n");
+    int64_t sizes[6];
+    rotgeo::NmsSizes z;
+    rotgeo::nms_bounds(group_sizes_host, num_groups, n, seg_cap, &z);
+    sizes_to(z, sizes);
+    need_out[0] = rotgeo_nms_sort_bytes(n, group_sizes_host, num_groups, seg_cap);
+    need_out[1] = rotgeo_nms_run_bytes(n, sizes);
+    if (sortws_bytes < need_out[0] || workspace_bytes < need_out[1] || !sortws || !workspace)
+        return fail(ROTGEO_ERR_WORKSPACE, "nms_grouped: buffers %zu / %zu bytes, need %zu / %zu", sortws_bytes,
+                    workspace_bytes, need_out[0], need_out[1]);
+    int rc = rotgeo_nms_sort(boxes, n, stride, scores, seg_ids, id_offsets, group_sizes_host, num_groups, seg_cap,
+                             sortws, sortws_bytes, stream);
+    if (rc) return rc;
+    return nms_run_checked(boxes, n, stride, offsets, (id_offsets && seg_ids) ? 1 : 0, group_sizes_host, num_groups,
+                           seg_cap, sortws, sizes, iou_threshold, keep_out, tail_out,
+                           want_group_counts ? tail_out + 2 : nullptr, workspace, workspace_bytes, stream, scores,
+                           dets_out);
 }
 
 size_t rotgeo_multiclass_nms_workspace_bytes(int64_t rows, int num_classes) {

@@ -155,7 +155,7 @@ int nms_read_plan(const void *sortws, int64_t n, int64_t ngroups, int64_t seg_ca
 int nms_run(const float *boxes, int64_t n, int stride, const float *offsets, int sort_offsets,
             const int64_t *group_sizes_host, int64_t ngroups, int64_t seg_cap, const void *sortws, const NmsSizes &z,
             float thr, int64_t *keep_out, int64_t *num_keep_out, int64_t *group_counts_out, void *workspace,
-            cudaStream_t stream) {
+            cudaStream_t stream, const float *det_scores, float *dets_out) {
     int64_t max_group = 0;
     for (int64_t g = 0; g < ngroups; ++g) {
         const int64_t ng = group_sizes_host ? group_sizes_host[g] : n;
@@ -225,6 +225,14 @@ int nms_run(const float *boxes, int64_t n, int stride, const float *offsets, int
     a.flags = reinterpret_cast<uint8_t *>(ws + l.off_flags);
     a.keep_out = keep_out;
     a.num_keep_out = num_keep_out;
+    if (dets_out && det_scores) {
+        a.mc.boxes = boxes;
+        a.mc.box_stride = stride;
+        a.mc.scores = det_scores;
+        a.mc.classes = 0;
+        a.mc.dets_out = dets_out;
+        a.mc.cap = n;
+    }
     int rc = launch_nms_device_planned(a, stream);
     if (rc) return rc;
     if (group_counts_out) {

@@ -142,7 +142,9 @@ struct McOut {
     const float *boxes;      // (rows, 5) if shared else (rows * classes, 5), contiguous
     const float *scores;     // (rows, score_stride) raw scores
     const float *factors;    // nullable (rows,)
-    int classes, score_stride, shared;
+    int classes, score_stride, shared;   // classes == 0: plain rows — kept index = box row, boxes have box_stride
+    int box_stride;                      // floats between rows and scores is (n,), no labels
+
     float *dets_out;         // (cap, 6)
     int64_t *labels_out;     // (cap,)
     int64_t cap;             // keep at most this many (max_num)
@@ -174,10 +176,12 @@ int nms_sort(const float *boxes, int64_t n, int stride, const float *scores, con
              const int64_t *group_sizes_host, int64_t ngroups, int64_t seg_cap, void *sortws, cudaStream_t stream);
 int nms_read_plan(const void *sortws, int64_t n, int64_t ngroups, int64_t seg_cap, int64_t max_group, NmsSizes *z,
                   unsigned int *error, cudaStream_t stream);
+// det_scores + dets_out (both nullable): the (kept, 6) rows cat(boxes[keep], scores[keep]) the reference's
+// nms_rotated / batched_nms return, written by the resolve kernel's compaction
 int nms_run(const float *boxes, int64_t n, int stride, const float *offsets, int sort_offsets,
             const int64_t *group_sizes_host, int64_t ngroups, int64_t seg_cap, const void *sortws, const NmsSizes &z,
             float thr, int64_t *keep_out, int64_t *num_keep_out, int64_t *group_counts_out, void *workspace,
-            cudaStream_t stream);
+            cudaStream_t stream, const float *det_scores = nullptr, float *dets_out = nullptr);
 
 // NMS over a plan made on the DEVICE (fused front-ends): grids and buffers are sized for
 // host-side upper bounds, the kernels read the actual counts from device memory.

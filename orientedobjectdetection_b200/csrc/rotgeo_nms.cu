@@ -946,15 +946,22 @@ nms_resolve_kernel(const ResolveArgs a_in) {
             const uint32_t id = s_list[j];
             a.keep_out[pos] = (int64_t)id;
             if (MC) {
-                // the output row of a kept candidate: its box, its (factored) score, its class
-                const uint32_t row = id / (uint32_t)a.mc.classes;
-                const int cls = (int)(id - row * (uint32_t)a.mc.classes);
-                const float *bx = a.mc.boxes + (a.mc.shared ? (int64_t)row : (int64_t)id) * 5;
-                float sc = a.mc.scores[(int64_t)row * a.mc.score_stride + cls];
-                if (a.mc.factors) sc *= a.mc.factors[row];
                 float *d = a.mc.dets_out + pos * 6;
-                d[0] = bx[0]; d[1] = bx[1]; d[2] = bx[2]; d[3] = bx[3]; d[4] = bx[4]; d[5] = sc;
-                a.mc.labels_out[pos] = cls;
+                if (a.mc.classes == 0) {
+                    // plain rows: cat(boxes[keep], scores[keep]) of mmcv's nms_rotated / batched_nms
+                    const float *bx = a.mc.boxes + (int64_t)id * a.mc.box_stride;
+                    d[0] = bx[0]; d[1] = bx[1]; d[2] = bx[2]; d[3] = bx[3]; d[4] = bx[4];
+                    d[5] = a.mc.scores[id];
+                } else {
+                    // the output row of a kept candidate: its box, its (factored) score, its class
+                    const uint32_t row = id / (uint32_t)a.mc.classes;
+                    const int cls = (int)(id - row * (uint32_t)a.mc.classes);
+                    const float *bx = a.mc.boxes + (a.mc.shared ? (int64_t)row : (int64_t)id) * 5;
+                    float sc = a.mc.scores[(int64_t)row * a.mc.score_stride + cls];
+                    if (a.mc.factors) sc *= a.mc.factors[row];
+                    d[0] = bx[0]; d[1] = bx[1]; d[2] = bx[2]; d[3] = bx[3]; d[4] = bx[4]; d[5] = sc;
+                    a.mc.labels_out[pos] = cls;
+                }
             }
         }
         base += wtotal;

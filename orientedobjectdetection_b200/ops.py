@@ -13,6 +13,7 @@ merge_results.py:115 with device='cpu') are moved to the current CUDA device
 and the result is returned on the caller's device — a transfer, never a CPU
 implementation.  No GPU or no library => RuntimeError.
 """
+import contextlib
 import ctypes
 
 import numpy as np
@@ -47,6 +48,15 @@ def _rows_f32(t, dev):
     if t.dim() != 2 or t.stride(1) != 1 or t.stride(0) < 5:
         t = t.contiguous()
     return t
+
+
+_NULL_CTX = contextlib.nullcontext()
+
+
+def _on_device(dev):
+    """``torch.cuda.device(dev)`` only when ``dev`` is not current already (the context manager costs
+    ~10 us per entry, a tenth of a small NMS call)"""
+    return _NULL_CTX if torch.cuda.current_device() == dev.index else torch.cuda.device(dev)
 
 
 def _stream(dev):
@@ -140,7 +150,7 @@ def _top1(s, lo=0, hi=None):
 
 
 def _nms_grouped(boxes, scores, iou_threshold, seg_ids=None, offsets=None, id_offsets=False,
-                 group_sizes=None, seg_cap=None, no_read=False):
+                 group_sizes=None, seg_cap=None, no_read=False, with_dets=False):
     """Greedy rotated NMS of one or several GROUPS of boxes stored back to back (group g owns
     ``group_sizes[g]`` consecutive rows; None = one group).  Suppression only among boxes of
     equal ``seg_ids`` inside a group.  Centre offsets (added to cx, cy before the geometry, as
@@ -158,6 +168,10 @@ def _nms_grouped(boxes, scores, iou_threshold, seg_ids=None, offsets=None, id_of
     bounds): no device->host read until the kept count is fetched at the end.  Jobs whose
     worst-case workspace exceeds _PLAN_LIMIT read the 64-byte plan back once instead.
 
+    ``with_dets=True``: returns ``(keep, counts, dets)`` with ``dets`` (k, 6) float32 =
+    ``cat(boxes[keep], scores[keep, None])`` written by the resolve kernel itself (None when the call took
+    the plan-read path; the caller gathers then).
+
     ``no_read=True`` (the multi-GPU callers, which push the result to their peers first and read
     once at the very end): nothing is read back; returns ``(keep (n,), tail)`` with ``tail`` the
     device int64 vector ``[kept in all, front-end error bits, kept per group ...]``; a non-zero
@@ -171,6 +185,9 @@ def _nms_grouped(boxes, scores, iou_threshold, seg_ids=None, offsets=None, id_of
     ngroups = int(sizes_h.shape[0]) if grouped else 1
     if no_read:
         assert grouped and n > 0 and float(iou_threshold) > 0.0
+    if with_dets and (n == 0 or not float(iou_threshold) > 0.0):
+        got = _nms_grouped(boxes, scores, iou_threshold, seg_ids, offsets, id_offsets, group_sizes, seg_cap)
+        return got[0], got[1], None
     if n == 0:
         return torch.zeros(0, dtype=torch.int64, device=dev), ([0] * ngroups if grouped else None)
     if not float(iou_threshold) > 0.0:
@@ -180,7 +197,7 @@ def _nms_grouped(boxes, scores, iou_threshold, seg_ids=None, offsets=None, id_of
         tops = [_top1(s, int(st[g]), int(st[g + 1])) - int(st[g]) for g in range(ngroups)]
         return torch.cat(tops), [int(t.numel()) for t in tops]
     L = _lib.load()
-    with torch.cuda.device(dev):
+    with _on_device(dev):
         seg_ptr = None
         if seg_ids is not None:
             seg = seg_ids.detach().to(device=dev, dtype=torch.int64).reshape(-1).contiguous()
@@ -198,38 +215,64 @@ def _nms_grouped(boxes, scores, iou_threshold, seg_ids=None, offsets=None, id_of
             cap = int(seg_cap)
         else:
             cap = min(max(max_group, 1), 256 if ngroups == 1 else 16, _SEG_CAP)
+        use_sort_off = 1 if (id_offsets and seg_ptr) else 0
         sizes = np.zeros(6, dtype=np.int64)
+        need = (ctypes.c_size_t * 2)()
         for attempt in range(2):
-            sbytes = L.rotgeo_nms_sort_bytes(n, sizes_ptr, ngroups, cap)
-            sortws = _workspace(dev, stream, 'nms_sort', sbytes)
-            _lib.check(L.rotgeo_nms_sort(b.data_ptr(), n, b.stride(0), s.data_ptr(), seg_ptr,
-                                         1 if (id_offsets and seg_ptr) else 0, sizes_ptr, ngroups, cap,
-                                         sortws.data_ptr(), sortws.numel(), stream), 'rotgeo_nms_sort')
-            _lib.check(L.rotgeo_nms_bounds(n, sizes_ptr, ngroups, cap, sizes.ctypes.data), 'rotgeo_nms_bounds')
-            nbytes = L.rotgeo_nms_run_bytes(n, sizes.ctypes.data)
+            keep = torch.empty(n, dtype=torch.int64, device=dev)
+            tail = torch.empty(2 + ngroups, dtype=torch.int64, device=dev)   # kept, error bits, kept per group
+            dets = torch.empty((n, 6), dtype=torch.float32, device=dev) if with_dets else None
+            # fast path: ONE C-ABI call (sort + bounds + run) over the cached buffers; it reports the sizes it
+            # needs, so a buffer that is too small costs one retry, once
+            launched = False
+            skey_s, skey_w = (dev.index, stream, 'nms_sort'), (dev.index, stream, 'nms_run')
+            for _ in range(2):
+                sortws, ws = _WS.get(skey_s), _WS.get(skey_w)
+                rc = L.rotgeo_nms_grouped(b.data_ptr(), n, b.stride(0), s.data_ptr(), seg_ptr, use_sort_off, off_ptr,
+                                          sizes_ptr, ngroups, cap, float(iou_threshold), keep.data_ptr(),
+                                          tail.data_ptr(), 1 if grouped else 0,
+                                          dets.data_ptr() if dets is not None else None,
+                                          sortws.data_ptr() if sortws is not None else None,
+                                          sortws.numel() if sortws is not None else 0,
+                                          ws.data_ptr() if ws is not None else None,
+                                          ws.numel() if ws is not None else 0, need, stream)
+                if rc == _lib.ERR_WORKSPACE and need[1] <= _PLAN_LIMIT:
+                    _workspace(dev, stream, 'nms_sort', need[0])
+                    _workspace(dev, stream, 'nms_run', need[1])
+                    continue
+                if rc != _lib.ERR_WORKSPACE:
+                    _lib.check(rc, 'rotgeo_nms_grouped')
+                    launched = True
+                break
             err = 0
-            if nbytes > _PLAN_LIMIT:
+            if not launched:
+                dets = None
+                # worst-case workspace not worth allocating: sort, read the 64-byte plan back once, run exactly
+                sbytes = L.rotgeo_nms_sort_bytes(n, sizes_ptr, ngroups, cap)
+                sortws = _workspace(dev, stream, 'nms_sort', sbytes)
+                _lib.check(L.rotgeo_nms_sort(b.data_ptr(), n, b.stride(0), s.data_ptr(), seg_ptr, use_sort_off,
+                                             sizes_ptr, ngroups, cap, sortws.data_ptr(), sortws.numel(), stream),
+                           'rotgeo_nms_sort')
                 rc = L.rotgeo_nms_read_plan(sortws.data_ptr(), n, sizes_ptr, ngroups, cap, sizes.ctypes.data, stream)
                 if rc == _lib.ERR_RANGE:
                     err = _plan_error_bits()
                 else:
                     _lib.check(rc, 'rotgeo_nms_read_plan')
                     nbytes = L.rotgeo_nms_run_bytes(n, sizes.ctypes.data)
+                    ws = _workspace(dev, stream, 'nms_run', nbytes)
+                    _lib.check(L.rotgeo_nms_run(b.data_ptr(), n, b.stride(0), off_ptr, use_sort_off, sizes_ptr, ngroups,
+                                                cap, sortws.data_ptr(), sizes.ctypes.data, float(iou_threshold),
+                                                keep.data_ptr(), tail.data_ptr(),
+                                                tail.data_ptr() + 16 if grouped else None,
+                                                ws.data_ptr(), ws.numel(), stream), 'rotgeo_nms_run')
             if not err:
-                ws = _workspace(dev, stream, 'nms_run', nbytes)
-                keep = torch.empty(n, dtype=torch.int64, device=dev)
-                tail = torch.empty(2 + ngroups, dtype=torch.int64, device=dev)   # kept, error bits, kept per group
-                _lib.check(L.rotgeo_nms_run(b.data_ptr(), n, b.stride(0), off_ptr,
-                                            1 if (id_offsets and seg_ptr) else 0, sizes_ptr, ngroups, cap,
-                                            sortws.data_ptr(), sizes.ctypes.data, float(iou_threshold),
-                                            keep.data_ptr(), tail.data_ptr(),
-                                            tail.data_ptr() + 16 if grouped else None,
-                                            ws.data_ptr(), ws.numel(), stream), 'rotgeo_nms_run')
                 if no_read:
                     return keep, tail
                 host = tail.tolist()          # the one device->host read of the call: sizes the outputs
                 err = int(host[1])
                 if not err:
+                    if with_dets:
+                        return keep[:host[0]], (host[2:] if grouped else None), (dets[:host[0]] if dets is not None else None)
                     return keep[:host[0]], (host[2:] if grouped else None)
             if (err & _ERR_RANGE_BIT) or attempt == 1 or cap >= min(max_group, _SEG_CAP):
                 return None
@@ -242,13 +285,16 @@ def _plan_error_bits():
     return _ERR_RANGE_BIT if 'span' in msg else _ERR_SEGMENTS_BIT
 
 
-def _nms_keep(boxes, scores, iou_threshold, seg_ids=None, offsets=None, id_offsets=False):
+def _nms_keep(boxes, scores, iou_threshold, seg_ids=None, offsets=None, id_offsets=False, with_dets=False):
     """kept indices (int64, score-descending, on the CUDA device) of a greedy rotated NMS of
     ONE group (see _nms_grouped); ids that the device front-end does not take (spread over
-    65536 values or more, more than 16384 segments) are renumbered and split."""
-    got = _nms_grouped(boxes, scores, iou_threshold, seg_ids, offsets, id_offsets)
+    65536 values or more, more than 16384 segments) are renumbered and split.
+    ``with_dets``: returns ``(keep, dets (k, 6) float32 | None)``."""
+    got = _nms_grouped(boxes, scores, iou_threshold, seg_ids, offsets, id_offsets, with_dets=with_dets)
     if got is not None:
-        return got[0]
+        return (got[0], got[2]) if with_dets else got[0]
+    if with_dets:
+        return _nms_keep(boxes, scores, iou_threshold, seg_ids, offsets, id_offsets), None
     dev = _cuda_device(boxes, scores)
     b = _rows_f32(boxes, dev)
     s = scores.detach().to(device=dev, dtype=torch.float32).reshape(-1).contiguous()
@@ -339,9 +385,11 @@ def nms_rotated(dets, scores, iou_threshold, labels=None, clockwise=True):
     if dets.shape[0] == 0:
         return dets, None
     assert dets.size(1) == 5, 'dets must be (N, 5) rotated boxes'
-    keep = _nms_keep(dets, scores, iou_threshold)
+    fused = dets.is_cuda and dets.dtype == torch.float32 and scores.dtype == torch.float32
+    keep, out = _nms_keep(dets, scores, iou_threshold, with_dets=fused) if fused else (_nms_keep(dets, scores, iou_threshold), None)
     keep = keep.to(dets.device)
-    out = torch.cat((dets[keep], scores[keep].reshape(-1, 1).to(dets.dtype)), dim=1)
+    if out is None:      # other dtypes / host tensors: the caller's own values, gathered
+        out = torch.cat((dets[keep], scores[keep].reshape(-1, 1).to(dets.dtype)), dim=1)
     return out, keep
 
 
@@ -390,8 +438,15 @@ def batched_nms(boxes, scores, idxs, nms_cfg, class_agnostic=False):
     if nms_type == 'nms_rotated' and boxes.size(-1) == 5:
         # not class_agnostic: the centre offset  id * (max(cx,cy) + max(w,h) + 1)  of mmcv, same
         # fp32 arithmetic, derived on the device
-        keep = _nms_keep(boxes, scores, thr, seg_ids=None if class_agnostic else idxs,
-                         id_offsets=not class_agnostic).to(boxes.device)
+        fused = boxes.is_cuda and boxes.dtype == torch.float32 and scores.dtype == torch.float32 and max_num <= 0
+        if fused:
+            keep, out = _nms_keep(boxes, scores, thr, seg_ids=None if class_agnostic else idxs,
+                                  id_offsets=not class_agnostic, with_dets=True)
+            if out is not None:
+                return out, keep
+        else:
+            keep = _nms_keep(boxes, scores, thr, seg_ids=None if class_agnostic else idxs,
+                             id_offsets=not class_agnostic).to(boxes.device)
     else:
         if class_agnostic:
             b = boxes

@@ -56,8 +56,17 @@ for _ in range(3):
     assert all(torch.equal(g.to(dev), w.to(dev)) for g, w in zip(got, want))
 out['nms_images_rank_local_equal'] = True
 mine_ = [i for i in range(len(imgs)) if owner[i] == rank]
-bat = rdist.Batched(torch.cat([imgs[i][0] for i in mine_]), torch.cat([imgs[i][1] for i in mine_]),
-                    torch.cat([imgs[i][2] for i in mine_]), sizes)
+
+
+def batched(src, idx, sizes_):
+    if not idx:      # a rank without images still takes part in the exchange
+        return rdist.Batched(torch.zeros((0, 5), device=dev), torch.zeros(0, device=dev),
+                             torch.zeros(0, dtype=torch.int64, device=dev), sizes_)
+    return rdist.Batched(torch.cat([src[i][0] for i in idx]), torch.cat([src[i][1] for i in idx]),
+                         torch.cat([src[i][2] for i in idx]), sizes_)
+
+
+bat = batched(imgs, mine_, sizes)
 for _ in range(2):
     got = rdist.nms_images_sharded(bat, 0.8, 500)
     assert all(torch.equal(g.to(dev), w.to(dev)) for g, w in zip(got, want))
@@ -140,8 +149,7 @@ owner = rdist.lpt_assign([float(v) ** 2 for v in sizes], world)
 local = [tuple(cu(x) for x in im) if owner[i] == rank else None for i, im in enumerate(c4)]
 out['c4_64img_sharded_rank_local'] = both(lambda: rdist.nms_images_sharded(local, 0.8, 2000, sizes=sizes))
 mine_ = [i for i in range(64) if owner[i] == rank]
-bat = rdist.Batched(torch.cat([local[i][0] for i in mine_]), torch.cat([local[i][1] for i in mine_]),
-                    torch.cat([local[i][2] for i in mine_]), sizes)
+bat = batched(local, mine_, sizes)
 out['c4_64img_sharded_rank_local_batched'] = both(lambda: rdist.nms_images_sharded(bat, 0.8, 2000))
 res, offs, shape = synth.c5_patch_results(0)
 for p_, o_ in zip(res, offs):
