@@ -797,10 +797,11 @@ __device__ __forceinline__ int block_sum(int v, int *s_red /* kResWarps */) {
 
 template <bool MC>
 __global__ void __launch_bounds__(kResThreads, 1)
-nms_resolve_kernel(const ResolveArgs a_in) {
-    ResolveArgs a = a_in;
-    if (a.nseg_dev) a.nseg = (int)*a.nseg_dev;
-    if (a.n_pad_dev) a.chunks = min(a.chunks, (int64_t)(*a.n_pad_dev >> 6));
+nms_resolve_kernel(const ResolveArgs a) {
+    // device-planned launches: the real counts (a copy of the argument struct with them patched in put the
+    // whole struct into local memory)
+    const int nseg = a.nseg_dev ? (int)*a.nseg_dev : a.nseg;
+    const int64_t chunks = a.n_pad_dev ? min(a.chunks, (int64_t)(*a.n_pad_dev >> 6)) : a.chunks;
     RT_DECL
     RT_MARK;   // 0 start
     // dynamic shared memory: the (kept, removed) pairs of one small segment
@@ -812,7 +813,7 @@ nms_resolve_kernel(const ResolveArgs a_in) {
     const unsigned int G = gridDim.x;
 
     // ---- small segments: one CTA each, state in shared memory ------------------------------
-    for (int s = blockIdx.x; s < a.nseg; s += G) {
+    for (int s = blockIdx.x; s < nseg; s += G) {
         const NmsSegment sg = a.segs[s];
         const int nch = sg.row_blocks;
         if (sg.len <= 0 || nch > kLocalChunks) continue;
@@ -845,16 +846,16 @@ nms_resolve_kernel(const ResolveArgs a_in) {
         // round (~10 us with 148 CTAs) to the chunks that wait for it.
         for (;;) {
             bool left = false;
-            for (int64_t gw = gwarp; gw < a.chunks; gw += nwarps) {
-                const NmsSegment &sg = a.segs[segment_of_slot(a.segs, a.nseg, gw * 64)];
+            for (int64_t gw = gwarp; gw < chunks; gw += nwarps) {
+                const NmsSegment &sg = a.segs[segment_of_slot(a.segs, nseg, gw * 64)];
                 const int64_t c = gw - (sg.pstart >> 6), w0 = 2 * (sg.pstart >> 6);
                 if (sg.row_blocks <= kLocalChunks || c >= sg.row_blocks) continue;
                 left |= resolve_chunk<false, false>(a, sg, (int)c, a.sc.kr + w0, a.sc.kr + w0, lane);
             }
             if (!left) break;
         }
-        for (int64_t gw = gwarp; gw < a.chunks; gw += nwarps) {
-            const NmsSegment &sg = a.segs[segment_of_slot(a.segs, a.nseg, gw * 64)];
+        for (int64_t gw = gwarp; gw < chunks; gw += nwarps) {
+            const NmsSegment &sg = a.segs[segment_of_slot(a.segs, nseg, gw * 64)];
             const int64_t c = gw - (sg.pstart >> 6);
             if (sg.row_blocks <= kLocalChunks || c >= sg.row_blocks) continue;
             write_flags(a, sg, (int)c, ldcg_u64x2(a.sc.kr + 2 * gw).x, lane);
