@@ -214,6 +214,63 @@ def translate_bboxes(bboxes, offset):
     return bboxes
 
 
+_STAGE = {}
+
+
+def _stage_rows(rows):
+    """pinned float32 staging rows of the merge upload, reused across calls (grown by halves)"""
+    buf = _STAGE.get('rows')
+    if buf is None or buf.shape[0] < rows:
+        buf = torch.empty((max(int(rows * 1.5), 1 << 16), 6), dtype=torch.float32, pin_memory=True)
+        _STAGE['rows'] = buf
+    return buf
+
+
+def _merge_results_fast(results, offsets, num_classes, iou_thr):
+    """merge_results for the usual input — every class a writable float32 (k,6) array: the
+    patches x classes walk (in-place shift + per-class concatenation, reference
+    merge_results.py:98-107) runs in the C helper csrc/hostpack.c straight into pinned staging
+    rows; one upload, one rotgeo_nms_grouped call with the classes as groups whose resolve
+    kernel writes the kept rows itself, one download.  None = input the helper does not take."""
+    from . import _hostpack
+    if not float(iou_thr) > 0.0:
+        return None
+    dev = ops._cuda_device()
+    offs = np.ascontiguousarray(np.asarray(offsets).reshape(len(results), 2), dtype=np.float64)
+    stage = _stage_rows(1)
+    got = _hostpack.gather_shift(results, offs, stage.numpy())
+    if got is not None and not got[2]:
+        stage = _stage_rows(got[0])
+        got = _hostpack.gather_shift(results, offs, stage.numpy())
+    if got is None:
+        return None
+    total, counts, _ = got
+    empty = np.zeros((0, 6), dtype=np.float32)
+    if total == 0:
+        return [empty.copy() for _ in range(num_classes)]
+    d = stage[:total].to(dev, non_blocking=True)
+    groups = [c for c in counts if c]
+    got = ops._nms_grouped(d[:, :5], d[:, 5], iou_thr, group_sizes=groups, with_dets=True)
+    if got is None:
+        raise RuntimeError('rotgeo: the grouped NMS refused a job without segment ids')
+    keep, kcounts, dets = got
+    if dets is None:
+        starts = np.concatenate([[0], np.cumsum(groups)])[:-1]
+        rows = keep + torch.repeat_interleave(torch.from_numpy(starts).to(dev),
+                                              torch.tensor(kcounts, device=dev), output_size=int(keep.numel()))
+        dets = d[rows]
+    kept = dets.cpu().numpy()
+    merged, at, j = [], 0, 0
+    for c in range(num_classes):
+        if counts[c]:
+            merged.append(kept[at:at + kcounts[j]])
+            at += kcounts[j]
+            j += 1
+        else:
+            merged.append(empty.copy())
+    return merged
+
+
 def merge_results(results, offsets, img_shape, iou_thr=0.1, device='cpu'):
     """Huge-image patch merge, same contract as reference
     mmrotate/core/patch/merge_results.py:69-127 for detection results
@@ -234,6 +291,10 @@ def merge_results(results, offsets, img_shape, iou_thr=0.1, device='cpu'):
     num_patches = len(results)
     num_classes = len(results[0])
 
+    fast = _merge_results_fast(results, offsets, num_classes, iou_thr)
+    if fast is not None:
+        return fast
+    # arrays the C helper does not take (horizontal (k,5) classes, float64 rows, read-only arrays): numpy walk
     per_cls = []
     for cls in range(num_classes):
         dets = [translate_bboxes(results[i][cls], offsets[i]) for i in range(num_patches)]

@@ -1,0 +1,93 @@
+"""_hostpack.gather_shift (csrc/hostpack.c) — the C walk over patches x classes of merge_results —
+against the numpy walk of the reference (mmrotate/core/patch/merge_results.py:7-29,98-107):
+bit-identical rows, identical in-place change of the caller's arrays, refusal of layouts it
+does not take (nothing modified then)."""
+import numpy as np
+import pytest
+
+from orientedobjectdetection_b200 import build
+
+build.build_hostpack()
+from orientedobjectdetection_b200 import _hostpack  # noqa: E402
+
+
+def _scene(seed, patches=7, classes=4, strided=False):
+    rng = np.random.default_rng(seed)
+    res = []
+    for _ in range(patches):
+        row = []
+        for c in range(classes):
+            k = int(rng.integers(0, 9)) if c != 2 else 0          # class 2 is empty everywhere
+            a = rng.uniform(-50, 1100, size=(k, 12 if strided else 6)).astype(np.float32)
+            row.append(a[:, ::2] if strided else a)
+        res.append(row)
+    offs = rng.integers(0, 16384, size=(patches, 2)).astype(np.int64)
+    return res, offs
+
+
+def _numpy_walk(res, offs):
+    per = []
+    for c in range(len(res[0])):
+        parts = []
+        for i in range(len(res)):
+            b = res[i][c]
+            b[:, :2] = b[:, :2] + offs[i]                        # the reference's translate_bboxes, (n,6) branch
+            parts.append(b)
+        per.append(np.concatenate(parts, axis=0))
+    return per
+
+
+@pytest.mark.parametrize('strided', [False, True])
+def test_gather_shift_equals_numpy_walk(strided):
+    res, offs = _scene(3, strided=strided)
+    mine = [[a.copy() if not strided else np.repeat(a, 2, axis=1)[:, ::2] for a in p] for p in res]
+    per = _numpy_walk(res, offs)
+    out = np.full((1000, 6), -1.0, dtype=np.float32)
+    total, counts, filled = _hostpack.gather_shift(mine, offs.astype(np.float64), out)
+    assert filled and total == sum(p.shape[0] for p in per) and counts == [p.shape[0] for p in per]
+    assert counts[2] == 0
+    assert np.array_equal(out[:total], np.concatenate(per, axis=0))
+    assert np.all(out[total:] == -1.0)
+    for pa, pb in zip(res, mine):                                  # the caller's arrays moved the same way
+        for a, b in zip(pa, pb):
+            assert np.array_equal(a, b)
+
+
+def test_gather_shift_float_offsets_and_tiny_values():
+    rng = np.random.default_rng(5)
+    a = (rng.uniform(-1, 1, size=(64, 6)) * 10.0 ** rng.integers(-30, 4, size=(64, 6))).astype(np.float32)
+    offs = np.array([[1234.5, 7.25]])
+    want = a.copy()
+    want[:, :2] = want[:, :2] + offs[0]
+    out = np.empty((64, 6), dtype=np.float32)
+    total, counts, filled = _hostpack.gather_shift([[a]], offs, out)
+    assert filled and total == 64 and counts == [64]
+    assert np.array_equal(out, want) and np.array_equal(a, want)
+
+
+def test_gather_shift_small_buffer_touches_nothing():
+    res, offs = _scene(4)
+    before = [[a.copy() for a in p] for p in res]
+    out = np.zeros((2, 6), dtype=np.float32)
+    total, counts, filled = _hostpack.gather_shift(res, offs.astype(np.float64), out)
+    assert not filled and total == sum(counts) > 2
+    assert np.all(out == 0)
+    assert all(np.array_equal(a, b) for pa, pb in zip(res, before) for a, b in zip(pa, pb))
+
+
+def test_gather_shift_refuses_other_layouts():
+    out = np.zeros((100, 6), dtype=np.float32)
+    offs = np.zeros((1, 2))
+    good = np.ones((3, 6), dtype=np.float32)
+    ro = np.ones((3, 6), dtype=np.float32)
+    ro.setflags(write=False)
+    for bad in (np.ones((3, 5), dtype=np.float32), np.ones((3, 6), dtype=np.float64), np.ones(6, dtype=np.float32), ro,
+                [[1.0] * 6]):
+        g = good.copy()
+        assert _hostpack.gather_shift([[g, bad]], offs + 5.0, out) is None
+        assert np.all(g == 1.0)                                    # validated before anything is shifted
+    with pytest.raises(ValueError):
+        _hostpack.gather_shift([[good]], np.zeros((2, 2)), out)
+    with pytest.raises(ValueError):
+        _hostpack.gather_shift([[good], [good, good]], np.zeros((2, 2)), out)
+    assert _hostpack.gather_shift([], np.zeros((0, 2)), out) == (0, [], True)
