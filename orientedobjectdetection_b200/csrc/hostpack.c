@@ -29,21 +29,31 @@ static int is_f32(const Py_buffer *v) {
     return f[0] == 'f' && f[1] == 0;
 }
 
-/* gather_shift(results, offsets, out) -> (total_rows, counts, filled) | None
+/* gather_shift(results, offsets, out[, take]) -> (total_rows, counts, filled) | None
  *   results  sequence over patches of sequences over classes of (k,6) float32 arrays
  *   offsets  contiguous float64 buffer, 2 values per patch
  *   out      writable contiguous buffer (the float32 staging rows)
+ *   take     optional bytes-like, one byte per class: rows of classes with a zero byte are shifted
+ *            in place like all others but not copied (multi-GPU: a rank stages its own classes);
+ *            total_rows then counts the copied classes only, counts still lists every class
  * None: some array is not a writable 2-D float32 array with 6 columns (caller takes the numpy
  * path); filled False: `out` is smaller than total_rows * 24 bytes — nothing was shifted. */
 static PyObject *gather_shift(PyObject *self, PyObject *args) {
-    PyObject *results, *offs_obj, *out_obj;
-    if (!PyArg_ParseTuple(args, "OOO", &results, &offs_obj, &out_obj)) return NULL;
-    Py_buffer offs, out;
+    PyObject *results, *offs_obj, *out_obj, *take_obj = NULL;
+    if (!PyArg_ParseTuple(args, "OOO|O", &results, &offs_obj, &out_obj, &take_obj)) return NULL;
+    if (take_obj == Py_None) take_obj = NULL;
+    Py_buffer offs, out, take;
     if (PyObject_GetBuffer(offs_obj, &offs, PyBUF_C_CONTIGUOUS | PyBUF_FORMAT) < 0) return NULL;
     if (PyObject_GetBuffer(out_obj, &out, PyBUF_C_CONTIGUOUS | PyBUF_WRITABLE) < 0) {
         PyBuffer_Release(&offs);
         return NULL;
     }
+    if (take_obj && PyObject_GetBuffer(take_obj, &take, PyBUF_C_CONTIGUOUS) < 0) {
+        PyBuffer_Release(&out);
+        PyBuffer_Release(&offs);
+        return NULL;
+    }
+    const unsigned char *takeb = take_obj ? (const unsigned char *)take.buf : NULL;
     PyObject *res_fast = PySequence_Fast(results, "results must be a sequence over patches");
     PyObject *ret = NULL, *counts = NULL;
     PyObject **rows_fast = NULL;
@@ -72,6 +82,10 @@ static PyObject *gather_shift(PyObject *self, PyObject *args) {
             goto done;
         }
     }
+    if (takeb && take.len != C) {
+        PyErr_SetString(PyExc_ValueError, "take must hold one byte per class");
+        goto done;
+    }
     views = (Py_buffer *)malloc((size_t)(P * C ? P * C : 1) * sizeof(Py_buffer));
     if (!views) { PyErr_NoMemory(); goto done; }
     /* pass 1: views + validation + rows per class; nothing is modified yet */
@@ -92,7 +106,7 @@ static PyObject *gather_shift(PyObject *self, PyObject *args) {
                 break;
             }
             cls_rows[c] += v->shape[0];
-            total += v->shape[0];
+            if (!takeb || takeb[c]) total += v->shape[0];
         }
     if (unsupported) {
         free(cls_rows);
@@ -118,7 +132,13 @@ static PyObject *gather_shift(PyObject *self, PyObject *args) {
                 const Py_ssize_t k = v->shape[0], s0 = v->strides[0], s1 = v->strides[1];
                 const double ox = off[2 * i], oy = off[2 * i + 1];
                 char *row = (char *)v->buf;
-                if (s1 == 4) {
+                if (takeb && !takeb[c]) {           /* somebody else's class: the in-place shift only */
+                    for (Py_ssize_t r = 0; r < k; ++r, row += s0) {
+                        float *px = (float *)row, *py = (float *)(row + s1);
+                        *px = (float)((double)*px + ox);
+                        *py = (float)((double)*py + oy);
+                    }
+                } else if (s1 == 4) {
                     for (Py_ssize_t r = 0; r < k; ++r, row += s0, dst += HP_COLS) {
                         float *p = (float *)row;
                         p[0] = (float)((double)p[0] + ox);
@@ -147,6 +167,7 @@ done:
         free(rows_fast);
     }
     Py_XDECREF(res_fast);
+    if (take_obj) PyBuffer_Release(&take);
     PyBuffer_Release(&out);
     PyBuffer_Release(&offs);
     return ret;
@@ -154,7 +175,7 @@ done:
 
 static PyMethodDef methods[] = {
     {"gather_shift", gather_shift, METH_VARARGS,
-     "gather_shift(results, offsets_f64, out) -> (total_rows, rows_per_class, filled) | None"},
+     "gather_shift(results, offsets_f64, out[, take]) -> (total_rows, rows_per_class, filled) | None"},
     {NULL, NULL, 0, NULL}};
 
 static struct PyModuleDef moddef = {PyModuleDef_HEAD_INIT, "_hostpack", "host-side row gathering of the patch merge", -1, methods};

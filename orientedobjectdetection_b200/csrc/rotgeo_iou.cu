@@ -317,6 +317,9 @@ iou_tile_kernel(const IouArgs g) {
         }
         __syncwarp();
         if (lane == 0) mbar_arrive(&sm.empty[s]);   // this warp is done with the stage
+        // (measured and dropped: prefetch.global.L1 of the geometry lines a tile's candidates can touch, issued here —
+        // the loads of the queue pops wait for first touches, a third of the stall samples of the dense C3 launch —
+        // made the kernel SLOWER, 47.1 -> 51.2 us sparse and 59.4 -> 66.6 us dense: profiles/r02_iou_dense_ncu.txt)
 
         // ---- survivors -> queue 1, at most one per lane and round ----------------------
         {

@@ -761,6 +761,142 @@ __device__ bool resolve_chunk(const ResolveArgs &a, const NmsSegment &sg, int c,
     return cand != 0ull;
 }
 
+// ---- the same evaluation by a TEAM of 8 warps (the grid path of large segments) -------------------
+// One warp per chunk walks its rows' column blocks one lane = two rows, block after block: on a dense
+// 30 000-box segment the first evaluation of a chunk took 12 .. 31 us and there are ten more before
+// the last chunk is decided, while nine warps in ten of the grid have no chunk at all
+// (profiles/r02_resolve_team.txt).  Here a chunk belongs to 256 threads: four lanes per row, each
+// taking four of the row's next sixteen column blocks, so sixteen mask loads of a row are in flight at
+// once and a lane has one row, not two.  The lanes of a row agree through shuffles inside their group of
+// four; the rows of the eight warps meet in shared memory, and every warp of the team then finishes
+// the chunk redundantly (same inputs, same result; warp 0 stores).
+constexpr int kTeamWarps = 8;
+constexpr int kTeams = kResWarps / kTeamWarps;
+struct TeamSmem {
+    unsigned long long D[64];        // in-chunk neighbour word per row
+    uint32_t exk[kTeamWarps], exu[kTeamWarps];
+};
+__device__ __forceinline__ void team_bar(int team) {
+    asm volatile("bar.sync %0, %1;" ::"r"(team + 1), "r"(kTeamWarps * 32) : "memory");
+}
+// bits 0, 4, 8 .. 28 -> bits 0 .. 7
+__device__ __forceinline__ uint32_t every_fourth_bit(uint32_t b) {
+    uint32_t x = b & 0x11111111u;
+    x = (x | (x >> 3)) & 0x03030303u;
+    x = (x | (x >> 6)) & 0x000f000fu;
+    return (x | (x >> 12)) & 0xffu;
+}
+__device__ bool resolve_chunk_team(const ResolveArgs &a, const NmsSegment &sg, int c, unsigned long long *kr,
+                                   TeamSmem &ts, int team, int tw, int lane) {
+    const int64_t pos0 = (int64_t)c * 64, len = sg.len;
+    const unsigned long long valid = len - pos0 >= 64 ? ~0ull : ((1ull << (len - pos0)) - 1ull);
+    // the chunk's own words are written by this team only, and every store is followed by a team barrier:
+    // all eight warps read the same value here, so the early return is taken by all or none
+    const ulonglong2 kr0 = ldcg_u64x2(kr + 2 * c);
+    unsigned long long Kc = kr0.x, Rc = kr0.y;
+    const unsigned long long und = valid & ~(Kc | Rc);
+    if (und == 0ull) return false;
+
+    const int W = sg.words;
+    const unsigned long long *const M = a.mask + sg.mask_base;
+    const unsigned long long *const S = a.sc.summary + (sg.pstart + pos0) * a.sc.sum_words;
+    const int q = tw * 8 + (lane >> 2), sub = lane & 3;
+    const unsigned gmask = 0xfu << (lane & 28);
+    unsigned long long Dq = 0ull;
+    int exK = 0, exU = 0;
+    if ((und >> q) & 1ull) {              // the same for the four lanes of the row
+        const int64_t row = pos0 + q;
+        const unsigned long long *mrow = M + row * W;
+        unsigned long long *srow = const_cast<unsigned long long *>(S) + q * a.sc.sum_words;
+        const int kmax = a.spatial ? (sg.words / 2 - 1) >> 6 : (int)(row >> 13);
+        for (int k = 0; k <= kmax; ++k) {
+            const unsigned long long sb0 = __ldcg(srow + k);
+            unsigned long long sb = sb0, live = sb0;
+            while (sb != 0ull) {          // sixteen set bits per round: sb is the same in the four lanes at this point
+                for (int i = 0; i < 4 * sub; ++i) sb &= sb - 1ull;
+                int J[4];
+                ulonglong2 m[4];
+#pragma unroll
+                for (int t = 0; t < 4; ++t) {
+                    J[t] = sb ? (k << 6) + __ffsll((long long)sb) - 1 : -1;
+                    sb &= sb - 1ull;
+                }
+                for (int i = 0; i < 4 * (3 - sub); ++i) sb &= sb - 1ull;
+#pragma unroll
+                for (int t = 0; t < 4; ++t)
+                    m[t] = J[t] >= 0 ? __ldg(reinterpret_cast<const ulonglong2 *>(mrow + 2 * J[t]))
+                                     : make_ulonglong2(0ull, 0ull);
+#pragma unroll
+                for (int t = 0; t < 4; ++t) {
+                    bool dead = J[t] >= 0;
+#pragma unroll
+                    for (int h = 0; h < 2; ++h) {
+                        const unsigned long long mv = h ? m[t].y : m[t].x;
+                        const int w = 2 * J[t] + h;
+                        if (mv == 0ull) continue;
+                        if (w != c) {
+                            const ulonglong2 o = ldcg_u64x2(kr + 2 * w);
+                            if (mv & o.x) exK = 1;
+                            if (mv & ~(o.x | o.y)) exU = 1;
+                            if (mv & ~o.y) dead = false;
+                        } else {
+                            Dq = mv;
+                            dead = false;
+                        }
+                    }
+                    if (dead) live &= ~(1ull << (J[t] & 63));
+                }
+            }
+            live &= __shfl_xor_sync(gmask, live, 1);
+            live &= __shfl_xor_sync(gmask, live, 2);
+            exK |= __shfl_xor_sync(gmask, exK, 1);
+            exK |= __shfl_xor_sync(gmask, exK, 2);
+            if (sub == 0 && live != sb0 && !exK) __stcg(srow + k, live);
+            if (exK) break;               // a kept neighbour: the row is removed, nothing else matters
+        }
+        Dq |= __shfl_xor_sync(gmask, Dq, 1);
+        Dq |= __shfl_xor_sync(gmask, Dq, 2);
+        exU |= __shfl_xor_sync(gmask, exU, 1);
+        exU |= __shfl_xor_sync(gmask, exU, 2);
+    }
+    __syncwarp();
+    const uint32_t bk = __ballot_sync(0xffffffffu, exK != 0), bu = __ballot_sync(0xffffffffu, exU != 0);
+    if (lane == 0) {
+        ts.exk[tw] = every_fourth_bit(bk);
+        ts.exu[tw] = every_fourth_bit(bu);
+    }
+    if (sub == 0) ts.D[q] = Dq;
+    team_bar(team);
+    unsigned long long EXK = 0ull, EXU = 0ull;
+#pragma unroll
+    for (int w = 0; w < kTeamWarps; ++w) {
+        EXK |= (unsigned long long)ts.exk[w] << (8 * w);
+        EXU |= (unsigned long long)ts.exu[w] << (8 * w);
+    }
+    const unsigned long long D[2] = {ts.D[lane], ts.D[lane + 32]};
+    Rc |= und & EXK;
+    unsigned long long cand = und & ~EXK;
+    for (;;) {
+        bool rm[2], kp[2];
+#pragma unroll
+        for (int p = 0; p < 2; ++p) {
+            const int r = lane + 32 * p;
+            const bool in = (cand >> r) & 1ull;
+            rm[p] = in && (D[p] & Kc) != 0ull;
+            kp[p] = in && !rm[p] && (D[p] & cand) == 0ull && !((EXU >> r) & 1ull);
+        }
+        const unsigned long long REM = ballot64(rm[0], rm[1]);
+        const unsigned long long KEEP = ballot64(kp[0], kp[1]);
+        if ((REM | KEEP) == 0ull) break;
+        Kc |= KEEP;
+        Rc |= REM;
+        cand &= ~(REM | KEEP);
+    }
+    if (tw == 0 && lane == 0 && (Kc != kr0.x || Rc != kr0.y)) kr_store<false>(kr + 2 * c, Kc, Rc);
+    team_bar(team);    // the store precedes every later read of these words by the team; ts is free again
+    return cand != 0ull;
+}
+
 // kept bits of one chunk -> per-box flags (indexed like the caller's boxes)
 __device__ __forceinline__ void write_flags(const ResolveArgs &a, const NmsSegment &sg, int c,
                                             unsigned long long K, int lane) {
@@ -809,6 +945,7 @@ nms_resolve_kernel(const ResolveArgs a) {
     __shared__ int s_red[kResWarps];
     __shared__ int s_warp_cnt[kResWarps];
     __shared__ uint32_t s_list[kEmitTile];   // kept indices of one emit tile
+    __shared__ TeamSmem s_team[kTeams];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const unsigned int G = gridDim.x;
 
@@ -839,12 +976,23 @@ nms_resolve_kernel(const ResolveArgs a) {
     if (a.has_large) {
         // consecutive chunks go to different CTAs: a mid-size segment is spread over every SM
         const int64_t gwarp = (int64_t)blockIdx.x + (int64_t)G * warp, nwarps = (int64_t)G * kResWarps;
-        // No rounds and no grid barrier here either: every warp re-evaluates its own chunks until
-        // they are decided, reading the state of earlier chunks through L2 (ld.cg / st.cg).  All
+        const int team = warp / kTeamWarps, tw = warp % kTeamWarps;
+        const int64_t gteam = (int64_t)blockIdx.x + (int64_t)G * team, nteams = (int64_t)G * kTeams;
+        // No rounds and no grid barrier here either: every team re-evaluates its own chunks until
+        // they are decided, reading the state of the other chunks through L2 (ld.cg / st.cg).  All
         // CTAs are co-resident (cooperative launch), the bitmaps only gain bits, so this ends with
         // the greedy result; a decision travels one L2 round trip instead of one grid-barrier
         // round (~10 us with 148 CTAs) to the chunks that wait for it.
-        for (;;) {
+#ifdef ROTGEO_RESOLVE_TIMING
+        unsigned long long pc_t0, pc_first = 0, pc_last = 0;
+        int pc_evals = 0;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(pc_t0));
+#endif
+        // Teams pay when there are fewer chunks than warps and the rows are long (one dense 30 000-box segment:
+        // 470 chunks, 155 -> 85 us); with thousands of short-row chunks (C5: 3125, C4 batch: 10 000) a warp per
+        // chunk keeps eight times as many chunks in flight and is the faster of the two (C5 35 vs 74 us).
+        const bool teams = chunks <= 2 * nteams;
+        for (; !teams;) {
             bool left = false;
             for (int64_t gw = gwarp; gw < chunks; gw += nwarps) {
                 const NmsSegment &sg = a.segs[segment_of_slot(a.segs, nseg, gw * 64)];
@@ -854,6 +1002,26 @@ nms_resolve_kernel(const ResolveArgs a) {
             }
             if (!left) break;
         }
+        for (; teams;) {
+            bool left = false;           // the same in the eight warps of a team
+            for (int64_t gw = gteam; gw < chunks; gw += nteams) {
+                const NmsSegment &sg = a.segs[segment_of_slot(a.segs, nseg, gw * 64)];
+                const int64_t c = gw - (sg.pstart >> 6), w0 = 2 * (sg.pstart >> 6);
+                if (sg.row_blocks <= kLocalChunks || c >= sg.row_blocks) continue;
+                left |= resolve_chunk_team(a, sg, (int)c, a.sc.kr + w0, s_team[team], team, tw, lane);
+#ifdef ROTGEO_RESOLVE_TIMING
+                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(pc_last));
+                if (pc_evals++ == 0) pc_first = pc_last;
+#endif
+            }
+            if (!left) break;
+        }
+#ifdef ROTGEO_RESOLVE_TIMING   // per-chunk: evaluations until decided, duration of the first one, time of the decision
+        if (lane == 0 && tw == 0 && gteam < chunks && gteam % 41 == 0)
+            printf("  chunk %lld: %d evaluations, first %.1f us, decided at %.1f us\n", (long long)gteam, pc_evals,
+                   (double)(pc_first - pc_t0) * 1e-3, (double)(pc_last - pc_t0) * 1e-3);
+#endif
+        __syncthreads();                 // every team of the CTA is done before the flags of its chunks are written
         for (int64_t gw = gwarp; gw < chunks; gw += nwarps) {
             const NmsSegment &sg = a.segs[segment_of_slot(a.segs, nseg, gw * 64)];
             const int64_t c = gw - (sg.pstart >> 6);
@@ -1098,10 +1266,12 @@ static int launch_resolve(const ResolveArgs &a_in, cudaStream_t stream) {
     const int limit = lim.sms < kNmsMaxBlocks ? lim.sms : kNmsMaxBlocks;
     // one small segment per CTA; with large segments, their chunks spread over every SM (the row
     // tests are latency-bound: more SMs, more loads in flight)
+    // (measured and dropped: sending mid-size segments — a C2-dense class, 32 chunks — to the grid's 8-warp teams as
+    // well instead of one CTA each changed nothing: resolve 48.3 vs 47.2 us on C2 dense, 19.9 vs 20.0 on a C4 image)
     int64_t want = a_in.has_large ? a_in.chunks : a_in.nseg;
     if (want < 1) want = 1;
-    // dynamic shared memory: one small segment's state
     ResolveArgs a = a_in;
+    // dynamic shared memory: one small segment's state
     const size_t dyn = 2 * kLocalChunks * sizeof(unsigned long long);
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)(want < limit ? want : limit));

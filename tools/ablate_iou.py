@@ -60,7 +60,7 @@ def run():
                 if i >= 3: ts.append(e0.elapsed_time(e1) * 1e3)
             if name == 'full':
                 want = out.clone()
-            same = bool(torch.equal(out, want)) if name.startswith('plain') else None
+            same = bool(torch.equal(out, want)) if name.startswith(('plain', 'no_prefetch')) else None
             print('extent %5.0f  %-20s same_as_full=%s  median %.1f us  best %.1f us' % (extent, name, same, float(np.median(ts)), min(ts)), flush=True)
 
 if __name__ == '__main__':

@@ -6,6 +6,9 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 import torch
 from torch.profiler import profile, ProfilerActivity
+from orientedobjectdetection_b200 import _lib as _l
+if os.environ.get('ROTGEO_SO'):
+    _l.SO_PATH = os.path.abspath(os.environ['ROTGEO_SO'])
 import orientedobjectdetection_b200 as rg
 from orientedobjectdetection_b200 import synth, dist as rdist, ops
 cu = lambda x: torch.from_numpy(x).cuda()

@@ -19,3 +19,7 @@ b1, s1, i1 = [torch.from_numpy(x).cuda() for x in synth.c4_rpn_image(0)]
 print('C4 one image', flush=True)
 for _ in range(3):
     rg.batched_nms(b1, s1, i1, dict(type='nms_rotated', iou_threshold=0.8)); torch.cuda.synchronize()
+bs, sc = torch.from_numpy(synth.le90_boxes(30000, 9, 1024.0)).cuda(), torch.from_numpy(synth.unique_scores(30000, 9)).cuda()
+print('single segment of 30000 boxes, extent 1024 (per-chunk lines: chunks 0, 41, 82, ...)', flush=True)
+for _ in range(2):
+    rg.nms_rotated(bs, sc, 0.1); torch.cuda.synchronize()
