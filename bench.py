@@ -453,6 +453,12 @@ def run_rotgeo(args, rank, world, local_rank):
         # stdout carries the one JSON line: NCCL's own messages (NCCL_DEBUG=VERSION on some boxes) go to stderr
         os.environ.setdefault('NCCL_DEBUG_FILE', '/dev/stderr')
         dist.init_process_group('nccl', device_id=dev)
+    # N > 1: every rank's pinned staging on the NUMA node of its own GPU (8 ranks x 268 MB device->host per step
+    # do not fit through one socket's memory: tools/numa_probe.py); before the first pinned allocation
+    host_cpus = None
+    if world > 1:
+        from orientedobjectdetection_b200 import peer as _peer
+        host_cpus = _peer.bind_host_to_gpu(dev)
     L = _lib.load()
 
     # rank r owns rows [r*N_ROWS, (r+1)*N_ROWS) of the global matrix; columns replicated
@@ -555,7 +561,10 @@ def run_rotgeo(args, rank, world, local_rank):
         'e2e': {'value': e2e_val, 'unit': 'Gpairs/s',
                 'h2d_bytes_per_step': int(a_host.numel() * 4 + b_host.numel() * 4),
                 'd2h_bytes_per_step': int(N_ROWS * N_COLS * 4), 'steps': e2e_steps,
-                'api': 'orientedobjectdetection_b200.rbbox_overlaps(pinned CPU tensors) -> pinned CPU tensor'},
+                'api': 'orientedobjectdetection_b200.rbbox_overlaps(pinned CPU tensors) -> pinned CPU tensor '
+                       '(four row chunks, copies overlapped with the kernels)',
+                'host_binding': ('rank pinned to the %d CPUs NVML lists as local to its GPU' % len(host_cpus)) if host_cpus
+                                else 'none'},
         'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
                      'frac': achieved / peak, 'traffic': measured_traffic(),
                      'traffic_source': 'committed ncu --set full capture of this kernel (profiles/r01_iou_tile_kernel_traffic.json), not re-measured in this run',

@@ -76,6 +76,9 @@ def _overlaps(bboxes1, bboxes2, mode, aligned, min_wh):
     dev = _cuda_device(bboxes1, bboxes2)
     b1, b2 = _rows_f32(bboxes1, dev), _rows_f32(bboxes2, dev)
     L = _lib.load()
+    if not aligned and not bboxes1.is_cuda and rows * cols * 4 >= _HOST_CHUNK_BYTES and rows >= 4 * 64:
+        out = _overlaps_to_host_chunked(L, dev, b1, b2, rows, cols, mode, min_wh)
+        return out if out.dtype == bboxes1.dtype else out.to(dtype=bboxes1.dtype)
     with torch.cuda.device(dev):
         out = torch.empty(out_shape, dtype=torch.float32, device=dev)
         if aligned:
@@ -99,6 +102,43 @@ def _overlaps(bboxes1, bboxes2, mode, aligned, min_wh):
     if out.dtype != bboxes1.dtype:
         out = out.to(dtype=bboxes1.dtype)
     return out
+
+
+_HOST_CHUNK_BYTES = 32 << 20
+_COPY_STREAMS = {}
+
+
+def _overlaps_to_host_chunked(L, dev, b1, b2, rows, cols, mode, min_wh):
+    """A big matrix for a CPU caller is bound by the device->host copy (268 MB at ~57 GB/s = 4.7 ms
+    against 0.05 ms of kernel at 8192 x 8192): four row chunks, each one rotgeo_iou_pairwise call on
+    the compute stream, its copy into the pinned result issued on a second stream as soon as the
+    chunk is done — the copies run back to back from the first quarter of the kernel time on,
+    instead of after the whole matrix."""
+    with torch.cuda.device(dev):
+        compute = torch.cuda.current_stream(dev)
+        copy = _COPY_STREAMS.get(dev.index)
+        if copy is None:
+            copy = _COPY_STREAMS[dev.index] = torch.cuda.Stream(dev)
+        out = torch.empty((rows, cols), dtype=torch.float32, device=dev)
+        out.record_stream(copy)
+        host = torch.empty((rows, cols), dtype=torch.float32, pin_memory=True)
+        step = (rows + 3) // 4
+        step = (step + 63) // 64 * 64
+        nbytes = L.rotgeo_iou_workspace_bytes(step, cols)
+        ws = _workspace(dev, compute.cuda_stream, 'iou_host', nbytes)
+        for lo in range(0, rows, step):
+            hi = min(rows, lo + step)
+            _lib.check(L.rotgeo_iou_pairwise(b1.data_ptr() + lo * b1.stride(0) * 4, hi - lo, b1.stride(0), b2.data_ptr(),
+                                             cols, b2.stride(0), _MODE[mode], float(min_wh),
+                                             out.data_ptr() + lo * cols * 4, cols, ws.data_ptr(), ws.numel(),
+                                             compute.cuda_stream), 'rotgeo_iou_pairwise')
+            ev = torch.cuda.Event()
+            ev.record(compute)
+            copy.wait_event(ev)
+            with torch.cuda.stream(copy):
+                host[lo:hi].copy_(out[lo:hi], non_blocking=True)
+        copy.synchronize()
+    return host
 
 
 def box_iou_rotated(bboxes1, bboxes2, mode='iou', aligned=False, clockwise=True):

@@ -94,3 +94,24 @@ def window(nbytes, group=None):
 
 def release():
     _WINDOWS.clear()
+
+
+def bind_host_to_gpu(device=None):
+    """Pin the calling thread to the CPUs NVML reports as local to ``device`` (default: the current
+    CUDA device), so that pinned staging memory allocated afterwards (the result buffers of the
+    host-tensor IoU path, the merge staging rows) is first-touched on the GPU's own NUMA node.
+    One process per GPU on a two-socket box otherwise puts every rank's pinned buffers — and 8 x 54
+    GB/s of device->host copies — on whatever node the launcher started on.  Process-wide side
+    effect, so it is a call the application makes (bench.py does at N > 1), never done implicitly.
+    Returns the sorted CPU list, or None when NVML or the UUID lookup is not available."""
+    import os
+    try:
+        import pynvml
+        idx = torch.cuda.current_device() if device is None else torch.device(device).index
+        uuid = str(torch.cuda.get_device_properties(idx).uuid)
+        pynvml.nvmlInit()
+        handle = pynvml.nvmlDeviceGetHandleByUUID(('GPU-' + uuid) if not uuid.startswith('GPU-') else uuid)
+        pynvml.nvmlDeviceSetCpuAffinity(handle)
+        return sorted(os.sched_getaffinity(0))
+    except Exception:
+        return None

@@ -93,6 +93,19 @@ def test_iou_cpu_tensor_roundtrip_and_float64():
     assert out64.dtype == torch.float64
 
 
+def test_iou_big_matrix_for_a_cpu_caller_is_chunked_and_identical():
+    # >= 32 MB of result for CPU tensors: four row chunks, copies overlapped with the kernels (ops._overlaps_to_host_chunked)
+    a, b = synth.c1_iou(seed=6, n=4100, m=2100, extent=900.0)
+    for mode in ('iou', 'iof'):
+        host = rg.rbbox_overlaps(torch.from_numpy(a), torch.from_numpy(b), mode=mode)
+        assert not host.is_cuda and host.shape == (4100, 2100)
+        dev = rg.rbbox_overlaps(_cuda(a), _cuda(b), mode=mode).cpu()
+        assert (dev > 0).sum() > 1000
+        assert torch.equal(host, dev)
+    want = ref_api.rbbox_overlaps(torch.from_numpy(a[4000:4100]), torch.from_numpy(b[:300]), mode='iof').numpy()
+    assert np.abs(host.numpy()[4000:4100, :300] - want).max() <= IOU_TOL       # the last (ragged) chunk against the oracle
+
+
 def test_iou_empty_and_errors():
     e = torch.zeros((0, 5)).cuda()
     b = _cuda(synth.le90_boxes(7, 0))
