@@ -802,6 +802,9 @@ __device__ bool resolve_chunk_team(const ResolveArgs &a, const NmsSegment &sg, i
     const unsigned long long *const S = a.sc.summary + (sg.pstart + pos0) * a.sc.sum_words;
     const int q = tw * 8 + (lane >> 2), sub = lane & 3;
     const unsigned gmask = 0xfu << (lane & 28);
+    // (measured and dropped: one coalesced copy of the segment's (kept, removed) words into shared memory per
+    // evaluation instead of an L2 lookup per non-empty mask word — evaluations got no shorter, the staler state cost
+    // one or two more of them: 85 -> 100 us on the dense 30 000-box segment.  The mask loads are the latency.)
     unsigned long long Dq = 0ull;
     int exK = 0, exU = 0;
     if ((und >> q) & 1ull) {              // the same for the four lanes of the row
