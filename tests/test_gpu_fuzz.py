@@ -140,3 +140,74 @@ def test_fuzz_iou_matrix(seed):
         stable = np.abs(want - w64) <= 1e-6
         assert np.abs(got - want)[stable].max() <= IOU_TOL
         assert np.abs(got - w64).max() <= IOU_TOL
+
+
+@pytest.mark.parametrize('seed', range(12))
+def test_fuzz_multiclass_nms(seed):
+    rng = np.random.default_rng(4000 + seed)
+    n = SIZES[(3 * seed + 1) % len(SIZES)]
+    C = int(rng.choice([1, 3, 15, 40]))
+    extent = float(rng.choice([60.0, 400.0]))
+    thr = float(rng.choice([0.1, 0.5]))
+    score_thr = float(rng.choice([0.05, 0.3, 0.95]))
+    max_num = int(rng.choice([-1, 7, 100]))
+    shared, _ = _scene(rng, n, extent)
+    if rng.random() < 0.5:
+        boxes = shared
+    else:
+        boxes = np.concatenate([_scene(rng, n, extent)[0] for _ in range(C)], axis=1)      # (n, C*5)
+    ms = rng.random((n, C + 1)).astype(np.float32) ** 3
+    if rng.random() < 0.5:
+        ms = np.round(ms, 2)
+    sf = rng.uniform(0.3, 1.0, n).astype(np.float32) if rng.random() < 0.5 else None
+    wd, wl, wk = ref_api.multiclass_nms_rotated(torch.from_numpy(boxes), torch.from_numpy(ms), score_thr, thr, max_num,
+                                                None if sf is None else torch.from_numpy(sf))
+    gd, gl, gk = rg.multiclass_nms_rotated(_cuda(boxes), _cuda(ms), score_thr, dict(iou_thr=thr), max_num,
+                                           None if sf is None else _cuda(sf), return_inds=True)
+    if gk.cpu().tolist() != wk.tolist():
+        # candidate table of the reference (bbox_nms_rotated.py:33-79), for the listing of the disputed pair
+        nb = torch.from_numpy(boxes).view(n, -1, 5) if boxes.shape[1] > 5 else torch.from_numpy(boxes)[:, None].expand(n, C, 5)
+        sc = torch.from_numpy(ms)[:, :-1]
+        valid = (sc > score_thr).reshape(-1)
+        if sf is not None:
+            sc = sc * torch.from_numpy(sf)[:, None]
+        lab = torch.arange(C)[None].expand(n, C).reshape(-1)[valid]
+        cb, cs = nb.reshape(-1, 5)[valid], sc.reshape(-1)[valid]
+        off = lab.to(cb) * (cb[:, :2].max() + cb[:, 2:4].max() + 1)
+        shifted = torch.cat([cb[:, :2] + off[:, None], cb[:, 2:5]], dim=-1).numpy()
+        _check_keep(shifted, cs.numpy(), thr, gk.cpu().numpy(), wk.numpy(), max_num if max_num > 0 else None)
+    else:
+        assert torch.equal(gl.cpu(), wl) and torch.equal(gd.cpu(), wd)
+
+
+@pytest.mark.parametrize('seed', range(8))
+def test_fuzz_merge_results(seed):
+    rng = np.random.default_rng(5000 + seed)
+    P, C = int(rng.integers(1, 9)), int(rng.choice([1, 2, 6]))
+    thr = float(rng.choice([0.1, 0.5]))
+    res, offs = [], rng.integers(0, 900, size=(P, 2)).astype(np.int64)
+    for _ in range(P):
+        row = []
+        for c in range(C):
+            k = int(rng.choice([0, 0, 1, 40, 200]))
+            b, s = _scene(rng, k, 300.0)
+            row.append(np.concatenate([b, s[:, None]], axis=1).astype(np.float32))
+        res.append(row)
+    mine = [[a.copy() for a in p] for p in res]
+    theirs = [[a.copy() for a in p] for p in res]
+    want = ref_api.merge_results(theirs, offs, thr)
+    got = rg.merge_results(mine, offs, (2000, 2000), thr)
+    assert len(got) == C
+    for c in range(C):
+        if got[c].shape != want[c].shape or not np.array_equal(got[c], want[c]):
+            allc = np.concatenate([res[p][c][:, :5] + np.concatenate([offs[p], [0, 0, 0]]).astype(np.float32) for p in range(P)])
+            alls = np.concatenate([res[p][c][:, 5] for p in range(P)])
+            # rows are unique up to exact duplicates: map the kept rows back to indices through the score order
+            _, wk = ref.nms_rotated(allc, alls, thr)
+            _, gk64 = ref.nms_rotated(allc.astype(np.float64), alls.astype(np.float64), thr)
+            assert got[c].shape[0] in (len(wk), len(gk64))
+            assert np.array_equal(got[c], np.concatenate([allc[gk64], alls[gk64, None]], axis=1)) or \
+                np.array_equal(got[c], np.concatenate([allc[wk], alls[wk, None]], axis=1))
+    for pa, pb in zip(mine, theirs):                   # shifted in place exactly like the reference
+        for a, b, in zip(pa, pb):
+            assert np.array_equal(a, b)
