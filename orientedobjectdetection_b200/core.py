@@ -87,16 +87,16 @@ def _multiclass_nms_fused(multi_bboxes, multi_scores, score_thr, iou_thr, max_nu
         sf = score_factors.detach().to(device=dev, dtype=torch.float32).reshape(-1).contiguous()
     cap = min(max_num, n * num_classes) if max_num > 0 else n * num_classes
     with torch.cuda.device(dev):
-        ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+        stream = ops._stream(dev)
+        ws = ops._workspace(dev, stream, 'multiclass', nbytes)      # scratch, reused across calls on this stream
         dets = torch.empty((cap, 6), dtype=torch.float32, device=dev)
-        labels = torch.empty((cap,), dtype=torch.int64, device=dev)
-        flat = torch.empty((cap,), dtype=torch.int64, device=dev)
-        num = torch.empty(1, dtype=torch.int64, device=dev)
+        ints = torch.empty(2 * cap + 1, dtype=torch.int64, device=dev)   # labels | flat indices | count: one allocation
+        labels, flat, num = ints[:cap], ints[cap:2 * cap], ints[2 * cap:]
         _lib.check(L.rotgeo_multiclass_nms(mb.data_ptr(), mb.shape[1], ms.data_ptr(),
                                            sf.data_ptr() if sf is not None else None, n, num_classes,
                                            float(score_thr), float(iou_thr), cap, dets.data_ptr(),
                                            labels.data_ptr(), flat.data_ptr(), num.data_ptr(),
-                                           ws.data_ptr(), nbytes, ops._stream(dev)),
+                                           ws.data_ptr(), ws.numel(), stream),
                    'rotgeo_multiclass_nms')
         k = int(num.item())        # the one device->host read: sizes the outputs
     dets, labels = dets[:k], labels[:k]

@@ -259,8 +259,8 @@ def _nms_grouped(boxes, scores, iou_threshold, seg_ids=None, offsets=None, id_of
         sizes = np.zeros(6, dtype=np.int64)
         need = (ctypes.c_size_t * 2)()
         for attempt in range(2):
-            keep = torch.empty(n, dtype=torch.int64, device=dev)
-            tail = torch.empty(2 + ngroups, dtype=torch.int64, device=dev)   # kept, error bits, kept per group
+            ints = torch.empty(n + 2 + ngroups, dtype=torch.int64, device=dev)   # one allocation: keep | tail
+            keep, tail = ints[:n], ints[n:]                                      # tail = kept, error bits, kept per group
             dets = torch.empty((n, 6), dtype=torch.float32, device=dev) if with_dets else None
             # fast path: ONE C-ABI call (sort + bounds + run) over the cached buffers; it reports the sizes it
             # needs, so a buffer that is too small costs one retry, once
