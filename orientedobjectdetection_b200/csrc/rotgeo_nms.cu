@@ -81,6 +81,7 @@ struct __align__(16) MaskSmem {
     uint64_t empty[kMaxStages];
     uint64_t sched[kInfoSlots];
     uint64_t ready[kInfoSlots];
+    uint64_t zeroed[kInfoSlots];        // list mode: all eight warps have zeroed their rows of my k-th tile
     // the scheduler's state (the duty rotates over the warps; nobody carries it in registers)
     struct Sched {
         unsigned next_ask, next_resp;   // launch-control requests issued / answers consumed, from 1
@@ -97,6 +98,7 @@ struct MaskArgs {
     const NmsSegment *segs;
     int nseg;
     const long long *nseg_dev;    // nullable: actual segment count (device-planned launch)
+    int zero_in_kernel;           // list mode: the mask kernel zeroes the listed tiles itself (one tile ahead)
     float thr;
     float area_ratio;             // pairs with min(area) < area_ratio * max(area) cannot reach thr
     float inter_need;             // 0.999 thr / (1 + thr): intersection / (areaA + areaB) a pair needs to reach thr
@@ -181,6 +183,8 @@ nms_tile_list_kernel(const NmsSegment *__restrict__ segs, int nseg_in, const lon
             ((unsigned long long)ti.seg << 32) | ((unsigned long long)ti.I << 16) | (unsigned long long)ti.J;
 }
 
+#ifdef ROTGEO_ZERO_KERNEL   // probe builds only: the separate zeroing pass of the first list-mode version (A/B against the
+                            // in-kernel zeroing one tile ahead: C5 282 -> 244 us of GPU time per call, profiles/r02_c5_zero_in_kernel.txt)
 // The mask words of the listed tiles start from zero — BOTH word blocks of a pair of blocks, because a
 // pair's bit lands in the row of its lower-ranked box, which may be the column box.  Zeroed here and not
 // in the mask kernel: there any warp of a CTA may hit any row of the mirrored block while another warp's
@@ -206,6 +210,7 @@ nms_tile_zero_kernel(const NmsSegment *__restrict__ segs, const unsigned long lo
         }
     }
 }
+#endif
 
 // AREA: the packed set carries the area axis of the index (high thresholds, see
 // nms_area_axis_ratio): 3 ring stages of 7.7 KB instead of 4 of 5 KB, one more range lookup
@@ -230,6 +235,7 @@ nms_mask_kernel(const MaskArgs g) {
         for (int s = 0; s < kInfoSlots; ++s) {
             mbar_init(&sm.sched[s], 1);
             mbar_init(&sm.ready[s], 1);
+            mbar_init(&sm.zeroed[s], kWarps);
         }
         fence_mbar_init();
     }
@@ -389,7 +395,34 @@ nms_mask_kernel(const MaskArgs g) {
     QEntry *const q2 = sm.queue2[warp];
     int n1 = 0, n2 = 0;
     const uint32_t lt = (1u << lane) - 1u;
+    // List mode: the mask words of a listed tile — BOTH word blocks of the pair of blocks, a pair's bit lands in the
+    // row of its lower-ranked box — are zeroed by the CTA that owns the tile, one tile ahead: at the end of tile k
+    // every warp zeroes 16 rows of either block of tile k + 1 and arrives on zeroed[k + 1]; the first bit a warp sets
+    // during tile k + 1 waits for that barrier (any warp may hit any row of either block).  Queue entries carried over
+    // from earlier tiles were covered by earlier barriers.  A separate zeroing kernel before this one cost 46 us of
+    // the 275 us C5 call, latency-bound; here the stores hide under the cull.
+    unsigned kcur = 0;
+    bool zero_ok = true;
+    auto zero_tile = [&](const TileInfo &tz, unsigned kz) {
+        const NmsSegment &sz = g.segs[tz.seg];
+        const int64_t Lz = sz.len, Wz = sz.words;
+        unsigned long long *const Mz = g.mask + sz.mask_base;
+        const int rr = warp + kWarps * (lane & 15);
+        if (lane < 16) {
+            const int64_t ri = (int64_t)tz.I * kTile + rr;
+            if (ri < Lz) *reinterpret_cast<uint4 *>(Mz + ri * Wz + 2 * tz.J) = make_uint4(0u, 0u, 0u, 0u);
+        } else if (tz.I != tz.J) {
+            const int64_t rj = (int64_t)tz.J * kTile + rr;
+            if (rj < Lz) *reinterpret_cast<uint4 *>(Mz + rj * Wz + 2 * tz.I) = make_uint4(0u, 0u, 0u, 0u);
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&sm.zeroed[kz % kInfoSlots]);
+    };
     auto clip32 = [&](int take) {            // pop `take` <= 32 entries of queue 2
+        if (!zero_ok) {
+            mbar_wait(&sm.zeroed[kcur % kInfoSlots], (kcur / kInfoSlots) & 1);
+            zero_ok = true;
+        }
         if (lane < take) {
             const QEntry e = q2[n2 - take + lane];
             const float v = rect_overlap<0>(__ldg(g.p0 + e.prow), __ldg(g.p1 + e.prow),
@@ -445,8 +478,12 @@ nms_mask_kernel(const MaskArgs g) {
     mbar_wait(&sm.ready[0], 0);
     TileInfo ti = sm.info[0];
     if (!ti.valid) return;       // launched past the device-side tile count
+    const bool zero_here = LIST && g.zero_in_kernel;
+    if (zero_here) zero_tile(ti, 0u);
 
     for (unsigned k = 0;; ++k) {
+        kcur = k;
+        zero_ok = !zero_here;
         const int s = k % kStages;
         const NmsSegment sg = g.segs[ti.seg];
         const int L = (int)sg.len, W = sg.words;
@@ -558,6 +595,7 @@ nms_mask_kernel(const MaskArgs g) {
         mbar_wait(&sm.ready[(k + 1) % kInfoSlots], ((k + 1) / kInfoSlots) & 1);
         const TileInfo tnext = sm.info[(k + 1) % kInfoSlots];
         const bool more = tnext.valid != 0;
+        if (zero_here && more) zero_tile(tnext, k + 1u);
 
         if (!more) {            // last tile of this CTA: flush both queues
             if (n1 > 0) circle32(n1);
@@ -1317,6 +1355,7 @@ int launch_nms(const NmsPlan &plan, const void *packed, const NmsSegment *segmen
     g.total_tiles = nullptr;
     g.nseg_dev = nullptr;
     g.tile_list = nullptr;
+    g.zero_in_kernel = 0;
     g.rank = nullptr;
     g.tile_next = nullptr;
     int rc = launch_mask(g, plan.total_tiles, stream);
@@ -1356,6 +1395,7 @@ int launch_nms_device_planned(const NmsDevLaunch &d, cudaStream_t stream) {
     g.total_tiles = d.total_tiles_dev;
     g.nseg_dev = d.nseg_dev;
     g.tile_list = nullptr;
+    g.zero_in_kernel = 0;
     g.rank = nullptr;
     g.tile_next = nullptr;
     if (d.tile_list) {
@@ -1365,13 +1405,18 @@ int launch_nms_device_planned(const NmsDevLaunch &d, cudaStream_t stream) {
         if (d.tiles_bound > 0) {
             nms_tile_list_kernel<<<(unsigned)((d.tiles_bound + 255) / 256), 256, 0, stream>>>(
                 d.segs_dev, d.nseg, d.nseg_dev, d.total_tiles_dev, d.tiles_bound, d.aabb, d.tile_list, count);
+#ifdef ROTGEO_ZERO_KERNEL   // probe builds: the separate zeroing pass of the first list-mode version
             DeviceLimits zl;
             if (device_limits(&zl)) return -3;
             nms_tile_zero_kernel<<<(unsigned)(zl.sms * 8), 256, 0, stream>>>(
                 d.segs_dev, d.tile_list, count, reinterpret_cast<unsigned long long *>(d.mask));
+#endif
             if (cudaGetLastError() != cudaSuccess) return -3;
         }
         g.tile_list = d.tile_list;
+#ifndef ROTGEO_ZERO_KERNEL
+        g.zero_in_kernel = 1;
+#endif
         g.rank = d.rank;
         g.tile_next = reinterpret_cast<unsigned long long *>(d.scratch.sync + 10);
         g.total_tiles = reinterpret_cast<const int64_t *>(count);
