@@ -204,7 +204,7 @@ def rbbox_overlaps_max_sharded(bboxes1, bboxes2, mode='iou', group=None):
 
 # ------------------------------------------------------------------ NMS results through peer memory
 def _nms_exchange_peer(boxes, scores, ids, id_offsets, local_sizes, local_gids, ngroups, cap, iou_threshold,
-                       group, rows_src=None):
+                       group, rows_src=None, want_keep=True):
     """Grouped NMS of THIS rank's groups (no host read) + push of the keep lists (and, with
     ``rows_src`` (n, 6), of the kept rows) into every rank's window + ONE read of the counts.
     Returns ``(counts[ngroups], keep (ngroups, cap) int64, rows (ngroups, cap, 6) | None)`` —
@@ -256,7 +256,7 @@ def _nms_exchange_peer(boxes, scores, ids, id_offsets, local_sizes, local_gids, 
         if any(head[ngroups:]):                                          # group of ALL ranks + error words
             return None
         used = max(1, max(head[:ngroups]))
-        keep_all = w.view(off + (ngroups + world) * 8, (ngroups, cap), torch.int64)[:, :used].clone()
+        keep_all = w.view(off + (ngroups + world) * 8, (ngroups, cap), torch.int64)[:, :used].clone() if want_keep else None
         rows_all = None
         if rows_src is not None:
             rows_all = w.view(off + (ngroups + world) * 8 + ngroups * cap * 8, (ngroups, cap, 6),
@@ -454,7 +454,8 @@ def merge_dets_sharded(dets, sizes, iou_thr=0.1, group=None):
         return out
     cap = max(1, max(int(v) for v in sizes))
     got = _nms_exchange_peer(d[:, :5] if d is not None else None, d[:, 5] if d is not None else None, None, False,
-                             lsz, mine, ncls, cap, iou_thr, group, rows_src=d if d is not None else torch.zeros((0, 6), device=dev))
+                             lsz, mine, ncls, cap, iou_thr, group, rows_src=d if d is not None else torch.zeros((0, 6), device=dev),
+                             want_keep=False)
     if got is None:
         raise RuntimeError('rotgeo: class-sharded merge failed in the NMS front-end')
     counts, _, rows_all = got
