@@ -429,14 +429,15 @@ def nms_block(torch, rg, synth):
 
 
 def measured_traffic():
-    """DRAM bytes per launch of the dominant kernel from the committed ncu --set full capture
-    (profiles/r01_iou_tile_kernel_traffic.json, written from the .ncu-rep by tools/ncu_traffic.py)"""
-    p = os.path.join(ROOT, 'profiles', 'r01_iou_tile_kernel_traffic.json')
-    if os.path.exists(p):
-        try:
-            return float(json.load(open(p))['dram_bytes_per_launch'])
-        except Exception:
-            return None
+    """DRAM bytes per launch of the dominant kernel from the newest committed ncu --set full capture
+    (profiles/r02_iou_tile_kernel_traffic.json, written from the .ncu-rep by tools/ncu_traffic.py)"""
+    for name in ('r02_iou_tile_kernel_traffic.json', 'r01_iou_tile_kernel_traffic.json'):
+        p = os.path.join(ROOT, 'profiles', name)
+        if os.path.exists(p):
+            try:
+                return float(json.load(open(p))['dram_bytes_per_launch'])
+            except Exception:
+                continue
     return None
 
 
@@ -567,7 +568,7 @@ def run_rotgeo(args, rank, world, local_rank):
                                 else 'none'},
         'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
                      'frac': achieved / peak, 'traffic': measured_traffic(),
-                     'traffic_source': 'committed ncu --set full capture of this kernel (profiles/r01_iou_tile_kernel_traffic.json), not re-measured in this run',
+                     'traffic_source': 'committed ncu --set full capture of this kernel (profiles/r02_iou_tile_kernel_traffic.json, round 2), not re-measured in this run',
                      'kernel': 'iou_tile_kernel<0,true>',
                      'kernel_ms': k_ms, 'peak_source': peak_src,
                      'algorithmic_bytes_per_launch': alg_bytes,
