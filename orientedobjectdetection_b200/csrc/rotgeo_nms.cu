@@ -1086,6 +1086,9 @@ nms_resolve_kernel(const ResolveArgs a) {
     // equal shares of the order for all CTAs: the flag gathers are random 32-byte sectors, and one
     // SM's L2 bandwidth made a single CTA with a full 8192-position tile the slowest part of the
     // small calls (count 4.6 us, emit 12 us on C2 with everything in CTA 0)
+    // (measured again in round 2 and dropped: for jobs of at most two emit tiles, let the LAST CTA to finish its
+    // segments compact alone — no grid barrier, no counting pass.  Resolve kernel 24.3 -> 26.8 us on C2 sparse and
+    // 19.7 -> 53.8 us on a C4 image: one SM gathering 10 000 flags and 2 000 rows is slower than both barriers.)
     const int64_t per = (n + G - 1) / G;
     const int64_t lo = min(n, (int64_t)blockIdx.x * per), hi = min(n, lo + per);
     {
