@@ -91,3 +91,17 @@ def test_gather_shift_refuses_other_layouts():
     with pytest.raises(ValueError):
         _hostpack.gather_shift([[good], [good, good]], np.zeros((2, 2)), out)
     assert _hostpack.gather_shift([], np.zeros((0, 2)), out) == (0, [], True)
+
+
+def test_bind_host_to_gpu_is_harmless_without_a_gpu():
+    """peer.bind_host_to_gpu(): returns the CPU list it pinned the thread to, or None when NVML / CUDA is not
+    there (this container) — never raises, never leaves the affinity empty"""
+    import os
+
+    from orientedobjectdetection_b200 import peer
+    before = os.sched_getaffinity(0)
+    got = peer.bind_host_to_gpu(0)
+    assert got is None or (isinstance(got, list) and len(got) > 0)
+    assert len(os.sched_getaffinity(0)) > 0
+    if got is None:
+        assert os.sched_getaffinity(0) == before
