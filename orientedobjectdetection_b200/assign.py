@@ -21,7 +21,7 @@ from collections import namedtuple
 import torch
 
 from . import _lib
-from .ops import _MODE, _cuda_device, _rows_f32, _stream
+from .ops import _MODE, _cuda_device, _on_device, _rows_f32, _stream
 
 AssignResult = namedtuple('AssignResult', ['num_gts', 'gt_inds', 'max_overlaps', 'labels'])
 
@@ -39,7 +39,7 @@ def rbbox_overlaps_max(bboxes1, bboxes2, mode='iou', min_wh=1e-3):
     n1, n2 = bboxes1.size(0), bboxes2.size(0)
     b1, b2 = _rows_f32(bboxes1, dev), _rows_f32(bboxes2, dev)
     L = _lib.load()
-    with torch.cuda.device(dev):
+    with _on_device(dev):
         row_max = torch.empty(n1, dtype=torch.float32, device=dev)
         row_arg = torch.empty(n1, dtype=torch.int64, device=dev)
         col_max = torch.empty(n2, dtype=torch.float32, device=dev)
@@ -100,7 +100,7 @@ class MaxIoUAssigner(object):
             dev = _cuda_device(bboxes, gt_bboxes)
             g, b = _rows_f32(gt_bboxes, dev), _rows_f32(bboxes, dev)
             L = _lib.load()
-            with torch.cuda.device(dev):
+            with _on_device(dev):
                 gt_inds = torch.empty(num_bboxes, dtype=torch.int64, device=dev)
                 max_overlaps = torch.empty(num_bboxes, dtype=torch.float32, device=dev)
                 nbytes = L.rotgeo_iou_max_workspace_bytes(num_gts, num_bboxes)

@@ -86,7 +86,7 @@ def _multiclass_nms_fused(multi_bboxes, multi_scores, score_thr, iou_thr, max_nu
     if score_factors is not None:
         sf = score_factors.detach().to(device=dev, dtype=torch.float32).reshape(-1).contiguous()
     cap = min(max_num, n * num_classes) if max_num > 0 else n * num_classes
-    with torch.cuda.device(dev):
+    with ops._on_device(dev):
         stream = ops._stream(dev)
         ws = ops._workspace(dev, stream, 'multiclass', nbytes)      # scratch, reused across calls on this stream
         dets = torch.empty((cap, 6), dtype=torch.float32, device=dev)

@@ -139,7 +139,7 @@ def _overlaps_allgather_peer(bboxes1, bboxes2, mode, lo, hi, group):
     b1 = ops._rows_f32(bboxes1[lo:hi], dev)
     b2 = ops._rows_f32(bboxes2, dev)
     L = _lib.load()
-    with torch.cuda.device(dev):
+    with ops._on_device(dev):
         stream = ops._stream(dev)
         off = 4096
         w = peer.window(off + n * m * 4, group)
@@ -184,7 +184,7 @@ def rbbox_overlaps_max_sharded(bboxes1, bboxes2, mode='iou', group=None):
     b1 = ops._rows_f32(bboxes1[lo:hi], dev)
     b2 = ops._rows_f32(bboxes2, dev)
     L = _lib.load()
-    with torch.cuda.device(dev):
+    with ops._on_device(dev):
         stream = ops._stream(dev)
         off = 4096
         w = peer.window(off + L.rotgeo_dist_rowcol_stage_bytes(n, m, world), group)
@@ -219,7 +219,7 @@ def _nms_exchange_peer(boxes, scores, ids, id_offsets, local_sizes, local_gids, 
     if nlocal > 64:
         return None
     row_floats = 6 if rows_src is not None else 0
-    with torch.cuda.device(dev):
+    with ops._on_device(dev):
         stream = ops._stream(dev)
         region = L.rotgeo_dist_keeps_bytes(ngroups, cap, world, row_floats)
         w = peer.window(4096 + 2 * region, group)

@@ -10,7 +10,7 @@ import numpy as np
 import torch
 
 from . import _lib
-from .ops import _cuda_device, _stream
+from .ops import _cuda_device, _on_device, _stream
 
 
 def average_precision(recalls, precisions, mode='area'):
@@ -105,7 +105,7 @@ def tpfp_segments(dets, det_off, gts, gt_off, gt_ignore, iou_thr=0.5):
     if nd == 0:
         return tp, fp
     L = _lib.load()
-    with torch.cuda.device(dev):
+    with _on_device(dev):
         d = torch.from_numpy(dets).to(dev)
         g = torch.from_numpy(gts).to(dev)
         do, go = torch.from_numpy(det_off).to(dev), torch.from_numpy(gt_off).to(dev)

@@ -15,7 +15,7 @@ import torch
 import torch.nn as nn
 
 from . import _lib
-from .ops import _cuda_device, _stream
+from .ops import _cuda_device, _on_device, _stream
 
 
 class _DiffIoU(torch.autograd.Function):
@@ -27,7 +27,7 @@ class _DiffIoU(torch.autograd.Function):
         b = box2.detach().reshape(-1, 5).to(device=dev, dtype=torch.float32).contiguous()
         n = a.shape[0]
         L = _lib.load()
-        with torch.cuda.device(dev):
+        with _on_device(dev):
             iou = torch.empty(n, dtype=torch.float32, device=dev)
             need1, need2 = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
             g1 = torch.empty((n, 5), dtype=torch.float32, device=dev) if need1 else None
