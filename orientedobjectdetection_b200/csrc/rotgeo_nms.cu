@@ -1319,6 +1319,12 @@ static int launch_resolve(const ResolveArgs &a_in, cudaStream_t stream) {
     // (measured and dropped: sending mid-size segments — a C2-dense class, 32 chunks — to the grid's 8-warp teams as
     // well instead of one CTA each changed nothing: resolve 48.3 vs 47.2 us on C2 dense, 19.9 vs 20.0 on a C4 image)
     int64_t want = a_in.has_large ? a_in.chunks : a_in.nseg;
+#ifndef ROTGEO_RESOLVE_SHARE
+#define ROTGEO_RESOLVE_SHARE 512
+#endif
+    // the compaction shares the score order out over the grid: with one CTA per small segment only (15 for the C2
+    // classes) every CTA gathered 2000 flags and rows; at least one CTA per ROTGEO_RESOLVE_SHARE positions
+    if (ROTGEO_RESOLVE_SHARE > 0 && want < a_in.n / ROTGEO_RESOLVE_SHARE) want = a_in.n / ROTGEO_RESOLVE_SHARE;
     if (want < 1) want = 1;
     ResolveArgs a = a_in;
     // dynamic shared memory: one small segment's state
