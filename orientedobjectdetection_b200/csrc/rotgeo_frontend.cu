@@ -63,7 +63,10 @@ void nms_bounds(const int64_t *group_sizes_host, int64_t ngroups, int64_t n, int
         const int64_t S = seg_cap < ng ? seg_cap : ng;
         const int64_t B = C + S - 1;          // every further segment adds at most one partial block
         blocks += B;
-        tiles += B * (B + 1) / 2;             // convex: the worst split is none
+        // tiles = sum of C_i (C_i + 1) / 2 over the segments, with sum C_i <= C + k - 1 for k <= S segments and every
+        // C_i >= 1: convex, so the worst case is one segment with C blocks and k - 1 single-block ones
+        // (B (B + 1) / 2, all blocks in one segment, was 16 times the possible for one C4 image)
+        tiles += C * (C + 1) / 2 + (S - 1);
         words += ng * 2 * C;                  // a row of a segment has at most 2 C words
         maxc = C > maxc ? C : maxc;
         nseg += S;

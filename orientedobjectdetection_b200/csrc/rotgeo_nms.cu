@@ -223,6 +223,11 @@ nms_mask_kernel(const MaskArgs g) {
     constexpr uint32_t tab_words = AREA ? kTableWords : kTableXYWords;
     const int nseg = g.nseg_dev ? (int)*g.nseg_dev : g.nseg;
     const bool LIST = g.tile_list != nullptr;       // launch-uniform
+    // Launches whose tile count is only known on the device (every fused front-end) run a persistent grid that
+    // takes tiles from a global counter.  Launch-control stealing needs a grid sized for the host-side BOUND: one C4
+    // image is 680 tiles under a bound of 55 945 (now 3 415), and cancelling the empty CTA ids one round trip at a
+    // time was most of that kernel (ncu: 65 % of the samples in the response wait, 94 waves per SM).
+    const bool COUNTER = g.tile_next != nullptr;
     if (LIST) pdl_wait();                           // the list and its length come from the kernel before this one
 
     if (tid == 0) {
@@ -311,6 +316,16 @@ nms_mask_kernel(const MaskArgs g) {
                 tn = st.grp_next++;
                 --st.grp_left;
                 step = true;
+            } else if (COUNTER) {
+                if (!st.alive) break;
+                const unsigned long long cta = (unsigned long long)gridDim.x + atomicAdd(g.tile_next, 1ull);
+                if ((int64_t)(cta * G) >= limit) {       // the counter only grows: nothing left for anybody
+                    st.alive = 0;
+                    break;
+                }
+                tn = (unsigned)(cta * G);
+                st.grp_next = tn + 1u;
+                st.grp_left = G - 1u;
             } else {
                 if (!st.alive) break;
                 const unsigned a = st.next_resp++;
@@ -502,7 +517,7 @@ nms_mask_kernel(const MaskArgs g) {
             pdl_wait();
             if (tid == 0) {
                 issue_cull_data(0, ti);
-                if (!LIST)
+                if (!COUNTER)
                     for (int e = 0; e < D; ++e) ask_next(sm.st.next_ask++);
                 for (int j = 1; j <= D; ++j) take_tile((unsigned)j);   // incl. this iteration's duty
             }
@@ -1292,7 +1307,7 @@ static int launch_mask(const MaskArgs &g_in, int64_t tiles, cudaStream_t stream)
     g.tiles = tiles;
     g.group = g.tile_list ? 1 : mask_group(tiles, lim);
     int64_t ctas = (tiles + g.group - 1) / g.group;
-    if (g.tile_list && ctas > lim.mask_slots) ctas = lim.mask_slots;      // persistent: one CTA per resident slot
+    if (g.tile_next && ctas > lim.mask_slots) ctas = lim.mask_slots;      // persistent: one CTA per resident slot
     // one CTA per tile; running CTAs steal the not-yet-launched ones (launch control)
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)ctas);
@@ -1406,7 +1421,8 @@ int launch_nms_device_planned(const NmsDevLaunch &d, cudaStream_t stream) {
     g.tile_list = nullptr;
     g.zero_in_kernel = 0;
     g.rank = nullptr;
-    g.tile_next = nullptr;
+    // the tile count lives on the device: persistent grid + global tile counter (zeroed by the pack kernel)
+    g.tile_next = reinterpret_cast<unsigned long long *>(d.scratch.sync + 10);
     if (d.tile_list) {
         // spatially packed: list the block pairs whose bounding boxes touch, then visit only those
         if (d.tiles_bound > 0x7fffffffLL) return -1;
