@@ -39,7 +39,7 @@ def build_hostpack(force=False):
             and os.path.getmtime(HOSTPACK_SO) >= max(os.path.getmtime(HOSTPACK_SRC), os.path.getmtime(__file__))):
         return HOSTPACK_SO
     cc = '/usr/bin/gcc' if os.path.exists('/usr/bin/gcc') else 'gcc'
-    cmd = [cc, '-O2', '-Wall', '-fPIC', '-shared', '-I', sysconfig.get_paths()['include'], HOSTPACK_SRC, '-o', HOSTPACK_SO]
+    cmd = [cc, '-O2', '-Wall', '-fopenmp', '-fPIC', '-shared', '-I', sysconfig.get_paths()['include'], HOSTPACK_SRC, '-o', HOSTPACK_SO]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         sys.stderr.write(r.stdout + r.stderr)

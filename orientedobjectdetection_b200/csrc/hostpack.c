@@ -21,6 +21,11 @@
 
 #define HP_COLS 6
 
+static int cmp_ptr(const void *a, const void *b) {
+    const uintptr_t x = *(const uintptr_t *)a, y = *(const uintptr_t *)b;
+    return x < y ? -1 : x > y;
+}
+
 static int is_f32(const Py_buffer *v) {
     const char *f = v->format;
     if (v->itemsize != 4) return 0;
@@ -36,8 +41,8 @@ static int is_f32(const Py_buffer *v) {
  *   take     optional bytes-like, one byte per class: rows of classes with a zero byte are shifted
  *            in place like all others but not copied (multi-GPU: a rank stages its own classes);
  *            total_rows then counts the copied classes only, counts still lists every class
- * None: some array is not a writable 2-D float32 array with 6 columns (caller takes the numpy
- * path); filled False: `out` is smaller than total_rows * 24 bytes — nothing was shifted. */
+ * None: some array is not a writable 2-D float32 array with 6 columns, or the same non-empty array appears
+ * twice (caller takes the numpy path); filled False: `out` is smaller than total_rows * 24 bytes — nothing was shifted. */
 static PyObject *gather_shift(PyObject *self, PyObject *args) {
     PyObject *results, *offs_obj, *out_obj, *take_obj = NULL;
     if (!PyArg_ParseTuple(args, "OOO|O", &results, &offs_obj, &out_obj, &take_obj)) return NULL;
@@ -114,6 +119,27 @@ static PyObject *gather_shift(PyObject *self, PyObject *args) {
         Py_INCREF(ret);
         goto done;
     }
+    {
+        /* the same non-empty array twice in `results`: the reference's loop shifts it twice and concatenates the
+         * final state twice (it collects references and concatenates afterwards) — left to the numpy walk */
+        const Py_ssize_t items = P * C;
+        uintptr_t *ptrs = (uintptr_t *)malloc((size_t)(items ? items : 1) * sizeof(uintptr_t));
+        int aliased = 0;
+        if (!ptrs) { free(cls_rows); PyErr_NoMemory(); goto done; }
+        Py_ssize_t m = 0;
+        for (Py_ssize_t t = 0; t < items; ++t)
+            if (views[t].shape[0] > 0) ptrs[m++] = (uintptr_t)views[t].buf;
+        qsort(ptrs, (size_t)m, sizeof(uintptr_t), cmp_ptr);
+        for (Py_ssize_t t = 1; t < m; ++t)
+            if (ptrs[t] == ptrs[t - 1]) { aliased = 1; break; }
+        free(ptrs);
+        if (aliased) {
+            free(cls_rows);
+            ret = Py_None;
+            Py_INCREF(ret);
+            goto done;
+        }
+    }
     counts = PyList_New(C);
     if (!counts) { free(cls_rows); goto done; }
     for (Py_ssize_t c = 0; c < C; ++c) PyList_SET_ITEM(counts, c, PyLong_FromLongLong(cls_rows[c]));
@@ -122,38 +148,56 @@ static PyObject *gather_shift(PyObject *self, PyObject *args) {
         ret = Py_BuildValue("(LOO)", (long long)total, counts, Py_False);
         goto done;
     }
-    /* pass 2: shift in place + copy, class-major */
+    /* pass 2: shift in place + copy, class-major.  Every (class, patch) array has its own destination range, so
+     * the 6000 items are independent: a few OpenMP threads share them (memory-bound; the GIL stays with the caller,
+     * nothing below touches a Python object). */
     {
-        float *dst = (float *)out.buf;
+        float *dst0 = (float *)out.buf;
         const double *off = (const double *)offs.buf;
+        int64_t *start = (int64_t *)malloc((size_t)(P * C ? P * C : 1) * sizeof(int64_t));
+        if (!start) { PyErr_NoMemory(); goto done; }
+        int64_t run = 0;
         for (Py_ssize_t c = 0; c < C; ++c)
             for (Py_ssize_t i = 0; i < P; ++i) {
-                const Py_buffer *v = &views[i * C + c];
-                const Py_ssize_t k = v->shape[0], s0 = v->strides[0], s1 = v->strides[1];
-                const double ox = off[2 * i], oy = off[2 * i + 1];
-                char *row = (char *)v->buf;
-                if (takeb && !takeb[c]) {           /* somebody else's class: the in-place shift only */
-                    for (Py_ssize_t r = 0; r < k; ++r, row += s0) {
-                        float *px = (float *)row, *py = (float *)(row + s1);
-                        *px = (float)((double)*px + ox);
-                        *py = (float)((double)*py + oy);
-                    }
-                } else if (s1 == 4) {
-                    for (Py_ssize_t r = 0; r < k; ++r, row += s0, dst += HP_COLS) {
-                        float *p = (float *)row;
-                        p[0] = (float)((double)p[0] + ox);
-                        p[1] = (float)((double)p[1] + oy);
-                        memcpy(dst, p, HP_COLS * sizeof(float));
-                    }
-                } else {
-                    for (Py_ssize_t r = 0; r < k; ++r, row += s0, dst += HP_COLS) {
-                        float *px = (float *)row, *py = (float *)(row + s1);
-                        *px = (float)((double)*px + ox);
-                        *py = (float)((double)*py + oy);
-                        for (int j = 0; j < HP_COLS; ++j) dst[j] = *(float *)(row + j * s1);
-                    }
+                start[c * P + i] = run;
+                if (!takeb || takeb[c]) run += views[i * C + c].shape[0];
+            }
+        const Py_ssize_t items = P * C;
+        const int threads = total >= 20000 ? 4 : 1;
+        (void)threads;
+#ifdef _OPENMP
+#pragma omp parallel for schedule(dynamic, 32) num_threads(threads)
+#endif
+        for (Py_ssize_t t = 0; t < items; ++t) {
+            const Py_ssize_t c = t / P, i = t % P;
+            const Py_buffer *v = &views[i * C + c];
+            const Py_ssize_t k = v->shape[0], s0 = v->strides[0], s1 = v->strides[1];
+            const double ox = off[2 * i], oy = off[2 * i + 1];
+            char *row = (char *)v->buf;
+            float *dst = dst0 + start[t] * HP_COLS;
+            if (takeb && !takeb[c]) {           /* somebody else's class: the in-place shift only */
+                for (Py_ssize_t r = 0; r < k; ++r, row += s0) {
+                    float *px = (float *)row, *py = (float *)(row + s1);
+                    *px = (float)((double)*px + ox);
+                    *py = (float)((double)*py + oy);
+                }
+            } else if (s1 == 4) {
+                for (Py_ssize_t r = 0; r < k; ++r, row += s0, dst += HP_COLS) {
+                    float *p = (float *)row;
+                    p[0] = (float)((double)p[0] + ox);
+                    p[1] = (float)((double)p[1] + oy);
+                    memcpy(dst, p, HP_COLS * sizeof(float));
+                }
+            } else {
+                for (Py_ssize_t r = 0; r < k; ++r, row += s0, dst += HP_COLS) {
+                    float *px = (float *)row, *py = (float *)(row + s1);
+                    *px = (float)((double)*px + ox);
+                    *py = (float)((double)*py + oy);
+                    for (int j = 0; j < HP_COLS; ++j) dst[j] = *(float *)(row + j * s1);
                 }
             }
+        }
+        free(start);
     }
     ret = Py_BuildValue("(LOO)", (long long)total, counts, Py_True);
 done:

@@ -105,3 +105,24 @@ def test_bind_host_to_gpu_is_harmless_without_a_gpu():
     assert len(os.sched_getaffinity(0)) > 0
     if got is None:
         assert os.sched_getaffinity(0) == before
+
+
+def test_gather_shift_large_scene_threads_and_aliased_arrays():
+    """above 20 000 rows the copy pass runs on a few threads: same bytes as the numpy walk; an array that appears
+    twice is refused (the numpy walk reproduces the reference's double shift)"""
+    rng = np.random.default_rng(9)
+    res = [[rng.uniform(0, 900, size=(int(rng.integers(20, 60)), 6)).astype(np.float32) for _ in range(5)] for _ in range(150)]
+    offs = rng.integers(0, 16000, size=(150, 2)).astype(np.int64)
+    mine = [[a.copy() for a in p] for p in res]
+    per = _numpy_walk(res, offs)
+    out = np.empty((sum(p.shape[0] for p in per) + 7, 6), dtype=np.float32)
+    total, counts, filled = _hostpack.gather_shift(mine, offs.astype(np.float64), out)
+    assert filled and total >= 20000 and counts == [p.shape[0] for p in per]
+    assert np.array_equal(out[:total], np.concatenate(per, axis=0))
+    assert all(np.array_equal(a, b) for pa, pb in zip(res, mine) for a, b in zip(pa, pb))
+    # aliased: patch 1 reuses patch 0's array object for class 0 -> refused untouched (the reference collects references,
+    # shifts the array twice and concatenates its final state twice: the numpy walk of merge_results does that)
+    mine[1][0] = mine[0][0]
+    before = mine[0][0].copy()
+    assert _hostpack.gather_shift(mine, offs.astype(np.float64), out) is None
+    assert np.array_equal(mine[0][0], before)
